@@ -1,0 +1,329 @@
+// ga_collision.cu -- K6: batched disk-footprint collision checks and motion-primitive rollout.
+//
+// Replaces CollisionChecker::checkGrid / checkGridVariant / checkPose / getYawIdx /
+// getPathCollisionIndex / checkPathCollision (collision_checking.cpp:333-452) and the
+// collision-relevant part of HybridAStar::setNeighbors (hybrid_a_star_lib.cpp:492-534) with
+// Vehicle::move / move_car_some_steps / turn_on_rear_axis (vehicle.cpp:34-122).
+//
+// Arithmetic notes: compiled with -fmad=false so every product and sum rounds separately, as the
+// reference's baseline x86-64 build does.  fmod, division, sqrt, conversions are IEEE-exact on
+// the device; sin/cos/tan are CUDA libm (<= 2 ulp) and may differ from glibc in the last bit, so
+// ga_expand flags primitives whose poses come within 1e-9 cells of a discretisation boundary.
+#include <climits>
+#include <cmath>
+
+#include "ga_internal.cuh"
+
+#define GA_CON2GM (1.0 / 0.15625)   // grid_tf::con2gm_  (transforms.hpp:73-74, params.hpp:8)
+#define GA_CON2STAR (1.0 / 0.625)   // grid_tf::con2star_ (transforms.hpp:76-77, params.hpp:7)
+#define GA_PI 3.14159265358979323846
+
+// util::constrainAngleZero2Pi (util1.cpp:8-15)
+__device__ __forceinline__ double angle_0_2pi(double a)
+{
+  while (a < 0) a += 2 * GA_PI;
+  return fmod(a, 2 * GA_PI);
+}
+// util::constrainAngleMinPIPlusPi (util1.cpp:17-24)
+__device__ __forceinline__ double angle_mpi_pi(double a)
+{
+  while (a < 0) a += 2 * GA_PI;
+  return fmod(a + GA_PI, 2.0 * GA_PI) - GA_PI;
+}
+// util::getAngleDiff (util1.cpp:26-34)
+__device__ __forceinline__ double angle_diff(double a1, double a2)
+{
+  a2 = angle_mpi_pi(a2);
+  a1 = angle_mpi_pi(a1);
+  return angle_mpi_pi(a2 - a1);
+}
+
+struct coll_view
+{
+  const uint8_t* safety;
+  const int* centers;
+  int patch_dim;
+  int nb_disks;
+  int nb_yaws;
+  double yaw_res_rad;
+};
+
+// checkPose (collision_checking.cpp:389-396) -> checkGrid(/Variant) (:344-387); 1 = valid.
+// frac_margin (optional) receives the smallest distance of x*con2gm, y*con2gm, yaw/res to an
+// integer boundary.
+__device__ __forceinline__ int check_pose_dev(const coll_view& v, double x, double y, double yaw, int variant,
+                                              double* frac_margin)
+{
+  const double fx = x * GA_CON2GM;
+  const double fy = y * GA_CON2GM;
+  const int gx = (int)fx;
+  const int gy = (int)fy;
+  // getYawIdx (:333-337)
+  const double fa = angle_0_2pi(yaw) / v.yaw_res_rad;
+  int yi = (int)fa;
+  yi = yi < v.nb_yaws - 1 ? yi : v.nb_yaws - 1;
+  if (frac_margin)
+  {
+    const double mx = fabs(fx - rint(fx)), my = fabs(fy - rint(fy)), ma = fabs(fa - rint(fa));
+    *frac_margin = fmin(fmin(mx, my), ma);
+  }
+  const int* cen = v.centers + (size_t)yi * v.nb_disks * 2;
+  for (int k = 0; k < v.nb_disks; ++k)
+  {
+    const int px = cen[2 * k] + gx;
+    const int py = cen[2 * k + 1] + gy;
+    if (px >= v.patch_dim || py >= v.patch_dim || px < 0 || py < 0)
+    {
+      if (variant) continue;
+      return 0;
+    }
+    if (v.safety[(size_t)py * v.patch_dim + px] == GA_OCC) return 0;
+  }
+  return 1;
+}
+
+// ---- ga_check_poses ---------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256)
+check_poses_kernel(coll_view v, const double* __restrict__ x, const double* __restrict__ y,
+                   const double* __restrict__ yaw, int n_poses, const int* __restrict__ seg_off, int n_seg,
+                   int variant, int* __restrict__ first_hit)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_poses) return;
+  if (check_pose_dev(v, x[i], y[i], yaw[i], variant, nullptr)) return;
+  // segment of pose i: largest s with seg_off[s] <= i
+  int lo = 0, hi = n_seg;
+  while (hi - lo > 1)
+  {
+    const int mid = (lo + hi) >> 1;
+    if (seg_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  atomicMin(&first_hit[lo], i - seg_off[lo]);
+}
+
+__global__ void fill_i32_kernel(int* p, int n, int v)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+__global__ void fix_first_hit_kernel(int* p, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && p[i] == INT_MAX) p[i] = -1;
+}
+
+static coll_view make_view(const ga_ctx* c)
+{
+  coll_view v;
+  v.safety = c->d_safety;
+  v.centers = c->d_centers;
+  v.patch_dim = c->patch_dim;
+  v.nb_disks = c->cp.nb_disks;
+  v.nb_yaws = c->nb_yaws;
+  v.yaw_res_rad = c->yaw_res_coll_rad;
+  return v;
+}
+
+extern "C" int ga_check_poses(ga_ctx* c, const double* x, const double* y, const double* yaw, int n_poses,
+                              const int* seg_off, int n_seg, int variant, int* first_hit)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, n_poses >= 0 && n_seg >= 0 && first_hit && seg_off, GA_ERR_ARG, "bad arguments");
+  GA_REQUIRE(c, n_poses == 0 || (x && y && yaw), GA_ERR_ARG, "null pose arrays");
+  if (n_seg == 0) return GA_OK;
+  GA_REQUIRE(c, seg_off[0] == 0 && seg_off[n_seg] == n_poses, GA_ERR_ARG, "seg_off must span [0, n_poses]");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  // staging layout: x | y | yaw | seg_off | first_hit
+  const size_t b_pose = sizeof(double) * (size_t)n_poses;
+  const size_t b_seg = sizeof(int) * (size_t)(n_seg + 1);
+  const size_t b_hit = sizeof(int) * (size_t)n_seg;
+  const size_t total = 3 * b_pose + b_seg + b_hit + 64;
+  int rc = ga_stage_reserve(c, total);
+  if (rc) return rc;
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));  // staging buffer reuse
+  char* h = (char*)c->h_stage;
+  char* d = (char*)c->d_stage;
+  memcpy(h, x, b_pose);
+  memcpy(h + b_pose, y, b_pose);
+  memcpy(h + 2 * b_pose, yaw, b_pose);
+  memcpy(h + 3 * b_pose, seg_off, b_seg);
+  const size_t off_hit = (3 * b_pose + b_seg + 15) & ~(size_t)15;
+  GA_CUDA(c, cudaMemcpyAsync(d, h, 3 * b_pose + b_seg, cudaMemcpyHostToDevice, c->stream));
+  int* d_hit = (int*)(d + off_hit);
+  fill_i32_kernel<<<(n_seg + 255) / 256, 256, 0, c->stream>>>(d_hit, n_seg, INT_MAX);
+  if (n_poses > 0)
+  {
+    ga_launch_scope ls(c, GA_K_COLLISION);
+    check_poses_kernel<<<(n_poses + 255) / 256, 256, 0, c->stream>>>(
+        make_view(c), (const double*)d, (const double*)(d + b_pose), (const double*)(d + 2 * b_pose), n_poses,
+        (const int*)(d + 3 * b_pose), n_seg, variant, d_hit);
+  }
+  fix_first_hit_kernel<<<(n_seg + 255) / 256, 256, 0, c->stream>>>(d_hit, n_seg);
+  GA_CUDA(c, cudaGetLastError());
+  GA_CUDA(c, cudaMemcpyAsync(h + off_hit, d_hit, b_hit, cudaMemcpyDeviceToHost, c->stream));
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  memcpy(first_hit, h + off_hit, b_hit);
+  return GA_OK;
+}
+
+// ---- ga_expand ----------------------------------------------------------------------------------
+
+struct expand_view
+{
+  double steer[GA_MAX_STEER];
+  double ra_delta[GA_MAX_RA];
+  double wheel_base, arc_l;
+  double yaw_res_inv;        // a_star_yaw_res_inv_ = 1 / (YAW_RES * TO_RAD), hybrid_a_star_lib.cpp:38-40
+  double yaw_res_coll_deg;   // yaw_res_coll_ handed to turn_on_rear_axis (:359)
+  int nb_steer, n_ra, astar_dim;
+};
+
+#define GA_EDGE_EPS 1e-9
+
+// one thread per (node, primitive); primitives in the reference's order: steer-major,
+// direction +1 then -1 (direction_inputs_, hybrid_a_star_lib.hpp:50), then the rear-axis deltas
+__global__ void __launch_bounds__(128)
+expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int n_nodes, ga_succ* __restrict__ out)
+{
+  const int stride = 2 * e.nb_steer + e.n_ra;
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= (long long)n_nodes * stride) return;
+  const int node = (int)(t / stride);
+  const int k = (int)(t % stride);
+  const ga_node nd = nodes[node];
+  ga_succ s;
+  s.x = nd.x; s.y = nd.y; s.yaw = nd.yaw;
+  s.xi = s.yi = s.yawi = 0;
+  s.n_poses = 0;
+  s.valid = 0;
+  s.near_cell_edge = 0;
+  for (int i = 0; i < 6; ++i) s.pad_[i] = 0;
+
+  double x = nd.x, y = nd.y, yaw = nd.yaw;
+  double margin = 1.0, m;
+  if (k < 2 * e.nb_steer)
+  {
+    // calcNextNode (hybrid_a_star_lib.cpp:427-483)
+    const double steer = e.steer[k >> 1];
+    const int direction = (k & 1) ? -1 : 1;
+    // Vehicle::move_car_some_steps (vehicle.cpp:100-122)
+    const long long nb = (long long)round(e.arc_l / nd.motion_res);
+    const double dist = nd.motion_res * direction;
+    int ok = 1, n = 0;
+    for (long long i = 0; i < nb; ++i)
+    {
+      // Vehicle::move (vehicle.cpp:34-43)
+      x += dist * cos(yaw);
+      y += dist * sin(yaw);
+      yaw += dist * tan(steer) / e.wheel_base;
+      yaw = angle_mpi_pi(yaw);
+      ++n;
+      if (ok)
+      {
+        ok = check_pose_dev(v, x, y, yaw, 0, &m);
+        margin = fmin(margin, m);
+      }
+    }
+    s.n_poses = n;
+    if (n > 0)
+    {
+      // mapCont2Disc (:410-417)
+      const double fx = x * GA_CON2STAR, fy = y * GA_CON2STAR, fa = yaw * e.yaw_res_inv;
+      s.x = x; s.y = y; s.yaw = yaw;
+      s.xi = (int)fx;
+      s.yi = (int)fy;
+      s.yawi = (int)round(fa);
+      margin = fmin(margin, fmin(fabs(fx - rint(fx)), fabs(fy - rint(fy))));
+      margin = fmin(margin, fabs(fabs(fa - trunc(fa)) - 0.5));
+      // verifyIndex (:150-154)
+      const int on_grid = (-1 < s.xi && s.xi < e.astar_dim) && (-1 < s.yi && s.yi < e.astar_dim);
+      s.valid = (uint8_t)(on_grid && ok);
+    }
+  }
+  else if (nd.with_rear_axis)
+  {
+    // calcRearAxisNode (:350-403) with Vehicle::turn_on_rear_axis (vehicle.cpp:45-98)
+    const double delta_angle = e.ra_delta[k - 2 * e.nb_steer];
+    const double goal_yaw = angle_mpi_pi(yaw + delta_angle);
+    const double res = e.yaw_res_coll_deg * (GA_PI / 180);
+    const double sg = (double)((0.0 < delta_angle) - (delta_angle < 0.0));
+    double ang_margin;
+    int ok = 1, n = 0;
+    double prev_yaw = yaw;
+    int have_prev = 0;
+    do
+    {
+      // the previous yaw is final once a next one is produced: check it now
+      if (have_prev && ok)
+      {
+        ok = check_pose_dev(v, x, y, prev_yaw, 0, &m);
+        margin = fmin(margin, m);
+      }
+      yaw = angle_mpi_pi(yaw + sg * res);
+      prev_yaw = yaw;
+      have_prev = 1;
+      ++n;
+      ang_margin = fabs(angle_diff(yaw, goal_yaw));
+    } while (ang_margin >= res && n < 4096);
+    // the last element is replaced by goal_yaw (vehicle.cpp:72-76)
+    if (ok)
+    {
+      ok = check_pose_dev(v, x, y, goal_yaw, 0, &m);
+      margin = fmin(margin, m);
+    }
+    const double fa = goal_yaw * e.yaw_res_inv;
+    s.n_poses = n;
+    s.yaw = goal_yaw;
+    s.xi = (int)(x * GA_CON2STAR);
+    s.yi = (int)(y * GA_CON2STAR);
+    s.yawi = (int)round(fa);
+    margin = fmin(margin, fabs(fabs(fa - trunc(fa)) - 0.5));
+    s.valid = (uint8_t)ok;
+  }
+  s.near_cell_edge = (uint8_t)(margin < GA_EDGE_EPS);
+  out[t] = s;
+}
+
+extern "C" int ga_expand(ga_ctx* c, const ga_node* nodes, int n_nodes, ga_succ* out)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp && c->have_ep, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, n_nodes >= 0 && (n_nodes == 0 || (nodes && out)), GA_ERR_ARG, "bad arguments");
+  if (n_nodes == 0) return GA_OK;
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int stride = 2 * c->ep.nb_steer + c->n_ra;
+  const size_t b_in = sizeof(ga_node) * (size_t)n_nodes;
+  const size_t b_out = sizeof(ga_succ) * (size_t)n_nodes * stride;
+  const size_t off_out = (b_in + 63) & ~(size_t)63;
+  int rc = ga_stage_reserve(c, off_out + b_out);
+  if (rc) return rc;
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  char* h = (char*)c->h_stage;
+  char* d = (char*)c->d_stage;
+  memcpy(h, nodes, b_in);
+  GA_CUDA(c, cudaMemcpyAsync(d, h, b_in, cudaMemcpyHostToDevice, c->stream));
+  expand_view e;
+  memcpy(e.steer, c->steer, sizeof(e.steer));
+  memcpy(e.ra_delta, c->ra_delta, sizeof(e.ra_delta));
+  e.wheel_base = c->ep.wheel_base;
+  e.arc_l = c->ep.arc_l;
+  e.yaw_res_inv = 1.0 / (c->ep.yaw_res_deg * (M_PI / 180));
+  e.yaw_res_coll_deg = (double)c->cp.yaw_res_deg;
+  e.nb_steer = c->ep.nb_steer;
+  e.n_ra = c->n_ra;
+  e.astar_dim = c->astar_dim;
+  {
+    ga_launch_scope ls(c, GA_K_EXPAND);
+    const long long threads = (long long)n_nodes * stride;
+    expand_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, c->stream>>>(make_view(c), e, (const ga_node*)d, n_nodes,
+                                                                            (ga_succ*)(d + off_out));
+  }
+  GA_CUDA(c, cudaGetLastError());
+  GA_CUDA(c, cudaMemcpyAsync(h + off_out, d + off_out, b_out, cudaMemcpyDeviceToHost, c->stream));
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  memcpy(out, h + off_out, b_out);
+  return GA_OK;
+}

@@ -1,0 +1,128 @@
+// ga_internal.cuh -- context layout and launch helpers shared by the libgridaccel.so sources.
+// Product code: nothing here (or in any file of csrc/) includes, links or calls oracle/.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "gridaccel.h"
+
+#define GA_MAX_DISK_R 16   // 32 + 2r bits of one plane row must fit a 64-bit window
+#define GA_MAX_DISKS 16
+#define GA_MAX_STEER 31
+#define GA_MAX_RA 16       // rear-axis deltas per node
+#define GA_HEUR_TILE 32    // heuristic tile edge (cells)
+
+struct ga_se  // structuring element, passed to kernels by value
+{
+  int r;                 // radius in cells
+  int n_var;             // distinct half widths
+  int var_w[GA_MAX_DISK_R + 1];        // half width of variant v
+  int row_var[2 * GA_MAX_DISK_R + 1];  // variant index of SE row dy + r
+};
+
+struct ga_prof_rec
+{
+  int k;
+  cudaEvent_t e0, e1;
+};
+
+struct ga_ctx
+{
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  char err[512] = { 0 };
+  int sm_count = 148;
+
+  // ---- parameters
+  bool have_cp = false, have_ep = false, have_ap = false;
+  ga_collision_params cp{};
+  ga_expand_params ep{};
+  ga_astar_params ap{};
+  ga_se se{};
+  int nb_yaws = 0;
+  double yaw_res_coll_rad = 0.0;
+  int n_ra = 0;                 // rear-axis deltas per node
+  double ra_delta[GA_MAX_RA] = { 0 };
+  double steer[GA_MAX_STEER] = { 0 };
+  int* d_centers = nullptr;     // nb_yaws * nb_disks * 2
+
+  // ---- grids
+  int patch_dim = 0, astar_dim = 0;
+  int plane_pitch = 0;          // words per bit-plane row
+  uint8_t* d_patch = nullptr;
+  uint8_t* d_safety = nullptr;
+  uint32_t* d_plane_occ = nullptr;  // bit = thresholded cell == OCC
+  uint32_t* d_plane_nf = nullptr;   // bit = thresholded cell != FREE
+  uint8_t* d_astar = nullptr;
+  uint8_t* d_fence = nullptr;
+  double* d_mc = nullptr;
+  double* d_prox = nullptr;
+  double* d_mres = nullptr;
+  float* d_odist = nullptr;
+  float* d_vdist = nullptr;
+  int vor_alloc = 0;
+  double* d_hcost[2] = { nullptr, nullptr };
+  double* d_hdist[2] = { nullptr, nullptr };
+  int32_t* d_hparent[2] = { nullptr, nullptr };
+  uint8_t* d_hflags[2] = { nullptr, nullptr };
+
+  // ---- heuristic scratch
+  int tiles_x = 0, n_tiles = 0;
+  int* d_tile_active = nullptr;   // 2 * n_tiles (double buffered)
+  int* d_hctl = nullptr;          // control words (counters)
+  int32_t* d_jump = nullptr;      // pointer-jumping scratch: 2 * ncell
+  int32_t* d_cnt = nullptr;       // (n_straight, n_diag) pairs: 2 * 2 * ncell
+  int relax_grid = 0;             // co-resident CTAs of the persistent relax kernel
+
+  // ---- staging (pinned host + device) for pose batches
+  void* h_stage = nullptr;
+  size_t h_stage_bytes = 0;
+  void* d_stage = nullptr;
+  size_t d_stage_bytes = 0;
+
+  // ---- measurement
+  bool prof_on = false;
+  std::vector<ga_prof_rec> prof;
+  std::vector<cudaEvent_t> ev_pool;
+  long long launches = 0;
+  long long k_launches[GA_K_COUNT] = { 0 };
+};
+
+int ga_fail(ga_ctx* ctx, int code, const char* fmt, ...);
+
+#define GA_CUDA(ctx, call)                                                                        \
+  do                                                                                              \
+  {                                                                                               \
+    cudaError_t e__ = (call);                                                                     \
+    if (e__ != cudaSuccess)                                                                       \
+      return ga_fail((ctx), GA_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call,             \
+                     cudaGetErrorString(e__));                                                    \
+  } while (0)
+
+#define GA_REQUIRE(ctx, cond, code, msg)                                                          \
+  do                                                                                              \
+  {                                                                                               \
+    if (!(cond)) return ga_fail((ctx), (code), "%s: %s", __func__, (msg));                        \
+  } while (0)
+
+// Brackets one kernel launch: counts it and, when profiling, records events around it.
+struct ga_launch_scope
+{
+  ga_ctx* c;
+  int k;
+  cudaEvent_t e1 = nullptr;
+  ga_launch_scope(ga_ctx* ctx, int kid);
+  ~ga_launch_scope();
+};
+
+int ga_stage_reserve(ga_ctx* ctx, size_t bytes);
+
+// implemented per subsystem
+int ga_heur_alloc(ga_ctx* ctx);
+void ga_heur_free(ga_ctx* ctx);

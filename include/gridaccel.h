@@ -1,0 +1,251 @@
+/*
+ * gridaccel.h -- C ABI of libgridaccel.so, the B200 (sm_100a) backend for the data-parallel grid
+ * work of guided-extended-hybrid-astar's freespace_planner library.
+ *
+ * The reference has no FFI layer for this path: the work sits behind two all-static C++ classes
+ * (CollisionChecker, AStar) and one pybind11 module.  Every entry point below names the reference
+ * function(s) it replaces (LIB = src/freespace_planner/library in the reference tree).  The C++
+ * mirror classes that keep the reference's names on top of this ABI live in
+ * guided-extended-hybrid-astar_b200/host/, the binding a reference maintainer would add is in
+ * INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every host buffer, the context owns every
+ *     device buffer and one CUDA stream;
+ *   - every function returns 0 on success, a negative ga_status on failure, never throws, never
+ *     exits; ga_last_error() gives the text of the last failure of that context;
+ *   - all work of one context is ordered on its stream; functions that return data to the host
+ *     synchronise that stream, the others only enqueue (ga_sync waits);
+ *   - one context per planner instance; a context is not thread-safe, different contexts are
+ *     independent (this is what lifts the reference's one-planner-per-process restriction);
+ *   - there is no CPU fallback: without a CUDA device ga_create fails with GA_ERR_CUDA.
+ *   - grids are dense row-major, index = y * dim + x, exactly Vec2DFlat<T>
+ *     (LIB/include/util_lib/data_structures1.hpp:338-514).
+ */
+#ifndef GRIDACCEL_H
+#define GRIDACCEL_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GA_ABI_VERSION 1
+
+typedef struct ga_ctx ga_ctx;
+
+typedef enum
+{
+  GA_OK = 0,
+  GA_ERR_ARG = -1,    /* bad argument / call order */
+  GA_ERR_CUDA = -2,   /* CUDA runtime error (text in ga_last_error) */
+  GA_ERR_STATE = -3,  /* required state missing (no patch, no params ...) */
+  GA_ERR_NOMEM = -4
+} ga_status;
+
+/* GRID_VAL, LIB/include/collision_checker_lib/collision_checking.hpp:39-47 */
+enum { GA_FREE = 0, GA_UNKNOWN = 1, GA_OCC = 2, GA_SENSOR_UNKNOWN = 127 };
+
+/* device grids that ga_upload / ga_download / ga_device_ptr address */
+typedef enum
+{
+  GA_GRID_PATCH = 0,          /* u8  patch_dim^2   CollisionChecker::patch_arr_            */
+  GA_GRID_SAFETY = 1,         /* u8  patch_dim^2   CollisionChecker::patch_safety_arr_     */
+  GA_GRID_ASTAR = 2,          /* u8  astar_dim^2   AStar::astar_grid_                      */
+  GA_GRID_GEOFENCE = 3,       /* u8  astar_dim^2   AStar::restr_geofence_grid_             */
+  GA_GRID_MOVEMENT_COST = 4,  /* f64 astar_dim^2   AStar::movement_cost_map_               */
+  GA_GRID_H_PROX = 5,         /* f64 astar_dim^2   AStar::h_prox_arr_                      */
+  GA_GRID_MOTION_RES = 6,     /* f64 astar_dim^2   AStar::motion_res_map_                  */
+  GA_GRID_OBSTACLE_DIST = 7,  /* f32 vor_dim^2     AStar::obstacle_dist_                   */
+  GA_GRID_VORONOI_DIST = 8,   /* f32 vor_dim^2     AStar::voronoi_dist_                    */
+  /* heuristic result planes, slot 0 = closed_set_guidance_, slot 1 = closed_set_path_
+   * (dense restatement of std::unordered_map<size_t, NodeDisc>, a_star.hpp:69-72,
+   * NodeDisc data_structures2.hpp:47-67): id = base + slot */
+  GA_GRID_HEUR_COST = 16,     /* f64 astar_dim^2   NodeDisc::cost_        (+inf = not in set) */
+  GA_GRID_HEUR_DIST = 18,     /* f64 astar_dim^2   NodeDisc::cost_dist_                      */
+  GA_GRID_HEUR_PARENT = 20,   /* i32 astar_dim^2   NodeDisc::parent_index_ (-1 root, -2 none) */
+  GA_GRID_HEUR_FLAGS = 22     /* u8  astar_dim^2   bit0 in closed set, bit1 is_unknown_       */
+} ga_grid_id;
+
+enum { GA_H_CLOSED = 1, GA_H_UNKNOWN = 2 };
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+
+int ga_abi_version(void);
+int ga_create(int device, ga_ctx** out);
+int ga_destroy(ga_ctx* ctx);
+const char* ga_last_error(const ga_ctx* ctx);
+int ga_sync(ga_ctx* ctx);
+/* the context's cudaStream_t, for callers that record their own events on it */
+void* ga_stream(ga_ctx* ctx);
+
+/* ---- occupancy: patch, threshold, dilation, pooling --------------------------------------- */
+
+/* CollisionChecker::initialize / calculateDisks (collision_checking.cpp:12-31,75-145): the host
+ * computes the footprint model exactly as the reference does and hands over the results.
+ * centers = disk_centers_ LUT, [(yaw_idx * nb_disks + disk) * 2 + {0:x, 1:y}] gm cells.
+ * disk_r_c = CollisionChecker::disk_r_c_; the structuring element is the
+ * cv::getStructuringElement(MORPH_ELLIPSE, (2r+1)^2) raster of collision_checking.cpp:106-107. */
+typedef struct
+{
+  int min_thresh;   /* config.yml MIN_THRESH */
+  int max_thresh;   /* config.yml MAX_THRESH */
+  int disk_r_c;     /* dilation radius in gm cells (<= 16) */
+  int yaw_res_deg;  /* config.yml YAW_RES_COLL */
+  int nb_disks;     /* <= 16 */
+  int pool_win;     /* ceil(grid_tf::star2gm_) = 4 (a_star.cpp:30-31) */
+} ga_collision_params;
+
+int ga_set_collision_params(ga_ctx* ctx, const ga_collision_params* p, const int* centers);
+
+/* CollisionChecker::resetPatch (collision_checking.cpp:37-42) + AStar::reinit's grid sizing
+ * (a_star.cpp:70-99): patch_arr_ <- 127, patch_safety_arr_ <- UNKNOWN, astar_dim =
+ * floor(patch_dim / pool_win); astar_grid_ <- UNKNOWN, movement cost <- astar_movement_cost,
+ * h_prox <- 0, motion_res <- motion_res_max, geofence <- 0, distance windows <- 0, heuristic
+ * slots emptied.  (Carrying h_prox / motion_res over a patch move, a_star.cpp:84-96, is a
+ * download / shift / upload the host mirror does.) */
+int ga_patch_reset(ga_ctx* ctx, int patch_dim);
+
+/* CollisionChecker::passLocalMapData (collision_checking.cpp:269-313): copy a dim x dim u8
+ * window (host memory) into patch_arr_ at (ox, oy).  Whole window dropped when it overhangs in
+ * x, rows skipped when they overhang in y -- as the reference does.  Only the window crosses
+ * PCIe; the patch stays device-resident. */
+int ga_patch_insert(ga_ctx* ctx, const uint8_t* window, int ox, int oy, int dim);
+
+/* CollisionChecker::processSafetyPatch (collision_checking.cpp:193-224) followed by
+ * AStar::calcAstarGridCuda -> Pooling::execute (a_star.cpp:536-542, LIB/src/cuda_lib/max_pool.cu:21-79):
+ * threshold -> disk dilation -> patch_safety_arr_, and its pool_win x pool_win max -> astar_grid_. */
+int ga_build_safety(ga_ctx* ctx);
+
+/* ---- footprint collision checks ------------------------------------------------------------ */
+
+/* CollisionChecker::getPathCollisionIndex / checkPathCollision / checkPose(/Variant)
+ * (collision_checking.cpp:389-452), batched: segment s covers poses [seg_off[s], seg_off[s+1]);
+ * first_hit[s] = index inside the segment of the first colliding pose, -1 if none.
+ * variant = 0: an off-map disk invalidates the pose (checkGrid :344-362); 1: it is skipped
+ * (checkGridVariant :369-387).  Host pointers; one kernel launch for the whole batch. */
+int ga_check_poses(ga_ctx* ctx, const double* x, const double* y, const double* yaw, int n_poses,
+                   const int* seg_off, int n_seg, int variant, int* first_hit);
+
+/* HybridAStar::setNeighbors' collision-relevant part for a batch of expanded nodes
+ * (LIB/src/hybridastar_planning_lib/hybrid_a_star_lib.cpp:492-534: calcNextNode :427-483,
+ * calcRearAxisNode :350-403, Vehicle::move_car_some_steps / turn_on_rear_axis
+ * LIB/src/collision_checker_lib/vehicle.cpp:45-122, mapCont2Disc :410-417): one launch rolls out
+ * every primitive of every node and checks every pose. */
+typedef struct
+{
+  double max_steer;               /* Vehicle::max_steer_ */
+  double wheel_base;              /* Vehicle::w_b_ */
+  double arc_l;                   /* HybridAStar::arc_l_ */
+  double yaw_res_deg;             /* config.yml YAW_RES (search yaw discretisation) */
+  double turn_on_point_angle_deg; /* config.yml TURN_ON_POINT_ANGLE */
+  int nb_steer;                   /* NB_STEER = 13 (hybrid_a_star_lib.hpp:48), <= 31 */
+} ga_expand_params;
+
+typedef struct
+{
+  double x, y, yaw;    /* parent pose, metres / rad, patch frame */
+  double motion_res;   /* AStar::motion_res_map_ at the parent (hybrid_a_star_lib.cpp:1483) */
+  int32_t with_rear_axis; /* 1: also the U-Shift rear-axis rotations (:512-533) */
+  int32_t pad_;
+} ga_node;
+
+typedef struct
+{
+  double x, y, yaw;    /* last pose of the primitive */
+  int32_t xi, yi, yawi; /* mapCont2Disc of the last pose */
+  int32_t n_poses;     /* poses rolled out */
+  uint8_t valid;       /* 1 = neighbour would be created (on grid and collision-free) */
+  uint8_t near_cell_edge; /* 1 = some pose lies within 1e-9 cells of a cell / yaw-bin boundary:
+                             device libm and glibc may disagree there, re-check on the host */
+  uint8_t pad_[6];
+} ga_succ;
+
+/* number of primitives ga_expand writes per node: 2*nb_steer, + rear-axis deltas when the node
+ * asks for them; out must hold n_nodes * ga_expand_stride(ctx) entries, unused entries have
+ * n_poses = 0 */
+int ga_set_expand_params(ga_ctx* ctx, const ga_expand_params* p);
+int ga_expand_stride(const ga_ctx* ctx);
+int ga_expand(ga_ctx* ctx, const ga_node* nodes, int n_nodes, ga_succ* out);
+
+/* ---- heuristic grid ------------------------------------------------------------------------- */
+
+typedef struct
+{
+  double astar_movement_cost;      /* params.yml astar_movement_cost_ (movement map fill) */
+  double astar_prox_cost;          /* params.yml astar_prox_cost_ */
+  double astar_lane_movement_cost; /* params.yml astar_lane_movement_cost_ (REFORDER only) */
+  double unknown_cost_w;           /* config.yml ASTAR_UNKNOWN_COST */
+  /* potential field, a_star.cpp:486-508 */
+  double alpha, do_max, do_min;
+  double motion_res_min, motion_res_max, dist_val_min, dist_val_max;
+  int vor_dim;                     /* VOR_DIM = 200, a_star.hpp:36 */
+  int dt_variant;                  /* ga_dt_variant */
+} ga_astar_params;
+
+typedef enum { GA_DT_FIXEDPOINT = 0, GA_DT_IPPFLOAT = 1 } ga_dt_variant;
+
+int ga_set_astar_params(ga_ctx* ctx, const ga_astar_params* p);
+
+/* AStar::calcDistanceHeuristic (a_star.cpp:110-295).  slot 0 = closed_set_guidance_
+ * (for_path = false), 1 = closed_set_path_.  Computes the least fixed point of the reference's
+ * edge relaxation  g(n) = min_p ((g(p) + len_i * mc(n)) + prox(p) * w_prox) + unk(p)  over the
+ * 8-connected grid from the goal, in fp64 with the reference's operand order, plus parent,
+ * cost_dist and is_unknown planes.  The reference's pop order, early exit and start cell only
+ * decide WHICH reachable cells it closes and, at a few cells, a suboptimal cost;
+ * the fixed point needs no start cell.  n_closed (may be NULL; forces a stream sync otherwise)
+ * receives the number of reachable cells. */
+int ga_build_heuristic(ga_ctx* ctx, int slot, int goal_x, int goal_y, int* n_closed);
+
+/* AStar::calcVoronoiPotentialField (a_star.cpp:440-479) around ego (astar cells): two chamfer
+ * distance transforms (createDistanceTransform :426-433) + setCostmapValue (:486-508).  The
+ * Fortune sweep (deps_lib/VoronoiDiagramGenerator.cpp, serial fp64 geometry) stays on the host:
+ * vor_xy = the n_vor edge end points it marks, window coordinates.  The host asks for the OCC
+ * cells of the window with ga_potential_sites first.  Returns GA_OK; *had_occ (may be NULL)
+ * tells whether the window held an obstacle (0 = early return of a_star.cpp:462-465). */
+int ga_potential_sites(ga_ctx* ctx, int ego_x, int ego_y, int* xy, int cap, int* n_sites);
+int ga_build_potential(ga_ctx* ctx, int ego_x, int ego_y, const int* vor_xy, int n_vor,
+                       int* had_occ);
+
+/* ---- data movement -------------------------------------------------------------------------- */
+
+/* whole-grid host <-> device copies (bytes must equal the grid's size) */
+int ga_upload(ga_ctx* ctx, int grid_id, const void* src, size_t bytes);
+int ga_download(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
+int ga_grid_bytes(const ga_ctx* ctx, int grid_id, size_t* bytes);
+/* device address of a grid (for zero-copy consumers such as the bench's resident-input leg) */
+int ga_device_ptr(ga_ctx* ctx, int grid_id, void** dptr);
+int ga_patch_dim(const ga_ctx* ctx);
+int ga_astar_dim(const ga_ctx* ctx);
+
+/* ---- measurement ---------------------------------------------------------------------------- */
+
+/* kernels this library launches; ga_prof_* brackets each launch with CUDA events on the
+ * context's stream when profiling is on (used by bench.py for the live roofline figure) */
+typedef enum
+{
+  GA_K_PACK = 0,      /* threshold + bit-plane pack                */
+  GA_K_DILATE = 1,    /* disk dilation + expand + 4x4 pool         */
+  GA_K_HEUR_INIT = 2,
+  GA_K_HEUR_RELAX = 3,
+  GA_K_HEUR_FINISH = 4,
+  GA_K_COLLISION = 5,
+  GA_K_EXPAND = 6,
+  GA_K_DT = 7,
+  GA_K_POTENTIAL = 8,
+  GA_K_COUNT = 9
+} ga_kernel_id;
+
+int ga_prof_enable(ga_ctx* ctx, int on);
+int ga_prof_reset(ga_ctx* ctx);
+/* total device milliseconds and launches of kernel k since the last reset (syncs the stream) */
+int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches);
+/* launches of ALL library kernels since ga_create / ga_prof_reset (always counted) */
+long long ga_launch_count(const ga_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -59,7 +59,8 @@ void gao_threshold(const uint8_t* patch, uint8_t* out, size_t n, int min_thresh,
   for (size_t i = 0; i < n; ++i)
   {
     const uint8_t v = patch[i];
-    out[i] = (v < lo) ? GAO_FREE : ((v > hi) ? GAO_OCC : GAO_UNKNOWN);
+    /* setTo(FREE), then setTo(OCC), then setTo(UNKNOWN where neither): OCC wins over FREE */
+    out[i] = (v > hi) ? GAO_OCC : ((v < lo) ? GAO_FREE : GAO_UNKNOWN);
   }
 }
 
