@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurement of the B200 grid backend (BASELINE.json configs[1]).
+
+Workload ("synthetic-4096"): synthetic 4096 x 4096 occupancy patch (SURVEY.md 8(d) gen_map, seed
+20240 + i) -> threshold + 21x21 disk dilation + 4x4 max-pool (ga_build_safety) -> obstacle-aware
+2D heuristic grid from a goal cell (ga_build_heuristic) on the 1024 x 1024 astar grid.
+One step = one such environment build.  metric = heuristic-grid Mcells/s = astar cells closed by
+the heuristic / step time (the dilation + pool that feed it are inside the step).
+
+value : inputs resident in HBM, device-timed with CUDA events on the library's stream.
+e2e   : same step through the reference-facing host API with HOST buffers: pinned patch -> H2D,
+        build, D2H of the closed-set planes (cost, cost_dist, parent, flags) the serial search reads.
+N > 1 : one process per GPU (torchrun), every rank builds its own environments (independent
+        queries, no data-path collective), value = all ranks' cells / max-over-ranks time.
+--impl reference : the reference's own CPU code for the same step (oracle/_ref when built, else
+        the oracle port), timed on the host cores.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "guided-extended-hybrid-astar_b200"))
+
+PATCH_DIM = 4096
+N_ROT = 4            # distinct environments rotated through so consecutive steps never share L2 contents
+METRIC = "heuristic_grid_mcells_per_s"
+UNIT = "Mcells/s"
+BYTES_PER_CELL_HEUR = 39.0   # read 1+1+8+8, write 8+8+4+1 per astar cell
+BYTES_PER_CELL_SAFETY = 2.0 + 1.0 / 16
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 6400.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz = None
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [v.strip() for v in out.strip().split(",")]
+                self.samples.append(float(f[0]))
+                self.max_mhz = float(f[1])
+                for n, v in zip(names, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def make_env(ga, device, seed, torch):
+    """one planner context with its 4096^2 patch resident, plus pinned host buffers for e2e"""
+    from ga_b200 import _abi
+    ctx = ga.GridContext(device)
+    cfg = ga.LibConfig()
+    astar = ga.AStar(ctx, cfg)
+    cc = ga.CollisionChecker(ctx, ga.Vehicle.from_config(ga.VehConfig()), cfg)
+    cc.initialize(PATCH_DIM)
+    patch = ga.gen_map(PATCH_DIM, seed)
+    h_patch = torch.from_numpy(patch).pin_memory()
+    ctx.upload(_abi.GRID_PATCH, h_patch.numpy())
+    cc.processSafetyPatch()
+    grid = astar.astar_grid_
+    goal = ga.sample_free_cells(grid, 1, seed + 1)[0]
+    adim = astar.astar_dim_
+    outs = {gid: torch.empty((adim, adim), dtype=dt).pin_memory() for gid, dt in
+            ((_abi.GRID_HEUR_COST, torch.float64), (_abi.GRID_HEUR_DIST, torch.float64),
+             (_abi.GRID_HEUR_PARENT, torch.int32), (_abi.GRID_HEUR_FLAGS, torch.uint8))}
+    return dict(ctx=ctx, cc=cc, astar=astar, patch=patch, h_patch=h_patch, goal=(int(goal[0]), int(goal[1])), outs=outs)
+
+
+def step_resident(env, n_closed=None):
+    lib, h = env["ctx"].lib, env["ctx"].h
+    env["ctx"].check(lib.ga_build_safety(h))
+    env["ctx"].check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], n_closed))
+
+
+def step_e2e(env):
+    from ga_b200 import _abi
+    ctx = env["ctx"]
+    lib, h = ctx.lib, ctx.h
+    hp = env["h_patch"]
+    ctx.check(lib.ga_upload(h, _abi.GRID_PATCH, C.c_void_p(hp.data_ptr()), hp.numel()))
+    ctx.check(lib.ga_build_safety(h))
+    ctx.check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], None))
+    for gid, t in env["outs"].items():
+        ctx.check(lib.ga_download(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+
+
+def cpu_reference_step(patch, goal, disk_r_c, use_ref):
+    """one step of the same workload on the host cores; returns (seconds, cells closed, kind)"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ga_oracle_py as go
+    t0 = time.perf_counter()
+    safety = go.process_safety_patch(patch, 100, 130, disk_r_c)
+    grid = go.pool_max(safety)
+    dim = grid.shape[0]
+    hp = go.HeurParams(dim, 5.0, 3.0, 0.0, 0, 10000, 0)  # early exit off: the whole reachable grid, as the GPU builds
+    mc = np.full((dim, dim), 5.0)
+    prox = np.zeros((dim, dim))
+    fence = np.zeros((dim, dim), np.uint8)
+    res = go.heuristic_reforder(hp, grid, fence, mc, prox, goal, goal)
+    return time.perf_counter() - t0, res["n_closed"], "port"
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ga_b200
+    dim = args.ref_dim
+    veh = ga_b200.Vehicle.from_config(ga_b200.VehConfig())
+    _, _, r_c, _ = ga_b200.calc_disks(veh, ga_b200.LibConfig())
+    times, cells = [], 0
+    kind = "port"
+    for i in range(args.warmup + args.steps):
+        patch = ga_b200.gen_map(dim, 20240 + i % N_ROT)
+        import ga_oracle_py as go
+        thr = go.threshold(patch, 100, 130)
+        free = np.argwhere(thr[::4, ::4] == 0)
+        goal = (int(free[len(free) // 2][1]), int(free[len(free) // 2][0]))
+        dt, n, kind = cpu_reference_step(patch, goal, r_c, False)
+        if i >= args.warmup:
+            times.append(dt)
+            cells += n
+    total = sum(times)
+    val = cells / total / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "synthetic-4096", "patch_dim": PATCH_DIM, "astar_dim": PATCH_DIM // 4,
+                       "sample_patch_dim": dim},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind,
+                             "sample": "%d step(s) of the same pipeline on a %dx%d patch (seeded like the GPU arm)" % (args.steps, dim, dim)},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ref-dim", type=int, default=2048, help="patch size of the bounded CPU sample (reference arm)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import ga_b200
+    from ga_b200 import _abi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the B200 backend has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    envs = [make_env(ga_b200, local_rank, 20240 + rank * N_ROT + i, torch) for i in range(N_ROT)]
+    hbm_peak, peak_src = load_peaks()
+
+    def barrier():
+        for e in envs:
+            e["ctx"].sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # cells closed per environment (fixed by the map), also the parity hook of smoke()
+    closed = []
+    for e in envs:
+        n = C.c_int()
+        step_resident(e, C.byref(n))
+        closed.append(n.value)
+
+    def timed(step_fn, steps, profile):
+        for i in range(args.warmup):
+            step_fn(envs[i % N_ROT])
+        barrier()
+        if profile:
+            for e in envs:
+                e["ctx"].prof_reset()
+                e["ctx"].prof_enable(True)
+        launches0 = sum(e["ctx"].launch_count() for e in envs)
+        t0 = time.perf_counter()
+        # steps run back to back on the device: step i+1's stream waits for step i's end event, so the
+        # span first-start .. last-end is exactly K serialised steps without any host synchronisation
+        first = last = None
+        for i in range(steps):
+            e = envs[i % N_ROT]
+            s = torch.cuda.ExternalStream(e["ctx"].stream())
+            if last is not None:
+                s.wait_event(last)
+            a = torch.cuda.Event(enable_timing=True)
+            a.record(s)
+            first = first or a
+            step_fn(e)
+            last = torch.cuda.Event(enable_timing=True)
+            last.record(s)
+        barrier()
+        wall = time.perf_counter() - t0
+        dev_ms = first.elapsed_time(last)
+        launches = sum(e["ctx"].launch_count() for e in envs) - launches0
+        cells = sum(closed[i % N_ROT] for i in range(steps))
+        if profile:
+            for e in envs:
+                e["ctx"].prof_enable(False)
+        return dev_ms, wall * 1e3, launches, cells
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    dev_ms, wall_ms, launches, cells = timed(step_resident, args.steps, True)
+    # per-kernel device time of the timed region (events around each launch on the library's stream)
+    kt = {}
+    for k, name in ((_abi.K_PACK, "pack"), (_abi.K_DILATE, "dilate_pool"), (_abi.K_HEUR_INIT, "heur_init"),
+                    (_abi.K_HEUR_RELAX, "heur_relax"), (_abi.K_HEUR_FINISH, "heur_finish")):
+        ms = n = 0
+        for e in envs:
+            m_, n_ = e["ctx"].prof_get(k)
+            ms += m_
+            n += n_
+        kt[name] = (ms, n)
+    # the steps are serialised on each context's stream; K steps' device time = sum of per-step event spans
+    e2e_dev_ms, e2e_wall_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
+    sampler.stop_flag = True
+
+    # max over ranks
+    t = torch.tensor([dev_ms, e2e_wall_ms, float(cells), float(e2e_cells), float(launches)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        dev_ms, e2e_wall_ms = float(tmax[0]), float(tmax[1])
+        cells, e2e_cells, launches = float(tsum[2]), float(tsum[3]), int(tsum[4])
+    value = cells / (dev_ms * 1e-3) / 1e6
+    e2e_value = e2e_cells / (e2e_wall_ms * 1e-3) / 1e6
+
+    if rank == 0:
+        adim = PATCH_DIM // 4
+        relax_ms, relax_n = kt["heur_relax"]
+        dil_ms, dil_n = kt["dilate_pool"]
+        # dominant kernel = the wavefront relaxation; algorithmic bytes = 39 B x astar cells of one grid per launch
+        alg_bytes = BYTES_PER_CELL_HEUR * adim * adim
+        achieved = alg_bytes / (relax_ms / max(relax_n, 1) * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "synthetic-4096", "patch_dim": PATCH_DIM, "astar_dim": adim,
+                           "disk_r_c": envs[0]["cc"].disk_r_c_, "l2": "inputs rotate over %d environments per rank (~130 MB each) > L2" % N_ROT,
+                           "cells_closed_per_step": cells / args.steps / world},
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": PATCH_DIM * PATCH_DIM,
+                        "d2h_bytes_per_step": adim * adim * 21, "ms_per_step": e2e_wall_ms / args.steps},
+                "gpu_launches": launches,
+                "roofline": {"bound": "hbm", "kernel": "heur_relax_kernel", "achieved": achieved, "peak": hbm_peak,
+                             "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": relax_ms / max(relax_n, 1)},
+                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
+                "dilate_roofline": {"achieved": BYTES_PER_CELL_SAFETY * PATCH_DIM * PATCH_DIM /
+                                    ((kt["pack"][0] + dil_ms) / max(dil_n, 1) * 1e-3) / 1e9, "unit": "GB/s",
+                                    "note": "pack + dilate_pool kernels, 2+1/16 B per gm cell"},
+                "clocks": sampler.result()}
+        if not args.no_cpu_baseline:
+            e0 = envs[0]
+            sub = 2048  # bounded sample: the same pipeline on the top-left 2048^2 of environment 0
+            patch = np.ascontiguousarray(e0["patch"][:sub, :sub])
+            import ga_oracle_py as go  # noqa: F401  (cpu_baseline leg: the oracle is the thing timed here, as the checker's twin)
+            thr = go.threshold(patch, 100, 130)
+            free = np.argwhere(thr[::4, ::4] == 0)
+            goal = (int(free[len(free) // 2][1]), int(free[len(free) // 2][0]))
+            dt, n, kind = cpu_reference_step(patch, goal, e0["cc"].disk_r_c_, False)
+            line["cpu_baseline"] = {"value": n / dt / 1e6, "unit": UNIT, "cores": 1, "kind": kind,
+                                    "sample": "1 step on the 2048x2048 corner of environment 0 (%.1f s)" % dt}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    for e in envs:
+        e["ctx"].close()
+
+
+if __name__ == "__main__":
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    main()

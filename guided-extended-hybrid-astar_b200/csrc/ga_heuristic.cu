@@ -219,3 +219,206 @@ __global__ void __launch_bounds__(H_THREADS, 1) heur_relax_kernel(heur_args a)
     }
   }
 }
+
+// ---------------------------------------------------------------------------------------------
+// finish: parent / is_unknown / closed flags from the converged cost plane, cost_dist by pointer
+// jumping over the parent forest (step counts are integers, so the result is order-free).
+// ---------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256) heur_finish_kernel(heur_args a)
+{
+  cg::grid_group grid = cg::this_grid();
+  const int ncell = a.dim * a.dim;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nthr = gridDim.x * blockDim.x;
+  int32_t* jump0 = a.jump;
+  int32_t* jump1 = a.jump + ncell;
+  int2* cnt0 = reinterpret_cast<int2*>(a.cnt);
+  int2* cnt1 = cnt0 + ncell;
+
+  // ---- phase 1: canonical parent = smallest motion index whose candidate reproduces g(n)
+  int closed = 0;
+  for (int n = tid; n < ncell; n += nthr)
+  {
+    const double gn = __ldcg(a.g + n);
+    int32_t par = -2;
+    uint8_t fl = 0;
+    int2 c = make_int2(0, 0);
+    if (gn < INFINITY)
+    {
+      ++closed;
+      fl = GA_H_CLOSED;
+      if (n == a.goal)
+      {
+        par = -1;
+        if (__ldg(a.grid + n) == GA_UNKNOWN) fl |= GA_H_UNKNOWN;  // goal_unknown, a_star.cpp:116
+      }
+      else
+      {
+        const int nx = n % a.dim, ny = n / a.dim;
+        const double m = __ldg(a.mc + n);
+        const double ln1 = a.L1 * m, ln2 = a.L2 * m;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+        {
+          const int px = nx - c_mdx[i], py = ny - c_mdy[i];
+          if (px < 0 || py < 0 || px >= a.dim || py >= a.dim) continue;
+          const int q = py * a.dim + px;
+          const double gq = __ldcg(a.g + q);
+          if (!(gq < INFINITY)) continue;
+          const bool unk = __ldg(a.grid + q) == GA_UNKNOWN;
+          double cand = gq + (i < 4 ? ln1 : ln2);
+          cand = cand + __ldg(a.prox + q) * a.w_prox;
+          cand = cand + (unk ? a.unk_w : 0.0);
+          if (cand == gn)
+          {
+            par = q;
+            if (unk) fl |= GA_H_UNKNOWN;  // NodeDisc::is_unknown_ = unknown-ness of the parent, :253,268
+            c = (i < 4) ? make_int2(1, 0) : make_int2(0, 1);
+            break;
+          }
+        }
+      }
+    }
+    a.parent[n] = par;
+    a.flags[n] = fl;
+    jump0[n] = par >= 0 ? par : -1;
+    cnt0[n] = c;
+  }
+  // closed-cell count
+  closed = __reduce_add_sync(0xFFFFFFFFu, closed);
+  if ((threadIdx.x & 31) == 0 && closed) atomicAdd(a.ctl + 2, closed);
+
+  // ---- phase 2: pointer jumping; ctl[4 + (r & 1)] = r + 1 when round r still moved a pointer
+  int32_t* jc = jump0;
+  int32_t* jn = jump1;
+  int2* cc = cnt0;
+  int2* cn = cnt1;
+  __threadfence();
+  grid.sync();
+  for (int r = 0;; ++r)
+  {
+    int moved = 0;
+    for (int n = tid; n < ncell; n += nthr)
+    {
+      const int32_t j = __ldcg(jc + n);
+      int2 c = __ldcg(cc + n);
+      int32_t jj = -1;
+      if (j >= 0)
+      {
+        jj = __ldcg(jc + j);
+        const int2 cj = __ldcg(cc + j);
+        c.x += cj.x;
+        c.y += cj.y;
+        moved |= (jj >= 0);
+      }
+      jn[n] = jj;
+      cn[n] = c;
+    }
+    if (__any_sync(0xFFFFFFFFu, moved) && (threadIdx.x & 31) == 0) a.ctl[4 + (r & 1)] = r + 1;
+    __threadfence();
+    grid.sync();
+    int32_t* tj = jc; jc = jn; jn = tj;
+    int2* tc = cc; cc = cn; cn = tc;
+    if (__ldcg(a.ctl + 4 + (r & 1)) != r + 1) break;
+  }
+
+  // ---- phase 3: NodeDisc::cost_dist_
+  for (int n = tid; n < ncell; n += nthr)
+  {
+    const int2 c = __ldcg(cc + n);
+    const bool in = a.flags[n] & GA_H_CLOSED;
+    a.dist[n] = in ? (double)c.x * a.L1 + (double)c.y * a.L2 : INFINITY;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------------------------
+
+void ga_heur_free(ga_ctx* c)
+{
+  void** ptrs[] = { (void**)&c->d_tile_active, (void**)&c->d_hctl, (void**)&c->d_jump, (void**)&c->d_cnt };
+  for (void** p : ptrs)
+  {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+  }
+}
+
+int ga_heur_alloc(ga_ctx* c)
+{
+  const size_t na = (size_t)c->astar_dim * c->astar_dim;
+  c->tiles_x = (c->astar_dim + HT - 1) / HT;
+  c->n_tiles = c->tiles_x * c->tiles_x;
+  GA_CUDA(c, cudaMalloc(&c->d_tile_active, sizeof(int) * 2 * (size_t)c->n_tiles));
+  GA_CUDA(c, cudaMalloc(&c->d_hctl, sizeof(int) * 16));
+  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * 2 * na));
+  GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 4 * na));
+  int per_sm = 0;
+  GA_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, heur_relax_kernel, H_THREADS, 0));
+  GA_REQUIRE(c, per_sm >= 1, GA_ERR_CUDA, "heuristic relax kernel does not fit an SM");
+  c->relax_grid = per_sm * c->sm_count;
+  int per_sm_f = 0;
+  GA_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_f, heur_finish_kernel, 256, 0));
+  GA_REQUIRE(c, per_sm_f >= 1, GA_ERR_CUDA, "heuristic finish kernel does not fit an SM");
+  c->finish_grid = per_sm_f * c->sm_count;
+  return GA_OK;
+}
+
+extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, int* n_closed)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_ap, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, slot == 0 || slot == 1, GA_ERR_ARG, "slot must be 0 (guidance) or 1 (path)");
+  const int dim = c->astar_dim;
+  GA_REQUIRE(c, goal_x >= 0 && goal_y >= 0 && goal_x < dim && goal_y < dim, GA_ERR_ARG, "goal outside the astar grid");
+  GA_CUDA(c, cudaSetDevice(c->device));
+
+  heur_args a;
+  a.grid = c->d_astar;
+  a.fence = c->d_fence;
+  a.mc = c->d_mc;
+  a.prox = c->d_prox;
+  a.g = c->d_hcost[slot];
+  a.parent = c->d_hparent[slot];
+  a.dist = c->d_hdist[slot];
+  a.flags = c->d_hflags[slot];
+  a.active = c->d_tile_active;
+  a.ctl = c->d_hctl;
+  a.jump = c->d_jump;
+  a.cnt = c->d_cnt;
+  a.dim = dim;
+  a.tiles_x = c->tiles_x;
+  a.n_tiles = c->n_tiles;
+  a.goal = goal_y * dim + goal_x;
+  a.w_prox = c->ap.astar_prox_cost;
+  a.unk_w = c->ap.unknown_cost_w;
+  // movement_distances_ (a_star.hpp:54-57): ASTAR_RES and ASTAR_RES * sqrt(2)
+  a.L1 = 0.625;
+  a.L2 = 0.625 * sqrt(2.0);
+
+  {
+    ga_launch_scope ls(c, GA_K_HEUR_INIT);
+    heur_init_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(a);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  void* args[] = { &a };
+  {
+    ga_launch_scope ls(c, GA_K_HEUR_RELAX);
+    const int g = c->relax_grid < c->n_tiles ? c->relax_grid : c->n_tiles;
+    GA_CUDA(c, cudaLaunchCooperativeKernel((const void*)heur_relax_kernel, dim3(g), dim3(H_THREADS), args, 0, c->stream));
+  }
+  {
+    ga_launch_scope ls(c, GA_K_HEUR_FINISH);
+    const int want = (int)(((size_t)dim * dim + 255) / 256);
+    const int g = c->finish_grid < want ? c->finish_grid : want;
+    GA_CUDA(c, cudaLaunchCooperativeKernel((const void*)heur_finish_kernel, dim3(g), dim3(256), args, 0, c->stream));
+  }
+  if (n_closed)
+  {
+    GA_CUDA(c, cudaMemcpyAsync(n_closed, c->d_hctl + 2, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return GA_OK;
+}

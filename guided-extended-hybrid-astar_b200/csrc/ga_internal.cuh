@@ -79,6 +79,7 @@ struct ga_ctx
   int32_t* d_jump = nullptr;      // pointer-jumping scratch: 2 * ncell
   int32_t* d_cnt = nullptr;       // (n_straight, n_diag) pairs: 2 * 2 * ncell
   int relax_grid = 0;             // co-resident CTAs of the persistent relax kernel
+  int finish_grid = 0;            // same for the finish kernel
 
   // ---- staging (pinned host + device) for pose batches
   void* h_stage = nullptr;

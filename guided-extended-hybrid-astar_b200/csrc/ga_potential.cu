@@ -1,0 +1,332 @@
+// ga_potential.cu -- K3 + K4: the two chamfer distance transforms and the Voronoi potential field
+// on the VOR_DIM x VOR_DIM window around ego.
+//
+// Replaces AStar::calcVoronoiPotentialField (a_star.cpp:440-479), createDistanceTransform
+// (:426-433, cv::distanceTransform(DIST_L2, DIST_MASK_5) of OpenCV 4.8.0) and setCostmapValue
+// (:486-508).  The Fortune sweep between the two transforms
+// (deps_lib/VoronoiDiagramGenerator.cpp:59-86) is serial fp64 geometry and stays on the host:
+// ga_potential_sites hands it the OCC cells in cv::findNonZero order, ga_build_potential takes the
+// edge end points it marks.
+//
+// Both OpenCV variants of the 5x5 chamfer are two-pass raster algorithms whose result depends on
+// the visiting order (exactly so for the IPP float variant), so the kernel keeps that order: the
+// whole window lives in shared memory (204^2 x 4 B = 166 KB), row y is owned by thread y, and the
+// rows run skewed by three columns -- cell (y, x) is visited at step x + 3y, after
+// (y, x-1), (y-1, x+2) and (y-2, x+1) -- 797 barrier steps per pass instead of 40 000 serial
+// cells.  One CTA per transform; the two transforms of a call run side by side.
+#include <cmath>
+
+#include "ga_internal.cuh"
+
+#define PB 2            // border cells around the staged window
+#define P_THREADS 256   // >= vor_dim
+
+template <bool IPP>
+struct dt_traits;
+template <>
+struct dt_traits<true>  // ippiDistanceTransform_5x5_8u32f_C1R: float32, metrics 1, 1.4, 2.1969
+{
+  typedef float T;
+  __device__ static T hv() { return 1.0f; }
+  __device__ static T dg() { return 1.4f; }
+  __device__ static T lg() { return 2.1969f; }
+  __device__ static T big() { return 3.4e38f; }
+  __device__ static float out(T v) { return v; }
+};
+template <>
+struct dt_traits<false>  // OpenCV distanceTransform_5x5: 16.16 fixed point, cvRound(metric * 65536)
+{
+  typedef unsigned int T;
+  __device__ static T hv() { return 65536u; }
+  __device__ static T dg() { return 91750u; }
+  __device__ static T lg() { return 143976u; }
+  __device__ static T big() { return 0x7fffffffu >> 2; }
+  __device__ static float out(T v)
+  {
+    const T c = v > big() ? big() : v;
+    return (float)c * (1.f / 65536.f);
+  }
+};
+
+struct pot_args
+{
+  const uint8_t* grid;   // astar_grid_
+  float* odist;          // obstacle_dist_
+  float* vdist;          // voronoi_dist_ (persistent, in/out)
+  double* prox;          // h_prox_arr_
+  double* mres;          // motion_res_map_
+  const int* vor_xy;     // end points, window coordinates
+  int* flag;             // [0] = number of OCC cells in the window
+  int n_vor, dim, V, ox, oy;
+  double alpha, do_max, mr_min, mr_max, dv_min, dv_max;
+};
+
+template <bool IPP>
+__global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
+{
+  typedef dt_traits<IPP> TR;
+  typedef typename TR::T T;
+  extern __shared__ unsigned char dt_smem[];
+  T* s = reinterpret_cast<T*>(dt_smem);
+  const int V = a.V, S = V + 2 * PB;
+  const int which = blockIdx.x;  // 0: obstacle transform, 1: Voronoi transform
+
+  // OCC cells of the window (both CTAs count: the Voronoi one must know about the early return)
+  int occ = 0;
+  for (int i = threadIdx.x; i < V * V; i += P_THREADS)
+    occ += a.grid[(size_t)(a.oy + i / V) * a.dim + a.ox + i % V] == GA_OCC;
+  occ = __syncthreads_count(occ > 0) ? 1 : 0;
+  if (which == 0 && threadIdx.x == 0) a.flag[0] = occ;
+  if (which == 1)
+  {
+    if (!occ) return;  // a_star.cpp:462-465: no obstacle, the old field stays
+    // generateVoronoi_wrapper marks the edge end points with OCC (VoronoiDiagramGenerator.cpp:83-84)
+    for (int i = threadIdx.x; i < a.n_vor; i += P_THREADS)
+    {
+      const int x = a.vor_xy[2 * i], y = a.vor_xy[2 * i + 1];
+      if (x >= 0 && y >= 0 && x < V && y < V) a.vdist[(size_t)y * V + x] = 2.0f;
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < S * S; i += P_THREADS)
+  {
+    const int x = i % S - PB, y = i / S - PB;
+    T v = TR::big();
+    if (x >= 0 && y >= 0 && x < V && y < V)
+    {
+      // source image 1 - (val == mat): zero exactly where the value is OCC (== 2)
+      const bool zero = which == 0 ? a.grid[(size_t)(a.oy + y) * a.dim + a.ox + x] == GA_OCC
+                                   : a.vdist[(size_t)y * V + x] == 2.0f;
+      v = zero ? (T)0 : TR::big();
+    }
+    s[i] = v;
+  }
+  __syncthreads();
+
+  const int y = threadIdx.x;
+  const int steps = (V - 1) + 3 * (V - 1) + 1;
+  // ---- forward pass
+  {
+    T* row = s + (size_t)(y + PB) * S + PB;
+    for (int t = 0; t < steps; ++t)
+    {
+      const int x = t - 3 * y;
+      if (y < V && x >= 0 && x < V && row[x] != (T)0)
+      {
+        T t0 = row[x - 2 * S - 1] + TR::lg();
+        t0 = min(t0, row[x - 2 * S + 1] + TR::lg());
+        t0 = min(t0, row[x - S - 2] + TR::lg());
+        t0 = min(t0, row[x - S - 1] + TR::dg());
+        t0 = min(t0, row[x - S] + TR::hv());
+        t0 = min(t0, row[x - S + 1] + TR::dg());
+        t0 = min(t0, row[x - S + 2] + TR::lg());
+        t0 = min(t0, row[x - 1] + TR::hv());
+        row[x] = IPP ? min(t0, TR::big()) : t0;
+      }
+      __syncthreads();
+    }
+  }
+  // ---- backward pass (mirrored skew)
+  {
+    const int yy = V - 1 - y;
+    T* row = s + (size_t)(yy + PB) * S + PB;
+    for (int t = 0; t < steps; ++t)
+    {
+      const int x = V - 1 - (t - 3 * y);
+      if (y < V && x >= 0 && x < V)
+      {
+        T t0 = row[x];
+        if (IPP || t0 > TR::hv())
+        {
+          t0 = min(t0, row[x + 2 * S + 1] + TR::lg());
+          t0 = min(t0, row[x + 2 * S - 1] + TR::lg());
+          t0 = min(t0, row[x + S + 2] + TR::lg());
+          t0 = min(t0, row[x + S + 1] + TR::dg());
+          t0 = min(t0, row[x + S] + TR::hv());
+          t0 = min(t0, row[x + S - 1] + TR::dg());
+          t0 = min(t0, row[x + S - 2] + TR::lg());
+          t0 = min(t0, row[x + 1] + TR::hv());
+          row[x] = t0;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // dist_map *= grid_tf::star2con_ (a_star.cpp:432): float element times 0.625
+  float* dst = which == 0 ? a.odist : a.vdist;
+  for (int i = threadIdx.x; i < V * V; i += P_THREADS)
+    dst[i] = TR::out(s[(size_t)(i / V + PB) * S + i % V + PB]) * 0.625f;
+}
+
+// K4: AStar::setCostmapValue (a_star.cpp:486-508)
+__global__ void __launch_bounds__(256) costmap_kernel(pot_args a)
+{
+  if (a.flag[0] == 0) return;  // early return of calcVoronoiPotentialField
+  const int V = a.V;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= V * V) return;
+  const int x = i % V, y = i / V;
+  const float d_o = a.odist[i];
+  const float d_v = a.vdist[i];
+  const size_t g = (size_t)(y + a.oy) * a.dim + x + a.ox;
+  double h = 0.0;
+  if ((double)d_o < a.do_max)
+  {
+    // std::pow(v, 2) is v * v (gcc expands pow(x, 2.0) to a multiplication at every -O level > 0)
+    const double q = (double)d_o - a.do_max;
+    h = (a.alpha / (a.alpha + (double)d_o)) * (double)(d_v / (d_o + d_v)) * (q * q) / (a.do_max * a.do_max);
+  }
+  a.prox[g] = h;
+  const float lo = (float)a.dv_min, hi = (float)a.dv_max;
+  const float cl = d_o < lo ? lo : (hi < d_o ? hi : d_o);  // std::clamp
+  const double mr = a.mr_min + ((a.mr_max - a.mr_min) / (a.dv_max - a.dv_min)) * ((double)cl - a.dv_min);
+  a.mres[g] = mr > a.mr_min ? mr : a.mr_min;
+}
+
+// OCC cells of the window in row-major (cv::findNonZero) order
+__global__ void __launch_bounds__(1024) sites_kernel(const uint8_t* __restrict__ grid, int dim, int V, int ox, int oy,
+                                                     int* __restrict__ xy, int cap, int* __restrict__ count)
+{
+  __shared__ int s_warp[32];
+  __shared__ int s_base;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i0 = 0; i0 < V * V; i0 += 1024)
+  {
+    const int i = i0 + threadIdx.x;
+    const int x = i % V, y = i / V;
+    const bool hit = i < V * V && grid[(size_t)(oy + y) * dim + ox + x] == GA_OCC;
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
+    if (lane == 0) s_warp[warp] = __popc(m);
+    __syncthreads();
+    int before = s_base;
+    for (int w = 0; w < warp; ++w) before += s_warp[w];
+    const int pos = before + __popc(m & ((1u << lane) - 1));
+    if (hit && pos < cap)
+    {
+      xy[2 * pos] = x;
+      xy[2 * pos + 1] = y;
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) s_base = pos + (hit ? 1 : 0);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = s_base;
+}
+
+static int window_origin(const ga_ctx* c, int ego_x, int ego_y, int* ox, int* oy)
+{
+  // getCurrentMapOrigin (a_star.cpp:527-531): clamped at 0 only; the reference's ROI would leave
+  // the matrix (OpenCV assertion) when the window overhangs the far border -- an argument error here
+  const int V = c->ap.vor_dim;
+  const int off = V / 2;
+  *ox = ego_x - off > 0 ? ego_x - off : 0;
+  *oy = ego_y - off > 0 ? ego_y - off : 0;
+  return (*ox + V <= c->astar_dim && *oy + V <= c->astar_dim) ? 0 : -1;
+}
+
+extern "C" int ga_potential_sites(ga_ctx* c, int ego_x, int ego_y, int* xy, int cap, int* n_sites)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_ap, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, n_sites && cap >= 0 && (cap == 0 || xy), GA_ERR_ARG, "bad arguments");
+  int ox, oy;
+  GA_REQUIRE(c, window_origin(c, ego_x, ego_y, &ox, &oy) == 0, GA_ERR_ARG, "potential window leaves the astar grid");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int V = c->ap.vor_dim;
+  const size_t b_xy = sizeof(int) * 2 * (size_t)V * V;
+  int rc = ga_stage_reserve(c, b_xy + 64);
+  if (rc) return rc;
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  int* d_cnt = (int*)c->d_stage;
+  int* d_xy = d_cnt + 16;
+  {
+    ga_launch_scope ls(c, GA_K_POTENTIAL);
+    sites_kernel<<<1, 1024, 0, c->stream>>>(c->d_astar, c->astar_dim, V, ox, oy, d_xy, V * V, d_cnt);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  int* h = (int*)c->h_stage;
+  GA_CUDA(c, cudaMemcpyAsync(h, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  const int n = h[0];
+  *n_sites = n;
+  const int take = n < cap ? n : cap;
+  if (take > 0)
+  {
+    GA_CUDA(c, cudaMemcpyAsync(h + 16, d_xy, sizeof(int) * 2 * (size_t)take, cudaMemcpyDeviceToHost, c->stream));
+    GA_CUDA(c, cudaStreamSynchronize(c->stream));
+    memcpy(xy, h + 16, sizeof(int) * 2 * (size_t)take);
+  }
+  return GA_OK;
+}
+
+extern "C" int ga_build_potential(ga_ctx* c, int ego_x, int ego_y, const int* vor_xy, int n_vor, int* had_occ)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_ap, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, n_vor >= 0 && (n_vor == 0 || vor_xy), GA_ERR_ARG, "bad arguments");
+  int ox, oy;
+  GA_REQUIRE(c, window_origin(c, ego_x, ego_y, &ox, &oy) == 0, GA_ERR_ARG, "potential window leaves the astar grid");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int V = c->ap.vor_dim;
+  GA_REQUIRE(c, V <= P_THREADS, GA_ERR_ARG, "vor_dim too large");
+  const size_t b_xy = sizeof(int) * 2 * (size_t)n_vor;
+  int rc = ga_stage_reserve(c, b_xy + 128);
+  if (rc) return rc;
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  int* d_flag = (int*)c->d_stage;
+  int* d_xy = d_flag + 16;
+  int* h = (int*)c->h_stage;
+  if (n_vor)
+  {
+    memcpy(h + 16, vor_xy, b_xy);
+    GA_CUDA(c, cudaMemcpyAsync(d_xy, h + 16, b_xy, cudaMemcpyHostToDevice, c->stream));
+  }
+  pot_args a;
+  a.grid = c->d_astar;
+  a.odist = c->d_odist;
+  a.vdist = c->d_vdist;
+  a.prox = c->d_prox;
+  a.mres = c->d_mres;
+  a.vor_xy = d_xy;
+  a.flag = d_flag;
+  a.n_vor = n_vor;
+  a.dim = c->astar_dim;
+  a.V = V;
+  a.ox = ox;
+  a.oy = oy;
+  a.alpha = c->ap.alpha;
+  a.do_max = c->ap.do_max;
+  a.mr_min = c->ap.motion_res_min;
+  a.mr_max = c->ap.motion_res_max;
+  a.dv_min = c->ap.dist_val_min;
+  a.dv_max = c->ap.dist_val_max;
+  const size_t smem = sizeof(float) * (size_t)(V + 2 * PB) * (V + 2 * PB);
+  {
+    ga_launch_scope ls(c, GA_K_DT);
+    if (c->ap.dt_variant == GA_DT_IPPFLOAT)
+    {
+      GA_CUDA(c, cudaFuncSetAttribute(dt_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      dt_kernel<true><<<2, P_THREADS, smem, c->stream>>>(a);
+    }
+    else
+    {
+      GA_CUDA(c, cudaFuncSetAttribute(dt_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      dt_kernel<false><<<2, P_THREADS, smem, c->stream>>>(a);
+    }
+  }
+  GA_CUDA(c, cudaGetLastError());
+  {
+    ga_launch_scope ls(c, GA_K_POTENTIAL);
+    costmap_kernel<<<(V * V + 255) / 256, 256, 0, c->stream>>>(a);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  if (had_occ)
+  {
+    GA_CUDA(c, cudaMemcpyAsync(h, d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    GA_CUDA(c, cudaStreamSynchronize(c->stream));
+    *had_occ = h[0];
+  }
+  return GA_OK;
+}

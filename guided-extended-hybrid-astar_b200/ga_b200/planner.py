@@ -1,0 +1,461 @@
+"""Host mirror of the reference's CollisionChecker / AStar / Vehicle interfaces.
+
+The reference keeps all state in static class members (one planner per process,
+collision_checking.hpp:50-76, a_star.hpp:38-99).  Here the state lives in a GridContext (one
+ga_ctx: device arenas + one CUDA stream), and CollisionChecker / AStar are views on it that keep
+the reference's method names, argument meaning and error behaviour
+(wrapper_hybrid_a_star_lib.cpp:176-199, 327-346).  Every grid computation runs in
+libgridaccel.so; nothing here computes a grid on the CPU.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _abi
+from ._abi import GaError
+
+GM_RES = 0.15625    # params.hpp:8
+ASTAR_RES = 0.625   # params.hpp:7
+CON2GM = 1 / GM_RES
+CON2STAR = 1 / ASTAR_RES
+TO_RAD = math.pi / 180
+FREE, UNKNOWN, OCC = 0, 1, 2   # GRID_VAL, collision_checking.hpp:39-47
+NB_STEER = 13                  # hybrid_a_star_lib.hpp:48
+
+
+class VehConfig:
+    """Default vehicle (python/path_planner_lib/data_structures.py:19-34)."""
+
+    def __init__(self, max_steer=0.55, width=2.13, wb=3.165, lf=3.993, lb=1.17, is_ushift=False):
+        self.max_steer, self.width, self.wb, self.lf, self.lb = max_steer, width, wb, lf, lb
+        self.is_ushift = is_ushift
+
+
+class LibConfig:
+    """The keys of config/config.yml and config/params.yml the grid path reads, shipped values."""
+
+    def __init__(self, **kw):
+        self.YAW_RES_COLL = 3
+        self.DOUBLE_DISK_ROWS = False
+        self.LEN_PER_DISK = 2.0
+        self.SAFETY_DISTANCE_M = 0.1
+        self.MIN_THRESH = 100
+        self.MAX_THRESH = 130
+        self.ASTAR_UNKNOWN_COST = 0.0
+        self.MAX_EXTRA_NODES_ASTAR = 10000
+        self.HEURISTIC_EARLY_EXIT = True
+        self.TURN_ON_POINT_ANGLE = 90.0
+        self.YAW_RES = 10
+        self.MOTION_RES_MIN = 0.1
+        self.MOTION_RES_MAX = 1.0
+        self.MIN_DIST_VAL = 3.0
+        self.MAX_DIST_VAL = 10.0
+        self.RA_FREQ = 5
+        # params.yml
+        self.astar_prox_cost_ = 5.0
+        self.astar_movement_cost_ = 5.0
+        self.astar_lane_movement_cost_ = 3.0
+        self.alpha_ = 100.0
+        self.do_max_ = 7.0
+        self.do_min_ = 3.0
+        # a_star.hpp:36; IPP float chamfer = what the reference's Docker OpenCV (WITH_IPP) runs
+        self.VOR_DIM = 200
+        self.DT_VARIANT = _abi.DT_IPPFLOAT
+        for k, v in kw.items():
+            if not hasattr(self, k):
+                raise KeyError(k)
+            setattr(self, k, v)
+
+    @classmethod
+    def from_yaml(cls, path2config, path2params=None):
+        import yaml
+        cfg = cls()
+        for path in (path2config, path2params):
+            if path is None:
+                continue
+            with open(path) as f:
+                for k, v in (yaml.safe_load(f) or {}).items():
+                    if hasattr(cfg, k):
+                        setattr(cfg, k, v)
+        return cfg
+
+
+class Vehicle:
+    """Vehicle::initialize (vehicle.cpp:11-32)."""
+
+    def __init__(self, max_steer, w_b, l_f, l_b, width, is_ushift):
+        self.max_steer_, self.w_b_, self.lf_, self.lb_ = max_steer, w_b, l_f, l_b
+        self.length_ = l_f + l_b
+        self.width_ = width
+        self.is_ushift_ = is_ushift
+
+    @classmethod
+    def from_config(cls, v):
+        return cls(v.max_steer, v.wb, v.lf, v.lb, v.width, v.is_ushift)
+
+
+def _cround(v):
+    """std::round: half away from zero."""
+    return int(math.floor(v + 0.5)) if v >= 0 else -int(math.floor(-v + 0.5))
+
+
+def calc_disks(veh, cfg):
+    """CollisionChecker::calculateDisks / getDiskRadius / getDiskPositions
+    (collision_checking.cpp:44-145): footprint disks and the per-yaw centre LUT, in fp64 on the
+    host exactly as the reference initialises them.  Returns (nb_disks, disk_r, disk_r_c,
+    centers[nb_yaws, nb_disks, 2] int32)."""
+    eff_nb = int(math.ceil(veh.length_ / cfg.LEN_PER_DISK))
+    mult = 2 if cfg.DOUBLE_DISK_ROWS else 1
+    nb_disks = mult * eff_nb
+    eff_width = veh.width_ / mult
+    radius = math.sqrt(((veh.length_ * veh.length_) / (eff_nb * eff_nb) + (eff_width * eff_width)) / 4)
+    dist = 2 * math.sqrt((radius * radius) - (eff_width * eff_width) / 4)
+    first = dist / 2 - veh.lb_
+    positions = [first + i * dist for i in range(eff_nb)]
+    disk_r = radius + cfg.SAFETY_DISTANCE_M
+    disk_r_c = int(math.ceil(disk_r * CON2GM))
+    nb_yaws = 360 // cfg.YAW_RES_COLL
+    yaw_res_rad = cfg.YAW_RES_COLL * TO_RAD
+    centers = np.zeros((nb_yaws, nb_disks, 2), np.int32)
+    for yi in range(nb_yaws):
+        yaw = yi * yaw_res_rad
+        c, s = math.cos(yaw), math.sin(yaw)
+        k = 0
+        for pos in positions:
+            offs = (eff_width / 2.0, -eff_width / 2.0) if cfg.DOUBLE_DISK_ROWS else (0.0,)
+            for yo in offs:
+                rx = pos * c - yo * s
+                ry = pos * s + yo * c
+                centers[yi, k, 0] = _cround(rx * CON2GM)
+                centers[yi, k, 1] = _cround(ry * CON2GM)
+                k += 1
+    return nb_disks, disk_r, disk_r_c, centers
+
+
+class GridContext:
+    """One planner instance = one ga_ctx."""
+
+    def __init__(self, device=0):
+        self.lib = _abi.load()
+        h = C.c_void_p()
+        rc = self.lib.ga_create(device, C.byref(h))
+        if rc != 0:
+            raise GaError("ga_create(device=%d) failed with %d: no usable CUDA device "
+                          "(this backend has no CPU path)" % (device, rc))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ga_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != 0:
+            raise GaError("%s (status %d)" % (self.lib.ga_last_error(self.h).decode(), rc))
+
+    def sync(self):
+        self.check(self.lib.ga_sync(self.h))
+
+    def stream(self):
+        return self.lib.ga_stream(self.h)
+
+    def grid_shape(self, gid):
+        if gid in (_abi.GRID_PATCH, _abi.GRID_SAFETY):
+            d = self.lib.ga_patch_dim(self.h)
+        elif gid in (_abi.GRID_OBSTACLE_DIST, _abi.GRID_VORONOI_DIST):
+            nb = C.c_size_t()
+            self.check(self.lib.ga_grid_bytes(self.h, gid, C.byref(nb)))
+            d = int(round(math.sqrt(nb.value // 4)))
+        else:
+            d = self.lib.ga_astar_dim(self.h)
+        return (d, d)
+
+    def download(self, gid):
+        out = np.empty(self.grid_shape(gid), _abi.GRID_DTYPES[gid])
+        self.check(self.lib.ga_download(self.h, gid, _abi.ptr(out), out.nbytes))
+        return out
+
+    def upload(self, gid, arr):
+        a = np.ascontiguousarray(arr, _abi.GRID_DTYPES[gid])
+        if a.shape != self.grid_shape(gid):
+            raise GaError("grid %d expects shape %s, got %s" % (gid, self.grid_shape(gid), a.shape))
+        self.check(self.lib.ga_upload(self.h, gid, _abi.ptr(a), a.nbytes))
+        self.sync()  # `a` may be a temporary
+
+    def device_ptr(self, gid):
+        p = C.c_void_p()
+        self.check(self.lib.ga_device_ptr(self.h, gid, C.byref(p)))
+        return p.value
+
+    # measurement
+    def prof_enable(self, on=True):
+        self.check(self.lib.ga_prof_enable(self.h, int(on)))
+
+    def prof_reset(self):
+        self.check(self.lib.ga_prof_reset(self.h))
+
+    def prof_get(self, k):
+        ms, n = C.c_double(), C.c_longlong()
+        self.check(self.lib.ga_prof_get(self.h, k, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def launch_count(self):
+        return self.lib.ga_launch_count(self.h)
+
+
+class CollisionChecker:
+    """Mirror of the reference's CollisionChecker (collision_checking.hpp:36-120)."""
+
+    FREE, UNKNOWN, OCC = FREE, UNKNOWN, OCC
+
+    def __init__(self, ctx, vehicle, cfg=None):
+        self.ctx, self.vehicle, self.cfg = ctx, vehicle, cfg or LibConfig()
+        self.patch_dim_ = 0
+        self.params_set_ = False
+
+    # -- initialize / calculateDisks / resetPatch (collision_checking.cpp:12-42, 75-145)
+    def initialize(self, patch_dim, path2config=None):
+        if path2config is not None:
+            self.cfg = LibConfig.from_yaml(path2config)
+        self.calculateDisks()
+        self.resetPatch(patch_dim)
+
+    def calculateDisks(self):
+        cfg = self.cfg
+        self.nb_disks_, self.disk_r_, self.disk_r_c_, self.disk_centers_ = calc_disks(self.vehicle, cfg)
+        self.yaw_res_coll_ = cfg.YAW_RES_COLL
+        self.nb_disc_yaws_ = 360 // cfg.YAW_RES_COLL
+        p = _abi.CollisionParams(int(cfg.MIN_THRESH), int(cfg.MAX_THRESH), self.disk_r_c_,
+                                 int(cfg.YAW_RES_COLL), self.nb_disks_, 4)
+        cen = np.ascontiguousarray(self.disk_centers_, np.int32)
+        self.ctx.check(self.ctx.lib.ga_set_collision_params(self.ctx.h, C.byref(p), _abi.ptr(cen)))
+        self.params_set_ = True
+
+    def resetPatch(self, patch_dim):
+        self.ctx.check(self.ctx.lib.ga_patch_reset(self.ctx.h, int(patch_dim)))
+        self.patch_dim_ = int(patch_dim)
+
+    # -- passLocalMap (collision_checking.cpp:176-191, 269-313)
+    def passLocalMap(self, local_map, origin, dim):
+        a = np.ascontiguousarray(local_map, np.uint8)
+        if a.size != dim * dim:
+            raise GaError("local map must hold dim*dim cells")
+        self.ctx.check(self.ctx.lib.ga_patch_insert(self.ctx.h, _abi.ptr(a), int(origin[0]), int(origin[1]), int(dim)))
+        self.ctx.sync()
+
+    passLocalMapData = passLocalMap
+
+    # -- processSafetyPatch (collision_checking.cpp:193-224); the pooled astar grid comes with it
+    def processSafetyPatch(self):
+        self.ctx.check(self.ctx.lib.ga_build_safety(self.ctx.h))
+
+    @property
+    def patch_arr_(self):
+        return self.ctx.download(_abi.GRID_PATCH)
+
+    @property
+    def patch_safety_arr_(self):
+        return self.ctx.download(_abi.GRID_SAFETY)
+
+    # -- checks (collision_checking.cpp:333-452)
+    def getYawIdx(self, yaw):
+        a = yaw
+        while a < 0:
+            a += 2 * math.pi
+        a = math.fmod(a, 2 * math.pi)
+        return min(int(a / (self.yaw_res_coll_ * TO_RAD)), self.nb_disc_yaws_ - 1)
+
+    def returnDiskPositions(self, yaw):
+        return [tuple(int(v) for v in c) for c in self.disk_centers_[self.getYawIdx(yaw)]]
+
+    def _check(self, x, y, yaw, seg_off, variant):
+        x = np.ascontiguousarray(x, np.float64)
+        y = np.ascontiguousarray(y, np.float64)
+        yaw = np.ascontiguousarray(yaw, np.float64)
+        if not (x.shape == y.shape == yaw.shape and x.ndim == 1):
+            raise GaError("x, y, yaw must be 1-D and of equal length")
+        seg = np.ascontiguousarray(seg_off, np.int32)
+        hit = np.empty(len(seg) - 1, np.int32)
+        self.ctx.check(self.ctx.lib.ga_check_poses(self.ctx.h, _abi.ptr(x), _abi.ptr(y), _abi.ptr(yaw), len(x),
+                                                   _abi.ptr(seg), len(seg) - 1, int(variant), _abi.ptr(hit)))
+        return hit
+
+    def checkPose(self, pose):
+        return bool(self._check([pose[0]], [pose[1]], [pose[2]], [0, 1], 0)[0] < 0)
+
+    def checkPoseVariant(self, pose):
+        return bool(self._check([pose[0]], [pose[1]], [pose[2]], [0, 1], 1)[0] < 0)
+
+    def checkGrid(self, pose):
+        """pose = (x, y, yaw_idx) in gm cells / yaw bins (collision_checking.cpp:344-362)."""
+        return self.checkPose(((pose[0] + 0.5) * GM_RES, (pose[1] + 0.5) * GM_RES,
+                               (pose[2] + 0.5) * self.yaw_res_coll_ * TO_RAD)) if pose[0] >= 0 and pose[1] >= 0 \
+            else False
+
+    checkGridVariant = checkGrid  # the pybind name is bound to checkGrid (wrapper:193)
+
+    def getPathCollisionIndex(self, x_list, y_list, yaw_list):
+        return int(self._check(x_list, y_list, yaw_list, [0, len(x_list)], 0)[0])
+
+    def checkPathCollision(self, x_list, y_list, yaw_list):
+        return self.getPathCollisionIndex(x_list, y_list, yaw_list) < 0
+
+    # batched forms (one launch per expansion batch)
+    def checkSegments(self, x, y, yaw, seg_off, variant=0):
+        return self._check(x, y, yaw, seg_off, variant)
+
+    def setExpandParams(self, arc_l=ASTAR_RES * 1.5, nb_steer=NB_STEER):
+        cfg, v = self.cfg, self.vehicle
+        p = _abi.ExpandParams(v.max_steer_, v.w_b_, arc_l, float(cfg.YAW_RES), float(cfg.TURN_ON_POINT_ANGLE), nb_steer)
+        self.ctx.check(self.ctx.lib.ga_set_expand_params(self.ctx.h, C.byref(p)))
+        self.expand_stride_ = self.ctx.lib.ga_expand_stride(self.ctx.h)
+
+    def expandNodes(self, nodes):
+        """nodes: structured array _abi.NODE_DTYPE -> successors [n_nodes, stride] _abi.SUCC_DTYPE"""
+        nodes = np.ascontiguousarray(nodes, _abi.NODE_DTYPE)
+        out = np.zeros((len(nodes), self.expand_stride_), _abi.SUCC_DTYPE)
+        self.ctx.check(self.ctx.lib.ga_expand(self.ctx.h, _abi.ptr(nodes), len(nodes), _abi.ptr(out)))
+        return out
+
+
+class NodeDisc:
+    """data_structures2.hpp:47-67"""
+    __slots__ = ("pos", "cost_", "cost_dist_", "parent_index_", "is_unknown_")
+
+    def __init__(self, pos, cost, cost_dist, parent, unk):
+        self.pos, self.cost_, self.cost_dist_, self.parent_index_, self.is_unknown_ = pos, cost, cost_dist, parent, unk
+
+
+class ClosedSet:
+    """Read API of std::unordered_map<size_t, NodeDisc> (closed_set_guidance_ / closed_set_path_,
+    a_star.hpp:69-72) over the dense result planes."""
+
+    def __init__(self, cost, dist, parent, flags):
+        self.cost, self.dist, self.parent, self.flags = cost, dist, parent, flags
+        self.dim = cost.shape[0]
+
+    def contains(self, idx):
+        return 0 <= idx < self.flags.size and bool(self.flags.flat[idx] & _abi.H_CLOSED)
+
+    __contains__ = contains
+
+    def at(self, idx):
+        if not self.contains(idx):
+            raise KeyError(idx)
+        return NodeDisc((idx % self.dim, idx // self.dim), float(self.cost.flat[idx]), float(self.dist.flat[idx]),
+                        int(self.parent.flat[idx]), bool(self.flags.flat[idx] & _abi.H_UNKNOWN))
+
+    __getitem__ = at
+
+    def size(self):
+        return int(np.count_nonzero(self.flags & _abi.H_CLOSED))
+
+    __len__ = size
+
+    def keys(self):
+        return np.flatnonzero(self.flags.ravel() & _abi.H_CLOSED)
+
+
+class AStar:
+    """Mirror of the reference's AStar grid builder (a_star.hpp:32-140)."""
+
+    def __init__(self, ctx, cfg=None):
+        self.ctx, self.cfg = ctx, cfg or LibConfig()
+        self.closed_sets_ = [None, None]
+        self.set_params()
+
+    def set_params(self):
+        c = self.cfg
+        p = _abi.AstarParams(c.astar_movement_cost_, c.astar_prox_cost_, c.astar_lane_movement_cost_,
+                             float(c.ASTAR_UNKNOWN_COST), c.alpha_, c.do_max_, c.do_min_, c.MOTION_RES_MIN,
+                             c.MOTION_RES_MAX, float(c.MIN_DIST_VAL), float(c.MAX_DIST_VAL), int(c.VOR_DIM),
+                             int(c.DT_VARIANT))
+        self.ctx.check(self.ctx.lib.ga_set_astar_params(self.ctx.h, C.byref(p)))
+
+    @property
+    def astar_dim_(self):
+        return self.ctx.lib.ga_astar_dim(self.ctx.h)
+
+    # grids (a_star.hpp:73-99): value copies, like Vec2DFlat::getNumpyArr
+    astar_grid_ = property(lambda s: s.ctx.download(_abi.GRID_ASTAR))
+    h_prox_arr_ = property(lambda s: s.ctx.download(_abi.GRID_H_PROX))
+    motion_res_map_ = property(lambda s: s.ctx.download(_abi.GRID_MOTION_RES))
+    movement_cost_map_ = property(lambda s: s.ctx.download(_abi.GRID_MOVEMENT_COST))
+    restr_geofence_grid_ = property(lambda s: s.ctx.download(_abi.GRID_GEOFENCE))
+    obstacle_dist_ = property(lambda s: s.ctx.download(_abi.GRID_OBSTACLE_DIST))
+    voronoi_dist_ = property(lambda s: s.ctx.download(_abi.GRID_VORONOI_DIST))
+
+    def calcAstarGridCuda(self):
+        """Pooling::execute is fused into processSafetyPatch's kernel (ga_build_safety): the pooled
+        grid is already current.  Kept for call-order compatibility (a_star.cpp:536-542)."""
+        return None
+
+    def calcIndex(self, x, y):
+        return y * self.astar_dim_ + x  # a_star.cpp:303-316
+
+    def potentialSites(self, ego_index):
+        V = self.cfg.VOR_DIM
+        xy = np.empty((V * V, 2), np.int32)
+        n = C.c_int()
+        self.ctx.check(self.ctx.lib.ga_potential_sites(self.ctx.h, int(ego_index[0]), int(ego_index[1]), _abi.ptr(xy),
+                                                       V * V, C.byref(n)))
+        return xy[:n.value].copy()
+
+    def calcVoronoiPotentialField(self, ego_index, voronoi_endpoints):
+        """a_star.cpp:440-479.  voronoi_endpoints: [n,2] window cells marked by the host-side Fortune
+        sweep (generateVoronoi_wrapper) for the sites potentialSites() returned."""
+        v = np.ascontiguousarray(voronoi_endpoints, np.int32).reshape(-1, 2)
+        had = C.c_int()
+        self.ctx.check(self.ctx.lib.ga_build_potential(self.ctx.h, int(ego_index[0]), int(ego_index[1]),
+                                                       _abi.ptr(v) if len(v) else None, len(v), C.byref(had)))
+        return bool(had.value)
+
+    def calcDistanceHeuristic(self, goal_pos, start_pos=None, for_path=True, get_only_near=False):
+        """a_star.cpp:110-295.  Fixed-point mode: every cell reachable from the goal is closed; the
+        start cell only steers the reference's early exit and is not needed."""
+        slot = 1 if for_path else 0
+        n = C.c_int()
+        self.ctx.check(self.ctx.lib.ga_build_heuristic(self.ctx.h, slot, int(goal_pos[0]), int(goal_pos[1]), C.byref(n)))
+        self.closed_sets_[slot] = None
+        return n.value
+
+    def _closed(self, slot):
+        if self.closed_sets_[slot] is None:
+            d = self.ctx.download
+            self.closed_sets_[slot] = ClosedSet(d(_abi.GRID_HEUR_COST + slot), d(_abi.GRID_HEUR_DIST + slot),
+                                                d(_abi.GRID_HEUR_PARENT + slot), d(_abi.GRID_HEUR_FLAGS + slot))
+        return self.closed_sets_[slot]
+
+    closed_set_guidance_ = property(lambda s: s._closed(0))
+    closed_set_path_ = property(lambda s: s._closed(1))
+
+    def findValidNeighborIndex(self, index, cs=None):
+        cs = cs or self.closed_set_guidance_
+        for b in (index + 1, index - 1, index + self.astar_dim_, index - self.astar_dim_):  # a_star.cpp:351-378
+            if cs.contains(b):
+                return b
+        return -1
+
+    def getAstarPath(self, x_index, y_index):
+        """a_star.cpp:386-421: parent walk in closed_set_guidance_."""
+        cs = self.closed_set_guidance_
+        idx = self.calcIndex(x_index, y_index)
+        if not cs.contains(idx):
+            idx = self.findValidNeighborIndex(idx, cs)
+            if idx == -1:
+                return [], []
+        xs, ys = [], []
+        par = cs.parent.ravel()
+        while idx != -1:
+            xs.append(idx % cs.dim)
+            ys.append(idx // cs.dim)
+            idx = int(par[idx])
+        return xs, ys

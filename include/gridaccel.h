@@ -34,6 +34,12 @@ extern "C" {
 
 #define GA_ABI_VERSION 1
 
+#if defined(GA_BUILD) && defined(__GNUC__)
+#define GA_API __attribute__((visibility("default")))
+#else
+#define GA_API
+#endif
+
 typedef struct ga_ctx ga_ctx;
 
 typedef enum
@@ -73,13 +79,13 @@ enum { GA_H_CLOSED = 1, GA_H_UNKNOWN = 2 };
 
 /* ---- lifetime ------------------------------------------------------------------------------ */
 
-int ga_abi_version(void);
-int ga_create(int device, ga_ctx** out);
-int ga_destroy(ga_ctx* ctx);
-const char* ga_last_error(const ga_ctx* ctx);
-int ga_sync(ga_ctx* ctx);
+GA_API int ga_abi_version(void);
+GA_API int ga_create(int device, ga_ctx** out);
+GA_API int ga_destroy(ga_ctx* ctx);
+GA_API const char* ga_last_error(const ga_ctx* ctx);
+GA_API int ga_sync(ga_ctx* ctx);
 /* the context's cudaStream_t, for callers that record their own events on it */
-void* ga_stream(ga_ctx* ctx);
+GA_API void* ga_stream(ga_ctx* ctx);
 
 /* ---- occupancy: patch, threshold, dilation, pooling --------------------------------------- */
 
@@ -98,7 +104,7 @@ typedef struct
   int pool_win;     /* ceil(grid_tf::star2gm_) = 4 (a_star.cpp:30-31) */
 } ga_collision_params;
 
-int ga_set_collision_params(ga_ctx* ctx, const ga_collision_params* p, const int* centers);
+GA_API int ga_set_collision_params(ga_ctx* ctx, const ga_collision_params* p, const int* centers);
 
 /* CollisionChecker::resetPatch (collision_checking.cpp:37-42) + AStar::reinit's grid sizing
  * (a_star.cpp:70-99): patch_arr_ <- 127, patch_safety_arr_ <- UNKNOWN, astar_dim =
@@ -106,18 +112,18 @@ int ga_set_collision_params(ga_ctx* ctx, const ga_collision_params* p, const int
  * h_prox <- 0, motion_res <- motion_res_max, geofence <- 0, distance windows <- 0, heuristic
  * slots emptied.  (Carrying h_prox / motion_res over a patch move, a_star.cpp:84-96, is a
  * download / shift / upload the host mirror does.) */
-int ga_patch_reset(ga_ctx* ctx, int patch_dim);
+GA_API int ga_patch_reset(ga_ctx* ctx, int patch_dim);
 
 /* CollisionChecker::passLocalMapData (collision_checking.cpp:269-313): copy a dim x dim u8
  * window (host memory) into patch_arr_ at (ox, oy).  Whole window dropped when it overhangs in
  * x, rows skipped when they overhang in y -- as the reference does.  Only the window crosses
  * PCIe; the patch stays device-resident. */
-int ga_patch_insert(ga_ctx* ctx, const uint8_t* window, int ox, int oy, int dim);
+GA_API int ga_patch_insert(ga_ctx* ctx, const uint8_t* window, int ox, int oy, int dim);
 
 /* CollisionChecker::processSafetyPatch (collision_checking.cpp:193-224) followed by
  * AStar::calcAstarGridCuda -> Pooling::execute (a_star.cpp:536-542, LIB/src/cuda_lib/max_pool.cu:21-79):
  * threshold -> disk dilation -> patch_safety_arr_, and its pool_win x pool_win max -> astar_grid_. */
-int ga_build_safety(ga_ctx* ctx);
+GA_API int ga_build_safety(ga_ctx* ctx);
 
 /* ---- footprint collision checks ------------------------------------------------------------ */
 
@@ -126,7 +132,7 @@ int ga_build_safety(ga_ctx* ctx);
  * first_hit[s] = index inside the segment of the first colliding pose, -1 if none.
  * variant = 0: an off-map disk invalidates the pose (checkGrid :344-362); 1: it is skipped
  * (checkGridVariant :369-387).  Host pointers; one kernel launch for the whole batch. */
-int ga_check_poses(ga_ctx* ctx, const double* x, const double* y, const double* yaw, int n_poses,
+GA_API int ga_check_poses(ga_ctx* ctx, const double* x, const double* y, const double* yaw, int n_poses,
                    const int* seg_off, int n_seg, int variant, int* first_hit);
 
 /* HybridAStar::setNeighbors' collision-relevant part for a batch of expanded nodes
@@ -166,9 +172,9 @@ typedef struct
 /* number of primitives ga_expand writes per node: 2*nb_steer, + rear-axis deltas when the node
  * asks for them; out must hold n_nodes * ga_expand_stride(ctx) entries, unused entries have
  * n_poses = 0 */
-int ga_set_expand_params(ga_ctx* ctx, const ga_expand_params* p);
-int ga_expand_stride(const ga_ctx* ctx);
-int ga_expand(ga_ctx* ctx, const ga_node* nodes, int n_nodes, ga_succ* out);
+GA_API int ga_set_expand_params(ga_ctx* ctx, const ga_expand_params* p);
+GA_API int ga_expand_stride(const ga_ctx* ctx);
+GA_API int ga_expand(ga_ctx* ctx, const ga_node* nodes, int n_nodes, ga_succ* out);
 
 /* ---- heuristic grid ------------------------------------------------------------------------- */
 
@@ -187,7 +193,7 @@ typedef struct
 
 typedef enum { GA_DT_FIXEDPOINT = 0, GA_DT_IPPFLOAT = 1 } ga_dt_variant;
 
-int ga_set_astar_params(ga_ctx* ctx, const ga_astar_params* p);
+GA_API int ga_set_astar_params(ga_ctx* ctx, const ga_astar_params* p);
 
 /* AStar::calcDistanceHeuristic (a_star.cpp:110-295).  slot 0 = closed_set_guidance_
  * (for_path = false), 1 = closed_set_path_.  Computes the least fixed point of the reference's
@@ -197,7 +203,7 @@ int ga_set_astar_params(ga_ctx* ctx, const ga_astar_params* p);
  * decide WHICH reachable cells it closes and, at a few cells, a suboptimal cost;
  * the fixed point needs no start cell.  n_closed (may be NULL; forces a stream sync otherwise)
  * receives the number of reachable cells. */
-int ga_build_heuristic(ga_ctx* ctx, int slot, int goal_x, int goal_y, int* n_closed);
+GA_API int ga_build_heuristic(ga_ctx* ctx, int slot, int goal_x, int goal_y, int* n_closed);
 
 /* AStar::calcVoronoiPotentialField (a_star.cpp:440-479) around ego (astar cells): two chamfer
  * distance transforms (createDistanceTransform :426-433) + setCostmapValue (:486-508).  The
@@ -205,20 +211,20 @@ int ga_build_heuristic(ga_ctx* ctx, int slot, int goal_x, int goal_y, int* n_clo
  * vor_xy = the n_vor edge end points it marks, window coordinates.  The host asks for the OCC
  * cells of the window with ga_potential_sites first.  Returns GA_OK; *had_occ (may be NULL)
  * tells whether the window held an obstacle (0 = early return of a_star.cpp:462-465). */
-int ga_potential_sites(ga_ctx* ctx, int ego_x, int ego_y, int* xy, int cap, int* n_sites);
-int ga_build_potential(ga_ctx* ctx, int ego_x, int ego_y, const int* vor_xy, int n_vor,
+GA_API int ga_potential_sites(ga_ctx* ctx, int ego_x, int ego_y, int* xy, int cap, int* n_sites);
+GA_API int ga_build_potential(ga_ctx* ctx, int ego_x, int ego_y, const int* vor_xy, int n_vor,
                        int* had_occ);
 
 /* ---- data movement -------------------------------------------------------------------------- */
 
 /* whole-grid host <-> device copies (bytes must equal the grid's size) */
-int ga_upload(ga_ctx* ctx, int grid_id, const void* src, size_t bytes);
-int ga_download(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
-int ga_grid_bytes(const ga_ctx* ctx, int grid_id, size_t* bytes);
+GA_API int ga_upload(ga_ctx* ctx, int grid_id, const void* src, size_t bytes);
+GA_API int ga_download(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
+GA_API int ga_grid_bytes(const ga_ctx* ctx, int grid_id, size_t* bytes);
 /* device address of a grid (for zero-copy consumers such as the bench's resident-input leg) */
-int ga_device_ptr(ga_ctx* ctx, int grid_id, void** dptr);
-int ga_patch_dim(const ga_ctx* ctx);
-int ga_astar_dim(const ga_ctx* ctx);
+GA_API int ga_device_ptr(ga_ctx* ctx, int grid_id, void** dptr);
+GA_API int ga_patch_dim(const ga_ctx* ctx);
+GA_API int ga_astar_dim(const ga_ctx* ctx);
 
 /* ---- measurement ---------------------------------------------------------------------------- */
 
@@ -238,12 +244,12 @@ typedef enum
   GA_K_COUNT = 9
 } ga_kernel_id;
 
-int ga_prof_enable(ga_ctx* ctx, int on);
-int ga_prof_reset(ga_ctx* ctx);
+GA_API int ga_prof_enable(ga_ctx* ctx, int on);
+GA_API int ga_prof_reset(ga_ctx* ctx);
 /* total device milliseconds and launches of kernel k since the last reset (syncs the stream) */
-int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches);
+GA_API int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches);
 /* launches of ALL library kernels since ga_create / ga_prof_reset (always counted) */
-long long ga_launch_count(const ga_ctx* ctx);
+GA_API long long ga_launch_count(const ga_ctx* ctx);
 
 #ifdef __cplusplus
 }

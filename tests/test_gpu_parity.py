@@ -1,0 +1,367 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle, on a B200."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+import ga_b200
+from ga_b200 import _abi
+
+
+def _setup(planner, patch_dim, patch):
+    ctx, cc, astar = planner
+    cc.initialize(patch_dim)
+    ctx.upload(_abi.GRID_PATCH, patch)
+    cc.processSafetyPatch()
+    return ctx, cc, astar
+
+
+# ---- K1 + K2: threshold, disk dilation, 4x4 pool -- bit-exact ---------------------------------
+
+@pytest.mark.parametrize("dim,seed", [(64, 1), (333, 2), (500, 3), (1000, 4), (1492, 5), (2048, 6), (2050, 7), (4096, 20240)])
+def test_safety_and_pool_bit_exact(planner, oracle, dim, seed):
+    patch = ga_b200.gen_map(dim, seed)
+    # sprinkle every u8 value so both thresholds are exercised at their edges
+    rng = np.random.default_rng(seed)
+    idx = rng.integers(0, dim * dim, dim)
+    patch.ravel()[idx] = rng.integers(0, 256, dim).astype(np.uint8)
+    ctx, cc, astar = _setup(planner, dim, patch)
+    want = oracle.process_safety_patch(patch, 100, 130, cc.disk_r_c_)
+    got = cc.patch_safety_arr_
+    assert np.array_equal(got, want)
+    assert np.array_equal(astar.astar_grid_, oracle.pool_max(want))
+
+
+@pytest.mark.parametrize("r", [0, 1, 3, 10, 16])
+def test_dilation_radii(planner, oracle, r):
+    ctx, cc, astar = planner
+    dim = 300
+    cc.calculateDisks()
+    p = _abi.CollisionParams(100, 130, r, 3, cc.nb_disks_, 4)
+    cen = np.ascontiguousarray(cc.disk_centers_, np.int32)
+    ctx.check(ctx.lib.ga_set_collision_params(ctx.h, C.byref(p), _abi.ptr(cen)))
+    cc.resetPatch(dim)
+    rng = np.random.default_rng(r)
+    patch = np.where(rng.random((dim, dim)) < 0.003, 255, 0).astype(np.uint8)
+    patch[rng.random((dim, dim)) < 0.003] = 127
+    ctx.upload(_abi.GRID_PATCH, patch)
+    cc.processSafetyPatch()
+    assert np.array_equal(cc.patch_safety_arr_, oracle.process_safety_patch(patch, 100, 130, r))
+
+
+def test_empty_and_full_patches(planner, oracle):
+    ctx, cc, astar = planner
+    cc.initialize(256)
+    cc.processSafetyPatch()  # fresh patch: all 127 -> all UNKNOWN
+    assert np.all(cc.patch_safety_arr_ == 1) and np.all(astar.astar_grid_ == 1)
+    ctx.upload(_abi.GRID_PATCH, np.zeros((256, 256), np.uint8))
+    cc.processSafetyPatch()
+    assert np.all(cc.patch_safety_arr_ == 0) and np.all(astar.astar_grid_ == 0)
+    ctx.upload(_abi.GRID_PATCH, np.full((256, 256), 255, np.uint8))
+    cc.processSafetyPatch()
+    assert np.all(cc.patch_safety_arr_ == 2)
+
+
+def test_safety_idempotent_and_monotone_4096(planner):
+    """size-independent properties at the full config-2 size: dilation only grows values, a
+    second build of the same patch gives the same bytes, pooled grid == block max."""
+    dim = 4096
+    patch = ga_b200.gen_map(dim, 20240)
+    ctx, cc, astar = _setup(planner, dim, patch)
+    s1 = cc.patch_safety_arr_
+    cc.processSafetyPatch()
+    assert np.array_equal(s1, cc.patch_safety_arr_)
+    thr = np.where(patch > 130, 2, np.where(patch < 100, 0, 1)).astype(np.uint8)
+    assert np.all(s1 >= thr)
+    a = astar.astar_grid_
+    assert np.array_equal(a, s1.reshape(1024, 4, 1024, 4).max(axis=(1, 3)))
+
+
+# ---- K7: window insertion ------------------------------------------------------------------------
+
+def test_patch_insert_semantics(planner, oracle):
+    ctx, cc, astar = planner
+    dim = 500
+    cc.initialize(dim)
+    want = np.full((dim, dim), 127, np.uint8)
+    rng = np.random.default_rng(0)
+    for (ox, oy, d) in [(10, 20, 100), (450, 10, 100), (-5, 10, 50), (100, -30, 80), (200, 460, 90), (0, 0, 500),
+                        (300, 300, 1)]:
+        win = rng.integers(0, 256, (d, d)).astype(np.uint8)
+        cc.passLocalMap(win, (ox, oy), d)
+        oracle.pass_local_map(want, win, ox, oy)
+    assert np.array_equal(cc.patch_arr_, want)
+
+
+# ---- K6: collision checks -- bit-exact ------------------------------------------------------------
+
+def _random_poses(rng, n, patch_dim):
+    ext = patch_dim * ga_b200.GM_RES
+    x = rng.uniform(-2.0, ext + 2.0, n)
+    y = rng.uniform(-2.0, ext + 2.0, n)
+    yaw = rng.uniform(-3 * math.pi, 3 * math.pi, n)
+    return x, y, yaw
+
+
+@pytest.mark.parametrize("dim,seed,variant", [(333, 1, 0), (1492, 2, 0), (1492, 3, 1), (2048, 4, 0)])
+def test_check_poses_bit_exact(planner, oracle, dim, seed, variant):
+    patch = ga_b200.gen_map(dim, seed)
+    ctx, cc, astar = _setup(planner, dim, patch)
+    safety = cc.patch_safety_arr_
+    rng = np.random.default_rng(seed)
+    n = 200000
+    x, y, yaw = _random_poses(rng, n, dim)
+    # ragged segments, including empty ones
+    cuts = np.sort(rng.integers(0, n + 1, 5000))
+    seg = np.concatenate([[0], cuts, [n]]).astype(np.int32)
+    got = cc.checkSegments(x, y, yaw, seg, variant)
+    want = oracle.check_segments(safety, cc.disk_centers_, 3, x, y, yaw, seg, variant)
+    assert np.array_equal(got, want)
+    assert (want >= 0).any() and (want < 0).any()
+
+
+def test_reference_known_answers(planner):
+    """LIB/test/cpp/collision_checker_lib_test/test_collision_checking.cpp:9-30: vehicle
+    (0.6, 2.7, 3.0, 1.5, 2.0), patch 1000, all-UNKNOWN grid."""
+    ctx, cc, astar = planner
+    cc.vehicle = ga_b200.Vehicle(0.6, 2.7, 3.0, 1.5, 2.0, False)
+    cc.initialize(1000)
+    assert cc.checkGrid((500, 500, 0)) is True
+    assert cc.checkGrid((0, 0, 0)) is False
+    assert cc.checkGrid((999, 999, 0)) is False
+
+
+def test_single_pose_api(planner, oracle):
+    patch = ga_b200.gen_map(333, 9)
+    ctx, cc, astar = _setup(planner, 333, patch)
+    safety = cc.patch_safety_arr_
+    rng = np.random.default_rng(9)
+    x, y, yaw = _random_poses(rng, 64, 333)
+    for i in range(64):
+        assert cc.checkPose((x[i], y[i], yaw[i])) == bool(oracle.check_pose(safety, cc.disk_centers_, 3, x[i], y[i], yaw[i], 0))
+        assert cc.checkPoseVariant((x[i], y[i], yaw[i])) == bool(oracle.check_pose(safety, cc.disk_centers_, 3, x[i], y[i], yaw[i], 1))
+    assert cc.getPathCollisionIndex(x, y, yaw) == int(oracle.check_segments(safety, cc.disk_centers_, 3, x, y, yaw, [0, 64])[0])
+    assert cc.getPathCollisionIndex([], [], []) == -1
+
+
+@pytest.mark.parametrize("ushift", [False, True])
+def test_expand_matches_oracle(planner, oracle, ushift):
+    dim = 1492
+    patch = ga_b200.gen_map(dim, 11)
+    ctx, cc, astar = _setup(planner, dim, patch)
+    cc.setExpandParams()
+    safety = cc.patch_safety_arr_
+    rng = np.random.default_rng(12)
+    n = 3000
+    nodes = np.zeros(n, _abi.NODE_DTYPE)
+    ext = dim * ga_b200.GM_RES
+    nodes["x"] = rng.uniform(1.0, ext - 1.0, n)
+    nodes["y"] = rng.uniform(1.0, ext - 1.0, n)
+    nodes["yaw"] = rng.uniform(-math.pi, math.pi, n)
+    nodes["motion_res"] = rng.choice([0.1, 0.25, 0.5, 0.9375, 1.0], n)
+    nodes["with_rear_axis"] = 1 if ushift else 0
+    got = cc.expandNodes(nodes)
+    import ga_oracle_py as go
+    ep = go.ExpandParams(cc.vehicle.max_steer_, cc.vehicle.w_b_, 0.625 * 1.5, 10.0, 13, int(ushift), 90.0, dim // 4)
+    stride = got.shape[1]
+    assert stride == 26 + 6
+    n_flagged = 0
+    for i in range(n):
+        v, disc, end, npos = oracle.expand_node(safety, cc.disk_centers_, 3, ep, float(nodes["x"][i]), float(nodes["y"][i]),
+                                                float(nodes["yaw"][i]), float(nodes["motion_res"][i]))
+        k = len(v)
+        g = got[i]
+        assert np.array_equal(g["n_poses"][:k], npos)
+        assert np.all(g["n_poses"][k:] == 0)
+        # continuous end poses: device libm vs glibc, a few ulp
+        assert np.allclose(np.stack([g["x"][:k], g["y"][:k], g["yaw"][:k]], 1), end, rtol=0, atol=1e-12)
+        safe = g["near_cell_edge"][:k] == 0
+        n_flagged += int((~safe).sum())
+        assert np.array_equal(g["valid"][:k][safe], v[safe])
+        gd = np.stack([g["xi"][:k], g["yi"][:k], g["yawi"][:k]], 1)
+        assert np.array_equal(gd[safe], disc[safe])
+    assert n_flagged < 0.001 * n * stride
+
+
+# ---- K5: heuristic grid ---------------------------------------------------------------------------
+
+def _heur_inputs(astar, ctx, rng, with_prox):
+    dim = astar.astar_dim_
+    grid = astar.astar_grid_
+    mc = np.full((dim, dim), 5.0)
+    lanes = rng.random((dim, dim)) < 0.05
+    mc[lanes] = 3.0
+    prox = np.zeros((dim, dim))
+    if with_prox:
+        prox = rng.random((dim, dim)) * (rng.random((dim, dim)) < 0.3)
+    fence = (rng.random((dim, dim)) < 0.002).astype(np.uint8)
+    ctx.upload(_abi.GRID_MOVEMENT_COST, mc)
+    ctx.upload(_abi.GRID_H_PROX, prox)
+    ctx.upload(_abi.GRID_GEOFENCE, fence)
+    return grid, mc, prox, fence
+
+
+@pytest.mark.parametrize("dim,seed,with_prox,unk_w", [(333, 1, False, 0.0), (1000, 2, True, 0.0), (1492, 3, True, 2.5),
+                                                      (2048, 4, True, 0.0), (4096, 20240, True, 0.0)])
+def test_heuristic_fixed_point(planner, oracle, dim, seed, with_prox, unk_w):
+    patch = ga_b200.gen_map(dim, seed)
+    ctx, cc, astar = planner
+    astar.cfg.ASTAR_UNKNOWN_COST = unk_w
+    astar.set_params()
+    cc.initialize(dim)
+    ctx.upload(_abi.GRID_PATCH, patch)
+    cc.processSafetyPatch()
+    rng = np.random.default_rng(seed)
+    grid, mc, prox, fence = _heur_inputs(astar, ctx, rng, with_prox)
+    goal = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, seed)[0]
+    n = astar.calcDistanceHeuristic(goal, None, for_path=False)
+    import ga_oracle_py as go
+    hp = go.HeurParams(astar.astar_dim_, 5.0, 3.0, unk_w, 0, 0, 0)
+    want = oracle.heuristic_fixedpoint(hp, grid, fence, mc, prox, goal)
+    cs = astar.closed_set_guidance_
+    assert n == want["n_closed"] == cs.size()
+    assert np.array_equal(cs.flags, want["flags"])
+    assert np.array_equal(cs.cost, want["cost"])          # bit-exact (tolerance allowed: 1e-5 rel)
+    assert np.array_equal(cs.parent, want["parent"])
+    m = want["flags"] & 1 > 0
+    assert np.array_equal(cs.dist[m], want["dist"][m])
+    # path walk
+    far = np.argwhere(m)[-1]
+    xs, ys = astar.getAstarPath(int(far[1]), int(far[0]))
+    oxs, oys = oracle.astar_path(want["parent"], want["flags"], int(far[1]), int(far[0]))
+    assert np.array_equal(xs, oxs) and np.array_equal(ys, oys)
+    assert (xs[-1], ys[-1]) == (goal[0], goal[1])
+
+
+@pytest.mark.parametrize("with_prox", [False, True])
+def test_heuristic_vs_reference_order(planner, oracle, with_prox):
+    """against the reference's own pop order (early exit off): the fixed point closes every cell the
+    reference closes, is never worse, and agrees within 1e-5 relative wherever the reference itself
+    is optimal.  The reference is an A* without re-opening whose Euclidean term is taken at the
+    parent (a_star.cpp:260-263), so some of ITS cells are suboptimal: counted here."""
+    dim = 1000
+    patch = ga_b200.gen_map(dim, 77)
+    ctx, cc, astar = _setup(planner, dim, patch)
+    rng = np.random.default_rng(77)
+    grid, mc, prox, fence = _heur_inputs(astar, ctx, rng, with_prox)
+    if not with_prox:
+        mc[:] = 5.0
+        ctx.upload(_abi.GRID_MOVEMENT_COST, mc)
+    goal = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, 5)[0]
+    start = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, 6)[0]
+    astar.calcDistanceHeuristic(goal, start, for_path=True)
+    cs = astar.closed_set_path_
+    import ga_oracle_py as go
+    hp = go.HeurParams(astar.astar_dim_, 5.0, 3.0, 0.0, 0, 10000, 0)
+    ref = oracle.heuristic_reforder(hp, grid, fence, mc, prox, goal, start)
+    m = ref["flags"] & 1 > 0
+    assert np.all((cs.flags[m] & 1) > 0)
+    assert np.all(cs.cost[m] <= ref["cost"][m])
+    rel = (ref["cost"][m] - cs.cost[m]) / np.maximum(cs.cost[m], 1e-300)
+    rel[cs.cost[m] == 0] = 0
+    n_sub = int((rel > 1e-5).sum())
+    print("reference-suboptimal cells (prox=%s): %d of %d, max rel %.3g" % (with_prox, n_sub, int(m.sum()), rel.max()))
+    if not with_prox:
+        assert n_sub < 0.02 * m.sum()
+    # where the reference is optimal the two agree to the last bit or within 1e-5 relative
+    assert np.all(rel[rel <= 1e-5] >= 0)
+
+
+def test_heuristic_slots_independent_and_rebuild(planner, oracle):
+    dim = 500
+    patch = ga_b200.gen_map(dim, 8)
+    ctx, cc, astar = _setup(planner, dim, patch)
+    grid = astar.astar_grid_
+    g0, g1 = ga_b200.sample_free_cells(grid, 2, 3)
+    astar.calcDistanceHeuristic(g0, None, for_path=False)
+    astar.calcDistanceHeuristic(g1, None, for_path=True)
+    c0 = astar.closed_set_guidance_.cost.copy()
+    c1 = astar.closed_set_path_.cost.copy()
+    assert c0[g0[1], g0[0]] == 0 and c1[g1[1], g1[0]] == 0
+    astar.calcDistanceHeuristic(g0, None, for_path=True)  # rebuild slot 1 with goal 0
+    assert np.array_equal(astar.closed_set_path_.cost, c0)
+
+
+# ---- K3 + K4: distance transforms + potential field ---------------------------------------------
+
+@pytest.mark.parametrize("variant", [_abi.DT_FIXEDPOINT, _abi.DT_IPPFLOAT])
+@pytest.mark.parametrize("ego", [(100, 100), (60, 250), (273, 273), (150, 180)])
+def test_potential_field(planner, oracle, variant, ego):
+    dim = 1492
+    ctx, cc, astar = planner
+    astar.cfg.DT_VARIANT = variant
+    astar.set_params()
+    cc.initialize(dim)
+    patch = ga_b200.gen_map(dim, 21)
+    ctx.upload(_abi.GRID_PATCH, patch)
+    cc.processSafetyPatch()
+    grid = astar.astar_grid_
+    adim = astar.astar_dim_
+    import ga_oracle_py as go
+    pp = go.PotParams(100.0, 7.0, 3.0, 0.1, 1.0, 3.0, 10.0, 200, variant)
+    o_od = np.zeros((200, 200), np.float32)
+    o_vd = np.zeros((200, 200), np.float32)
+    o_prox = np.zeros((adim, adim))
+    o_mres = np.full((adim, adim), 1.0)
+    rng = np.random.default_rng(ego[0])
+    for rep in range(2):  # second round exercises the persistent voronoi_dist_ window
+        sites = astar.potentialSites(ego)
+        ox, oy = max(ego[0] - 100, 0), max(ego[1] - 100, 0)
+        wy, wx = np.nonzero(grid[oy:oy + 200, ox:ox + 200] == 2)
+        assert np.array_equal(sites, np.stack([wx, wy], 1))
+        vor = rng.integers(0, 200, (300, 2)).astype(np.int32)
+        had = astar.calcVoronoiPotentialField(ego, vor)
+        want_had = oracle.voronoi_potential_field(pp, grid, ego, vor, o_od, o_vd, o_prox, o_mres)
+        assert had == bool(want_had)
+        assert np.array_equal(astar.obstacle_dist_, o_od)
+        assert np.array_equal(astar.voronoi_dist_, o_vd)
+        assert np.array_equal(astar.h_prox_arr_, o_prox, equal_nan=True)
+        assert np.array_equal(astar.motion_res_map_, o_mres)
+
+
+def test_potential_no_obstacle_early_return(planner, oracle):
+    ctx, cc, astar = planner
+    cc.initialize(1000)
+    ctx.upload(_abi.GRID_PATCH, np.zeros((1000, 1000), np.uint8))
+    cc.processSafetyPatch()
+    before = astar.h_prox_arr_
+    had = astar.calcVoronoiPotentialField((125, 125), np.zeros((0, 2), np.int32))
+    assert had is False
+    assert np.array_equal(astar.h_prox_arr_, before)
+    assert np.all(astar.voronoi_dist_ == 0)
+
+
+# ---- ABI behaviour --------------------------------------------------------------------------------
+
+def test_error_conventions(planner):
+    ctx, cc, astar = planner
+    lib = ctx.lib
+    assert lib.ga_build_safety(ctx.h) == -3          # GA_ERR_STATE: no patch yet
+    assert b"no patch" in lib.ga_last_error(ctx.h)
+    cc.initialize(128)
+    assert lib.ga_build_heuristic(ctx.h, 0, 999, 0, None) == -1
+    assert lib.ga_build_heuristic(ctx.h, 2, 0, 0, None) == -1
+    with pytest.raises(ga_b200.GaError):
+        ctx.upload(_abi.GRID_PATCH, np.zeros((64, 64), np.uint8))
+    assert lib.ga_launch_count(ctx.h) >= 0
+
+
+def test_two_contexts_are_independent(oracle):
+    a = ga_b200.GridContext(0)
+    b = ga_b200.GridContext(0)
+    veh = ga_b200.Vehicle.from_config(ga_b200.VehConfig())
+    out = []
+    for ctx, seed, dim in ((a, 1, 400), (b, 2, 600)):
+        ga_b200.AStar(ctx)
+        cc = ga_b200.CollisionChecker(ctx, veh)
+        cc.initialize(dim)
+        ctx.upload(_abi.GRID_PATCH, ga_b200.gen_map(dim, seed))
+        cc.processSafetyPatch()
+        out.append(cc)
+    for cc, seed, dim in ((out[0], 1, 400), (out[1], 2, 600)):
+        assert np.array_equal(cc.patch_safety_arr_, oracle.process_safety_patch(ga_b200.gen_map(dim, seed), 100, 130, 10))
+    a.close()
+    b.close()
