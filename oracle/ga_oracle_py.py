@@ -71,6 +71,7 @@ def lib():
         _lib.gao_turn_on_rear_axis.argtypes = [C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_int]
         _lib.gao_steering_inputs.argtypes = [C.c_double, C.c_int, C.c_void_p]
         _lib.gao_costmap_value.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        _lib.gao_check_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
     return _lib
 
 
