@@ -1,0 +1,3 @@
+// TEST INFRASTRUCTURE ONLY -- see imgproc.hpp
+#pragma once
+#include "imgproc.hpp"
