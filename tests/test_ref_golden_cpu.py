@@ -1,0 +1,71 @@
+"""CPU: the plain-C oracle against tests/golden/ref_golden.npz -- outputs of the reference's OWN
+code (tests/golden/make_ref_golden.py ran oracle/_ref/libga_ref.so).  Works without
+/root/reference, so the oracle stays pinned on the GPU box too."""
+import os
+
+import numpy as np
+import pytest
+
+from ga_b200.synth import gen_map
+
+R = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_golden.npz"))
+
+
+def test_safety_pool_disks(oracle):
+    dim, seed = (int(v) for v in R["A_dim_seed"])
+    info, cen = oracle.calc_disks(3.993 + 1.17, 2.13, 1.17)
+    assert np.array_equal(cen, R["A_centers"]) and info.disk_r_c == int(R["A_disk_r_c"])
+    s = oracle.process_safety_patch(gen_map(dim, seed), 100, 130, info.disk_r_c)
+    assert np.array_equal(s, R["A_safety"])
+    assert np.array_equal(oracle.pool_max(s), R["A_astar"])
+
+
+@pytest.mark.parametrize("tag,early", [("full", 0), ("early", 1)])
+def test_heuristic_reference_order(oracle, tag, early):
+    grid = R["A_astar"]
+    ad = grid.shape[0]
+    gx, gy, sx, sy = (int(v) for v in R["A_goal_start"])
+    hp = oracle.HeurParams(ad, 5.0, 3.0, 0.0, early, 500, 0)
+    got = oracle.heuristic_reforder(hp, grid, np.zeros((ad, ad), np.uint8), np.full((ad, ad), 5.0), np.zeros((ad, ad)),
+                                    (gx, gy), (sx, sy))
+    for k in ("cost", "dist", "parent", "flags"):
+        assert np.array_equal(got[k], R["A_heur_%s_%s" % (tag, k)]), k
+    xs, ys = oracle.astar_path(got["parent"], got["flags"], sx, sy)
+    assert np.array_equal(np.stack([xs, ys], 1), R["A_heur_%s_path" % tag])
+
+
+def test_pose_checks(oracle):
+    p, seg = R["A_pose_xyyaw"], R["A_seg"]
+    for v in (0, 1):
+        got = oracle.check_segments(R["A_safety"], R["A_centers"], 3, p[:, 0], p[:, 1], p[:, 2], seg, v)
+        assert np.array_equal(got, R["A_first_hit_v%d" % v])
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_potential_field(oracle, variant):
+    grid = R["B_astar"]
+    ad = grid.shape[0]
+    pp = oracle.PotParams(100.0, 7.0, 3.0, 0.1, 1.0, 3.0, 10.0, 200, variant)
+    od, vd = np.zeros((200, 200), np.float32), np.zeros((200, 200), np.float32)
+    prox, mres = np.zeros((ad, ad)), np.full((ad, ad), 1.0)
+    for rep in (0, 1):
+        t = "B_v%d_r%d_" % (variant, rep)
+        oracle.voronoi_potential_field(pp, grid, tuple(int(v) for v in R[t + "ego"]), R[t + "vor_xy"], od, vd, prox, mres)
+        assert np.array_equal(od, R[t + "obstacle_dist"])
+        assert np.array_equal(vd, R[t + "voronoi_dist"])
+        assert np.array_equal(prox, R[t + "h_prox"], equal_nan=True)
+        assert np.array_equal(mres, R[t + "motion_res"])
+
+
+def test_motion_primitives(oracle):
+    o = 0
+    for x, y, yaw, mres, st, dr, n in R["C_prim_in"]:
+        xs, ys, ws = oracle.move_car_some_steps(x, y, yaw, 0.9375, mres, int(dr), st, 3.165)
+        n = int(n)
+        assert len(xs) == n and np.array_equal(np.stack([xs, ys, ws], 1), R["C_prim_out"][o:o + n])
+        o += n
+    o = 0
+    for yaw, delta, n in R["C_ra_in"]:
+        n = int(n)
+        assert np.array_equal(oracle.turn_on_rear_axis(yaw, delta, 3.0), R["C_ra_out"][o:o + n])
+        o += n
