@@ -74,11 +74,13 @@ struct ga_ctx
 
   // ---- heuristic scratch
   int tiles_x = 0, n_tiles = 0;
-  int* d_tile_active = nullptr;   // 2 * n_tiles (double buffered)
-  int* d_hctl = nullptr;          // control words (counters)
+  int* d_tile_active = nullptr;   // per-tile state word (idle / queued / running / dirty)
+  int* d_hctl = nullptr;          // control words (ring cursors, counters)
+  int* d_hring = nullptr;         // ring buffer of activated tiles
+  int hring_cap = 0;              // power of two >= n_tiles
   int32_t* d_jump = nullptr;      // pointer-jumping scratch: 2 * ncell
   int32_t* d_cnt = nullptr;       // (n_straight, n_diag) pairs: 2 * 2 * ncell
-  int relax_grid = 0;             // co-resident CTAs of the persistent relax kernel
+  int relax_grid = 0;             // persistent CTAs of the relax kernel
   int finish_grid = 0;            // same for the finish kernel
 
   // ---- staging (pinned host + device) for pose batches

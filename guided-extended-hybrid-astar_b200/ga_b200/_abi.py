@@ -90,6 +90,7 @@ SYMBOLS = {
     "ga_prof_reset": (C.c_int, [_P]),
     "ga_prof_get": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
     "ga_launch_count": (C.c_longlong, [_P]),
+    "ga_heur_stats": (C.c_int, [_P, C.POINTER(C.c_longlong)]),
 }
 
 _lib = None

@@ -248,6 +248,10 @@ GA_API int ga_prof_enable(ga_ctx* ctx, int on);
 GA_API int ga_prof_reset(ga_ctx* ctx);
 /* total device milliseconds and launches of kernel k since the last reset (syncs the stream) */
 GA_API int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches);
+/* work counters of the last ga_build_heuristic on this context: out7 = { tile visits, inner
+ * relaxation iterations summed over visits, visits that improved a cell, SM cycles summed over
+ * visits spent waiting for a tile / staging / relaxing / writing back } (syncs the stream) */
+GA_API int ga_heur_stats(ga_ctx* ctx, long long* out7);
 /* launches of ALL library kernels since ga_create / ga_prof_reset (always counted) */
 GA_API long long ga_launch_count(const ga_ctx* ctx);
 
