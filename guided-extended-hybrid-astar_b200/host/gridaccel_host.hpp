@@ -146,6 +146,16 @@ public:
     if (rc != GA_OK) throw std::runtime_error(std::string("gridaccel: ") + ga_last_error(h_));
   }
   void sync() const { check(ga_sync(h_)); }
+  // ga_patch_reset sizes the astar-side grids too: a CollisionChecker used without an AStar (the
+  // reference's gtest does that) gets the shipped config.yml / params.yml values
+  bool astar_params_set = false;
+  void ensureAstarParams()
+  {
+    if (astar_params_set) return;
+    ga_astar_params p{ 5.0, 5.0, 3.0, 0.0, 100.0, 7.0, 3.0, 0.1, 1.0, 3.0, 10.0, 200, GA_DT_IPPFLOAT };
+    check(ga_set_astar_params(h_, &p));
+    astar_params_set = true;
+  }
   template <typename T>
   void download(int grid_id, Vec2DFlat<T>& out, size_t dim) const
   {
@@ -264,6 +274,7 @@ public:
   void resetPatch(size_t patch_dim)  // :37-42
   {
     patch_dim_ = patch_dim;
+    ctx_.ensureAstarParams();
     ctx_.check(ga_patch_reset(ctx_.handle(), (int)patch_dim));
   }
 
@@ -514,6 +525,7 @@ public:
     p.vor_dim = (int)VOR_DIM;
     p.dt_variant = dt_variant_;
     ctx_.check(ga_set_astar_params(ctx_.handle(), &p));
+    ctx_.astar_params_set = true;
   }
   // a_star.cpp:70-99.  CollisionChecker::resetPatch (ga_patch_reset) sizes and resets the device
   // grids; carrying h_prox_arr_ / motion_res_map_ over a patch move is a download / shift / upload.
