@@ -80,6 +80,7 @@ struct ga_ctx
   int hring_cap = 0;              // power of two >= n_tiles
   int32_t* d_jump = nullptr;      // pointer-jumping scratch: 2 * ncell
   int32_t* d_cnt = nullptr;       // (n_straight, n_diag) pairs: 2 * 2 * ncell
+  int heur_impl = 1;              // 1 = warp-per-tile sweep kernel, 0 = CTA-per-tile Jacobi kernel
   int relax_grid = 0;             // persistent CTAs of the relax kernel
   int finish_grid = 0;            // same for the finish kernel
 
