@@ -23,14 +23,10 @@
 // HBM/L2 layout: inputs astar_grid_ (u8), restr_geofence_grid_ (u8), movement_cost_map_ (f64),
 // h_prox_arr_ (f64); outputs cost (f64), cost_dist (f64), parent (i32), flags (u8), all dense
 // astar_dim^2 row-major.  Algorithmic bytes per cell: 18 read + 21 written = 39 B.
-#include <cooperative_groups.h>
-
 #include <cmath>
 #include <cstdlib>
 
 #include "ga_internal.cuh"
-
-namespace cg = cooperative_groups;
 
 #define HT GA_HEUR_TILE
 #define HS (HT + 2)            // staged edge incl. halo
@@ -89,8 +85,8 @@ struct heur_args  // finish kernel
   double* dist;
   uint8_t* flags;
   int* ctl;
-  int32_t* jump;  // [2][ncell]
-  int32_t* cnt;   // [2][ncell][2]  (straight, diagonal) steps to jump target
+  unsigned* scratch;  // [ncell] finish A: block-local terminal (10 bits) | straight steps (10) | diagonal steps (10)
+  int2* tot;          // [ncell] finish B: (straight, diagonal) steps of a terminal cell to the root
   int dim, goal;
   double w_prox, unk_w, L1, L2;
 };
@@ -918,115 +914,166 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
 }
 
 // ---------------------------------------------------------------------------------------------
-// finish: parent / is_unknown / closed flags from the converged cost plane, cost_dist by pointer
-// jumping over the parent forest (step counts are integers, so the result is order-free).
+// finish: parent / is_unknown / closed flags from the converged cost plane, and cost_dist =
+// (straight steps) * L1 + (diagonal steps) * L2 along the canonical parent chain (integers, so the
+// result is order-free).  Three plain launches, no grid-wide barrier:
+//   A  one CTA per 32x32 block: canonical parent of every cell (smallest motion index whose
+//      candidate reproduces g(n) bit for bit), then every cell walks its chain INSIDE the block in
+//      shared memory down to the block's terminal cell (the one whose parent lies outside, or the
+//      root) and keeps (terminal, steps to it);
+//   B  only terminal cells: walk terminal -> parent -> that block's terminal -> ... to the root,
+//      one L2 read pair per block crossed (a few dozen), summing the block-local step counts;
+//   C  every cell: its local counts + its terminal's total.
 // ---------------------------------------------------------------------------------------------
+#define FB 32            // finish block edge
+#define FS (FB + 2)      // staged edge incl. halo
 
-__global__ void __launch_bounds__(256) heur_finish_kernel(heur_args a)
+__device__ __forceinline__ unsigned fin_pack(int t_local, int cs, int cd) { return (unsigned)t_local | ((unsigned)cs << 10) | ((unsigned)cd << 20); }
+
+__global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single, const heur_args* many)
 {
-  cg::grid_group grid = cg::this_grid();
-  const int ncell = a.dim * a.dim;
-  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int nthr = gridDim.x * blockDim.x;
-  int32_t* jump0 = a.jump;
-  int32_t* jump1 = a.jump + ncell;
-  int2* cnt0 = reinterpret_cast<int2*>(a.cnt);
-  int2* cnt1 = cnt0 + ncell;
-
-  // ---- phase 1: canonical parent = smallest motion index whose candidate reproduces g(n)
-  int closed = 0;
-  for (int n = tid; n < ncell; n += nthr)
+  __shared__ double sg[FS * FS];
+  __shared__ double sb[FS * FS];
+  __shared__ uint8_t su[FS * FS];
+  __shared__ short lp[FB * FB];
+  __shared__ uint8_t lt[FB * FB];
+  const heur_args& a = many ? many[blockIdx.y] : single;
+  const int dim = a.dim, nbx = (dim + FB - 1) / FB;
+  if ((int)blockIdx.x >= nbx * nbx) return;  // batches of unequal grids
+  const int bx = blockIdx.x % nbx, by = blockIdx.x / nbx;
+  const int ox = bx * FB - 1, oy = by * FB - 1;
+  const double w_prox = a.w_prox, unk_w = a.unk_w;
+  for (int i = threadIdx.x; i < FS * FS; i += FB * FB)
   {
-    const double gn = __ldcg(a.g + n);
-    int32_t par = -2;
-    uint8_t fl = 0;
-    int2 c = make_int2(0, 0);
-    if (gn < INFINITY)
+    const int x = ox + i % FS, y = oy + i / FS;
+    double gv = INFINITY, bv = 0.0;
+    uint8_t u = 0;
+    if (x >= 0 && y >= 0 && x < dim && y < dim)
     {
-      ++closed;
-      fl = GA_H_CLOSED;
-      if (n == a.goal)
-      {
-        par = -1;
-        if (__ldg(a.grid + n) == GA_UNKNOWN) fl |= GA_H_UNKNOWN;  // goal_unknown, a_star.cpp:116
-      }
-      else
-      {
-        const int nx = n % a.dim, ny = n / a.dim;
-        const double m = __ldg(a.mc + n);
-        const double ln1 = a.L1 * m, ln2 = a.L2 * m;
+      const size_t id = (size_t)y * dim + x;
+      gv = __ldcg(a.g + id);
+      bv = __ldg(a.prox + id) * w_prox;
+      u = __ldg(a.grid + id) == GA_UNKNOWN;
+    }
+    sg[i] = gv;
+    sb[i] = bv;
+    su[i] = u;
+  }
+  __syncthreads();
+  const int lx = threadIdx.x % FB, ly = threadIdx.x / FB;
+  const int nx = ox + 1 + lx, ny = oy + 1 + ly;
+  const int me = (ly + 1) * FS + lx + 1;
+  const bool in = nx < dim && ny < dim;
+  const int n = ny * dim + nx;
+  const double gn = sg[me];
+  int32_t par = -2;
+  uint8_t fl = 0;
+  int lpar = -1, typ = 0;
+  if (in && gn < INFINITY)
+  {
+    fl = GA_H_CLOSED;
+    if (n == a.goal)
+    {
+      par = -1;
+      if (su[me]) fl |= GA_H_UNKNOWN;  // goal_unknown, a_star.cpp:116
+    }
+    else
+    {
+      const double m = __ldg(a.mc + n);
+      const double ln1 = a.L1 * m, ln2 = a.L2 * m;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 8; ++i)
+      {
+        const int dx = -c_mdx[i], dy = -c_mdy[i];  // predecessor p = n - motion_[i]
+        const int q = me + dy * FS + dx;
+        const double gq = sg[q];
+        if (!(gq < INFINITY)) continue;  // off-grid halo cells are +inf as well
+        double cand = gq + (i < 4 ? ln1 : ln2);
+        cand = cand + sb[q];
+        cand = cand + (su[q] ? unk_w : 0.0);
+        if (cand == gn)
         {
-          const int px = nx - c_mdx[i], py = ny - c_mdy[i];
-          if (px < 0 || py < 0 || px >= a.dim || py >= a.dim) continue;
-          const int q = py * a.dim + px;
-          const double gq = __ldcg(a.g + q);
-          if (!(gq < INFINITY)) continue;
-          const bool unk = __ldg(a.grid + q) == GA_UNKNOWN;
-          double cand = gq + (i < 4 ? ln1 : ln2);
-          cand = cand + __ldg(a.prox + q) * a.w_prox;
-          cand = cand + (unk ? a.unk_w : 0.0);
-          if (cand == gn)
-          {
-            par = q;
-            if (unk) fl |= GA_H_UNKNOWN;  // NodeDisc::is_unknown_ = unknown-ness of the parent, :253,268
-            c = (i < 4) ? make_int2(1, 0) : make_int2(0, 1);
-            break;
-          }
+          par = (ny + dy) * dim + (nx + dx);
+          if (su[q]) fl |= GA_H_UNKNOWN;  // NodeDisc::is_unknown_ = unknown-ness of the parent, :253,268
+          typ = i < 4 ? 0 : 1;
+          const int plx = lx + dx, ply = ly + dy;
+          if (plx >= 0 && ply >= 0 && plx < FB && ply < FB) lpar = ply * FB + plx;
+          break;
         }
       }
     }
+  }
+  lp[threadIdx.x] = (short)lpar;
+  lt[threadIdx.x] = (uint8_t)typ;
+  if (in)
+  {
     a.parent[n] = par;
     a.flags[n] = fl;
-    jump0[n] = par >= 0 ? par : -1;
-    cnt0[n] = c;
   }
-  // closed-cell count
-  closed = __reduce_add_sync(0xFFFFFFFFu, closed);
-  if ((threadIdx.x & 31) == 0 && closed) atomicAdd(a.ctl + HC_CLOSED, closed);
-
-  // ---- phase 2: pointer jumping; ctl[HC_JUMP0 + (r & 1)] = r + 1 when round r still moved a pointer
-  int32_t* jc = jump0;
-  int32_t* jn = jump1;
-  int2* cc = cnt0;
-  int2* cn = cnt1;
-  __threadfence();
-  grid.sync();
-  for (int r = 0;; ++r)
+  const int closed = __syncthreads_count(fl != 0);
+  if (threadIdx.x == 0 && closed) atomicAdd(a.ctl + HC_CLOSED, closed);
+  // chain walk inside the block
+  int cur = threadIdx.x, cs = 0, cd = 0;
+  for (int p = lpar; p >= 0; p = lp[cur])
   {
-    int moved = 0;
-    for (int n = tid; n < ncell; n += nthr)
+    if (lt[cur]) ++cd; else ++cs;
+    cur = p;
+  }
+  if (in) a.scratch[n] = fin_pack(cur, cs, cd);
+}
+
+__global__ void __launch_bounds__(256) heur_finish_b_kernel(heur_args single, const heur_args* many)
+{
+  const heur_args& a = many ? many[blockIdx.y] : single;
+  const int dim = a.dim, ncell = dim * dim;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncell) return;
+  int p = __ldg(a.parent + c);
+  if (p < 0) return;
+  int cx = c % dim, cy = c / dim;
+  int px = p % dim, py = p / dim;
+  if (px / FB == cx / FB && py / FB == cy / FB) return;  // not a terminal cell
+  int cs = 0, cd = 0;
+  for (;;)
+  {
+    if (px != cx && py != cy) ++cd; else ++cs;  // the step terminal -> parent
+    if (p == a.goal) break;
+    const unsigned s = __ldg(a.scratch + p);    // parent -> its block's terminal
+    cs += (s >> 10) & 1023;
+    cd += (s >> 20) & 1023;
+    const int t = ((py / FB) * FB + (int)((s & 1023) / FB)) * dim + (px / FB) * FB + (int)((s & 1023) % FB);
+    if (t == a.goal) break;
+    cx = t % dim;
+    cy = t / dim;
+    p = __ldg(a.parent + t);
+    px = p % dim;
+    py = p / dim;
+  }
+  a.tot[c] = make_int2(cs, cd);
+}
+
+__global__ void __launch_bounds__(256) heur_finish_c_kernel(heur_args single, const heur_args* many)
+{
+  const heur_args& a = many ? many[blockIdx.y] : single;
+  const int dim = a.dim, ncell = dim * dim;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncell) return;
+  double d = INFINITY;
+  if (a.flags[c] & GA_H_CLOSED)
+  {
+    const unsigned s = a.scratch[c];
+    int cs = (s >> 10) & 1023, cd = (s >> 20) & 1023;
+    const int cx = c % dim, cy = c / dim;
+    const int t = ((cy / FB) * FB + (int)((s & 1023) / FB)) * dim + (cx / FB) * FB + (int)((s & 1023) % FB);
+    if (t != a.goal)
     {
-      const int32_t j = __ldcg(jc + n);
-      int2 c = __ldcg(cc + n);
-      int32_t jj = -1;
-      if (j >= 0)
-      {
-        jj = __ldcg(jc + j);
-        const int2 cj = __ldcg(cc + j);
-        c.x += cj.x;
-        c.y += cj.y;
-        moved |= (jj >= 0);
-      }
-      jn[n] = jj;
-      cn[n] = c;
+      const int2 tt = a.tot[t];
+      cs += tt.x;
+      cd += tt.y;
     }
-    if (__any_sync(0xFFFFFFFFu, moved) && (threadIdx.x & 31) == 0) a.ctl[HC_JUMP0 + (r & 1)] = r + 1;
-    __threadfence();
-    grid.sync();
-    int32_t* tj = jc; jc = jn; jn = tj;
-    int2* tc = cc; cc = cn; cn = tc;
-    if (__ldcg(a.ctl + HC_JUMP0 + (r & 1)) != r + 1) break;
+    d = (double)cs * a.L1 + (double)cd * a.L2;  // NodeDisc::cost_dist_
   }
-
-  // ---- phase 3: NodeDisc::cost_dist_
-  for (int n = tid; n < ncell; n += nthr)
-  {
-    const int2 c = __ldcg(cc + n);
-    const bool in = a.flags[n] & GA_H_CLOSED;
-    a.dist[n] = in ? (double)c.x * a.L1 + (double)c.y * a.L2 : INFINITY;
-  }
+  a.dist[c] = d;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1073,10 +1120,6 @@ int ga_heur_alloc(ga_ctx* c)
                                     (int)(SW_WARPS * sizeof(sweep_tile))));
     c->relax_grid = c->sm_count;
   }
-  int per_sm_f = 0;
-  GA_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_f, heur_finish_kernel, 256, 0));
-  GA_REQUIRE(c, per_sm_f >= 1, GA_ERR_CUDA, "heuristic finish kernel does not fit an SM");
-  c->finish_grid = per_sm_f * c->sm_count;
   return GA_OK;
 }
 
@@ -1150,8 +1193,8 @@ extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, i
   a.dist = c->d_hdist[slot];
   a.flags = c->d_hflags[slot];
   a.ctl = c->d_hctl;
-  a.jump = c->d_jump;
-  a.cnt = c->d_cnt;
+  a.scratch = reinterpret_cast<unsigned*>(c->d_jump);
+  a.tot = reinterpret_cast<int2*>(c->d_cnt);
   a.dim = dim;
   a.goal = G.goal;
   a.w_prox = G.w_prox;
@@ -1159,13 +1202,14 @@ extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, i
   // movement_distances_ (a_star.hpp:54-57): ASTAR_RES and ASTAR_RES * sqrt(2)
   a.L1 = 0.625;
   a.L2 = 0.625 * sqrt(2.0);
-  void* args[] = { &a };
   {
     ga_launch_scope ls(c, GA_K_HEUR_FINISH);
-    const int want = (int)(((size_t)dim * dim + 255) / 256);
-    const int g = c->finish_grid < want ? c->finish_grid : want;
-    GA_CUDA(c, cudaLaunchCooperativeKernel((const void*)heur_finish_kernel, dim3(g), dim3(256), args, 0, c->stream));
+    const int nb = (dim + FB - 1) / FB, cells = (dim * dim + 255) / 256;
+    heur_finish_a_kernel<<<nb * nb, FB * FB, 0, c->stream>>>(a, nullptr);
+    heur_finish_b_kernel<<<cells, 256, 0, c->stream>>>(a, nullptr);
+    heur_finish_c_kernel<<<cells, 256, 0, c->stream>>>(a, nullptr);
   }
+  GA_CUDA(c, cudaGetLastError());
   if (n_closed)
   {
     GA_CUDA(c, cudaMemcpyAsync(n_closed, c->d_hctl + HC_CLOSED, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
