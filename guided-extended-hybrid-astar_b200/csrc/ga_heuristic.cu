@@ -9,13 +9,13 @@
 // bit-identical run to run and to a serial Dijkstra using the same operand order.
 //
 // Execution model (no grid-wide barrier anywhere in the relaxation):
-//   - the astar grid is cut into 32x32-cell tiles; a tile is relaxed by one CTA: tile + 1-cell halo
-//     staged in shared memory (cost plane g, prox * w, unknown cost), chaotic in-place relaxation
-//     with per-row activity stamps until no cell of the tile improves, improved cells written back;
+//   - the astar grid is cut into tiles of 30x30 owned cells; a tile is relaxed by ONE WARP: the
+//     32x32 block (tile + 1-cell halo ring) lives in the warp's slice of shared memory and is
+//     relaxed by Gauss-Seidel line sweeps (see the sweep section below), improved cells written back;
 //   - tiles whose facing border (or corner) cell improved are activated; activation is dataflow: a
-//     per-tile state word (idle / queued / running / running+dirty) and one device-wide ring buffer
-//     of tile ids.  Persistent CTAs pop the ring, so the wavefront is balanced dynamically over the
-//     148 SMs and a CTA never waits for another one;
+//     per-tile state word (idle / queued / running / running+dirty) and one device-wide ticket ring
+//     of tile ids.  Persistent warps (6 per SM) take tickets, so the wavefront is balanced
+//     dynamically over the 148 SMs and a worker never waits for another one;
 //   - termination: a counter of queued-or-running tiles reaches zero;
 //   - the same kernel serves a BATCH of independent grids (one descriptor per grid, ring entries
 //     carry the grid index): many queries' wavefronts fill the SMs where one grid cannot.
@@ -28,12 +28,6 @@
 
 #include "ga_internal.cuh"
 
-#define HT GA_HEUR_TILE
-#define HS (HT + 2)            // staged edge incl. halo
-#define H_ROWS_PER_THREAD 2    // cells per thread in the relax kernel (rows ly and ly + HT/2)
-#define H_THREADS (HT * HT / H_ROWS_PER_THREAD)
-#define H_WARPS (H_THREADS / 32)
-
 enum { T_IDLE = 0, T_QUEUED = 1, T_RUNNING = 2, T_DIRTY = 3 };
 
 // control block words (ga_ctx::d_hctl)
@@ -43,12 +37,10 @@ enum
   HC_TAIL = 1,      // ring producer cursor
   HC_PENDING = 2,   // tiles queued or running
   HC_CLOSED = 3,    // closed-cell count (finish kernel)
-  HC_JUMP0 = 4,     // pointer-jumping round stamps
-  HC_JUMP1 = 5,
-  HC_VISITS = 8,    // statistics: tile visits, inner iterations, visits that improved a cell
+  HC_VISITS = 8,    // statistics: tile visits, sweeps, visits that improved a cell
   HC_INNER = 9,
   HC_IMPROVING = 10,
-  HC_CYC = 16,      // u64 x 4: SM cycles spent by thread 0 in pop / stage / relax / write-back+activate
+  HC_CYC = 16,      // u64 x 4: SM cycles spent by the workers in pop / stage / sweeps (+ early publication) / final publication
   HC_WORDS = 24
 };
 
@@ -60,9 +52,12 @@ struct heur_grid
   const double* mc;
   const double* prox;
   double* g;
-  int* state;  // per tile
+  uint8_t* cls;  // per cell, written by the init kernel: bit0 = UNKNOWN, bit1 = blocked (OCC or geofence)
+  int* state;    // per tile
+  int* tprox;    // per tile: == epoch when some cell of the staged block carries a prox cost (set by the init kernel)
+  int epoch;     // build counter of the context (stamps need no clearing between builds)
   int dim, tiles_x, n_tiles, goal;
-  int edge;  // owned cells per tile edge (HT for the Jacobi kernel, SW_O for the sweep kernel)
+  int edge;  // owned cells per tile edge (SW_O)
   double w_prox, unk_w;
 };
 
@@ -72,7 +67,7 @@ struct heur_queue
   unsigned mask;  // capacity - 1 (power of two >= total tiles)
   int* ctl;
   unsigned poll_ns;  // back-off of an idle worker between two looks at its ring slot
-  unsigned early;    // sweep kernel: publish once after this many changing sweeps (0 = only when converged)
+  unsigned early;    // publish once after this many changing sweeps (0 = only when converged)
 };
 
 struct heur_args  // finish kernel
@@ -84,7 +79,7 @@ struct heur_args  // finish kernel
   int32_t* parent;
   double* dist;
   uint8_t* flags;
-  int* ctl;
+  int* closed;        // closed-cell counter of this grid
   unsigned* scratch;  // [ncell] finish A: block-local terminal (10 bits) | straight steps (10) | diagonal steps (10)
   int2* tot;          // [ncell] finish B: (straight, diagonal) steps of a terminal cell to the root
   int dim, goal;
@@ -129,25 +124,8 @@ __device__ __forceinline__ int tile_activate(const heur_queue& q, int* state, in
   }
 }
 
-// blocks until this CTA's ticket is served (returns the entry) or all work is done (returns -1)
-__device__ __forceinline__ int q_pop(const heur_queue& q)
-{
-  const unsigned h = atomicAdd(reinterpret_cast<unsigned*>(q.ctl + HC_HEAD), 1u);
-  int* slot = q.ring + (h & q.mask);
-  for (unsigned spin = 0;; ++spin)
-  {
-    const int e = ld_volatile(slot);
-    if (e != 0)
-    {
-      *reinterpret_cast<volatile int*>(slot) = 0;
-      return e;
-    }
-    if ((spin & 3) == 3 && ld_volatile(q.ctl + HC_PENDING) == 0) return -1;
-    __nanosleep(q.poll_ns);
-  }
-}
-
-// warp-wide variant: every lane executes the same control flow (lane 0 takes the ticket, all lanes
+// blocks until this worker's ticket is served (returns the entry) or all work is done (returns -1).
+// Warp-wide: every lane executes the same control flow (lane 0 takes the ticket, all lanes
 // poll the same word -> one request), so the warp stays converged and the sweeps' shuffles compile
 // to plain SHFL
 __device__ __forceinline__ int q_pop_warp(const heur_queue& q, const int lane)
@@ -173,338 +151,39 @@ __device__ __forceinline__ int q_pop_warp(const heur_queue& q, const int lane)
   return e;
 }
 
-__global__ void heur_init_kernel(heur_grid G, heur_queue q, int gi, int first)
+// one grid per blockIdx.y.  The control block (cursors, pending count) was zeroed by the host.
+__global__ void heur_init_kernel(heur_grid single, const heur_grid* many, heur_queue q)
 {
+  const int gi = blockIdx.y;
+  const heur_grid& G = many ? many[gi] : single;
   const size_t n = (size_t)G.dim * G.dim;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+  {
     G.g[i] = (i == (size_t)G.goal) ? 0.0 : INFINITY;
+    const uint8_t cell = G.grid[i];  // verifyNode (a_star.cpp:325-343) and unknown_cost (:253-254) inputs, folded once per build
+    G.cls[i] = (cell == GA_UNKNOWN ? 1 : 0) | ((cell == GA_OCC || G.fence[i] == 1) ? 2 : 0);
+    if (G.prox[i] * G.w_prox != 0.0)
+    {
+      // every tile whose staged block [t * edge - 1, t * edge + edge] holds the cell (at most 2 x 2)
+      const int x = (int)(i % G.dim), y = (int)(i / G.dim);
+      for (int ty = y / G.edge - 1; ty <= y / G.edge + 1; ++ty)
+        for (int tx = x / G.edge - 1; tx <= x / G.edge + 1; ++tx)
+          if (tx >= 0 && ty >= 0 && tx < G.tiles_x && ty < G.tiles_x && x >= tx * G.edge - 1 && x <= tx * G.edge + G.edge &&
+              y >= ty * G.edge - 1 && y <= ty * G.edge + G.edge)
+            G.tprox[ty * G.tiles_x + tx] = G.epoch;
+    }
+  }
   const int gx = G.goal % G.dim, gy = G.goal / G.dim;
   const int goal_tile = (gy / G.edge) * G.tiles_x + gx / G.edge;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < G.n_tiles; i += gridDim.x * blockDim.x)
     G.state[i] = (i == goal_tile) ? T_QUEUED : T_IDLE;
   if (blockIdx.x == 0 && threadIdx.x == 0)
   {
-    // the ring is empty between builds (every entry popped is cleared): seed it with the goal tile.
-    // first == 1: this launch also resets the cursors (one batch = one ring epoch)
-    if (first)
-    {
-      for (int k = 0; k < HC_WORDS; ++k) q.ctl[k] = 0;
-    }
-    __threadfence();
+    // the ring is empty between builds (every entry popped is cleared): seed it with the root's tile
     atomicAdd(q.ctl + HC_PENDING, 1);
     q_push(q, ((gi << 20) | goal_tile) + 1);
   }
 }
-
-// one cell: min over the 8 predecessors of ((g(p) + len_i * mc(n)) + prox(p) * w) + unk(p), operand
-// order of a_star.cpp:257.  The candidates are independent; the minimum is taken as a tree (min is
-// exact, so its association does not matter).  Without prox / unknown terms every straight
-// (diagonal) candidate adds the same constant, and fl(x + c) is monotone in x, so
-// min_i fl(g_i + c) == fl(min_i g_i + c) bit for bit: two additions instead of eight.
-// A NaN candidate (0/0 in h_prox_arr_, a_star.cpp:492-497) never wins: x < NaN, NaN < x are false.
-#define MIN2(a, b) ((b) < (a) ? (b) : (a))
-template <bool PROX, bool UNK>
-__device__ __forceinline__ double relax_cell(const double* sg, const double* sb, const double* sc, int me, double ln1,
-                                             double ln2)
-{
-  // staged offsets of the predecessors p = n - motion_[i], i = 0..7 (straight 0..3, diagonal 4..7)
-  constexpr int off[8] = { -1, -HS, 1, HS, HS + 1, -HS + 1, HS - 1, -HS - 1 };
-  if (!PROX && !UNK)
-  {
-    const double s01 = MIN2(sg[me + off[0]], sg[me + off[1]]), s23 = MIN2(sg[me + off[2]], sg[me + off[3]]);
-    const double d01 = MIN2(sg[me + off[4]], sg[me + off[5]]), d23 = MIN2(sg[me + off[6]], sg[me + off[7]]);
-    const double cs = MIN2(s01, s23) + ln1, cd = MIN2(d01, d23) + ln2;
-    return MIN2(cs, cd);
-  }
-  double c[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i)
-  {
-    const int p = me + off[i];
-    double cand = sg[p] + (i < 4 ? ln1 : ln2);
-    if (PROX) cand = cand + sb[p];
-    if (UNK) cand = cand + sc[p];
-    c[i] = cand;
-  }
-  const double m01 = MIN2(c[0], c[1]), m23 = MIN2(c[2], c[3]), m45 = MIN2(c[4], c[5]), m67 = MIN2(c[6], c[7]);
-  const double m0 = MIN2(m01, m23), m1 = MIN2(m45, m67);
-  return MIN2(m0, m1);
-}
-#undef MIN2
-
-// chaotic (in-place) relaxation of the staged tile until no cell improves.  srow[r] = last inner
-// iteration in which staged row r changed; a thread's rows are re-evaluated only if one of them or
-// a vertical neighbour changed in the previous or current iteration.  Returns improved ? 1 : 0.
-template <bool PROX, bool UNK>
-__device__ __forceinline__ int relax_tile_loop(double* sg, const double* sb, const double* sc, int* srow, int lx, int wy,
-                                               const bool* blocked, const double* ln1, const double* ln2, int* iters)
-{
-  const int lane = threadIdx.x & 31;
-  int any_change = 0;
-  int it = 1;
-  for (;; ++it)
-  {
-    int changed = 0;
-    int st = 0;
-#pragma unroll
-    for (int r = 0; r < H_ROWS_PER_THREAD; ++r)
-    {
-      const int ly = wy + r * H_WARPS;
-      st = max(st, max(srow[ly], max(srow[ly + 1], srow[ly + 2])));
-    }
-    if (st >= it - 1)
-    {
-      double best[H_ROWS_PER_THREAD], g0[H_ROWS_PER_THREAD];
-#pragma unroll
-      for (int r = 0; r < H_ROWS_PER_THREAD; ++r)
-      {
-        const int me = (wy + r * H_WARPS + 1) * HS + lx + 1;
-        g0[r] = sg[me];
-        best[r] = relax_cell<PROX, UNK>(sg, sb, sc, me, ln1[r], ln2[r]);
-      }
-#pragma unroll
-      for (int r = 0; r < H_ROWS_PER_THREAD; ++r)
-      {
-        const int ly = wy + r * H_WARPS;
-        const int ch = (!blocked[r] && best[r] < g0[r]) ? 1 : 0;
-        if (ch) sg[(ly + 1) * HS + lx + 1] = best[r];
-        if (__any_sync(0xFFFFFFFFu, ch) && lane == 0) srow[ly + 1] = it;
-        changed |= ch;
-      }
-    }
-    const int any = __syncthreads_or(changed);
-    if (!any) break;
-    any_change = 1;
-  }
-  *iters = it;
-  return any_change;
-}
-
-__global__ void __launch_bounds__(H_THREADS, 2) heur_relax_kernel(heur_grid single, const heur_grid* many, heur_queue q)
-{
-  __shared__ double sg[HS * HS];
-  __shared__ double sb[HS * HS];
-  __shared__ double sc[HS * HS];
-  __shared__ int srow[HS];
-  __shared__ int s_mark[8];
-  __shared__ int s_entry, s_cont;
-  __shared__ unsigned s_key[8];  // per direction: min improved border value (float bits, rounded down)
-
-  if (threadIdx.x == 0) s_cont = 0;
-  const int lx = threadIdx.x % HT, wy = threadIdx.x / HT;
-  const double L1 = 0.625, L2 = 0.625 * 1.4142135623730951;  // movement_distances_ (a_star.hpp:54-57)
-
-  for (;;)
-  {
-    __syncthreads();
-    long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-    if (threadIdx.x == 0)
-    {
-      t0 = clock64();
-      s_entry = s_cont ? s_cont : q_pop(q);
-      s_cont = 0;
-      t1 = clock64();
-    }
-    __syncthreads();
-    const int e = s_entry;
-    if (e < 0) return;
-    const int gi = (e - 1) >> 20, tile = (e - 1) & 0xFFFFF;
-    // field-wise select: taking the address of the by-value descriptor would spill it to local memory
-#define HG(f) (many ? many[gi].f : single.f)
-    heur_grid G;
-    G.grid = HG(grid);
-    G.fence = HG(fence);
-    G.mc = HG(mc);
-    G.prox = HG(prox);
-    G.g = HG(g);
-    G.state = HG(state);
-    G.dim = HG(dim);
-    G.tiles_x = HG(tiles_x);
-    G.goal = HG(goal);
-    G.w_prox = HG(w_prox);
-    G.unk_w = HG(unk_w);
-#undef HG
-    const int dim = G.dim, tiles_x = G.tiles_x;
-    double* __restrict__ gp = G.g;
-    if (threadIdx.x == 0)
-    {
-      atomicExch(G.state + tile, T_RUNNING);  // ring tiles: QUEUED -> RUNNING; continued tiles already are
-      // reserve the pending counts of the (at most 8) neighbours this visit may activate NOW, so the
-      // increment is performed long before any of them can finish; the unused ones are returned at
-      // release.  HC_PENDING can then never touch zero while work exists.
-      atomicAdd(q.ctl + HC_PENDING, 8);
-      __threadfence();
-    }
-    if (threadIdx.x < 8)
-    {
-      s_mark[threadIdx.x] = 0;
-      s_key[threadIdx.x] = 0xFFFFFFFFu;
-    }
-    if (threadIdx.x < HS) srow[threadIdx.x] = 0;
-    __syncthreads();
-
-    const int tx = tile % tiles_x, ty = tile / tiles_x;
-    const int ox = tx * HT - 1, oy = ty * HT - 1;
-    const double w_prox = G.w_prox, unk_w = G.unk_w;
-    // ---- stage g, prox * w and unknown cost of the tile + halo: own cells first, halo ring by the
-    //      first 4 * HT + 4 threads, all loads of a thread in flight together
-    int has_prox = 0;
-    bool blocked[H_ROWS_PER_THREAD];
-    double ln1[H_ROWS_PER_THREAD], ln2[H_ROWS_PER_THREAD], g_in[H_ROWS_PER_THREAD];
-    size_t id[H_ROWS_PER_THREAD];
-#pragma unroll
-    for (int r = 0; r < H_ROWS_PER_THREAD; ++r)
-    {
-      const int ly = wy + r * H_WARPS;
-      const int gx = ox + 1 + lx, gy = oy + 1 + ly;
-      double gv = INFINITY, bv = 0.0, cv = 0.0;
-      blocked[r] = true;
-      ln1[r] = ln2[r] = 0.0;
-      id[r] = 0;
-      if (gx < dim && gy < dim)
-      {
-        id[r] = (size_t)gy * dim + gx;
-        gv = __ldcg(gp + id[r]);
-        const uint8_t cell = __ldg(G.grid + id[r]);
-        bv = __ldg(G.prox + id[r]) * w_prox;                 // prox_cost, a_star.cpp:251
-        cv = (cell == GA_UNKNOWN) ? unk_w : 0.0;             // unknown_cost, :253-254
-        // verifyNode, a_star.cpp:325-343; the root keeps cost 0
-        blocked[r] = (cell == GA_OCC) || (__ldg(G.fence + id[r]) == 1) || ((int)id[r] == G.goal);
-        const double m = __ldg(G.mc + id[r]);
-        ln1[r] = L1 * m;  // movement_costs = movement_distances_[i] * movement_weigth, :244-245
-        ln2[r] = L2 * m;
-        has_prox |= (bv != 0.0);
-      }
-      const int me = (ly + 1) * HS + lx + 1;
-      sg[me] = gv;
-      sb[me] = bv;
-      sc[me] = cv;
-      g_in[r] = gv;
-    }
-    if (threadIdx.x < 4 * HT + 4)
-    {
-      // halo ring: rows 0 and HS-1 (HS cells each), then columns 0 and HS-1 of rows 1..HT
-      const int k = threadIdx.x;
-      int hx, hy;
-      if (k < HS) { hx = k; hy = 0; }
-      else if (k < 2 * HS) { hx = k - HS; hy = HS - 1; }
-      else if (k < 2 * HS + HT) { hx = 0; hy = k - 2 * HS + 1; }
-      else { hx = HS - 1; hy = k - 2 * HS - HT + 1; }
-      const int x = ox + hx, y = oy + hy;
-      double gv = INFINITY, bv = 0.0, cv = 0.0;
-      if (x >= 0 && y >= 0 && x < dim && y < dim)
-      {
-        const size_t hid = (size_t)y * dim + x;
-        gv = __ldcg(gp + hid);
-        bv = __ldg(G.prox + hid) * w_prox;
-        cv = (__ldg(G.grid + hid) == GA_UNKNOWN) ? unk_w : 0.0;
-        has_prox |= (bv != 0.0);
-      }
-      sg[hy * HS + hx] = gv;
-      sb[hy * HS + hx] = bv;
-      sc[hy * HS + hx] = cv;
-    }
-    has_prox = __syncthreads_or(has_prox);
-    if (threadIdx.x == 0) t2 = clock64();
-
-    int any, iters = 0;
-    if (has_prox)
-    {
-      if (unk_w != 0) any = relax_tile_loop<true, true>(sg, sb, sc, srow, lx, wy, blocked, ln1, ln2, &iters);
-      else any = relax_tile_loop<true, false>(sg, sb, sc, srow, lx, wy, blocked, ln1, ln2, &iters);
-    }
-    else
-    {
-      if (unk_w != 0) any = relax_tile_loop<false, true>(sg, sb, sc, srow, lx, wy, blocked, ln1, ln2, &iters);
-      else any = relax_tile_loop<false, false>(sg, sb, sc, srow, lx, wy, blocked, ln1, ln2, &iters);
-    }
-
-    if (threadIdx.x == 0) t3 = clock64();
-    // ---- write back improved cells, note which borders moved
-    if (any)
-    {
-#pragma unroll
-      for (int r = 0; r < H_ROWS_PER_THREAD; ++r)
-      {
-        const int ly = wy + r * H_WARPS;
-        const double g_out = sg[(ly + 1) * HS + lx + 1];
-        if (!blocked[r] && g_out < g_in[r])
-        {
-          __stcg(gp + id[r], g_out);
-          const bool w = lx == 0, ee = lx == HT - 1, n = ly == 0, s = ly == HT - 1;
-          if (w | ee | n | s)
-          {
-            const unsigned kb = __float_as_uint(__double2float_rd(g_out));
-            if (w) { s_mark[0] = 1; atomicMin(s_key + 0, kb); }
-            if (ee) { s_mark[1] = 1; atomicMin(s_key + 1, kb); }
-            if (n) { s_mark[2] = 1; atomicMin(s_key + 2, kb); }
-            if (s) { s_mark[3] = 1; atomicMin(s_key + 3, kb); }
-            if (w && n) { s_mark[4] = 1; atomicMin(s_key + 4, kb); }
-            if (ee && n) { s_mark[5] = 1; atomicMin(s_key + 5, kb); }
-            if (w && s) { s_mark[6] = 1; atomicMin(s_key + 6, kb); }
-            if (ee && s) { s_mark[7] = 1; atomicMin(s_key + 7, kb); }
-          }
-        }
-      }
-      __threadfence();
-    }
-    __syncthreads();
-    if (threadIdx.x < 32)
-    {
-      // ---- activate the neighbours whose halo changed.  The neighbour with the smallest improved
-      //      border value (the direction the wavefront moves) is continued by THIS CTA when it is
-      //      idle -- no ring hand-off on the critical chain -- the others go to the ring.
-      const int k = threadIdx.x;
-      int nt = -1;
-      unsigned key = 0xFFFFFFFFu;
-      if (k < 8 && s_mark[k])
-      {
-        const int nx = tx + c_ndx[k], ny = ty + c_ndy[k];
-        if (nx >= 0 && ny >= 0 && nx < tiles_x && ny < tiles_x)
-        {
-          nt = ny * tiles_x + nx;
-          key = ((unsigned)s_key[k] & ~7u) | (unsigned)k;
-        }
-      }
-      const unsigned want = __ballot_sync(0xFFFFFFFFu, nt >= 0);
-      const unsigned best_key = __reduce_min_sync(0xFFFFFFFFu, key);
-      const int n_act = __popc(want);
-      int unused = 0, cont = 0;
-      if (nt >= 0)
-      {
-        if (key == best_key && atomicCAS(G.state + nt, T_IDLE, T_RUNNING) == T_IDLE)
-          cont = ((gi << 20) | nt) + 1;
-        else
-          unused = tile_activate(q, G.state, gi, nt);
-      }
-      const int n_unused = __reduce_add_sync(0xFFFFFFFFu, unused);
-      const int cont_entry = __reduce_max_sync(0xFFFFFFFFu, cont);
-      if (k == 0)
-      {
-        atomicAdd(q.ctl + HC_VISITS, 1);
-        atomicAdd(q.ctl + HC_INNER, iters);
-        if (any) atomicAdd(q.ctl + HC_IMPROVING, 1);
-        // release the tile: re-queue it if a neighbour wrote into our halo meanwhile
-        int dec = (8 - n_act) + n_unused + 1;
-        if (atomicCAS(G.state + tile, T_RUNNING, T_IDLE) == T_DIRTY)
-        {
-          atomicExch(G.state + tile, T_QUEUED);
-          q_push(q, e);
-          dec -= 1;
-        }
-        if (dec) atomicSub(q.ctl + HC_PENDING, dec);
-        s_cont = cont_entry;
-        unsigned long long* cyc = reinterpret_cast<unsigned long long*>(q.ctl + HC_CYC);
-        const long long t4 = clock64();
-        atomicAdd(cyc + 0, (unsigned long long)(t1 - t0));
-        atomicAdd(cyc + 1, (unsigned long long)(t2 - t1));
-        atomicAdd(cyc + 2, (unsigned long long)(t3 - t2));
-        atomicAdd(cyc + 3, (unsigned long long)(t4 - t3));
-      }
-    }
-  }
-}
-
 
 // ---------------------------------------------------------------------------------------------
 // Sweep relaxation: one WARP per tile, Gauss-Seidel line sweeps.
@@ -517,8 +196,8 @@ __global__ void __launch_bounds__(H_THREADS, 2) heur_relax_kernel(heur_grid sing
 // carries a value across the whole tile along any path inside its 3-move cone ({S,SE,SW} for the
 // downward sweep, ...).  The four sweeps (down, right, up, left) cover all eight moves; the tile is
 // converged when three sweeps in a row after the last changing one (or four from the start) change
-// nothing (a sweep is idempotent).  Compared with the Jacobi iteration of heur_relax_kernel this
-// moves a front 30 cells per ~1 us with 32 threads instead of 1 cell per 0.46 us with 512.
+// nothing (a sweep is idempotent).  A CTA-per-tile Jacobi iteration (round 1's first kernel) moved a
+// front 1 cell per 0.46 us with 512 threads; a sweep moves it 30 cells per 1.7 us with 32.
 // Warps are independent workers on the ticket ring (no __syncthreads anywhere).
 // ---------------------------------------------------------------------------------------------
 #define SW_O 30                    // owned cells per tile edge
@@ -531,12 +210,22 @@ struct sweep_tile
   double g[32 * SW_P];   // cost plane, relaxed in place
   double w[32 * SW_P];   // value last read from / written to global memory
   double mc[32 * SW_P];  // movement_cost_map_ of the cell (edge length factor of the DESTINATION); +inf = blocked
-  double pb[32 * SW_P];  // h_prox_arr_ * astar_prox_cost_ of the cell (term of the PREDECESSOR)
+  double pb[32 * SW_P];  // h_prox_arr_ of the cell (x astar_prox_cost_ = prox_cost, term of the PREDECESSOR)
   unsigned urow[32], ucol[32];  // UNKNOWN masks: urow[y] bit x / ucol[x] bit y
 };
 
 // NaN-safe minimum (a NaN candidate, 0/0 in h_prox_arr_, never wins -- a_star.cpp:492-497)
 __device__ __forceinline__ double dmin(double a, double b) { return fmin(a, b); }
+
+__device__ __forceinline__ double umin_f64(double a, double b)
+{
+#ifdef SW_DMIN
+  return b < a ? b : a;
+#else
+  const unsigned long long ua = (unsigned long long)__double_as_longlong(a), ub = (unsigned long long)__double_as_longlong(b);
+  return __longlong_as_double((long long)(ub < ua ? ub : ua));
+#endif
+}
 
 // One line step of a sweep: the new value of cell `lane` of line s from the three cells of line sp
 // (a = this lane's value there; the neighbours' arrive by shuffle).  ORIENT 0: lane = x, lines are
@@ -545,7 +234,7 @@ __device__ __forceinline__ double dmin(double a, double b) { return fmin(a, b); 
 // halo cells, so what their missing neighbour "sends" does not matter.
 template <int ORIENT, bool PROX, bool UNK>
 __device__ __forceinline__ double sweep_step(const sweep_tile& S, const int lane, const int sp, const int s, const double a,
-                                             const double unk_w, const double L1, const double L2, double* old_out)
+                                             const double w_prox, const double unk_w, const double L1, const double L2, double* old_out)
 {
   constexpr int dl = ORIENT == 0 ? 1 : SW_P;  // index stride of the lane
   constexpr int ds = ORIENT == 0 ? SW_P : 1;  // index stride of the line
@@ -558,20 +247,22 @@ __device__ __forceinline__ double sweep_step(const sweep_tile& S, const int lane
   if (!PROX && !UNK)
   {
     // equal addends: min_i fl(g_i + c) == fl(min_i g_i + c); no NaN on this path
+    // values are >= 0 or +inf here, so the IEEE order is the order of the bit patterns: the minima
+    // run on the integer pipe (shorter latency than DSETP + select on the dependent chain)
     const double c1 = a + ln1;
-    const double m0 = c1 < old ? c1 : old;  // overlaps the shuffle latency
-    const double m2 = ar < al ? ar : al;
+    const double m0 = umin_f64(c1, old);  // overlaps the shuffle latency
+    const double m2 = umin_f64(ar, al);
     const double c2 = m2 + ln2;
-    return c2 < m0 ? c2 : m0;
+    return umin_f64(c2, m0);
   }
   const int lm = lane > 0 ? lane - 1 : 0, lp = lane < 31 ? lane + 1 : 31;
   double c0 = a + ln1, c1 = al + ln2, c2 = ar + ln2;
   if (PROX)
   {
     const int pi = sp * ds;
-    c0 = c0 + S.pb[pi + lane * dl];
-    c1 = c1 + S.pb[pi + lm * dl];
-    c2 = c2 + S.pb[pi + lp * dl];
+    c0 = c0 + S.pb[pi + lane * dl] * w_prox;  // prox_cost of the predecessor, a_star.cpp:251
+    c1 = c1 + S.pb[pi + lm * dl] * w_prox;
+    c2 = c2 + S.pb[pi + lp * dl] * w_prox;
   }
   if (UNK)
   {
@@ -585,7 +276,7 @@ __device__ __forceinline__ double sweep_step(const sweep_tile& S, const int lane
 
 // one sweep over the 30 owned lines; dir = +1 / -1: line order.  Returns 1 if this lane improved a cell.
 template <int ORIENT, bool PROX, bool UNK>
-__device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const int dir, const double unk_w,
+__device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const int dir, const double w_prox, const double unk_w,
                                            const double L1, const double L2)
 {
   constexpr int dl = ORIENT == 0 ? 1 : SW_P, ds = ORIENT == 0 ? SW_P : 1;
@@ -598,7 +289,7 @@ __device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const 
     const int sp = s;
     s += dir;
     double old;
-    const double nv = sweep_step<ORIENT, PROX, UNK>(S, lane, sp, s, a, unk_w, L1, L2, &old);
+    const double nv = sweep_step<ORIENT, PROX, UNK>(S, lane, sp, s, a, w_prox, unk_w, L1, L2, &old);
     const bool imp = nv < old;
     if (imp) S.g[s * ds + lane * dl] = nv;
     changed |= imp;
@@ -609,27 +300,27 @@ __device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const 
 
 // can the halo improve a border cell?  (first line step of each of the four sweeps, nothing stored)
 template <bool PROX, bool UNK>
-__device__ __forceinline__ int halo_improves(const sweep_tile& S, const int lane, const double unk_w, const double L1,
+__device__ __forceinline__ int halo_improves(const sweep_tile& S, const int lane, const double w_prox, const double unk_w, const double L1,
                                              const double L2)
 {
   double old;
   int imp = 0;
-  imp |= sweep_step<0, PROX, UNK>(S, lane, 0, 1, S.g[lane], unk_w, L1, L2, &old) < old;
-  imp |= sweep_step<0, PROX, UNK>(S, lane, 31, 30, S.g[31 * SW_P + lane], unk_w, L1, L2, &old) < old;
-  imp |= sweep_step<1, PROX, UNK>(S, lane, 0, 1, S.g[lane * SW_P], unk_w, L1, L2, &old) < old;
-  imp |= sweep_step<1, PROX, UNK>(S, lane, 31, 30, S.g[lane * SW_P + 31], unk_w, L1, L2, &old) < old;
+  imp |= sweep_step<0, PROX, UNK>(S, lane, 0, 1, S.g[lane], w_prox, unk_w, L1, L2, &old) < old;
+  imp |= sweep_step<0, PROX, UNK>(S, lane, 31, 30, S.g[31 * SW_P + lane], w_prox, unk_w, L1, L2, &old) < old;
+  imp |= sweep_step<1, PROX, UNK>(S, lane, 0, 1, S.g[lane * SW_P], w_prox, unk_w, L1, L2, &old) < old;
+  imp |= sweep_step<1, PROX, UNK>(S, lane, 31, 30, S.g[lane * SW_P + 31], w_prox, unk_w, L1, L2, &old) < old;
   return __any_sync(SW_FULL, imp);
 }
 
 template <bool PROX, bool UNK>
-__device__ __forceinline__ int sweep_once(sweep_tile& S, const int lane, const int d, const double unk_w, const double L1,
+__device__ __forceinline__ int sweep_once(sweep_tile& S, const int lane, const int d, const double w_prox, const double unk_w, const double L1,
                                           const double L2)
 {
   int ch;
-  if (d == 0) ch = sweep_lines<0, PROX, UNK>(S, lane, +1, unk_w, L1, L2);
-  else if (d == 1) ch = sweep_lines<1, PROX, UNK>(S, lane, +1, unk_w, L1, L2);
-  else if (d == 2) ch = sweep_lines<0, PROX, UNK>(S, lane, -1, unk_w, L1, L2);
-  else ch = sweep_lines<1, PROX, UNK>(S, lane, -1, unk_w, L1, L2);
+  if (d == 0) ch = sweep_lines<0, PROX, UNK>(S, lane, +1, w_prox, unk_w, L1, L2);
+  else if (d == 1) ch = sweep_lines<1, PROX, UNK>(S, lane, +1, w_prox, unk_w, L1, L2);
+  else if (d == 2) ch = sweep_lines<0, PROX, UNK>(S, lane, -1, w_prox, unk_w, L1, L2);
+  else ch = sweep_lines<1, PROX, UNK>(S, lane, -1, w_prox, unk_w, L1, L2);
   ch = __any_sync(SW_FULL, ch);
   __syncwarp();
   return ch;
@@ -678,7 +369,7 @@ __device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V
        : lane == 6 ? k_sw : lane == 7 ? k_se : 0xFFFFFFFFu;
   }
   // the stores above are visible before any neighbour is told to look and before the tile is released
-  if (__any_sync(SW_FULL, col_key != 0xFFFFFFFFu)) __threadfence();
+  if (__any_sync(SW_FULL, col_key != 0xFFFFFFFFu)) asm volatile("fence.acq_rel.gpu;" ::: "memory");
   __syncwarp();
   if (!__any_sync(SW_FULL, kk != 0xFFFFFFFFu)) return 0;
   int nt = -1;
@@ -712,15 +403,15 @@ __device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V
 // 0 = never) so that the tiles downstream start while this one is still confirming convergence
 template <bool PROX, bool UNK>
 __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
-                                               int d, const bool must_run, const double unk_w, const double L1,
+                                               int d, const bool must_run, const double w_prox, const double unk_w, const double L1,
                                                const double L2, int* n_sweeps, int* n_act, int* n_unused)
 {
   *n_sweeps = 0;
-  if (!must_run && !halo_improves<PROX, UNK>(S, lane, unk_w, L1, L2)) return 0;
+  if (!must_run && !halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2)) return 0;
   int streak = 0, n = 0, n_changing = 0;
   while (streak < 4)
   {
-    const int ch = sweep_once<PROX, UNK>(S, lane, d, unk_w, L1, L2);
+    const int ch = sweep_once<PROX, UNK>(S, lane, d, w_prox, unk_w, L1, L2);
     streak = ch ? 1 : streak + 1;  // a sweep is idempotent: after a changing one, three clean others suffice
     n_changing += ch;
     d = (d + 1) & 3;
@@ -758,25 +449,15 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     V.gi = (e - 1) >> 20;
     const int gi = V.gi, tile = (e - 1) & 0xFFFFF;
 #define HG(f) (many ? many[gi].f : single.f)
-    const uint8_t* __restrict__ p_grid = HG(grid);
-    const uint8_t* __restrict__ p_fence = HG(fence);
+    const uint8_t* __restrict__ p_cls = HG(cls);
     const double* __restrict__ p_mc = HG(mc);
     const double* __restrict__ p_prox = HG(prox);
     double* __restrict__ gp = HG(g);
     int* state = HG(state);
     const int dim = HG(dim), tiles_x = HG(tiles_x), goal = HG(goal);
     const double w_prox = HG(w_prox), unk_w = HG(unk_w);
+    const int has_prox = __ldg(HG(tprox) + tile) == HG(epoch);
 #undef HG
-    if (lane == 0)
-    {
-      atomicExch(state + tile, T_RUNNING);
-      // reserve the pending counts of the activations this visit may make NOW, long before any of
-      // them can finish; the unused ones are returned at release (see heur_relax_kernel)
-      atomicAdd(q.ctl + HC_PENDING, SW_RESERVE);
-      __threadfence();
-    }
-    __syncwarp();
-
     const int tx = tile % tiles_x, ty = tile / tiles_x;
     const int ox = tx * SW_O - 1, oy = ty * SW_O - 1;
     V.gp = gp; V.state = state; V.dim = dim; V.tiles_x = tiles_x; V.tx = tx; V.ty = ty; V.ox = ox; V.oy = oy;
@@ -785,7 +466,8 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     const int gx = ox + lane;
     const bool x_in = gx >= 0 && gx < dim;
     const int cx = min(max(gx, 0), dim - 1);
-    // (a) the static planes go straight to shared memory (read-only during the kernel: L1 is fine)
+    // (a) the static planes go straight to shared memory (read-only during the kernel: L1 is fine);
+    //     issued before the tile is marked RUNNING -- they do not depend on what neighbours write
     {
       const unsigned s_mc = (unsigned)__cvta_generic_to_shared(S.mc + lane), s_pb = (unsigned)__cvta_generic_to_shared(S.pb + lane);
 #pragma unroll 8
@@ -794,41 +476,62 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
         const int cy = min(max(oy + r, 0), dim - 1);
         const size_t id = (size_t)cy * dim + cx;
         cp_async8(s_mc + r * SW_P * 8, p_mc + id);
-        cp_async8(s_pb + r * SW_P * 8, p_prox + id);
+        if (has_prox) cp_async8(s_pb + r * SW_P * 8, p_prox + id);
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    // (b) the cost plane (L2: other tiles write it), cell and fence bytes through registers
+#ifdef SW_DBG
+    const long long ta = clock64();
+#endif
+    if (lane == 0)
+    {
+      // reserve the pending counts of the activations this visit may make NOW, long before any of
+      // them can finish; the unused ones are returned at release, so HC_PENDING can never touch
+      // zero while work exists
+      atomicAdd(q.ctl + HC_PENDING, SW_RESERVE);
+      // acquire: whoever moved the state word before us (activation = release fence + CAS) has its
+      // cost-plane writes visible to the loads below; a writer that comes later sees RUNNING and
+      // marks the tile dirty.  One L2 round trip instead of a full fence.sc.
+      int old_state;  // not needed: the visit owns the tile whatever it was
+      asm volatile("atom.acquire.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old_state) : "l"(state + tile), "r"((int)T_RUNNING) : "memory");
+      (void)old_state;  // the visit owns the tile whatever the word held
+      (void)old_state;
+    }
+    __syncwarp();
+#ifdef SW_DBG
+    const long long tb = clock64();
+#endif
+    // (b) the cost plane (L2: other tiles write it) and the cell class bytes through registers
     const int r_lo = max(0, -oy), r_hi = min(32, dim - oy);  // staged rows inside the grid
     const unsigned vm = x_in ? ((r_hi >= 32 ? 0xFFFFFFFFu : ((1u << r_hi) - 1u)) & ~((1u << r_lo) - 1u)) : 0u;
     unsigned uc = 0, bc = 0;
-    for (int r0 = 0; r0 < 32; r0 += 16)
     {
-      double v_g[16];
-      uint8_t v_c[16], v_f[16];
+      double v_g[32];
+      uint8_t v_c[32];
 #pragma unroll
-      for (int j = 0; j < 16; ++j)
+      for (int r = 0; r < 32; ++r)
       {
-        const int cy = min(max(oy + r0 + j, 0), dim - 1);
+        const int cy = min(max(oy + r, 0), dim - 1);
         const size_t id = (size_t)cy * dim + cx;
-        v_g[j] = __ldcg(gp + id);
-        v_c[j] = __ldg(p_grid + id);
-        v_f[j] = __ldg(p_fence + id);
+        v_g[r] = __ldcg(gp + id);
+        v_c[r] = __ldg(p_cls + id);
       }
+      __syncwarp();  // keeps every load ahead of the first use: one memory round trip, not several
 #pragma unroll
-      for (int j = 0; j < 16; ++j)
+      for (int r = 0; r < 32; ++r)
       {
-        const int r = r0 + j;
-        const unsigned in = (vm >> r) & 1u;
-        const double gv = in ? v_g[j] : INFINITY;
+        const double gv = ((vm >> r) & 1u) ? v_g[r] : INFINITY;
         const int idx = r * SW_P + lane;
         S.g[idx] = gv;
         S.w[idx] = gv;
-        uc |= (v_c[j] == GA_UNKNOWN ? 1u : 0u) << r;                   // unknown_cost, a_star.cpp:253-254
-        bc |= ((v_c[j] == GA_OCC) | (v_f[j] == 1) ? 1u : 0u) << r;     // verifyNode, a_star.cpp:325-343
+        uc |= (unsigned)(v_c[r] & 1) << r;
+        bc |= (unsigned)((v_c[r] >> 1) & 1) << r;
       }
     }
     uc &= vm;
+#ifdef SW_DBG
+    const long long tc = clock64();
+#endif
     // blocked: off-grid, OCC / geofence, the halo ring (it belongs to the neighbour tiles), the root (keeps cost 0)
     bc |= ~vm | 0x80000001u | ((lane == 0 || lane == 31) ? 0xFFFFFFFFu : 0u);
     const int glx = goal % dim - ox, gly = goal / dim - oy;
@@ -844,20 +547,16 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
         if (lane == r) S.urow[r] = um;
       }
     }
-    // (c) static planes arrived: blocked cells get mc = +inf, prox becomes prox_cost (a_star.cpp:251)
+    // (c) static planes arrived: blocked cells get mc = +inf (off-grid cells hold clamped copies of
+    //     prox: harmless, they are blocked sources with g = +inf)
     asm volatile("cp.async.wait_all;" ::: "memory");
-    int has_prox = 0;
 #pragma unroll 8
     for (int r = 0; r < 32; ++r)
-    {
-      const int idx = r * SW_P + lane;
-      if ((bc >> r) & 1u) S.mc[idx] = INFINITY;
-      const double bv = ((vm >> r) & 1u) ? S.pb[idx] * w_prox : 0.0;
-      S.pb[idx] = bv;
-      has_prox |= (bv != 0.0);
-    }
-    has_prox = __any_sync(SW_FULL, has_prox);
+      if ((bc >> r) & 1u) S.mc[r * SW_P + lane] = INFINITY;
     __syncwarp();
+#ifdef SW_DBG
+    const long long td = clock64();
+#endif
     // first sweep: away from the side whose halo holds the smallest value (where the front comes from)
     int d0 = 0;
     {
@@ -877,13 +576,13 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     int any, n_sweeps = 0, n_act = 0, n_unused = 0;
     if (has_prox)
     {
-      if (unk_w != 0) any = sweep_tile_loop<true, true>(S, V, q, lane, d0, must_run, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
-      else any = sweep_tile_loop<true, false>(S, V, q, lane, d0, must_run, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
+      if (unk_w != 0) any = sweep_tile_loop<true, true>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
+      else any = sweep_tile_loop<true, false>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
     }
     else
     {
-      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
-      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
+      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
+      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
     }
     const long long t3 = clock64();
 
@@ -904,10 +603,17 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
       if (dec) atomicSub(q.ctl + HC_PENDING, dec);
       unsigned long long* cyc = reinterpret_cast<unsigned long long*>(q.ctl + HC_CYC);
       const long long t4 = clock64();
+#ifdef SW_DBG
+      atomicAdd(cyc + 0, (unsigned long long)(ta - t1));
+      atomicAdd(cyc + 1, (unsigned long long)(tb - ta));
+      atomicAdd(cyc + 2, (unsigned long long)(tc - tb));
+      atomicAdd(cyc + 3, (unsigned long long)(td - tc));
+#else
       atomicAdd(cyc + 0, (unsigned long long)(t1 - t0));
       atomicAdd(cyc + 1, (unsigned long long)(t2 - t1));
       atomicAdd(cyc + 2, (unsigned long long)(t3 - t2));
       atomicAdd(cyc + 3, (unsigned long long)(t4 - t3));
+#endif
     }
     __syncwarp();
   }
@@ -1011,7 +717,7 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     a.flags[n] = fl;
   }
   const int closed = __syncthreads_count(fl != 0);
-  if (threadIdx.x == 0 && closed) atomicAdd(a.ctl + HC_CLOSED, closed);
+  if (threadIdx.x == 0 && closed) atomicAdd(a.closed, closed);
   // chain walk inside the block
   int cur = threadIdx.x, cs = 0, cd = 0;
   for (int p = lpar; p >= 0; p = lp[cur])
@@ -1083,63 +789,119 @@ __global__ void __launch_bounds__(256) heur_finish_c_kernel(heur_args single, co
 void ga_heur_free(ga_ctx* c)
 {
   void** ptrs[] = { (void**)&c->d_tile_active, (void**)&c->d_hctl, (void**)&c->d_jump, (void**)&c->d_cnt,
-                    (void**)&c->d_hring };
+                    (void**)&c->d_hring, (void**)&c->d_hcls, (void**)&c->d_bring, (void**)&c->d_bdesc };
   for (void** p : ptrs)
   {
     if (*p) cudaFree(*p);
     *p = nullptr;
   }
+  c->bring_cap = c->bdesc_cap = 0;
+  if (c->ev_batch) cudaEventDestroy(c->ev_batch);
+  c->ev_batch = nullptr;
+}
+
+static unsigned ring_capacity(size_t n_tiles)
+{
+  unsigned cap = 64;
+  while (cap < 4u * (unsigned)n_tiles + 4096u) cap <<= 1;  // every tile at most once + one ticket per persistent worker
+  return cap;
 }
 
 int ga_heur_alloc(ga_ctx* c)
 {
   const size_t na = (size_t)c->astar_dim * c->astar_dim;
-  const char* impl = getenv("GA_HEUR_IMPL");  // development switch: "jacobi" = CTA-per-tile Jacobi kernel
-  c->heur_impl = (impl && !strcmp(impl, "jacobi")) ? 0 : 1;
-  const int edge = c->heur_impl ? SW_O : HT;
-  c->tiles_x = (c->astar_dim + edge - 1) / edge;
+  c->tiles_x = (c->astar_dim + SW_O - 1) / SW_O;
   c->n_tiles = c->tiles_x * c->tiles_x;
   GA_REQUIRE(c, c->n_tiles < (1 << 20), GA_ERR_ARG, "astar grid too large for the tile ring encoding");
-  unsigned cap = 64;
-  while (cap < 4u * (unsigned)c->n_tiles + 4096u) cap <<= 1;  // + one ticket per persistent worker
-  c->hring_cap = (int)cap;
-  GA_CUDA(c, cudaMalloc(&c->d_tile_active, sizeof(int) * (size_t)c->n_tiles));  // per-tile state words
-  GA_CUDA(c, cudaMalloc(&c->d_hring, sizeof(int) * (size_t)cap));
-  GA_CUDA(c, cudaMemsetAsync(c->d_hring, 0, sizeof(int) * (size_t)cap, c->stream));
+  c->hring_cap = (int)ring_capacity((size_t)c->n_tiles);
+  // per-tile state words + prox stamps (stamp == build epoch: the tile's block carries a prox cost)
+  GA_CUDA(c, cudaMalloc(&c->d_tile_active, sizeof(int) * 2 * (size_t)c->n_tiles));
+  GA_CUDA(c, cudaMemsetAsync(c->d_tile_active, 0, sizeof(int) * 2 * (size_t)c->n_tiles, c->stream));
+  c->heur_epoch = 0;
+  GA_CUDA(c, cudaMalloc(&c->d_hring, sizeof(int) * (size_t)c->hring_cap));
+  GA_CUDA(c, cudaMemsetAsync(c->d_hring, 0, sizeof(int) * (size_t)c->hring_cap, c->stream));
   GA_CUDA(c, cudaMalloc(&c->d_hctl, sizeof(int) * HC_WORDS));
   GA_CUDA(c, cudaMemsetAsync(c->d_hctl, 0, sizeof(int) * HC_WORDS, c->stream));
-  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * 2 * na));
-  GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 4 * na));
-  int per_sm = 0;
-  GA_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, heur_relax_kernel, H_THREADS, 0));
-  GA_REQUIRE(c, per_sm >= 1, GA_ERR_CUDA, "heuristic relax kernel does not fit an SM");
-  c->relax_grid = per_sm * c->sm_count;
-  if (c->heur_impl)
-  {
-    GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(SW_WARPS * sizeof(sweep_tile))));
-    c->relax_grid = c->sm_count;
-  }
+  GA_CUDA(c, cudaMalloc(&c->d_hcls, na));
+  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * na));
+  GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS * sizeof(sweep_tile))));
+  // development knobs (read once per patch): workers per SM, idle back-off, early publication
+  c->sw_warps = SW_WARPS;
+  c->sw_poll_ns = 20;
+  c->sw_early = 1;
+  if (const char* s = getenv("GA_SW_WARPS")) c->sw_warps = atoi(s) >= 1 && atoi(s) <= SW_WARPS ? atoi(s) : SW_WARPS;
+  if (const char* s = getenv("GA_POLL_NS")) c->sw_poll_ns = atoi(s);
+  if (const char* s = getenv("GA_SW_EARLY")) c->sw_early = atoi(s);
   return GA_OK;
 }
 
-static heur_grid make_grid_desc(ga_ctx* c, int slot, int goal_x, int goal_y)
+static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed, heur_grid* G, heur_args* a)
 {
-  heur_grid G;
-  G.grid = c->d_astar;
-  G.fence = c->d_fence;
-  G.mc = c->d_mc;
-  G.prox = c->d_prox;
-  G.g = c->d_hcost[slot];
-  G.state = c->d_tile_active;
-  G.dim = c->astar_dim;
-  G.tiles_x = c->tiles_x;
-  G.n_tiles = c->n_tiles;
-  G.edge = c->heur_impl ? SW_O : HT;
-  G.goal = goal_y * c->astar_dim + goal_x;
-  G.w_prox = c->ap.astar_prox_cost;
-  G.unk_w = c->ap.unknown_cost_w;
-  return G;
+  ++c->heur_epoch;
+  G->grid = c->d_astar;
+  G->fence = c->d_fence;
+  G->mc = c->d_mc;
+  G->prox = c->d_prox;
+  G->g = c->d_hcost[slot];
+  G->cls = c->d_hcls;
+  G->state = c->d_tile_active;
+  G->tprox = c->d_tile_active + c->n_tiles;
+  G->epoch = c->heur_epoch;
+  G->dim = c->astar_dim;
+  G->tiles_x = c->tiles_x;
+  G->n_tiles = c->n_tiles;
+  G->edge = SW_O;
+  G->goal = goal_y * c->astar_dim + goal_x;
+  G->w_prox = c->ap.astar_prox_cost;
+  G->unk_w = c->ap.unknown_cost_w;
+  a->grid = c->d_astar;
+  a->mc = c->d_mc;
+  a->prox = c->d_prox;
+  a->g = c->d_hcost[slot];
+  a->parent = c->d_hparent[slot];
+  a->dist = c->d_hdist[slot];
+  a->flags = c->d_hflags[slot];
+  a->closed = closed;
+  a->scratch = reinterpret_cast<unsigned*>(c->d_jump);
+  a->tot = reinterpret_cast<int2*>(c->d_cnt);
+  a->dim = c->astar_dim;
+  a->goal = G->goal;
+  a->w_prox = G->w_prox;
+  a->unk_w = G->unk_w;
+  // movement_distances_ (a_star.hpp:54-57): ASTAR_RES and ASTAR_RES * sqrt(2)
+  a->L1 = 0.625;
+  a->L2 = 0.625 * sqrt(2.0);
+}
+
+// init -> sweep relaxation -> finish A/B/C for n grids (descriptors in device memory when n > 1)
+static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& a0, const heur_grid* dG, const heur_args* dA,
+                        const heur_queue& q, int max_dim, size_t total_tiles)
+{
+  GA_CUDA(c, cudaMemsetAsync(q.ctl, 0, sizeof(int) * HC_WORDS, c->stream));  // ring cursors, pending count, statistics
+  {
+    ga_launch_scope ls(c, GA_K_HEUR_INIT);
+    heur_init_kernel<<<dim3(c->sm_count * 4 / (n > 4 ? 4 : 1), n), 256, 0, c->stream>>>(G0, dG, q);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  {
+    ga_launch_scope ls(c, GA_K_HEUR_RELAX);
+    const int nw = c->sw_warps;
+    const size_t want = (total_tiles + nw - 1) / nw;
+    const int g = (size_t)c->sm_count < want ? c->sm_count : (int)want;
+    heur_sweep_kernel<<<g, nw * 32, nw * sizeof(sweep_tile), c->stream>>>(G0, dG, q);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  {
+    ga_launch_scope ls(c, GA_K_HEUR_FINISH);
+    const int nb = (max_dim + FB - 1) / FB, cells = (max_dim * max_dim + 255) / 256;
+    heur_finish_a_kernel<<<dim3(nb * nb, n), FB * FB, 0, c->stream>>>(a0, dA);
+    heur_finish_b_kernel<<<dim3(cells, n), 256, 0, c->stream>>>(a0, dA);
+    heur_finish_c_kernel<<<dim3(cells, n), 256, 0, c->stream>>>(a0, dA);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  return GA_OK;
 }
 
 extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, int* n_closed)
@@ -1151,69 +913,104 @@ extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, i
   GA_REQUIRE(c, goal_x >= 0 && goal_y >= 0 && goal_x < dim && goal_y < dim, GA_ERR_ARG, "goal outside the astar grid");
   GA_CUDA(c, cudaSetDevice(c->device));
 
-  const heur_grid G = make_grid_desc(c, slot, goal_x, goal_y);
+  heur_grid G;
+  heur_args a;
+  make_descs(c, slot, goal_x, goal_y, c->d_hctl + HC_CLOSED, &G, &a);
   heur_queue q;
   q.ring = c->d_hring;
   q.mask = (unsigned)c->hring_cap - 1;
   q.ctl = c->d_hctl;
-  q.poll_ns = 20;
-  q.early = 1;
-  if (const char* s = getenv("GA_SW_EARLY")) q.early = (unsigned)atoi(s);
-  if (const char* s = getenv("GA_POLL_NS")) q.poll_ns = (unsigned)atoi(s);
-  {
-    ga_launch_scope ls(c, GA_K_HEUR_INIT);
-    heur_init_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(G, q, 0, 1);
-  }
-  GA_CUDA(c, cudaGetLastError());
-  {
-    ga_launch_scope ls(c, GA_K_HEUR_RELAX);
-    if (c->heur_impl)
-    {
-      int nw = SW_WARPS;
-      if (const char* s = getenv("GA_SW_WARPS")) nw = atoi(s);
-      const int want = (c->n_tiles + nw - 1) / nw;
-      int g = c->relax_grid < want ? c->relax_grid : want;
-      if (const char* s = getenv("GA_SW_CTAS")) g = atoi(s);
-      heur_sweep_kernel<<<g, nw * 32, nw * sizeof(sweep_tile), c->stream>>>(G, nullptr, q);
-    }
-    else
-    {
-      const int g = c->relax_grid < c->n_tiles ? c->relax_grid : c->n_tiles;
-      heur_relax_kernel<<<g, H_THREADS, 0, c->stream>>>(G, nullptr, q);
-    }
-  }
-  GA_CUDA(c, cudaGetLastError());
-
-  heur_args a;
-  a.grid = c->d_astar;
-  a.mc = c->d_mc;
-  a.prox = c->d_prox;
-  a.g = c->d_hcost[slot];
-  a.parent = c->d_hparent[slot];
-  a.dist = c->d_hdist[slot];
-  a.flags = c->d_hflags[slot];
-  a.ctl = c->d_hctl;
-  a.scratch = reinterpret_cast<unsigned*>(c->d_jump);
-  a.tot = reinterpret_cast<int2*>(c->d_cnt);
-  a.dim = dim;
-  a.goal = G.goal;
-  a.w_prox = G.w_prox;
-  a.unk_w = G.unk_w;
-  // movement_distances_ (a_star.hpp:54-57): ASTAR_RES and ASTAR_RES * sqrt(2)
-  a.L1 = 0.625;
-  a.L2 = 0.625 * sqrt(2.0);
-  {
-    ga_launch_scope ls(c, GA_K_HEUR_FINISH);
-    const int nb = (dim + FB - 1) / FB, cells = (dim * dim + 255) / 256;
-    heur_finish_a_kernel<<<nb * nb, FB * FB, 0, c->stream>>>(a, nullptr);
-    heur_finish_b_kernel<<<cells, 256, 0, c->stream>>>(a, nullptr);
-    heur_finish_c_kernel<<<cells, 256, 0, c->stream>>>(a, nullptr);
-  }
-  GA_CUDA(c, cudaGetLastError());
+  q.poll_ns = (unsigned)c->sw_poll_ns;
+  q.early = (unsigned)c->sw_early;
+  const int rc = launch_build(c, 1, G, a, nullptr, nullptr, q, dim, (size_t)c->n_tiles);
+  if (rc != GA_OK) return rc;
   if (n_closed)
   {
     GA_CUDA(c, cudaMemcpyAsync(n_closed, c->d_hctl + HC_CLOSED, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return GA_OK;
+}
+
+// n independent grids (one context each, same device) as ONE launch chain on the first context's
+// stream: the wavefronts of all grids share the ticket ring and fill the SMs together.
+extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, const int* goal_xy, int* n_closed)
+{
+  if (!ctxs || n < 1 || !ctxs[0]) return GA_ERR_ARG;
+  ga_ctx* c = ctxs[0];
+  GA_REQUIRE(c, goal_xy != nullptr, GA_ERR_ARG, "goal_xy is NULL");
+  GA_REQUIRE(c, slot == 0 || slot == 1, GA_ERR_ARG, "slot must be 0 (guidance) or 1 (path)");
+  GA_REQUIRE(c, n <= 2047, GA_ERR_ARG, "at most 2047 grids per batch (ring entry encoding)");
+  size_t total_tiles = 0;
+  int max_dim = 0;
+  for (int i = 0; i < n; ++i)
+  {
+    ga_ctx* k = ctxs[i];
+    GA_REQUIRE(c, k != nullptr, GA_ERR_ARG, "NULL context in the batch");
+    GA_REQUIRE(c, k->device == c->device, GA_ERR_ARG, "all contexts of a batch must live on one device");
+    GA_REQUIRE(c, k->patch_dim > 0 && k->have_ap, GA_ERR_STATE, "a context of the batch has no patch / params");
+    for (int j = 0; j < i; ++j) GA_REQUIRE(c, ctxs[j] != k, GA_ERR_ARG, "a context appears twice in the batch");
+    const int gx = goal_xy[2 * i], gy = goal_xy[2 * i + 1];
+    GA_REQUIRE(c, gx >= 0 && gy >= 0 && gx < k->astar_dim && gy < k->astar_dim, GA_ERR_ARG, "goal outside the astar grid");
+    total_tiles += (size_t)k->n_tiles;
+    max_dim = k->astar_dim > max_dim ? k->astar_dim : max_dim;
+  }
+  GA_CUDA(c, cudaSetDevice(c->device));
+  // batch scratch on the leading context: ring for all tiles, descriptors, closed counters
+  const unsigned cap = ring_capacity(total_tiles);
+  if ((int)cap > c->bring_cap)
+  {
+    if (c->d_bring) GA_CUDA(c, cudaFree(c->d_bring));
+    c->d_bring = nullptr;
+    GA_CUDA(c, cudaMalloc(&c->d_bring, sizeof(int) * (size_t)cap));
+    GA_CUDA(c, cudaMemsetAsync(c->d_bring, 0, sizeof(int) * (size_t)cap, c->stream));
+    c->bring_cap = (int)cap;
+  }
+  const size_t desc_bytes = (size_t)n * (sizeof(heur_grid) + sizeof(heur_args) + sizeof(int));
+  if (desc_bytes > c->bdesc_cap)
+  {
+    if (c->d_bdesc) GA_CUDA(c, cudaFree(c->d_bdesc));
+    c->d_bdesc = nullptr;
+    GA_CUDA(c, cudaMalloc(&c->d_bdesc, desc_bytes));
+    c->bdesc_cap = desc_bytes;
+  }
+  heur_grid* dG = reinterpret_cast<heur_grid*>(c->d_bdesc);
+  heur_args* dA = reinterpret_cast<heur_args*>(dG + n);
+  int* dClosed = reinterpret_cast<int*>(dA + n);
+  std::vector<heur_grid> hG((size_t)n);
+  std::vector<heur_args> hA((size_t)n);
+  for (int i = 0; i < n; ++i) make_descs(ctxs[i], slot, goal_xy[2 * i], goal_xy[2 * i + 1], dClosed + i, &hG[i], &hA[i]);
+  // order the leading stream after whatever the other contexts still have in flight
+  for (int i = 1; i < n; ++i)
+  {
+    ga_ctx* k = ctxs[i];
+    if (!k->ev_batch) GA_CUDA(c, cudaEventCreateWithFlags(&k->ev_batch, cudaEventDisableTiming));
+    GA_CUDA(c, cudaEventRecord(k->ev_batch, k->stream));
+    GA_CUDA(c, cudaStreamWaitEvent(c->stream, k->ev_batch, 0));
+  }
+  GA_CUDA(c, cudaMemcpyAsync(dG, hG.data(), sizeof(heur_grid) * n, cudaMemcpyHostToDevice, c->stream));
+  GA_CUDA(c, cudaMemcpyAsync(dA, hA.data(), sizeof(heur_args) * n, cudaMemcpyHostToDevice, c->stream));
+  GA_CUDA(c, cudaMemsetAsync(dClosed, 0, sizeof(int) * n, c->stream));
+  heur_queue q;
+  q.ring = c->d_bring;
+  q.mask = cap - 1;
+  q.ctl = c->d_hctl;
+  q.poll_ns = (unsigned)c->sw_poll_ns;
+  q.early = (unsigned)c->sw_early;
+  const int rc = launch_build(c, n, hG[0], hA[0], dG, dA, q, max_dim, total_tiles);
+  if (rc != GA_OK) return rc;
+  // the other contexts' streams continue after the batch
+  if (!c->ev_batch) GA_CUDA(c, cudaEventCreateWithFlags(&c->ev_batch, cudaEventDisableTiming));
+  GA_CUDA(c, cudaEventRecord(c->ev_batch, c->stream));
+  for (int i = 1; i < n; ++i) GA_CUDA(c, cudaStreamWaitEvent(ctxs[i]->stream, c->ev_batch, 0));
+  if (n_closed)
+  {
+    GA_CUDA(c, cudaMemcpyAsync(n_closed, dClosed, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+    GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  else
+  {
+    // hG / hA are pageable host vectors: the copies above have been staged, nothing else to keep alive
   }
   return GA_OK;
 }

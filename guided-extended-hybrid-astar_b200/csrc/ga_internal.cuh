@@ -16,7 +16,6 @@
 #define GA_MAX_DISKS 16
 #define GA_MAX_STEER 31
 #define GA_MAX_RA 16       // rear-axis deltas per node
-#define GA_HEUR_TILE 32    // heuristic tile edge (cells)
 
 struct ga_se  // structuring element, passed to kernels by value
 {
@@ -78,11 +77,16 @@ struct ga_ctx
   int* d_hctl = nullptr;          // control words (ring cursors, counters)
   int* d_hring = nullptr;         // ring buffer of activated tiles
   int hring_cap = 0;              // power of two >= n_tiles
-  int32_t* d_jump = nullptr;      // pointer-jumping scratch: 2 * ncell
-  int32_t* d_cnt = nullptr;       // (n_straight, n_diag) pairs: 2 * 2 * ncell
-  int heur_impl = 1;              // 1 = warp-per-tile sweep kernel, 0 = CTA-per-tile Jacobi kernel
-  int relax_grid = 0;             // persistent CTAs of the relax kernel
-  int finish_grid = 0;            // same for the finish kernel
+  uint8_t* d_hcls = nullptr;      // per-cell class byte of the current build (bit0 UNKNOWN, bit1 blocked)
+  int32_t* d_jump = nullptr;      // finish scratch: block-local (terminal, steps) per cell
+  int32_t* d_cnt = nullptr;       // finish scratch: (n_straight, n_diag) of terminal cells to the root
+  int heur_epoch = 0;             // build counter (stamps the per-tile prox flags)
+  int sw_warps = 6, sw_poll_ns = 20, sw_early = 1;  // sweep kernel knobs (GA_SW_WARPS / GA_POLL_NS / GA_SW_EARLY)
+  int* d_bring = nullptr;         // batch ring (leading context of ga_build_heuristic_batch)
+  int bring_cap = 0;
+  void* d_bdesc = nullptr;        // batch descriptors + closed counters
+  size_t bdesc_cap = 0;
+  cudaEvent_t ev_batch = nullptr; // stream ordering between the contexts of a batch
 
   // ---- staging (pinned host + device) for pose batches
   void* h_stage = nullptr;

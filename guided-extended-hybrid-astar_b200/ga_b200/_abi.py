@@ -78,6 +78,7 @@ SYMBOLS = {
     "ga_expand": (C.c_int, [_P, _P, C.c_int, _P]),
     "ga_set_astar_params": (C.c_int, [_P, C.POINTER(AstarParams)]),
     "ga_build_heuristic": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
+    "ga_build_heuristic_batch": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "ga_potential_sites": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.POINTER(C.c_int)]),
     "ga_build_potential": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.POINTER(C.c_int)]),
     "ga_upload": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),

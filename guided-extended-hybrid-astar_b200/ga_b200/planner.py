@@ -427,6 +427,22 @@ class AStar:
         self.closed_sets_[slot] = None
         return n.value
 
+    @staticmethod
+    def calcDistanceHeuristicBatch(astars, goals, for_path=True):
+        """calcDistanceHeuristic for a batch of independent planners (one AStar / context each, same
+        device) as one kernel chain (ga_build_heuristic_batch); returns the closed-cell counts."""
+        slot = 1 if for_path else 0
+        n = len(astars)
+        hs = (C.c_void_p * n)(*[a.ctx.h for a in astars])
+        g = np.ascontiguousarray(goals, np.int32).reshape(n, 2)
+        out = np.zeros(n, np.int32)
+        lead = astars[0].ctx
+        lead.check(lead.lib.ga_build_heuristic_batch(hs, n, slot, g.ctypes.data_as(C.POINTER(C.c_int)),
+                                                     out.ctypes.data_as(C.POINTER(C.c_int))))
+        for a in astars:
+            a.closed_sets_[slot] = None
+        return out
+
     def _closed(self, slot):
         if self.closed_sets_[slot] is None:
             d = self.ctx.download

@@ -205,6 +205,16 @@ GA_API int ga_set_astar_params(ga_ctx* ctx, const ga_astar_params* p);
  * receives the number of reachable cells. */
 GA_API int ga_build_heuristic(ga_ctx* ctx, int slot, int goal_x, int goal_y, int* n_closed);
 
+/* The same for n independent queries at once (BASELINE config 5: batches of start/goal queries,
+ * one heuristic grid per query; the reference needs one process per planner for this because all
+ * of AStar's state is static, a_star.hpp:65-134).  ctxs[i] = the i-th query's context (all on one
+ * device, each at most once), goal_xy[2i], goal_xy[2i+1] its goal cell, n_closed[i] (array of n,
+ * may be NULL; forces a sync otherwise) its reachable-cell count.  All grids are relaxed by ONE
+ * kernel chain on ctxs[0]'s stream -- their wavefronts share the worker warps of the GPU -- and
+ * every other context's stream is ordered before and after it, so later calls on any of the
+ * contexts see the finished planes.  Errors are reported on ctxs[0]. */
+GA_API int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, const int* goal_xy, int* n_closed);
+
 /* AStar::calcVoronoiPotentialField (a_star.cpp:440-479) around ego (astar cells): two chamfer
  * distance transforms (createDistanceTransform :426-433) + setCostmapValue (:486-508).  The
  * Fortune sweep (deps_lib/VoronoiDiagramGenerator.cpp, serial fp64 geometry) stays on the host:
@@ -249,8 +259,8 @@ GA_API int ga_prof_reset(ga_ctx* ctx);
 /* total device milliseconds and launches of kernel k since the last reset (syncs the stream) */
 GA_API int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches);
 /* work counters of the last ga_build_heuristic on this context: out7 = { tile visits, inner
- * relaxation iterations summed over visits, visits that improved a cell, SM cycles summed over
- * visits spent waiting for a tile / staging / relaxing / writing back } (syncs the stream) */
+ * line sweeps summed over visits, visits that improved a cell, SM cycles summed over
+ * visits spent waiting for a tile / staging / sweeping / publishing } (syncs the stream) */
 GA_API int ga_heur_stats(ga_ctx* ctx, long long* out7);
 /* launches of ALL library kernels since ga_create / ga_prof_reset (always counted) */
 GA_API long long ga_launch_count(const ga_ctx* ctx);

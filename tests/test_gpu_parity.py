@@ -236,6 +236,48 @@ def test_heuristic_fixed_point(planner, oracle, dim, seed, with_prox, unk_w):
     assert (xs[-1], ys[-1]) == (goal[0], goal[1])
 
 
+def test_heuristic_batch_matches_oracle(oracle):
+    """ga_build_heuristic_batch: independent grids of different sizes relaxed by one kernel chain are
+    bit-identical to the oracle's fixed point of each grid (and so to the one-by-one builds)."""
+    import ga_oracle_py as go
+    cases = [(512, 11, False, 0.0), (1000, 12, True, 0.0), (333, 13, True, 2.5), (2048, 14, False, 0.0), (640, 15, True, 0.0)]
+    ctxs, astars, goals, wants = [], [], [], []
+    try:
+        for dim, seed, with_prox, unk_w in cases:
+            ctx = ga_b200.GridContext(0)
+            ctxs.append(ctx)
+            cfg = ga_b200.LibConfig()
+            cfg.ASTAR_UNKNOWN_COST = unk_w
+            astar = ga_b200.AStar(ctx, cfg)
+            cc = ga_b200.CollisionChecker(ctx, ga_b200.Vehicle.from_config(ga_b200.VehConfig()), cfg)
+            cc.initialize(dim)
+            ctx.upload(_abi.GRID_PATCH, ga_b200.gen_map(dim, seed))
+            cc.processSafetyPatch()
+            rng = np.random.default_rng(seed)
+            grid, mc, prox, fence = _heur_inputs(astar, ctx, rng, with_prox)
+            goal = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, seed)[0]
+            hp = go.HeurParams(astar.astar_dim_, 5.0, 3.0, unk_w, 0, 0, 0)
+            wants.append(oracle.heuristic_fixedpoint(hp, grid, fence, mc, prox, goal))
+            astars.append(astar)
+            goals.append(goal)
+        for rep in range(2):  # twice: the epoch-stamped tile flags and the ring must be reusable
+            n = ga_b200.AStar.calcDistanceHeuristicBatch(astars, goals, for_path=bool(rep))
+            for i, (astar, want) in enumerate(zip(astars, wants)):
+                cs = astar.closed_set_path_ if rep else astar.closed_set_guidance_
+                assert n[i] == want["n_closed"] == cs.size()
+                assert np.array_equal(cs.cost, want["cost"])
+                assert np.array_equal(cs.parent, want["parent"])
+                assert np.array_equal(cs.flags, want["flags"])
+                m = want["flags"] & 1 > 0
+                assert np.array_equal(cs.dist[m], want["dist"][m])
+        # a single build on one of the contexts afterwards still works (own ring, own counters)
+        assert astars[1].calcDistanceHeuristic(goals[1], None, for_path=False) == wants[1]["n_closed"]
+        assert np.array_equal(astars[1].closed_set_guidance_.cost, wants[1]["cost"])
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 @pytest.mark.parametrize("with_prox", [False, True])
 def test_heuristic_vs_reference_order(planner, oracle, with_prox):
     """against the reference's own pop order (early exit off): the fixed point closes every cell the
