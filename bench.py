@@ -35,6 +35,9 @@ METRIC = "heuristic_grid_mcells_per_s"
 UNIT = "Mcells/s"
 BYTES_PER_CELL_HEUR = 39.0   # read 1+1+8+8, write 8+8+4+1 per astar cell
 BYTES_PER_CELL_SAFETY = 2.0 + 1.0 / 16
+# dram__bytes_read.sum + dram__bytes_write.sum of one heur_sweep_kernel launch on the 1024^2 grid of
+# this workload, from the `ncu --set full` capture summarised in profiles/ (None until captured)
+NCU_TRAFFIC_BYTES = None
 
 
 def load_peaks():
@@ -46,14 +49,42 @@ def load_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line):
+    NVML every 2 ms when nvidia_ml_py is importable, the nvidia-smi query otherwise."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
-        self.max_mhz = None
+        self.max_mhz, self.active = None, False
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
 
-    def run(self):
+    def _nvml(self):
+        nv = self.nv
+        bits = ((nv.nvmlClocksThrottleReasonHwSlowdown, "hw_slowdown"),
+                (nv.nvmlClocksThrottleReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                (nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_thermal_slowdown"),
+                (nv.nvmlClocksThrottleReasonSwPowerCap, "sw_power_cap"))
+        while not self.stop_flag:
+            if self.active:
+                try:
+                    self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for bit, name in bits:
+                        if r & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(0.002)
+
+    def _smi(self):
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -62,19 +93,23 @@ class ClockSampler(threading.Thread):
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
                 f = [v.strip() for v in out.strip().split(",")]
-                self.samples.append(float(f[0]))
+                if self.active:
+                    self.samples.append(float(f[0]))
                 self.max_mhz = float(f[1])
                 for n, v in zip(names, f[2:]):
-                    if v.lower().startswith("active"):
+                    if self.active and v.lower().startswith("active"):
                         self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.02)
+
+    def run(self):
+        (self._nvml if self.nv else self._smi)()
 
     def result(self):
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "source": "nvml" if self.nv else "nvidia-smi"}
 
 
 def make_env(ga, device, seed, torch):
@@ -116,63 +151,167 @@ def step_e2e(env):
         ctx.check(lib.ga_download(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
 
 
-def cpu_reference_step(patch, goal, disk_r_c, use_ref):
-    """one step of the same workload on the host cores; returns (seconds, cells closed, kind)"""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+def _ref_goal(patch):
     import ga_oracle_py as go
-    t0 = time.perf_counter()
-    safety = go.process_safety_patch(patch, 100, 130, disk_r_c)
-    grid = go.pool_max(safety)
-    dim = grid.shape[0]
-    hp = go.HeurParams(dim, 5.0, 3.0, 0.0, 0, 10000, 0)  # early exit off: the whole reachable grid, as the GPU builds
-    mc = np.full((dim, dim), 5.0)
-    prox = np.zeros((dim, dim))
-    fence = np.zeros((dim, dim), np.uint8)
-    res = go.heuristic_reforder(hp, grid, fence, mc, prox, goal, goal)
-    return time.perf_counter() - t0, res["n_closed"], "port"
+    thr = go.threshold(patch, 100, 130)
+    free = np.argwhere(thr[::4, ::4] == 0)
+    return int(free[len(free) // 2][1]), int(free[len(free) // 2][0])
+
+
+def cpu_reference_steps(dim, seeds, disk_r_c):
+    """the same step on the host cores, one thread (the reference keeps all planner state in static
+    members: one planner per process).  oracle/_ref (the reference's own translation units) when it
+    was built, else the plain-C oracle port.  Returns (seconds, cells closed, kind)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ga_b200
+    import ga_oracle_py as go
+    import ga_ref_py as gr
+    total, cells = 0.0, 0
+    if gr.available():
+        gr.init(dim)
+        gr.set_heuristic_config(early_exit=False, max_extra_nodes=1 << 30, unknown_cost_w=0.0)  # whole reachable grid, as the GPU builds
+        L = gr.lib()
+        for seed in seeds:
+            patch = ga_b200.gen_map(dim, seed)
+            goal = _ref_goal(patch)
+            t0 = time.perf_counter()
+            gr.set_grid(gr.PATCH, patch)       # CollisionChecker::patch_arr_
+            gr.process_safety_patch()          # collision_checking.cpp:193-224
+            gr.calc_astar_grid()               # a_star.cpp:536-542 (CPU max in place of cuDNN)
+            n = L.gar_calc_distance_heuristic(goal[0], goal[1], goal[0], goal[1], 0, 0)  # a_star.cpp:110-295
+            total += time.perf_counter() - t0
+            cells += n
+        return total, cells, "reference"
+    for seed in seeds:
+        patch = ga_b200.gen_map(dim, seed)
+        goal = _ref_goal(patch)
+        t0 = time.perf_counter()
+        safety = go.process_safety_patch(patch, 100, 130, disk_r_c)
+        grid = go.pool_max(safety)
+        ad = grid.shape[0]
+        hp = go.HeurParams(ad, 5.0, 3.0, 0.0, 0, 1 << 30, 0)
+        res = go.heuristic_reforder(hp, grid, np.zeros((ad, ad), np.uint8), np.full((ad, ad), 5.0), np.zeros((ad, ad)), goal, goal)
+        total += time.perf_counter() - t0
+        cells += res["n_closed"]
+    return total, cells, "port"
+
+
+def _ref_worker(a):
+    dim, seeds, r_c = a
+    return cpu_reference_steps(dim, seeds, r_c)  # (seconds inside the reference's calls, cells, kind)
 
 
 def run_reference(args, rank):
+    """--impl reference: the reference's own CPU implementation of the step, one planner process per
+    host core (its only way to use more than one core), each step = cores x one 2048^2 sample."""
     if rank != 0:
         return
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import multiprocessing as mp
     import ga_b200
     dim = args.ref_dim
+    if dim <= 0:
+        # bounded sample: the whole --steps/--warmup run stays within ~2 minutes of host time
+        budget = 120.0 / (args.steps + args.warmup)
+        dim = 2048 if budget >= 0.9 else 1024 if budget >= 0.25 else 512
     veh = ga_b200.Vehicle.from_config(ga_b200.VehConfig())
     _, _, r_c, _ = ga_b200.calc_disks(veh, ga_b200.LibConfig())
-    times, cells = [], 0
-    kind = "port"
-    for i in range(args.warmup + args.steps):
-        patch = ga_b200.gen_map(dim, 20240 + i % N_ROT)
-        import ga_oracle_py as go
-        thr = go.threshold(patch, 100, 130)
-        free = np.argwhere(thr[::4, ::4] == 0)
-        goal = (int(free[len(free) // 2][1]), int(free[len(free) // 2][0]))
-        dt, n, kind = cpu_reference_step(patch, goal, r_c, False)
-        if i >= args.warmup:
-            times.append(dt)
+    cores = max(1, min(len(os.sched_getaffinity(0)), args.ref_procs))
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(cores) as pool:
+        def one_step(i):
+            # the processes run concurrently; the step lasts as long as the slowest planner's calls
+            # (map generation and process start-up are not the reference's work and stay outside)
+            out = pool.map(_ref_worker, [(dim, [20240 + (i * cores + w) % 64], r_c) for w in range(cores)])
+            return max(o[0] for o in out), sum(o[1] for o in out), out[0][2]
+        for i in range(args.warmup):
+            one_step(i)
+        total, cells, kind = 0.0, 0, "port"
+        for i in range(args.steps):
+            dt, n, kind = one_step(args.warmup + i)
+            total += dt
             cells += n
-    total = sum(times)
     val = cells / total / 1e6
+    sample = "%d step(s); one step = %d planner processes x (threshold + dilate + pool + heuristic) on a %dx%d patch" % (
+        args.steps, cores, dim, dim)
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic-4096", "patch_dim": PATCH_DIM, "astar_dim": PATCH_DIM // 4,
                        "sample_patch_dim": dim},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind,
-                             "sample": "%d step(s) of the same pipeline on a %dx%d patch (seeded like the GPU arm)" % (args.steps, dim, dim)},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak):
+    """BASELINE config 5's shape on one GPU: a batch of independent queries on 2048^2 maps (64 queries
+    share a map), one heuristic grid per query, all grids relaxed by ONE kernel chain
+    (ga_build_heuristic_batch).  Reports grids/s, Mcells/s and the algorithmic-bytes rate."""
+    from ga_b200 import _abi
+    nq, dim = args.batch, 2048
+    maps = {}
+    ctxs, astars, goals = [], [], []
+    for qi in range(nq):
+        seed = 50000 + rank * 1000 + qi // 64
+        if seed not in maps:
+            maps[seed] = ga.gen_map(dim, seed)
+        ctx = ga.GridContext(device)
+        cfg = ga.LibConfig()
+        astar = ga.AStar(ctx, cfg)
+        cc = ga.CollisionChecker(ctx, ga.Vehicle.from_config(ga.VehConfig()), cfg)
+        cc.initialize(dim)
+        ctx.upload(_abi.GRID_PATCH, maps[seed])
+        cc.processSafetyPatch()
+        if qi % 64 == 0:
+            grid = astar.astar_grid_
+            free = ga.sample_free_cells(grid, 64, seed + 1)
+        ctxs.append(ctx)
+        astars.append(astar)
+        goals.append(free[qi % 64])
+    closed = ga.AStar.calcDistanceHeuristicBatch(astars, goals, for_path=False)
+    lead = ctxs[0]
+    hs = (C.c_void_p * nq)(*[c.h for c in ctxs])
+    g = np.ascontiguousarray(goals, np.int32).reshape(nq, 2)
+    gp = g.ctypes.data_as(C.POINTER(C.c_int))
+    reps = max(3, min(20, args.steps // 10))
+    for _ in range(2):
+        lead.check(lead.lib.ga_build_heuristic_batch(hs, nq, 0, gp, None))
+    lead.sync()
+    lead.prof_reset()
+    lead.prof_enable(True)
+    s = torch.cuda.ExternalStream(lead.stream())
+    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.active = True
+    a.record(s)
+    for _ in range(reps):
+        lead.check(lead.lib.ga_build_heuristic_batch(hs, nq, 0, gp, None))
+    b_.record(s)
+    lead.sync()
+    sampler.active = False
+    lead.prof_enable(False)
+    ms = a.elapsed_time(b_) / reps
+    relax_ms = lead.prof_get(_abi.K_HEUR_RELAX)[0] / reps
+    adim = dim // 4
+    alg = BYTES_PER_CELL_HEUR * adim * adim * nq
+    out = {"workload": "%d queries on 2048x2048 maps (64 per map), one 512x512 heuristic grid each, one kernel chain" % nq,
+           "grids_per_s": nq / (ms * 1e-3), "mcells_per_s": float(closed.sum()) / (ms * 1e-3) / 1e6, "ms_per_batch": ms,
+           "sweep_kernel_ms": relax_ms, "sweep_kernel_algorithmic_gbs": alg / (relax_ms * 1e-3) / 1e9,
+           "sweep_kernel_roofline_frac": alg / (relax_ms * 1e-3) / 1e9 / hbm_peak}
+    for c in ctxs:
+        c.close()
+    return out
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ref-dim", type=int, default=2048, help="patch size of the bounded CPU sample (reference arm)")
+    ap.add_argument("--ref-dim", type=int, default=0, help="patch size of the bounded CPU sample (reference arm); 0 = from --steps")
+    ap.add_argument("--ref-procs", type=int, default=64, help="planner processes of the reference arm (capped by the host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch", type=int, default=32, help="queries of the batched-heuristic leg (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -222,6 +361,7 @@ def main():
                 e["ctx"].prof_reset()
                 e["ctx"].prof_enable(True)
         launches0 = sum(e["ctx"].launch_count() for e in envs)
+        sampler.active = True
         t0 = time.perf_counter()
         # steps run back to back on the device: step i+1's stream waits for step i's end event, so the
         # span first-start .. last-end is exactly K serialised steps without any host synchronisation
@@ -239,6 +379,7 @@ def main():
             last.record(s)
         barrier()
         wall = time.perf_counter() - t0
+        sampler.active = False
         dev_ms = first.elapsed_time(last)
         launches = sum(e["ctx"].launch_count() for e in envs) - launches0
         cells = sum(closed[i % N_ROT] for i in range(steps))
@@ -250,8 +391,10 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    dev_ms, wall_ms, launches, cells = timed(step_resident, args.steps, True)
-    # per-kernel device time of the timed region (events around each launch on the library's stream)
+    dev_ms, wall_ms, launches, cells = timed(step_resident, args.steps, False)
+    # per-kernel device time: the same K steps once more with CUDA events around every launch on the
+    # library's stream (kept out of the run `value` comes from: the event records cost a little)
+    timed(step_resident, args.steps, True)
     kt = {}
     for k, name in ((_abi.K_PACK, "pack"), (_abi.K_DILATE, "dilate_pool"), (_abi.K_HEUR_INIT, "heur_init"),
                     (_abi.K_HEUR_RELAX, "heur_relax"), (_abi.K_HEUR_FINISH, "heur_finish")):
@@ -263,6 +406,7 @@ def main():
         kt[name] = (ms, n)
     # the steps are serialised on each context's stream; K steps' device time = sum of per-step event spans
     e2e_dev_ms, e2e_wall_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
+    batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
     sampler.stop_flag = True
 
     # max over ranks
@@ -293,25 +437,23 @@ def main():
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": PATCH_DIM * PATCH_DIM,
                         "d2h_bytes_per_step": adim * adim * 21, "ms_per_step": e2e_wall_ms / args.steps},
                 "gpu_launches": launches,
-                "roofline": {"bound": "hbm", "kernel": "heur_relax_kernel", "achieved": achieved, "peak": hbm_peak,
-                             "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "roofline": {"bound": "hbm", "kernel": "heur_sweep_kernel", "achieved": achieved, "peak": hbm_peak,
+                             "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES, "peak_source": peak_src,
+                             "note": "dependency-depth bound, not bandwidth bound: one grid's wavefront keeps ~5% of the "
+                                     "worker warps busy; see `batch` for the same kernel fed with independent grids",
                              "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": relax_ms / max(relax_n, 1)},
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
                 "dilate_roofline": {"achieved": BYTES_PER_CELL_SAFETY * PATCH_DIM * PATCH_DIM /
                                     ((kt["pack"][0] + dil_ms) / max(dil_n, 1) * 1e-3) / 1e9, "unit": "GB/s",
                                     "note": "pack + dilate_pool kernels, 2+1/16 B per gm cell"},
                 "clocks": sampler.result()}
+        if batch:
+            line["batch"] = batch
         if not args.no_cpu_baseline:
-            e0 = envs[0]
-            sub = 2048  # bounded sample: the same pipeline on the top-left 2048^2 of environment 0
-            patch = np.ascontiguousarray(e0["patch"][:sub, :sub])
-            import ga_oracle_py as go  # noqa: F401  (cpu_baseline leg: the oracle is the thing timed here, as the checker's twin)
-            thr = go.threshold(patch, 100, 130)
-            free = np.argwhere(thr[::4, ::4] == 0)
-            goal = (int(free[len(free) // 2][1]), int(free[len(free) // 2][0]))
-            dt, n, kind = cpu_reference_step(patch, goal, e0["cc"].disk_r_c_, False)
+            # bounded sample of the same step on the host: a 2048^2 patch seeded like environment 0
+            dt, n, kind = cpu_reference_steps(2048, [20240], envs[0]["cc"].disk_r_c_)
             line["cpu_baseline"] = {"value": n / dt / 1e6, "unit": UNIT, "cores": 1, "kind": kind,
-                                    "sample": "1 step on the 2048x2048 corner of environment 0 (%.1f s)" % dt}
+                                    "sample": "1 step (threshold + dilate + pool + heuristic) on a 2048x2048 patch, seed 20240 (%.1f s)" % dt}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
