@@ -36,7 +36,7 @@ enum
   HC_HEAD = 0,      // ring consumer cursor
   HC_TAIL = 1,      // ring producer cursor
   HC_PENDING = 2,   // tiles queued or running
-  HC_CLOSED = 3,    // closed-cell count (finish kernel)
+  HC_CLOSED = 3,    // closed-cell count, HC_CLOSED + 1: terminal-cell count (finish kernels)
   HC_VISITS = 8,    // statistics: tile visits, sweeps, visits that improved a cell
   HC_INNER = 9,
   HC_IMPROVING = 10,
@@ -79,8 +79,9 @@ struct heur_args  // finish kernel
   int32_t* parent;
   double* dist;
   uint8_t* flags;
-  int* closed;        // closed-cell counter of this grid
-  unsigned* scratch;  // [ncell] finish A: block-local terminal (10 bits) | straight steps (10) | diagonal steps (10)
+  int* closed;        // [2] counters of this grid: closed cells, terminal cells
+  int* tlist;         // [ncell / 4 + 1024] finish A: the terminal cells (parent in another 32x32 block)
+  unsigned* scratch;  // [ncell] finish A: displacement of the block's terminal cell and (straight, diagonal) steps to it
   int2* tot;          // [ncell] finish B: (straight, diagonal) steps of a terminal cell to the root
   int dim, goal;
   double w_prox, unk_w, L1, L2;
@@ -627,22 +628,30 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
 //      candidate reproduces g(n) bit for bit), then every cell walks its chain INSIDE the block in
 //      shared memory down to the block's terminal cell (the one whose parent lies outside, or the
 //      root) and keeps (terminal, steps to it);
-//   B  only terminal cells: walk terminal -> parent -> that block's terminal -> ... to the root,
-//      one L2 read pair per block crossed (a few dozen), summing the block-local step counts;
+//   B  one thread per terminal cell (A appended them to a list): walk terminal -> parent -> that
+//      block's terminal -> ... to the root, one L2 read pair per block crossed (a few dozen),
+//      summing the block-local step counts;
 //   C  every cell: its local counts + its terminal's total.
 // ---------------------------------------------------------------------------------------------
 #define FB 32            // finish block edge
 #define FS (FB + 2)      // staged edge incl. halo
 
-__device__ __forceinline__ unsigned fin_pack(int t_local, int cs, int cd) { return (unsigned)t_local | ((unsigned)cs << 10) | ((unsigned)cd << 20); }
+// scratch word of a cell: displacement of its block's terminal cell (dx + 32, dy + 32: 6 bits each),
+// straight steps to it (10 bits), diagonal steps (10 bits)
+__device__ __forceinline__ unsigned fin_pack(int dx, int dy, int cs, int cd)
+{
+  return (unsigned)(dx + 32) | ((unsigned)(dy + 32) << 6) | ((unsigned)cs << 12) | ((unsigned)cd << 22);
+}
+__device__ __forceinline__ int fin_target(unsigned s, int cell, int dim) { return cell + ((int)((s >> 6) & 63) - 32) * dim + (int)(s & 63) - 32; }
 
 __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single, const heur_args* many)
 {
   __shared__ double sg[FS * FS];
   __shared__ double sb[FS * FS];
   __shared__ uint8_t su[FS * FS];
-  __shared__ short lp[FB * FB];
-  __shared__ uint8_t lt[FB * FB];
+  __shared__ short lp[FB * FB];  // -1: terminal (parent outside the block, root, or not closed); else parent's local index | step type << 10
+  __shared__ int s_cnt[2][FB];   // per warp: closed cells, terminal cells
+  __shared__ int s_base;
   const heur_args& a = many ? many[blockIdx.y] : single;
   const int dim = a.dim, nbx = (dim + FB - 1) / FB;
   if ((int)blockIdx.x >= nbx * nbx) return;  // batches of unequal grids
@@ -666,7 +675,7 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     su[i] = u;
   }
   __syncthreads();
-  const int lx = threadIdx.x % FB, ly = threadIdx.x / FB;
+  const int lx = threadIdx.x % FB, ly = threadIdx.x / FB, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nx = ox + 1 + lx, ny = oy + 1 + ly;
   const int me = (ly + 1) * FS + lx + 1;
   const bool in = nx < dim && ny < dim;
@@ -674,7 +683,7 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
   const double gn = sg[me];
   int32_t par = -2;
   uint8_t fl = 0;
-  int lpar = -1, typ = 0;
+  int lpar = -1;
   if (in && gn < INFINITY)
   {
     fl = GA_H_CLOSED;
@@ -701,59 +710,79 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
         {
           par = (ny + dy) * dim + (nx + dx);
           if (su[q]) fl |= GA_H_UNKNOWN;  // NodeDisc::is_unknown_ = unknown-ness of the parent, :253,268
-          typ = i < 4 ? 0 : 1;
           const int plx = lx + dx, ply = ly + dy;
-          if (plx >= 0 && ply >= 0 && plx < FB && ply < FB) lpar = ply * FB + plx;
+          if (plx >= 0 && ply >= 0 && plx < FB && ply < FB) lpar = (ply * FB + plx) | (i < 4 ? 0 : 1024);
           break;
         }
       }
     }
   }
   lp[threadIdx.x] = (short)lpar;
-  lt[threadIdx.x] = (uint8_t)typ;
   if (in)
   {
     a.parent[n] = par;
     a.flags[n] = fl;
   }
-  const int closed = __syncthreads_count(fl != 0);
-  if (threadIdx.x == 0 && closed) atomicAdd(a.closed, closed);
-  // chain walk inside the block
-  int cur = threadIdx.x, cs = 0, cd = 0;
-  for (int p = lpar; p >= 0; p = lp[cur])
+  // counters: closed cells, and the block's terminal cells appended to the grid's terminal list
+  const bool term = par >= 0 && lpar < 0;
+  const unsigned m_closed = __ballot_sync(0xFFFFFFFFu, fl != 0), m_term = __ballot_sync(0xFFFFFFFFu, term);
+  if (lane == 0)
   {
-    if (lt[cur]) ++cd; else ++cs;
-    cur = p;
+    s_cnt[0][warp] = __popc(m_closed);
+    s_cnt[1][warp] = __popc(m_term);
   }
-  if (in) a.scratch[n] = fin_pack(cur, cs, cd);
+  __syncthreads();
+  if (warp == 0)
+  {
+    const int nc = s_cnt[0][lane], nt = s_cnt[1][lane];
+    int incl = nt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+      const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const int tot_c = __reduce_add_sync(0xFFFFFFFFu, nc);
+    s_cnt[1][lane] = incl - nt;  // exclusive offset of the warp
+    if (lane == 31)
+    {
+      if (tot_c) atomicAdd(a.closed, tot_c);
+      s_base = incl ? atomicAdd(a.closed + 1, incl) : 0;
+    }
+  }
+  __syncthreads();
+  if (term) a.tlist[s_base + s_cnt[1][warp] + __popc(m_term & ((1u << lane) - 1u))] = n;
+  // chain walk inside the block (shared memory, one load per hop)
+  int cur = threadIdx.x, cs = 0, cd = 0;
+  for (int v = lpar; v >= 0; v = lp[cur])
+  {
+    cd += v >> 10;
+    cs += 1 - (v >> 10);
+    cur = v & 1023;
+  }
+  if (in) a.scratch[n] = fin_pack(cur % FB - lx, cur / FB - ly, cs, cd);
 }
 
-__global__ void __launch_bounds__(256) heur_finish_b_kernel(heur_args single, const heur_args* many)
+// one thread per terminal cell: terminal -> parent -> that block's terminal -> ... -> root
+__global__ void __launch_bounds__(128) heur_finish_b_kernel(heur_args single, const heur_args* many)
 {
   const heur_args& a = many ? many[blockIdx.y] : single;
-  const int dim = a.dim, ncell = dim * dim;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= ncell) return;
-  int p = __ldg(a.parent + c);
-  if (p < 0) return;
-  int cx = c % dim, cy = c / dim;
-  int px = p % dim, py = p / dim;
-  if (px / FB == cx / FB && py / FB == cy / FB) return;  // not a terminal cell
-  int cs = 0, cd = 0;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= __ldcg(a.closed + 1)) return;
+  const int dim = a.dim, goal = a.goal;
+  const int c = a.tlist[i];
+  int cur = c, cs = 0, cd = 0;
   for (;;)
   {
-    if (px != cx && py != cy) ++cd; else ++cs;  // the step terminal -> parent
-    if (p == a.goal) break;
-    const unsigned s = __ldg(a.scratch + p);    // parent -> its block's terminal
-    cs += (s >> 10) & 1023;
-    cd += (s >> 20) & 1023;
-    const int t = ((py / FB) * FB + (int)((s & 1023) / FB)) * dim + (px / FB) * FB + (int)((s & 1023) % FB);
-    if (t == a.goal) break;
-    cx = t % dim;
-    cy = t / dim;
-    p = __ldg(a.parent + t);
-    px = p % dim;
-    py = p / dim;
+    const int p = __ldg(a.parent + cur);
+    const int d = p - cur;
+    if (d == 1 || d == -1 || d == dim || d == -dim) ++cs; else ++cd;  // the step terminal -> parent
+    if (p == goal) break;
+    const unsigned s = __ldg(a.scratch + p);  // parent -> its block's terminal
+    cs += (s >> 12) & 1023;
+    cd += (s >> 22) & 1023;
+    cur = fin_target(s, p, dim);
+    if (cur == goal) break;
   }
   a.tot[c] = make_int2(cs, cd);
 }
@@ -768,9 +797,8 @@ __global__ void __launch_bounds__(256) heur_finish_c_kernel(heur_args single, co
   if (a.flags[c] & GA_H_CLOSED)
   {
     const unsigned s = a.scratch[c];
-    int cs = (s >> 10) & 1023, cd = (s >> 20) & 1023;
-    const int cx = c % dim, cy = c / dim;
-    const int t = ((cy / FB) * FB + (int)((s & 1023) / FB)) * dim + (cx / FB) * FB + (int)((s & 1023) % FB);
+    int cs = (s >> 12) & 1023, cd = (s >> 22) & 1023;
+    const int t = fin_target(s, c, dim);
     if (t != a.goal)
     {
       const int2 tt = a.tot[t];
@@ -823,7 +851,7 @@ int ga_heur_alloc(ga_ctx* c)
   GA_CUDA(c, cudaMalloc(&c->d_hctl, sizeof(int) * HC_WORDS));
   GA_CUDA(c, cudaMemsetAsync(c->d_hctl, 0, sizeof(int) * HC_WORDS, c->stream));
   GA_CUDA(c, cudaMalloc(&c->d_hcls, na));
-  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * na));
+  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * (na + na / 4 + 1024)));  // scratch words + terminal list (terminals are block-border cells: < 1/8 of the grid)
   GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
   GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS * sizeof(sweep_tile))));
@@ -865,6 +893,7 @@ static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed,
   a->flags = c->d_hflags[slot];
   a->closed = closed;
   a->scratch = reinterpret_cast<unsigned*>(c->d_jump);
+  a->tlist = c->d_jump + (size_t)c->astar_dim * c->astar_dim;
   a->tot = reinterpret_cast<int2*>(c->d_cnt);
   a->dim = c->astar_dim;
   a->goal = G->goal;
@@ -897,7 +926,7 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
     ga_launch_scope ls(c, GA_K_HEUR_FINISH);
     const int nb = (max_dim + FB - 1) / FB, cells = (max_dim * max_dim + 255) / 256;
     heur_finish_a_kernel<<<dim3(nb * nb, n), FB * FB, 0, c->stream>>>(a0, dA);
-    heur_finish_b_kernel<<<dim3(cells, n), 256, 0, c->stream>>>(a0, dA);
+    heur_finish_b_kernel<<<dim3((max_dim * max_dim / 8 + 1024 + 127) / 128, n), 128, 0, c->stream>>>(a0, dA);
     heur_finish_c_kernel<<<dim3(cells, n), 256, 0, c->stream>>>(a0, dA);
   }
   GA_CUDA(c, cudaGetLastError());
@@ -966,7 +995,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
     GA_CUDA(c, cudaMemsetAsync(c->d_bring, 0, sizeof(int) * (size_t)cap, c->stream));
     c->bring_cap = (int)cap;
   }
-  const size_t desc_bytes = (size_t)n * (sizeof(heur_grid) + sizeof(heur_args) + sizeof(int));
+  const size_t desc_bytes = (size_t)n * (sizeof(heur_grid) + sizeof(heur_args) + 2 * sizeof(int));
   if (desc_bytes > c->bdesc_cap)
   {
     if (c->d_bdesc) GA_CUDA(c, cudaFree(c->d_bdesc));
@@ -979,7 +1008,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
   int* dClosed = reinterpret_cast<int*>(dA + n);
   std::vector<heur_grid> hG((size_t)n);
   std::vector<heur_args> hA((size_t)n);
-  for (int i = 0; i < n; ++i) make_descs(ctxs[i], slot, goal_xy[2 * i], goal_xy[2 * i + 1], dClosed + i, &hG[i], &hA[i]);
+  for (int i = 0; i < n; ++i) make_descs(ctxs[i], slot, goal_xy[2 * i], goal_xy[2 * i + 1], dClosed + 2 * i, &hG[i], &hA[i]);
   // order the leading stream after whatever the other contexts still have in flight
   for (int i = 1; i < n; ++i)
   {
@@ -990,7 +1019,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
   }
   GA_CUDA(c, cudaMemcpyAsync(dG, hG.data(), sizeof(heur_grid) * n, cudaMemcpyHostToDevice, c->stream));
   GA_CUDA(c, cudaMemcpyAsync(dA, hA.data(), sizeof(heur_args) * n, cudaMemcpyHostToDevice, c->stream));
-  GA_CUDA(c, cudaMemsetAsync(dClosed, 0, sizeof(int) * n, c->stream));
+  GA_CUDA(c, cudaMemsetAsync(dClosed, 0, sizeof(int) * 2 * n, c->stream));
   heur_queue q;
   q.ring = c->d_bring;
   q.mask = cap - 1;
@@ -1005,12 +1034,9 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
   for (int i = 1; i < n; ++i) GA_CUDA(c, cudaStreamWaitEvent(ctxs[i]->stream, c->ev_batch, 0));
   if (n_closed)
   {
-    GA_CUDA(c, cudaMemcpyAsync(n_closed, dClosed, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+    GA_CUDA(c, cudaMemcpy2DAsync(n_closed, sizeof(int), dClosed, 2 * sizeof(int), sizeof(int), (size_t)n,
+                                 cudaMemcpyDeviceToHost, c->stream));
     GA_CUDA(c, cudaStreamSynchronize(c->stream));
-  }
-  else
-  {
-    // hG / hA are pageable host vectors: the copies above have been staged, nothing else to keep alive
   }
   return GA_OK;
 }
