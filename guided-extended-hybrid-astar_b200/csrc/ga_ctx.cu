@@ -73,7 +73,7 @@ extern "C" int ga_create(int device, ga_ctx** out)
 
 static void free_grids(ga_ctx* c)
 {
-  void** ptrs[] = { (void**)&c->d_patch,   (void**)&c->d_safety, (void**)&c->d_plane_occ, (void**)&c->d_plane_nf,
+  void** ptrs[] = { (void**)&c->d_patch,   (void**)&c->d_safety,
                     (void**)&c->d_astar,   (void**)&c->d_fence,  (void**)&c->d_mc,        (void**)&c->d_prox,
                     (void**)&c->d_mres,    (void**)&c->d_odist,  (void**)&c->d_vdist,     (void**)&c->d_hcost[0],
                     (void**)&c->d_hcost[1], (void**)&c->d_hdist[0], (void**)&c->d_hdist[1], (void**)&c->d_hparent[0],
@@ -252,13 +252,9 @@ extern "C" int ga_patch_reset(ga_ctx* c, int patch_dim)
     free_grids(c);
     c->patch_dim = patch_dim;
     c->astar_dim = astar_dim;
-    c->plane_pitch = (patch_dim + 31) / 32;
-    const size_t pw = (size_t)c->plane_pitch * patch_dim * sizeof(uint32_t);
     const size_t nv = (size_t)c->ap.vor_dim * c->ap.vor_dim;
     GA_CUDA(c, cudaMalloc(&c->d_patch, np));
     GA_CUDA(c, cudaMalloc(&c->d_safety, np));
-    GA_CUDA(c, cudaMalloc(&c->d_plane_occ, pw));
-    GA_CUDA(c, cudaMalloc(&c->d_plane_nf, pw));
     GA_CUDA(c, cudaMalloc(&c->d_astar, na));
     GA_CUDA(c, cudaMalloc(&c->d_fence, na));
     GA_CUDA(c, cudaMalloc(&c->d_mc, na * 8));

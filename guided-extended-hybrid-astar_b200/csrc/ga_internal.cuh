@@ -53,11 +53,8 @@ struct ga_ctx
 
   // ---- grids
   int patch_dim = 0, astar_dim = 0;
-  int plane_pitch = 0;          // words per bit-plane row
   uint8_t* d_patch = nullptr;
   uint8_t* d_safety = nullptr;
-  uint32_t* d_plane_occ = nullptr;  // bit = thresholded cell == OCC
-  uint32_t* d_plane_nf = nullptr;   // bit = thresholded cell != FREE
   uint8_t* d_astar = nullptr;
   uint8_t* d_fence = nullptr;
   double* d_mc = nullptr;

@@ -242,8 +242,8 @@ GA_API int ga_astar_dim(const ga_ctx* ctx);
  * context's stream when profiling is on (used by bench.py for the live roofline figure) */
 typedef enum
 {
-  GA_K_PACK = 0,      /* threshold + bit-plane pack                */
-  GA_K_DILATE = 1,    /* disk dilation + expand + 4x4 pool         */
+  GA_K_PACK = 0,      /* unused (the pack step lives inside the fused kernel since round 1) */
+  GA_K_DILATE = 1,    /* fused threshold + disk dilation + expand + 4x4 pool */
   GA_K_HEUR_INIT = 2,
   GA_K_HEUR_RELAX = 3,
   GA_K_HEUR_FINISH = 4,
