@@ -26,8 +26,15 @@
 #define DT_SW (DT_TW + 2)  // staged plane words per row (one halo word each side)
 #define DT_THREADS 256
 
-// m has 0xFF / 0x00 per byte; returns bit k = byte k set
-__device__ __forceinline__ uint32_t nibble_of_mask(uint32_t m) { return ((m & 0x08040201u) * 0x01010101u) >> 24; }
+// SWAR byte compare: bit 7 of byte k of the result = (byte k of x > c), any c in 0..255.
+// k7 = 0x01010101 * (127 - (c & 127)): adding it to the low 7 bits carries into bit 7 iff they exceed c & 127.
+__device__ __forceinline__ uint32_t bytes_gt(uint32_t x, uint32_t k7, bool c_high)
+{
+  const uint32_t m = (x & 0x7F7F7F7Fu) + k7;
+  return (c_high ? (m & x) : (m | x)) & 0x80808080u;
+}
+// bits 7, 15, 23, 31 -> bits 0..3
+__device__ __forceinline__ uint32_t nibble_of_high_bits(uint32_t m) { return ((m >> 7) * 0x01020408u) >> 24; }
 
 __global__ void __launch_bounds__(DT_THREADS)
 safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ safety, uint8_t* __restrict__ astar,
@@ -45,6 +52,9 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
   const int w0 = blockIdx.x * DT_TW, y0 = blockIdx.y * DT_TH;
   const int tid = threadIdx.x;
   const bool vec = (dim & 15) == 0;
+  const uint32_t lo = lo4 & 0xFFu, hi = hi4 & 0xFFu;
+  const uint32_t hi_k7 = 0x01010101u * (127u - (hi & 127u)), lo_k7 = 0x01010101u * (127u - ((lo - 1u) & 127u));
+  const bool hi_high = hi >= 128u, lo_high = (lo - 1u) >= 128u && lo != 0u;
 
   {
     // table: byte k = ((idx >> k) & 1) + ((idx >> (4 + k)) & 1)
@@ -62,44 +72,68 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
   // ---- phase 0: threshold + pack.  One item = 16 cells (half a plane word); two neighbouring
   //      lanes make a word.  Cells outside the image are 0 in both planes (OpenCV ignores them).
   const int n_items = rows_in * DT_SW * 2;
-  for (int it = tid; it < ((n_items + 31) & ~31); it += DT_THREADS)  // whole warps: the shuffle below needs all lanes
+  constexpr int P0_MAX = ((DT_TH + 2 * GA_MAX_DISK_R) * DT_SW * 2 + DT_THREADS - 1) / DT_THREADS;  // items per thread, largest SE
+  if (vec)
   {
-    const int half = it & 1, wi = (it >> 1) % DT_SW, rl = (it >> 1) / DT_SW;
-    const int y = it < n_items ? y0 - r + rl : -1;
-    const int x = (w0 - 1 + wi) * 32 + half * 16;
-    uint32_t b_occ = 0, b_nf = 0;
-    if (y >= 0 && y < dim && x >= 0 && x < dim)
-    {
-      const uint8_t* p = patch + (size_t)y * dim + x;
-      if (vec)  // dim % 16 == 0: the 16 cells are inside and 16-byte aligned
-      {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
-        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+    // dim % 16 == 0: an item is 16 aligned bytes, fully inside or fully outside the image.  All loads
+    // of a thread are issued before the first one is used (one memory round trip per tile).
+    uint4 v[P0_MAX];
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-        {
-          b_occ |= nibble_of_mask(__vcmpgtu4(w[k], hi4)) << (4 * k);  // v > MAX_THRESH -> OCC  (collision_checking.cpp:214,220)
-          b_nf |= nibble_of_mask(__vcmpgeu4(w[k], lo4)) << (4 * k);   // !(v < MIN_THRESH)    (:213,219)
-        }
-      }
-      else
+    for (int j = 0; j < P0_MAX; ++j)
+    {
+      const int it = tid + j * DT_THREADS;
+      const int half = it & 1, wi = (it >> 1) % DT_SW, rl = (it >> 1) / DT_SW;
+      const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32 + half * 16;
+      v[j] = make_uint4(0, 0, 0, 0);  // below any MIN_THRESH > 0: FREE, the neutral element of the max filter
+      if (it < n_items && y >= 0 && y < dim && x >= 0 && x < dim) v[j] = __ldg(reinterpret_cast<const uint4*>(patch + (size_t)y * dim + x));
+    }
+#pragma unroll
+    for (int j = 0; j < P0_MAX; ++j)
+    {
+      const int it = tid + j * DT_THREADS;
+      if (it - (tid & 31) >= n_items) break;  // whole warps leave together: the shuffle below needs all lanes
+      const int half = it & 1, wi = (it >> 1) % DT_SW, rl = (it >> 1) / DT_SW;
+      const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32 + half * 16;
+      const bool inside = it < n_items && y >= 0 && y < dim && x >= 0 && x < dim;
+      const uint32_t w[4] = { v[j].x, v[j].y, v[j].z, v[j].w };
+      uint32_t b_occ = 0, b_nf = (lo == 0 && inside) ? 0xFFFFu : 0u;  // nothing is below 0
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
       {
-        const int n = min(16, dim - x);
+        b_occ |= nibble_of_high_bits(bytes_gt(w[k], hi_k7, hi_high)) << (4 * k);  // v > MAX_THRESH -> OCC  (collision_checking.cpp:214,220)
+        b_nf |= nibble_of_high_bits(bytes_gt(w[k], lo_k7, lo_high)) << (4 * k);    // !(v < MIN_THRESH), i.e. v > MIN_THRESH - 1  (:213,219)
+      }
+      if (!inside) b_occ = b_nf = 0;
+      b_nf |= b_occ;  // setTo(OCC) runs after setTo(FREE): OCC wins
+      // lanes 2k, 2k+1 hold the halves of one word
+      const uint32_t o_occ = __shfl_xor_sync(0xFFFFFFFFu, b_occ, 1), o_nf = __shfl_xor_sync(0xFFFFFFFFu, b_nf, 1);
+      if (!half && it < n_items)
+      {
+        sP[rl * DT_SW + wi] = b_occ | (o_occ << 16);
+        sP[(rows_in + rl) * DT_SW + wi] = b_nf | (o_nf << 16);
+      }
+    }
+  }
+  else
+  {
+    for (int it = tid; it < n_items / 2; it += DT_THREADS)  // one item = one plane word, byte loads
+    {
+      const int wi = it % DT_SW, rl = it / DT_SW;
+      const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32;
+      uint32_t b_occ = 0, b_nf = 0;
+      if (y >= 0 && y < dim && x >= 0 && x < dim)
+      {
+        const uint8_t* p = patch + (size_t)y * dim + x;
+        const int n = min(32, dim - x);
         for (int k = 0; k < n; ++k)
         {
-          const uint32_t v = __ldg(p + k);
-          b_occ |= (v > (hi4 & 0xFFu) ? 1u : 0u) << k;
-          b_nf |= (v >= (lo4 & 0xFFu) ? 1u : 0u) << k;
+          const uint32_t c = __ldg(p + k);
+          b_occ |= (c > hi ? 1u : 0u) << k;
+          b_nf |= (c >= lo ? 1u : 0u) << k;
         }
       }
-      b_nf |= b_occ;  // setTo(OCC) runs after setTo(FREE): OCC wins
-    }
-    // lanes 2k, 2k+1 hold the halves of one word (DT_THREADS and the item stride are even)
-    const uint32_t o_occ = __shfl_xor_sync(0xFFFFFFFFu, b_occ, 1), o_nf = __shfl_xor_sync(0xFFFFFFFFu, b_nf, 1);
-    if (!half && it < n_items)
-    {
-      sP[rl * DT_SW + wi] = b_occ | (o_occ << 16);
-      sP[(rows_in + rl) * DT_SW + wi] = b_nf | (o_nf << 16);
+      sP[rl * DT_SW + wi] = b_occ;
+      sP[(rows_in + rl) * DT_SW + wi] = b_nf | b_occ;
     }
   }
   __syncthreads();
@@ -107,6 +141,8 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
   // ---- phase A: horizontal span dilations of every staged row
   {
     const int wl = tid & (DT_TW - 1);
+    uint32_t keep = 0;  // bit w: half width w is one of the SE's
+    for (int w = 0; w <= r; ++w) keep |= (s_var_of_w[w] >= 0 ? 1u : 0u) << w;
     for (int pr = tid >> 3; pr < 2 * rows_in; pr += DT_THREADS / DT_TW)
     {
       const int pl = pr >= rows_in, rl = pr - pl * rows_in;
@@ -121,11 +157,18 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
         for (int v = 0; v < nv; ++v) dst[v * rows_in * DT_TW] = 0;
         continue;
       }
-      for (int w = 1; w <= r; ++w)
+      // build_se lists the half widths in increasing order, so the variant index just counts up
+      uint32_t* o = dst + (v0 >= 0 ? rows_in * DT_TW : 0);
+#pragma unroll
+      for (int w = 1; w <= GA_MAX_DISK_R; ++w)
       {
+        if (w > r) break;
         D |= __funnelshift_l(a, b, w) | __funnelshift_r(b, c, w);  // cells at distance exactly w, left and right
-        const int v = s_var_of_w[w];
-        if (v >= 0) dst[v * rows_in * DT_TW] = D;
+        if ((keep >> w) & 1u)
+        {
+          *o = D;
+          o += rows_in * DT_TW;
+        }
       }
     }
   }
