@@ -16,9 +16,9 @@ int ga_fail(ga_ctx* ctx, int code, const char* fmt, ...)
   return code;
 }
 
-ga_launch_scope::ga_launch_scope(ga_ctx* ctx, int kid) : c(ctx), k(kid)
+ga_launch_scope::ga_launch_scope(ga_ctx* ctx, int kid, int n_kernels) : c(ctx), k(kid)
 {
-  c->launches++;
+  c->launches += n_kernels;  // kernels launched inside the scope
   c->k_launches[k]++;
   if (c->prof_on && c->prof.size() < (1u << 18))
   {

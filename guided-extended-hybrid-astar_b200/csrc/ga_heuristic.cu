@@ -923,7 +923,7 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
   }
   GA_CUDA(c, cudaGetLastError());
   {
-    ga_launch_scope ls(c, GA_K_HEUR_FINISH);
+    ga_launch_scope ls(c, GA_K_HEUR_FINISH, 3);
     const int nb = (max_dim + FB - 1) / FB, cells = (max_dim * max_dim + 255) / 256;
     heur_finish_a_kernel<<<dim3(nb * nb, n), FB * FB, 0, c->stream>>>(a0, dA);
     heur_finish_b_kernel<<<dim3((max_dim * max_dim / 8 + 1024 + 127) / 128, n), 128, 0, c->stream>>>(a0, dA);

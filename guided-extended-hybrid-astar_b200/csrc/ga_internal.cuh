@@ -122,7 +122,7 @@ struct ga_launch_scope
   ga_ctx* c;
   int k;
   cudaEvent_t e1 = nullptr;
-  ga_launch_scope(ga_ctx* ctx, int kid);
+  ga_launch_scope(ga_ctx* ctx, int kid, int n_kernels = 1);
   ~ga_launch_scope();
 };
 
