@@ -302,6 +302,60 @@ def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak):
     return out
 
 
+def run_collision_leg(env, args, ga):
+    """BASELINE metric M3 (collision checks/s) on environment 0 (4096^2 patch, 3-disk footprint):
+    (a) pose checks through ga_check_poses: host pose arrays in, first-hit index per segment out, one
+        launch per batch (H2D + kernel + D2H inside the timing: the API takes host buffers);
+    (b) expansion batches through ga_expand: every motion primitive of every node (13 steers x 2
+        directions + the 6 U-Shift rear-axis rotations, config 4) rolled out and checked in one launch;
+    next to the reference's own checkPose loop on one host core."""
+    from ga_b200 import _abi
+    ctx, cc = env["ctx"], env["cc"]
+    rng = np.random.default_rng(7)
+    n, seg_len = 1 << 20, 8
+    ext = PATCH_DIM * 0.15625
+    x, y = rng.uniform(0, ext, n), rng.uniform(0, ext, n)
+    yaw = rng.uniform(-3.2, 3.2, n)
+    seg = np.arange(0, n + 1, seg_len, dtype=np.int32)
+    cc.checkSegments(x, y, yaw, seg)
+    ctx.sync()
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        hits = cc.checkSegments(x, y, yaw, seg)
+    ctx.sync()
+    dt = (time.perf_counter() - t0) / reps
+    out = {"pose_checks_per_s": n / dt, "poses_per_launch": n, "segments": len(seg) - 1, "disks": 3,
+           "free_segments": float((hits < 0).mean())}
+    # expansion batches
+    cc.setExpandParams()
+    nodes = np.zeros(4096, _abi.NODE_DTYPE)
+    nodes["x"], nodes["y"] = rng.uniform(20, ext - 20, 4096), rng.uniform(20, ext - 20, 4096)
+    nodes["yaw"], nodes["motion_res"], nodes["with_rear_axis"] = rng.uniform(-3.14, 3.14, 4096), 0.3125, 1
+    succ = cc.expandNodes(nodes)
+    ctx.sync()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        succ = cc.expandNodes(nodes)
+    ctx.sync()
+    dt = (time.perf_counter() - t0) / reps
+    poses = int(succ["n_poses"].sum())
+    out.update({"expand_nodes_per_s": len(nodes) / dt, "expand_primitives_per_s": int((succ["n_poses"] > 0).sum()) / dt,
+                "expand_pose_checks_per_s": poses / dt, "expand_batch_nodes": len(nodes), "ushift": True})
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import ga_ref_py as gr
+        if gr.available():
+            m = 200000
+            gr.init(PATCH_DIM)
+            gr.set_grid(gr.SAFETY, ctx.download(_abi.GRID_SAFETY))
+            t0 = time.perf_counter()
+            gr.check_segments(x[:m], y[:m], yaw[:m], seg[:m // seg_len + 1])
+            out["cpu_reference_pose_checks_per_s"] = m / (time.perf_counter() - t0)
+            out["cpu_reference_sample"] = "%d poses, CollisionChecker::getPathCollisionIndex per segment, 1 core" % m
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -311,6 +365,7 @@ def main():
     ap.add_argument("--ref-dim", type=int, default=0, help="patch size of the bounded CPU sample (reference arm); 0 = from --steps")
     ap.add_argument("--ref-procs", type=int, default=64, help="planner processes of the reference arm (capped by the host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-collision", action="store_true", help="skip the collision-checks/s leg")
     ap.add_argument("--batch", type=int, default=32, help="queries of the batched-heuristic leg (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -407,6 +462,7 @@ def main():
     # the steps are serialised on each context's stream; K steps' device time = sum of per-step event spans
     e2e_dev_ms, e2e_wall_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
+    collision = run_collision_leg(envs[0], args, ga_b200) if (rank == 0 and not args.no_collision) else None
     sampler.stop_flag = True
 
     # max over ranks
@@ -449,6 +505,8 @@ def main():
                 "clocks": sampler.result()}
         if batch:
             line["batch"] = batch
+        if collision:
+            line["collision"] = collision
         if not args.no_cpu_baseline:
             # bounded sample of the same step on the host: a 2048^2 patch seeded like environment 0
             dt, n, kind = cpu_reference_steps(2048, [20240], envs[0]["cc"].disk_r_c_)
