@@ -92,6 +92,7 @@ extern "C" int ga_destroy(ga_ctx* c)
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   free_grids(c);
+  ga_cart_free(c);
   if (c->d_centers) cudaFree(c->d_centers);
   if (c->d_stage) cudaFree(c->d_stage);
   if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -298,6 +299,7 @@ extern "C" int ga_patch_reset(ga_ctx* c, int patch_dim)
 
 extern "C" int ga_patch_dim(const ga_ctx* c) { return c ? c->patch_dim : GA_ERR_ARG; }
 extern "C" int ga_astar_dim(const ga_ctx* c) { return c ? c->astar_dim : GA_ERR_ARG; }
+extern "C" int ga_cart_dim(const ga_ctx* c) { return c ? c->cart_dim : GA_ERR_ARG; }
 
 static int grid_lookup(const ga_ctx* c, int id, void** p, size_t* bytes)
 {
@@ -307,6 +309,7 @@ static int grid_lookup(const ga_ctx* c, int id, void** p, size_t* bytes)
   switch (id)
   {
     case GA_GRID_PATCH: *p = c->d_patch; *bytes = np; return 0;
+    case GA_GRID_CART: *p = c->d_cart; *bytes = (size_t)c->cart_dim * c->cart_dim; return 0;
     case GA_GRID_SAFETY: *p = c->d_safety; *bytes = np; return 0;
     case GA_GRID_ASTAR: *p = c->d_astar; *bytes = na; return 0;
     case GA_GRID_GEOFENCE: *p = c->d_fence; *bytes = na; return 0;

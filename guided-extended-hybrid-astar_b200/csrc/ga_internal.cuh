@@ -68,6 +68,11 @@ struct ga_ctx
   int32_t* d_hparent[2] = { nullptr, nullptr };
   uint8_t* d_hflags[2] = { nullptr, nullptr };
 
+  // ---- accumulated map (Cartographing::patch_arr_ / temp_patch_)
+  uint8_t* d_cart = nullptr;
+  uint8_t* d_cart_prev = nullptr;
+  int cart_dim = 0, cart_prev_dim = 0;
+
   // ---- heuristic scratch
   int tiles_x = 0, n_tiles = 0;
   int* d_tile_active = nullptr;   // per-tile state word (idle / queued / running / dirty)
@@ -131,3 +136,4 @@ int ga_stage_reserve(ga_ctx* ctx, size_t bytes);
 // implemented per subsystem
 int ga_heur_alloc(ga_ctx* ctx);
 void ga_heur_free(ga_ctx* ctx);
+void ga_cart_free(ga_ctx* ctx);

@@ -170,6 +170,8 @@ class GridContext:
     def grid_shape(self, gid):
         if gid in (_abi.GRID_PATCH, _abi.GRID_SAFETY):
             d = self.lib.ga_patch_dim(self.h)
+        elif gid == _abi.GRID_CART:
+            d = self.lib.ga_cart_dim(self.h)
         elif gid in (_abi.GRID_OBSTACLE_DIST, _abi.GRID_VORONOI_DIST):
             nb = C.c_size_t()
             self.check(self.lib.ga_grid_bytes(self.h, gid, C.byref(nb)))
@@ -324,6 +326,40 @@ class CollisionChecker:
         out = np.zeros((len(nodes), self.expand_stride_), _abi.SUCC_DTYPE)
         self.ctx.check(self.ctx.lib.ga_expand(self.ctx.h, _abi.ptr(nodes), len(nodes), _abi.ptr(out)))
         return out
+
+
+class Cartographing:
+    """Mirror of the reference's Cartographing (LIB/include/cartographing_lib/cartographing.hpp:19-41,
+    pybind: wrapper_hybrid_a_star_lib.cpp) on top of ga_cart_*: the accumulated map of the
+    unknown-environment loop stays on the device, only sensor windows are uploaded."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def resetPatch(self, patch_dim):
+        self.ctx.check(self.ctx.lib.ga_cart_reset(self.ctx.h, int(patch_dim)))
+
+    def cartograph(self, local_map, origin, dim=None):
+        w = np.ascontiguousarray(local_map, np.uint8)
+        dim = w.shape[0] if dim is None else int(dim)
+        self.ctx.check(self.ctx.lib.ga_cartograph(self.ctx.h, _abi.ptr(w), int(origin[0]), int(origin[1]), dim))
+
+    def passLocalMap(self, origin, dim):
+        self.ctx.check(self.ctx.lib.ga_cart_pass_local_map(self.ctx.h, int(origin[0]), int(origin[1]), int(dim)))
+
+    @staticmethod
+    def _to_int(v):
+        # Point<double>::toInt = std::round, half away from zero (data_structures1.hpp:57-60)
+        return int(math.copysign(math.floor(abs(v) + 0.5), v))
+
+    def loadPrevPatch(self, prev_origin_utm, origin_utm):
+        c2g = 1.0 / GM_RES  # grid_tf::con2gm_
+        po = [self._to_int(v * c2g) for v in prev_origin_utm]
+        no = [self._to_int(v * c2g) for v in origin_utm]
+        self.ctx.check(self.ctx.lib.ga_cart_load_prev(self.ctx.h, po[0], po[1], no[0], no[1]))
+
+    def getMap(self):
+        return self.ctx.download(_abi.GRID_CART)
 
 
 class NodeDisc:

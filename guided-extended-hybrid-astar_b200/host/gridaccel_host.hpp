@@ -392,6 +392,34 @@ private:
   std::vector<int> disk_centers_;
 };
 
+// Cartographing (LIB/include/cartographing_lib/cartographing.hpp:19-41): the accumulated map of the
+// unknown-environment loop, device-resident.  Same member names; the map itself is fetched on demand.
+class Cartographing
+{
+public:
+  explicit Cartographing(Context& ctx) : ctx_(ctx) {}
+
+  void resetPatch(size_t patch_dim) { ctx_.check(ga_cart_reset(ctx_.handle(), (int)patch_dim)); }  // cartographing.cpp:7-15
+  void cartograph(const Vec2DFlat<uint8_t>& local_map, const Point<int>& origin, int dim)          // :57-96
+  {
+    ctx_.check(ga_cartograph(ctx_.handle(), local_map.getPtr(), origin.x, origin.y, dim));
+  }
+  void passLocalMap(const Point<int>& origin, int dim)                                            // :98-117
+  {
+    ctx_.check(ga_cart_pass_local_map(ctx_.handle(), origin.x, origin.y, dim));
+  }
+  void loadPrevPatch(const Point<double>& prev_origin_utm, const Point<double>& origin_utm)         // :119-129
+  {
+    const double con2gm = 1.0 / 0.15625;  // grid_tf::con2gm_; Point<double>::toInt = std::round
+    ctx_.check(ga_cart_load_prev(ctx_.handle(), (int)std::round(prev_origin_utm.x * con2gm), (int)std::round(prev_origin_utm.y * con2gm),
+                                 (int)std::round(origin_utm.x * con2gm), (int)std::round(origin_utm.y * con2gm)));
+  }
+  void getMap(Vec2DFlat<uint8_t>& out) const { ctx_.download(GA_GRID_CART, out, (size_t)ga_cart_dim(ctx_.handle())); }
+
+private:
+  Context& ctx_;
+};
+
 // Read API of std::unordered_map<size_t, NodeDisc> (AStar::closed_set_guidance_ / closed_set_path_,
 // a_star.hpp:79-80) over the dense result planes the device produces: find / end / at / contains /
 // size / clear / iteration -- what hybrid_a_star_lib.cpp:243,784,794 and the GUI use.

@@ -66,6 +66,7 @@ typedef enum
   GA_GRID_MOTION_RES = 6,     /* f64 astar_dim^2   AStar::motion_res_map_                  */
   GA_GRID_OBSTACLE_DIST = 7,  /* f32 vor_dim^2     AStar::obstacle_dist_                   */
   GA_GRID_VORONOI_DIST = 8,   /* f32 vor_dim^2     AStar::voronoi_dist_                    */
+  GA_GRID_CART = 9,           /* u8  cart_dim^2    Cartographing::patch_arr_ (accumulated map) */
   /* heuristic result planes, slot 0 = closed_set_guidance_, slot 1 = closed_set_path_
    * (dense restatement of std::unordered_map<size_t, NodeDisc>, a_star.hpp:69-72,
    * NodeDisc data_structures2.hpp:47-67): id = base + slot */
@@ -124,6 +125,25 @@ GA_API int ga_patch_insert(ga_ctx* ctx, const uint8_t* window, int ox, int oy, i
  * AStar::calcAstarGridCuda -> Pooling::execute (a_star.cpp:536-542, LIB/src/cuda_lib/max_pool.cu:21-79):
  * threshold -> disk dilation -> patch_safety_arr_, and its pool_win x pool_win max -> astar_grid_. */
 GA_API int ga_build_safety(ga_ctx* ctx);
+
+/* ---- accumulated map of the unknown-environment loop --------------- */
+
+/* Cartographing (LIB/src/cartographing_lib/cartographing.cpp:7-129): the map every sensor window is
+ * merged into, device-resident next to the collision checker's patch.
+ * ga_cart_reset        = resetPatch (:7-15): the old map is kept as temp_patch_, the new one is all 127;
+ * ga_cartograph        = cartograph (:17-96): cells of the dim x dim host window that land inside
+ *                        overwrite the map only where it is still 127 and the window holds 255 or 0;
+ * ga_cart_pass_local_map = passLocalMap (:98-117): window of the map -> CollisionChecker::patch_arr_
+ *                        (device to device, passLocalMapData's clipping); the window must lie inside
+ *                        the map (the reference reads out of bounds otherwise);
+ * ga_cart_load_prev    = loadPrevPatch (:119-129) + util::copyPatch2Patch (util2.hpp:32-67): overlap
+ *                        of the previous map copied in, then the whole map handed to the collision
+ *                        checker.  Origins in gm cells = (utm * con2gm).toInt(), i.e. std::round. */
+GA_API int ga_cart_reset(ga_ctx* ctx, int patch_dim);
+GA_API int ga_cartograph(ga_ctx* ctx, const uint8_t* window, int ox, int oy, int dim);
+GA_API int ga_cart_pass_local_map(ga_ctx* ctx, int ox, int oy, int dim);
+GA_API int ga_cart_load_prev(ga_ctx* ctx, int prev_ox, int prev_oy, int ox, int oy);
+GA_API int ga_cart_dim(const ga_ctx* ctx);
 
 /* ---- footprint collision checks ------------------------------------------------------------ */
 
@@ -251,7 +271,8 @@ typedef enum
   GA_K_EXPAND = 6,
   GA_K_DT = 7,
   GA_K_POTENTIAL = 8,
-  GA_K_COUNT = 9
+  GA_K_CARTOGRAPH = 9, /* window merge / patch-to-patch copy of the accumulated map */
+  GA_K_COUNT = 10
 } ga_kernel_id;
 
 GA_API int ga_prof_enable(ga_ctx* ctx, int on);

@@ -141,6 +141,38 @@ void gao_pass_local_map(uint8_t* patch, int patch_dim, const uint8_t* local_map,
   }
 }
 
+/* cartographing.cpp:17-96 (both overloads are the same loop) */
+void gao_cartograph(uint8_t* cart, int patch_dim, const uint8_t* local_map, int ox, int oy, int dim)
+{
+  for (int x = 0; x < dim; ++x)
+  {
+    for (int y = 0; y < dim; ++y)
+    {
+      const int px = ox + x, py = oy + y;
+      if (px >= patch_dim || px < 0 || py >= patch_dim || py < 0) continue;
+      uint8_t* cell = cart + (size_t)py * patch_dim + px;
+      if (*cell != 127) continue; /* only overwrite unknown parts */
+      const uint8_t v = local_map[(size_t)y * dim + x];
+      if (v == 255 || v == 0) *cell = v; /* SENSOR_FREE = 255, SENSOR_OCC = 0 (collision_checking.hpp:44-46) */
+    }
+  }
+}
+
+/* util2.hpp:32-67 */
+void gao_copy_patch_to_patch(const uint8_t* prev, int prev_dim, int prev_ox, int prev_oy, uint8_t* next,
+                             int next_dim, int ox, int oy)
+{
+  const int opp_x = prev_ox + prev_dim, opp_y = prev_oy + prev_dim;
+  const int sp_x = ox - prev_ox > 0 ? ox - prev_ox : 0, sp_y = oy - prev_oy > 0 ? oy - prev_oy : 0;
+  const int sn_x = prev_ox - ox > 0 ? prev_ox - ox : 0, sn_y = prev_oy - oy > 0 ? prev_oy - oy : 0;
+  const int en_x = opp_x - ox < next_dim - 1 ? opp_x - ox : next_dim - 1;
+  const int en_y = opp_y - oy < next_dim - 1 ? opp_y - oy : next_dim - 1;
+  const int nx = en_x - sn_x, ny = en_y - sn_y;
+  for (int x = 0; x < nx; ++x)
+    for (int y = 0; y < ny; ++y)
+      next[(size_t)(sn_y + y) * next_dim + sn_x + x] = prev[(size_t)(sp_y + y) * prev_dim + sp_x + x];
+}
+
 /* ========================================================================================
  * footprint disks + collision lookups
  * ====================================================================================== */

@@ -71,6 +71,18 @@ typedef struct
   int disk_r_c;    /* disk_r_c_ (cells) */
 } gao_disks_info;
 
+/* Cartographing::cartograph (LIB/src/cartographing_lib/cartographing.cpp:17-96): cells of the
+ * dim x dim window (row-major, [y][x]) that land inside the cartographed patch overwrite it only
+ * where the patch is still SENSOR_UNKNOWN (127) and the window value is 255 or 0. */
+void gao_cartograph(uint8_t* cart, int patch_dim, const uint8_t* local_map, int ox, int oy, int dim);
+
+/* util::copyPatch2Patch (LIB/include/util_lib/util2.hpp:32-67) as Cartographing::loadPrevPatch uses
+ * it (cartographing.cpp:119-129): copy the overlap of the previous patch (origin prev_o, gm cells)
+ * into the new one (origin o).  The reference's end point is clamped to next_dim - 1 and the loop
+ * is exclusive, so a clamped overlap loses its last row / column: reproduced. */
+void gao_copy_patch_to_patch(const uint8_t* prev, int prev_dim, int prev_ox, int prev_oy, uint8_t* next,
+                             int next_dim, int ox, int oy);
+
 /* CollisionChecker::calculateDisks / getDiskRadius / getDiskPositions,
  * collision_checking.cpp:44-145.  centers[(yaw_idx*nb_disks + disk)*2 + {0:x,1:y}] */
 int gao_calc_disks(double veh_length, double veh_width, double veh_lb, double len_per_disk,

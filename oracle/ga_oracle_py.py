@@ -121,6 +121,16 @@ def pass_local_map(patch, local_map, ox, oy):
     lib().gao_pass_local_map(_p(patch), patch.shape[0], _p(local_map), int(ox), int(oy), local_map.shape[0])
 
 
+def cartograph(cart, local_map, ox, oy):
+    local_map = np.ascontiguousarray(local_map, np.uint8)
+    lib().gao_cartograph(_p(cart), cart.shape[0], _p(local_map), int(ox), int(oy), local_map.shape[0])
+
+
+def copy_patch_to_patch(prev, prev_o, nxt, o):
+    lib().gao_copy_patch_to_patch(_p(prev), prev.shape[0], int(prev_o[0]), int(prev_o[1]), _p(nxt), nxt.shape[0],
+                                  int(o[0]), int(o[1]))
+
+
 def calc_disks(length, width, lb, len_per_disk=2.0, double_rows=False, safety=0.1, yaw_res_deg=3):
     info = DisksInfo()
     cen = np.zeros(360 * 32 * 2, np.int32)

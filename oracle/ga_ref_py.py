@@ -62,6 +62,10 @@ def lib():
         L.gar_astar_path.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.gar_calc_voronoi_potential_field.argtypes = [C.c_int, C.c_int, C.c_int]
         L.gar_yaw_idx.argtypes = [C.c_double]
+        L.gar_cartograph.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.gar_cart_load_prev.argtypes = [C.c_double] * 4
+        L.gar_cart_get.argtypes = [C.c_void_p, C.c_size_t]
+        L.gar_con2gm.restype = C.c_double
         L.gar_voronoi_endpoints.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_int]
         L.gar_check_grid.argtypes = [C.c_int] * 4
         L.gar_check_pose.argtypes = [C.c_double] * 3 + [C.c_int]
@@ -194,6 +198,34 @@ def voronoi_endpoints(sites_xy, vor_dim=200, min_dist=3.0):
     out = np.empty((vor_dim * vor_dim, 2), np.int32)
     n = _check(lib().gar_voronoi_endpoints(_p(s), len(s), vor_dim, float(min_dist), _p(out), len(out)))
     return out[:n].copy()
+
+
+def cart_reset(patch_dim):
+    _check(lib().gar_cart_reset(int(patch_dim)))
+
+
+def cartograph(win, ox, oy):
+    win = np.ascontiguousarray(win, np.uint8)
+    _check(lib().gar_cartograph(_p(win), int(ox), int(oy), win.shape[0]))
+
+
+def cart_pass_local_map(ox, oy, dim):
+    _check(lib().gar_cart_pass_local_map(int(ox), int(oy), int(dim)))
+
+
+def cart_load_prev(prev_utm, utm):
+    _check(lib().gar_cart_load_prev(float(prev_utm[0]), float(prev_utm[1]), float(utm[0]), float(utm[1])))
+
+
+def cart_get():
+    d = lib().gar_cart_dim()
+    out = np.empty((d, d), np.uint8)
+    _check(lib().gar_cart_get(_p(out), out.nbytes))
+    return out
+
+
+def con2gm():
+    return lib().gar_con2gm()
 
 
 def yaw_idx(yaw):

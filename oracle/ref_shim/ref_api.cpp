@@ -26,6 +26,7 @@
 #include "yaml-cpp/yaml.h"
 #define private public  // disk_centers_, nb_disks_ ... are private statics the checker must read
 #include "hybridastar_planning_lib/a_star.hpp"
+#include "cartographing_lib/cartographing.hpp"
 #undef private
 
 #include <cmath>
@@ -348,4 +349,30 @@ int gar_turn_on_rear_axis(double x, double y, double yaw, double delta_angle, do
   for (int i = 0; i < n && i < cap; ++i) yaws[i] = mp.yaw_list_[i];
   return n;
 }
+
+// ---- Cartographing (LIB/src/cartographing_lib/cartographing.cpp): the accumulated map of the
+//      unknown-environment loop.  Its patch is a private static: read through the access override.
+int gar_cart_reset(int patch_dim) { GAR_TRY(Cartographing::resetPatch((size_t)patch_dim)) }
+int gar_cartograph(const uint8_t* win, int ox, int oy, int dim)
+{
+  GAR_TRY({
+    Vec2DFlat<uint8_t> w;
+    w.resize_and_reset(dim, dim, 0);
+    std::memcpy(w.getPtr(), win, (size_t)dim * dim);
+    Cartographing::cartograph(w, Point<int>(ox, oy), dim);
+  })
+}
+int gar_cart_pass_local_map(int ox, int oy, int dim) { GAR_TRY(Cartographing::passLocalMap(Point<int>(ox, oy), dim)) }
+int gar_cart_load_prev(double prev_x, double prev_y, double x, double y)
+{
+  GAR_TRY(Cartographing::loadPrevPatch(Point<double>(prev_x, prev_y), Point<double>(x, y)))
+}
+int gar_cart_dim() { return (int)Cartographing::patch_dim_; }
+int gar_cart_get(uint8_t* dst, size_t bytes)
+{
+  if (bytes != Cartographing::patch_dim_ * Cartographing::patch_dim_) return -1;
+  std::memcpy(dst, Cartographing::patch_arr_.getPtr(), bytes);
+  return 0;
+}
+double gar_con2gm() { return grid_tf::con2gm_; }
 }  // extern "C"

@@ -407,3 +407,61 @@ def test_two_contexts_are_independent(oracle):
         assert np.array_equal(cc.patch_safety_arr_, oracle.process_safety_patch(ga_b200.gen_map(dim, seed), 100, 130, 10))
     a.close()
     b.close()
+
+
+def _sensor_window(rng, dim):
+    w = np.full((dim, dim), 127, np.uint8)
+    m = rng.random((dim, dim))
+    w[m < 0.45] = 255
+    w[m > 0.9] = 0
+    w[rng.integers(0, dim, 40), rng.integers(0, dim, 40)] = rng.integers(1, 255, 40)  # values cartograph must ignore
+    return w
+
+
+def test_cartographing_matches_oracle(planner, oracle):
+    """ga_cart_* (Cartographing::resetPatch / cartograph / passLocalMap / loadPrevPatch) against the
+    oracle, which tests/test_ref_pins_oracle.py pins on the reference's own cartographing.cpp:
+    accumulated map and collision-checker patch bit for bit, windows overhanging every edge, patch
+    moves in every direction and with changing patch sizes."""
+    ctx, cc, astar = planner
+    rng = np.random.default_rng(77)
+    dim = 600
+    cc.initialize(dim)
+    cart_api = ga_b200.Cartographing(ctx)
+    cart_api.resetPatch(dim)
+    cart = np.full((dim, dim), 127, np.uint8)
+    cc_patch = ctx.download(_abi.GRID_PATCH)
+    assert np.all(cc_patch == 127)
+    for ox, oy, wd in [(100, 120, 201), (150, 90, 201), (-30, 200, 101), (520, 300, 101), (250, -40, 151), (260, 500, 151),
+                       (0, 0, 600), (399, 399, 201), (-700, 0, 50), (3, 5, 1)]:
+        win = _sensor_window(rng, wd)
+        cart_api.cartograph(win, (ox, oy))
+        oracle.cartograph(cart, win, ox, oy)
+        assert np.array_equal(cart_api.getMap(), cart)
+    for ox, oy, wd in [(100, 120, 201), (0, 0, 600), (399, 399, 201), (10, 300, 300)]:
+        cart_api.passLocalMap((ox, oy), wd)
+        oracle.pass_local_map(cc_patch, cart[oy:oy + wd, ox:ox + wd], ox, oy)
+        assert np.array_equal(ctx.download(_abi.GRID_PATCH), cc_patch)
+    with pytest.raises(ga_b200.GaError):
+        cart_api.passLocalMap((500, 0), 200)  # leaves the map: the reference's out-of-bounds read
+    # the safety pipeline runs on what the cartographed map handed over
+    cc.processSafetyPatch()
+    assert np.array_equal(cc.patch_safety_arr_, oracle.process_safety_patch(cc_patch, 100, 130, cc.disk_r_c_))
+    prev_utm = np.array([1000.0, 2000.0])
+    c2g = 6.4
+    for k, (shift, ndim) in enumerate([((12.3, -7.9), 600), ((-20.0, 15.5), 600), ((5.1, 5.1), 520), ((-3.3, 30.2), 700),
+                                       ((200.0, 0.0), 600)]):
+        utm = prev_utm + np.array(shift)
+        cc.initialize(ndim)           # CollisionChecker::resetPatch + AStar::reinit of create_patch
+        cart_api.resetPatch(ndim)
+        cart_api.loadPrevPatch(prev_utm, utm)
+        nxt = np.full((ndim, ndim), 127, np.uint8)
+        oracle.copy_patch_to_patch(cart, [ga_b200.Cartographing._to_int(v * c2g) for v in prev_utm], nxt,
+                                   [ga_b200.Cartographing._to_int(v * c2g) for v in utm])
+        assert np.array_equal(cart_api.getMap(), nxt), k
+        assert np.array_equal(ctx.download(_abi.GRID_PATCH), nxt), k
+        cart, prev_utm = nxt, utm
+        win = _sensor_window(rng, 201)
+        cart_api.cartograph(win, (50 + 10 * k, 60))
+        oracle.cartograph(cart, win, 50 + 10 * k, 60)
+        assert np.array_equal(cart_api.getMap(), cart)

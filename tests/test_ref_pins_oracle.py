@@ -198,3 +198,62 @@ def test_voronoi_potential_field(variant, ego):
         assert np.array_equal(gr.get_grid(gr.VORONOI_DIST), o_vd)
         assert np.array_equal(gr.get_grid(gr.H_PROX), o_prox, equal_nan=True)
         assert np.array_equal(gr.get_grid(gr.MOTION_RES), o_mres)
+
+
+def _cround(v):
+    return int(math.copysign(math.floor(abs(v) + 0.5), v))
+
+
+def _sensor_window(rng, dim):
+    """a window as the simulator's ray-cast produces it: 0 = occupied, 255 = free, 127 = unknown"""
+    w = np.full((dim, dim), 127, np.uint8)
+    m = rng.random((dim, dim))
+    w[m < 0.45] = 255
+    w[m > 0.9] = 0
+    w[rng.integers(0, dim, 40), rng.integers(0, dim, 40)] = rng.integers(1, 255, 40)  # values cartograph must ignore
+    return w
+
+
+def test_cartographing_vs_reference():
+    """Cartographing::resetPatch / cartograph / passLocalMap / loadPrevPatch
+    (LIB/src/cartographing_lib/cartographing.cpp) against gao_cartograph, gao_copy_patch_to_patch
+    and gao_pass_local_map: the accumulated map and the collision checker's patch bit for bit,
+    over windows that overhang every patch edge and patch moves in every direction."""
+    rng = np.random.default_rng(77)
+    dim = 600
+    gr.init(dim, veh=VEH)
+    gr.cart_reset(dim)
+    cart = np.full((dim, dim), 127, np.uint8)
+    cc_patch = gr.get_grid(gr.PATCH).copy()
+    for k, (ox, oy, wd) in enumerate([(100, 120, 201), (150, 90, 201), (-30, 200, 101), (520, 300, 101), (250, -40, 151),
+                                      (260, 500, 151), (0, 0, 600), (399, 399, 201)]):
+        win = _sensor_window(rng, wd)
+        gr.cartograph(win, ox, oy)
+        go.cartograph(cart, win, ox, oy)
+        assert np.array_equal(gr.cart_get(), cart), "cartograph %d" % k
+    # passLocalMap: window of the accumulated map into the collision checker's patch (inside windows;
+    # the reference memcpy's rows without a bounds check, so overhanging windows are its UB)
+    for ox, oy, wd in [(100, 120, 201), (0, 0, 600), (399, 399, 201), (10, 300, 300)]:
+        gr.cart_pass_local_map(ox, oy, wd)
+        go.pass_local_map(cc_patch, cart[oy:oy + wd, ox:ox + wd], ox, oy)
+        assert np.array_equal(gr.get_grid(gr.PATCH), cc_patch)
+    # patch moves: resetPatch saves the old map, loadPrevPatch copies the overlap and hands the new map over
+    c2g = gr.con2gm()
+    prev_utm = np.array([1000.0, 2000.0])
+    for k, (shift, ndim) in enumerate([((12.3, -7.9), 600), ((-20.0, 15.5), 600), ((5.1, 5.1), 520), ((-3.3, 30.2), 700),
+                                       ((200.0, 0.0), 600)]):
+        utm = prev_utm + np.array(shift)
+        gr.reinit(ndim)
+        gr.cart_reset(ndim)
+        gr.cart_load_prev(prev_utm, utm)
+        nxt = np.full((ndim, ndim), 127, np.uint8)
+        po = tuple(_cround(v * c2g) for v in prev_utm)   # Point<double>::toInt = std::round (data_structures1.hpp:57-60)
+        no = tuple(_cround(v * c2g) for v in utm)
+        go.copy_patch_to_patch(cart, po, nxt, no)
+        assert np.array_equal(gr.cart_get(), nxt), "loadPrevPatch %d" % k
+        assert np.array_equal(gr.get_grid(gr.PATCH), nxt)
+        cart, prev_utm = nxt, utm
+        win = _sensor_window(rng, 201)
+        gr.cartograph(win, 50 + 10 * k, 60)
+        go.cartograph(cart, win, 50 + 10 * k, 60)
+        assert np.array_equal(gr.cart_get(), cart)
