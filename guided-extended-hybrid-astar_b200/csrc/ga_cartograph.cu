@@ -100,6 +100,24 @@ extern "C" int ga_cartograph(ga_ctx* c, const uint8_t* window, int ox, int oy, i
   return GA_OK;
 }
 
+// cartograph for a window that is already on the device: the ray-cast result of ga_raytrace
+// (simulation.py:262-277 feeds gmSimulation's output straight into Cartographing::cartograph)
+extern "C" int ga_cartograph_raytraced(ga_ctx* c, int ox, int oy)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->d_cart != nullptr, GA_ERR_STATE, "no cartographed patch (call ga_cart_reset)");
+  GA_REQUIRE(c, c->d_pmap != nullptr, GA_ERR_STATE, "no ray-cast window (call ga_raytrace)");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int dim = 801;  // GM_DIM, gridmap_sim.hpp:17
+  {
+    ga_launch_scope ls(c, GA_K_CARTOGRAPH);
+    const long long threads = (long long)((dim + 3) / 4) * dim;
+    cartograph_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, c->stream>>>(c->d_cart, c->cart_dim, c->d_pmap, ox, oy, dim);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  return GA_OK;
+}
+
 // CollisionChecker::passLocalMapData's clipping (collision_checking.cpp:287-301) for a source that
 // already lives on the device: the whole window is dropped when it overhangs the collision
 // checker's patch in x, rows outside are skipped

@@ -93,6 +93,7 @@ extern "C" int ga_destroy(ga_ctx* c)
   cudaStreamSynchronize(c->stream);
   free_grids(c);
   ga_cart_free(c);
+  ga_rt_free(c);
   if (c->d_centers) cudaFree(c->d_centers);
   if (c->d_stage) cudaFree(c->d_stage);
   if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -310,6 +311,7 @@ static int grid_lookup(const ga_ctx* c, int id, void** p, size_t* bytes)
   {
     case GA_GRID_PATCH: *p = c->d_patch; *bytes = np; return 0;
     case GA_GRID_CART: *p = c->d_cart; *bytes = (size_t)c->cart_dim * c->cart_dim; return 0;
+    case GA_GRID_PMAP: *p = c->d_pmap; *bytes = c->d_pmap ? (size_t)801 * 801 : 0; return 0;
     case GA_GRID_SAFETY: *p = c->d_safety; *bytes = np; return 0;
     case GA_GRID_ASTAR: *p = c->d_astar; *bytes = na; return 0;
     case GA_GRID_GEOFENCE: *p = c->d_fence; *bytes = na; return 0;

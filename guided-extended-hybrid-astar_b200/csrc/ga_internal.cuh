@@ -73,6 +73,12 @@ struct ga_ctx
   uint8_t* d_cart_prev = nullptr;
   int cart_dim = 0, cart_prev_dim = 0;
 
+  // ---- simulated lidar (GridMapSim): precast lists, ground-truth window, result window
+  int* d_rt_entries = nullptr;
+  int* d_rt_offsets = nullptr;
+  uint8_t* d_rt_gt = nullptr;
+  uint8_t* d_pmap = nullptr;
+
   // ---- heuristic scratch
   int tiles_x = 0, n_tiles = 0;
   int* d_tile_active = nullptr;   // per-tile state word (idle / queued / running / dirty)
@@ -137,3 +143,4 @@ int ga_stage_reserve(ga_ctx* ctx, size_t bytes);
 int ga_heur_alloc(ga_ctx* ctx);
 void ga_heur_free(ga_ctx* ctx);
 void ga_cart_free(ga_ctx* ctx);
+void ga_rt_free(ga_ctx* ctx);

@@ -42,12 +42,12 @@ assert NODE_DTYPE.itemsize == 40 and SUCC_DTYPE.itemsize == 48
 
 # ga_grid_id
 GRID_PATCH, GRID_SAFETY, GRID_ASTAR, GRID_GEOFENCE, GRID_MOVEMENT_COST, GRID_H_PROX, \
-    GRID_MOTION_RES, GRID_OBSTACLE_DIST, GRID_VORONOI_DIST, GRID_CART = range(10)
+    GRID_MOTION_RES, GRID_OBSTACLE_DIST, GRID_VORONOI_DIST, GRID_CART, GRID_PMAP = range(11)
 GRID_HEUR_COST, GRID_HEUR_DIST, GRID_HEUR_PARENT, GRID_HEUR_FLAGS = 16, 18, 20, 22
 GRID_DTYPES = {GRID_PATCH: np.uint8, GRID_SAFETY: np.uint8, GRID_ASTAR: np.uint8,
                GRID_GEOFENCE: np.uint8, GRID_MOVEMENT_COST: np.float64, GRID_H_PROX: np.float64,
                GRID_MOTION_RES: np.float64, GRID_OBSTACLE_DIST: np.float32,
-               GRID_VORONOI_DIST: np.float32, GRID_CART: np.uint8}
+               GRID_VORONOI_DIST: np.float32, GRID_CART: np.uint8, GRID_PMAP: np.uint8}
 for _s in (0, 1):
     GRID_DTYPES[GRID_HEUR_COST + _s] = np.float64
     GRID_DTYPES[GRID_HEUR_DIST + _s] = np.float64
@@ -55,7 +55,7 @@ for _s in (0, 1):
     GRID_DTYPES[GRID_HEUR_FLAGS + _s] = np.uint8
 
 K_PACK, K_DILATE, K_HEUR_INIT, K_HEUR_RELAX, K_HEUR_FINISH, K_COLLISION, K_EXPAND, K_DT, \
-    K_POTENTIAL, K_CARTOGRAPH, K_COUNT = range(11)
+    K_POTENTIAL, K_CARTOGRAPH, K_RAYTRACE, K_COUNT = range(12)
 DT_FIXEDPOINT, DT_IPPFLOAT = 0, 1
 H_CLOSED, H_UNKNOWN = 1, 2
 
@@ -82,6 +82,8 @@ SYMBOLS = {
     "ga_cart_pass_local_map": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "ga_cart_load_prev": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int]),
     "ga_cart_dim": (C.c_int, [_P]),
+    "ga_raytrace": (C.c_int, [_P, C.c_void_p, C.c_void_p]),
+    "ga_cartograph_raytraced": (C.c_int, [_P, C.c_int, C.c_int]),
     "ga_build_heuristic": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ga_build_heuristic_batch": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "ga_potential_sites": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.POINTER(C.c_int)]),

@@ -172,6 +172,8 @@ class GridContext:
             d = self.lib.ga_patch_dim(self.h)
         elif gid == _abi.GRID_CART:
             d = self.lib.ga_cart_dim(self.h)
+        elif gid == _abi.GRID_PMAP:
+            d = 801
         elif gid in (_abi.GRID_OBSTACLE_DIST, _abi.GRID_VORONOI_DIST):
             nb = C.c_size_t()
             self.check(self.lib.ga_grid_bytes(self.h, gid, C.byref(nb)))
@@ -344,6 +346,10 @@ class Cartographing:
         dim = w.shape[0] if dim is None else int(dim)
         self.ctx.check(self.ctx.lib.ga_cartograph(self.ctx.h, _abi.ptr(w), int(origin[0]), int(origin[1]), dim))
 
+    def cartographRaytraced(self, origin):
+        """cartograph of the window ga_raytrace left on the device (no host round trip)"""
+        self.ctx.check(self.ctx.lib.ga_cartograph_raytraced(self.ctx.h, int(origin[0]), int(origin[1])))
+
     def passLocalMap(self, origin, dim):
         self.ctx.check(self.ctx.lib.ga_cart_pass_local_map(self.ctx.h, int(origin[0]), int(origin[1]), int(dim)))
 
@@ -360,6 +366,23 @@ class Cartographing:
 
     def getMap(self):
         return self.ctx.download(_abi.GRID_CART)
+
+
+class GridMapSim:
+    """Mirror of the reference's GridMapSim (LIB/include/gridmap_sim_lib/gridmap_sim.hpp:92-112):
+    the simulated lidar ray-cast on an 801 x 801 ground-truth window."""
+    GM_DIM = 801
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def gmSimulation(self, grid_map_gt, fetch=True):
+        gt = np.ascontiguousarray(grid_map_gt, np.uint8)
+        if gt.shape != (self.GM_DIM, self.GM_DIM):
+            raise ValueError("grid_map_gt must be 801 x 801 (GM_DIM)")
+        out = np.empty_like(gt) if fetch else None
+        self.ctx.check(self.ctx.lib.ga_raytrace(self.ctx.h, _abi.ptr(gt), _abi.ptr(out) if fetch else None))
+        return out
 
 
 class NodeDisc:

@@ -67,6 +67,7 @@ typedef enum
   GA_GRID_OBSTACLE_DIST = 7,  /* f32 vor_dim^2     AStar::obstacle_dist_                   */
   GA_GRID_VORONOI_DIST = 8,   /* f32 vor_dim^2     AStar::voronoi_dist_                    */
   GA_GRID_CART = 9,           /* u8  cart_dim^2    Cartographing::patch_arr_ (accumulated map) */
+  GA_GRID_PMAP = 10,          /* u8  801^2         GridMapSim::pmap_ (last ray-cast window)    */
   /* heuristic result planes, slot 0 = closed_set_guidance_, slot 1 = closed_set_path_
    * (dense restatement of std::unordered_map<size_t, NodeDisc>, a_star.hpp:69-72,
    * NodeDisc data_structures2.hpp:47-67): id = base + slot */
@@ -144,6 +145,17 @@ GA_API int ga_cartograph(ga_ctx* ctx, const uint8_t* window, int ox, int oy, int
 GA_API int ga_cart_pass_local_map(ga_ctx* ctx, int ox, int oy, int dim);
 GA_API int ga_cart_load_prev(ga_ctx* ctx, int prev_ox, int prev_oy, int ox, int oy);
 GA_API int ga_cart_dim(const ga_ctx* ctx);
+
+/* GridMapSim::gmSimulation / raytracing (LIB/src/gridmap_sim_lib/gridmap_sim.cpp:42-103, SURVEY.md
+ * 8(f) rank 2): the simulated lidar of the unknown-environment loop.  grid_map_gt = 801 x 801 u8
+ * ground-truth window around the ego cell in host memory (255 = occupied); result: 0 free up to the
+ * first occupied cell of each of the 180 two-degree sectors, 255 that cell, 127 behind it.  It stays
+ * on the device (GA_GRID_PMAP) and is also copied to pmap_out when that is not NULL.
+ * ga_cartograph_raytraced = Cartographing::cartograph of that device-resident window at (ox, oy)
+ * (simulation.py:262-277 -> planning.py): the cycle window -> ray-cast -> merge -> hand-over ->
+ * safety grid never leaves the GPU after the ground-truth upload. */
+GA_API int ga_raytrace(ga_ctx* ctx, const uint8_t* grid_map_gt, uint8_t* pmap_out);
+GA_API int ga_cartograph_raytraced(ga_ctx* ctx, int ox, int oy);
 
 /* ---- footprint collision checks ------------------------------------------------------------ */
 
@@ -272,7 +284,8 @@ typedef enum
   GA_K_DT = 7,
   GA_K_POTENTIAL = 8,
   GA_K_CARTOGRAPH = 9, /* window merge / patch-to-patch copy of the accumulated map */
-  GA_K_COUNT = 10
+  GA_K_RAYTRACE = 10,  /* simulated lidar ray-cast */
+  GA_K_COUNT = 11
 } ga_kernel_id;
 
 GA_API int ga_prof_enable(ga_ctx* ctx, int on);

@@ -131,6 +131,31 @@ def copy_patch_to_patch(prev, prev_o, nxt, o):
                                   int(o[0]), int(o[1]))
 
 
+GM_DIM = 801
+
+
+def precast_lists():
+    off = np.zeros(181, np.int32)
+    ent = np.zeros(2 * GM_DIM * GM_DIM + 4096, np.int32)
+    n = lib().gao_precast_lists(_p(ent), ent.size, _p(off))
+    assert n <= ent.size
+    return ent[:n].copy(), off
+
+
+_PRECAST = None
+
+
+def raytrace(grid_map_gt):
+    """GridMapSim::raytracing (gridmap_sim.cpp:42-80) on an 801 x 801 window"""
+    global _PRECAST
+    if _PRECAST is None:
+        _PRECAST = precast_lists()
+    gt = np.ascontiguousarray(grid_map_gt, np.uint8)
+    out = np.empty((GM_DIM, GM_DIM), np.uint8)
+    lib().gao_raytrace(_p(gt), _p(_PRECAST[0]), _p(_PRECAST[1]), _p(out))
+    return out
+
+
 def calc_disks(length, width, lb, len_per_disk=2.0, double_rows=False, safety=0.1, yaw_res_deg=3):
     info = DisksInfo()
     cen = np.zeros(360 * 32 * 2, np.int32)

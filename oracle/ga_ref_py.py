@@ -66,6 +66,9 @@ def lib():
         L.gar_cart_load_prev.argtypes = [C.c_double] * 4
         L.gar_cart_get.argtypes = [C.c_void_p, C.c_size_t]
         L.gar_con2gm.restype = C.c_double
+        L.gar_raytrace.argtypes = [C.c_void_p, C.c_void_p]
+        L.gar_precast_lists.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.gar_gm_last_error.restype = C.c_char_p
         L.gar_voronoi_endpoints.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_int]
         L.gar_check_grid.argtypes = [C.c_int] * 4
         L.gar_check_pose.argtypes = [C.c_double] * 3 + [C.c_int]
@@ -226,6 +229,28 @@ def cart_get():
 
 def con2gm():
     return lib().gar_con2gm()
+
+
+GM_DIM = 801  # gridmap_sim.hpp:17
+
+
+def raytrace(grid_map_gt):
+    """GridMapSim::raytracing on an 801 x 801 ground-truth window (0 free / 255 occupied)"""
+    gt = np.ascontiguousarray(grid_map_gt, np.uint8)
+    assert gt.shape == (GM_DIM, GM_DIM)
+    out = np.empty((GM_DIM, GM_DIM), np.uint8)
+    if lib().gar_raytrace(_p(gt), _p(out)) < 0:
+        raise RuntimeError("reference: " + lib().gar_gm_last_error().decode())
+    return out
+
+
+def precast_lists():
+    """the reference's 180 distance-sorted precast lists, flattened: (entries = ix * 801 + iy, offsets[181])"""
+    off = np.zeros(181, np.int32)
+    ent = np.zeros(2 * GM_DIM * GM_DIM + 4096, np.int32)
+    n = lib().gar_precast_lists(_p(ent), ent.size, _p(off))
+    assert n <= ent.size
+    return ent[:n].copy(), off
 
 
 def yaw_idx(yaw):

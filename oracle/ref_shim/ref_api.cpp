@@ -375,4 +375,5 @@ int gar_cart_get(uint8_t* dst, size_t bytes)
   return 0;
 }
 double gar_con2gm() { return grid_tf::con2gm_; }
+
 }  // extern "C"

@@ -465,3 +465,59 @@ def test_cartographing_matches_oracle(planner, oracle):
         cart_api.cartograph(win, (50 + 10 * k, 60))
         oracle.cartograph(cart, win, 50 + 10 * k, 60)
         assert np.array_equal(cart_api.getMap(), cart)
+
+
+def test_raytracing_matches_oracle(planner, oracle):
+    """ga_raytrace (GridMapSim::gmSimulation) against the oracle pinned on the reference's
+    gridmap_sim.cpp: bit-exact windows for empty, sparse, walled, dense and full ground truths."""
+    ctx, cc, astar = planner
+    sim = ga_b200.GridMapSim(ctx)
+    rng = np.random.default_rng(5)
+    for density, walls in [(0.0, False), (0.0005, True), (0.01, True), (0.2, False), (1.0, False)]:
+        gt = np.where(rng.random((801, 801)) < density, 255, 0).astype(np.uint8)
+        if walls:
+            gt[rng.integers(0, 801), 100:700] = 255
+            gt[150:650, rng.integers(0, 801)] = 255
+        got = sim.gmSimulation(gt)
+        assert np.array_equal(got, oracle.raytrace(gt))
+        assert np.array_equal(ctx.download(_abi.GRID_PMAP), got)
+    gt = np.zeros((801, 801), np.uint8)
+    gt[400, 400] = 255
+    assert np.array_equal(sim.gmSimulation(gt), oracle.raytrace(gt))
+    with pytest.raises(ValueError):
+        sim.gmSimulation(np.zeros((800, 800), np.uint8))
+
+
+def test_unknown_environment_cycle(planner, oracle):
+    """BASELINE config 3, one vehicle driving through an unknown map: per cycle ray-cast the 801^2
+    ground-truth window around the ego cell, merge it into the accumulated map, hand the window to the
+    collision checker, rebuild safety + pooled grid (simulation.py:262-277, planning.py:595-603).
+    Device-resident chain (ga_raytrace -> ga_cartograph_raytraced -> ga_cart_pass_local_map ->
+    ga_build_safety) against the oracle's chain, every cycle, every grid, bit for bit."""
+    ctx, cc, astar = planner
+    dim = 1492
+    world = ga_b200.gen_map(2600, 31)
+    world = np.where(world == 255, 255, 0).astype(np.uint8)  # ground truth: occupied or free
+    cc.initialize(dim)
+    cart_api, sim = ga_b200.Cartographing(ctx), ga_b200.GridMapSim(ctx)
+    cart_api.resetPatch(dim)
+    cart = np.full((dim, dim), 127, np.uint8)
+    patch = np.full((dim, dim), 127, np.uint8)
+    patch_origin = np.array([500, 400])      # patch origin inside the world, gm cells
+    for cyc in range(6):
+        ego = patch_origin + np.array([420 + 35 * cyc, 430 + 20 * cyc])   # ego cell in the world
+        gt = world[ego[1] - 400:ego[1] + 401, ego[0] - 400:ego[0] + 401]
+        win_o = ego - patch_origin - 400      # window origin inside the patch
+        sim.gmSimulation(gt, fetch=False)
+        cart_api.cartographRaytraced(win_o)
+        cart_api.passLocalMap(win_o, 801)
+        cc.processSafetyPatch()
+        pm = oracle.raytrace(gt)
+        oracle.cartograph(cart, pm, win_o[0], win_o[1])
+        oracle.pass_local_map(patch, cart[win_o[1]:win_o[1] + 801, win_o[0]:win_o[0] + 801], win_o[0], win_o[1])
+        want = oracle.process_safety_patch(patch, 100, 130, cc.disk_r_c_)
+        assert np.array_equal(cart_api.getMap(), cart), cyc
+        assert np.array_equal(ctx.download(_abi.GRID_PATCH), patch), cyc
+        assert np.array_equal(cc.patch_safety_arr_, want), cyc
+        assert np.array_equal(astar.astar_grid_, oracle.pool_max(want)), cyc
+    assert (cart != 127).mean() > 0.05

@@ -257,3 +257,29 @@ def test_cartographing_vs_reference():
         gr.cartograph(win, 50 + 10 * k, 60)
         go.cartograph(cart, win, 50 + 10 * k, 60)
         assert np.array_equal(gr.cart_get(), cart)
+
+
+def _gt_window(rng, density, walls=True):
+    gt = np.where(rng.random((801, 801)) < density, 255, 0).astype(np.uint8)
+    if walls:
+        gt[rng.integers(0, 801), 100:700] = 255
+        gt[150:650, rng.integers(0, 801)] = 255
+    return gt
+
+
+def test_raytracing_vs_reference():
+    """GridMapSim::calculatePrecasts / raytracing (LIB/src/gridmap_sim_lib/gridmap_sim.cpp:14-80)
+    against gao_precast_lists / gao_raytrace: the 180 sorted precast lists entry for entry (their
+    order under equal distances is std::sort's), and the ray-cast window bit for bit."""
+    e_ref, o_ref = gr.precast_lists()
+    e_orc, o_orc = go.precast_lists()
+    assert np.array_equal(o_ref, o_orc) and np.array_equal(e_ref, e_orc)
+    rng = np.random.default_rng(5)
+    for density, walls in [(0.0, False), (0.0005, True), (0.01, True), (0.2, False), (1.0, False)]:
+        gt = _gt_window(rng, density, walls)
+        want = gr.raytrace(gt)
+        assert np.array_equal(go.raytrace(gt), want)
+        assert set(np.unique(want)) <= {0, 127, 255}
+    gt = np.zeros((801, 801), np.uint8)
+    gt[400, 400] = 255  # the sensor cell itself: every list starts there
+    assert np.array_equal(go.raytrace(gt), gr.raytrace(gt))
