@@ -339,7 +339,7 @@ extern "C" int ga_grid_bytes(const ga_ctx* c, int grid_id, size_t* bytes)
 extern "C" int ga_device_ptr(ga_ctx* c, int grid_id, void** dptr)
 {
   if (!c || !dptr) return GA_ERR_ARG;
-  GA_REQUIRE(c, c->patch_dim > 0, GA_ERR_STATE, "no patch (call ga_patch_reset)");
+  GA_REQUIRE(c, c->patch_dim > 0 || grid_id == GA_GRID_CART || grid_id == GA_GRID_PMAP, GA_ERR_STATE, "no patch (call ga_patch_reset)");
   size_t b;
   GA_REQUIRE(c, grid_lookup(c, grid_id, dptr, &b) == 0, GA_ERR_ARG, "unknown grid id");
   return GA_OK;
@@ -349,7 +349,7 @@ extern "C" int ga_upload(ga_ctx* c, int grid_id, const void* src, size_t bytes)
 {
   if (!c) return GA_ERR_ARG;
   GA_REQUIRE(c, src, GA_ERR_ARG, "null source");
-  GA_REQUIRE(c, c->patch_dim > 0, GA_ERR_STATE, "no patch (call ga_patch_reset)");
+  GA_REQUIRE(c, c->patch_dim > 0 || grid_id == GA_GRID_CART || grid_id == GA_GRID_PMAP, GA_ERR_STATE, "no patch (call ga_patch_reset)");
   void* p;
   size_t b;
   GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");
@@ -365,7 +365,7 @@ extern "C" int ga_download(ga_ctx* c, int grid_id, void* dst, size_t bytes)
 {
   if (!c) return GA_ERR_ARG;
   GA_REQUIRE(c, dst, GA_ERR_ARG, "null destination");
-  GA_REQUIRE(c, c->patch_dim > 0, GA_ERR_STATE, "no patch (call ga_patch_reset)");
+  GA_REQUIRE(c, c->patch_dim > 0 || grid_id == GA_GRID_CART || grid_id == GA_GRID_PMAP, GA_ERR_STATE, "no patch (call ga_patch_reset)");
   void* p;
   size_t b;
   GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");

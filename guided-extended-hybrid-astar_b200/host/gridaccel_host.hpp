@@ -392,6 +392,19 @@ private:
   std::vector<int> disk_centers_;
 };
 
+// GridMapSim (LIB/include/gridmap_sim_lib/gridmap_sim.hpp:92-112): simulated lidar ray-cast on an
+// 801 x 801 ground-truth window; the result also stays on the device for Cartographing::cartographRaytraced
+class GridMapSim
+{
+public:
+  static constexpr size_t GM_DIM = 801;
+  explicit GridMapSim(Context& ctx) : ctx_(ctx) {}
+  void gmSimulation(const uint8_t* grid_map_gt, uint8_t* pmap_out) { ctx_.check(ga_raytrace(ctx_.handle(), grid_map_gt, pmap_out)); }
+
+private:
+  Context& ctx_;
+};
+
 // Cartographing (LIB/include/cartographing_lib/cartographing.hpp:19-41): the accumulated map of the
 // unknown-environment loop, device-resident.  Same member names; the map itself is fetched on demand.
 class Cartographing
@@ -404,6 +417,7 @@ public:
   {
     ctx_.check(ga_cartograph(ctx_.handle(), local_map.getPtr(), origin.x, origin.y, dim));
   }
+  void cartographRaytraced(const Point<int>& origin) { ctx_.check(ga_cartograph_raytraced(ctx_.handle(), origin.x, origin.y)); }
   void passLocalMap(const Point<int>& origin, int dim)                                            // :98-117
   {
     ctx_.check(ga_cart_pass_local_map(ctx_.handle(), origin.x, origin.y, dim));

@@ -69,3 +69,32 @@ def test_motion_primitives(oracle):
         n = int(n)
         assert np.array_equal(oracle.turn_on_rear_axis(yaw, delta, 3.0), R["C_ra_out"][o:o + n])
         o += n
+
+
+def test_unknown_environment_rows(oracle):
+    """tests/golden/ref_golden_env.npz (the reference's own gridmap_sim.cpp + cartographing.cpp, see
+    make_ref_golden_env.py) against the oracle: ray-cast windows, accumulated map, collision-checker
+    patch and the map carried over a patch move, bit for bit."""
+    import importlib.util
+    import os
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    spec = importlib.util.spec_from_file_location("make_ref_golden_env", os.path.join(here, "make_ref_golden_env.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    g = np.load(os.path.join(here, "ref_golden_env.npz"))
+    world = gen.make_world()
+    dim = gen.DIM
+    cart = np.full((dim, dim), 127, np.uint8)
+    patch = np.full((dim, dim), 127, np.uint8)
+    for cyc in range(3):
+        gt, wo = gen.cycle_inputs(world, cyc)
+        pm = oracle.raytrace(gt)
+        assert np.array_equal(pm, g["pmap_%d" % cyc])
+        oracle.cartograph(cart, pm, wo[0], wo[1])
+        oracle.pass_local_map(patch, cart[wo[1]:wo[1] + 801, wo[0]:wo[0] + 801], wo[0], wo[1])
+    assert np.array_equal(cart, g["cart"]) and np.array_equal(patch, g["patch"])
+    prev_utm, utm = g["moved_utm"]
+    rnd = lambda v: int(np.copysign(np.floor(abs(v) + 0.5), v))  # noqa: E731  Point<double>::toInt = std::round
+    nxt = np.full((dim, dim), 127, np.uint8)
+    oracle.copy_patch_to_patch(cart, [rnd(v * 6.4) for v in prev_utm], nxt, [rnd(v * 6.4) for v in utm])
+    assert np.array_equal(nxt, g["cart_moved"])
