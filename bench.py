@@ -302,6 +302,72 @@ def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak):
     return out
 
 
+def run_replan_leg(ga, device, args):
+    """BASELINE config 3's shape: the unknown-environment replanning cycle on the default scenario's
+    patch size (1492^2, astar 373^2).  One cycle = ray-cast the 801^2 ground-truth window (host buffer
+    in), merge it into the accumulated map, hand the window to the collision checker, rebuild the
+    safety + pooled grids and the guidance heuristic.  Timed end to end on the host clock; the
+    reference's own code for the same cycle (gridmap_sim.cpp, cartographing.cpp,
+    collision_checking.cpp, a_star.cpp) on one core beside it."""
+    from ga_b200 import _abi
+    dim = 1492
+    world = ga.gen_map(2600, 31)
+    world = np.where(world == 255, 255, 0).astype(np.uint8)
+    origin = np.array([500, 400])
+    cycles = [(origin + np.array([420 + 7 * k, 430 + 4 * k])) for k in range(30)]
+    wins = [np.ascontiguousarray(world[e[1] - 400:e[1] + 401, e[0] - 400:e[0] + 401]) for e in cycles]
+    ctx = ga.GridContext(device)
+    cfg = ga.LibConfig()
+    astar = ga.AStar(ctx, cfg)
+    cc = ga.CollisionChecker(ctx, ga.Vehicle.from_config(ga.VehConfig()), cfg)
+    cc.initialize(dim)
+    cart, sim = ga.Cartographing(ctx), ga.GridMapSim(ctx)
+    cart.resetPatch(dim)
+    goal = (300, 60)
+
+    def cycle(k):
+        wo = cycles[k] - origin - 400
+        sim.gmSimulation(wins[k], fetch=False)
+        cart.cartographRaytraced(wo)
+        cart.passLocalMap(wo, 801)
+        cc.processSafetyPatch()
+        ctx.check(ctx.lib.ga_build_heuristic(ctx.h, 0, goal[0], goal[1], None))
+
+    for k in range(3):
+        cycle(k)
+    ctx.sync()
+    t0 = time.perf_counter()
+    for k in range(3, len(cycles)):
+        cycle(k)
+    ctx.sync()
+    dt = (time.perf_counter() - t0) / (len(cycles) - 3)
+    out = {"workload": "unknown-environment cycle on a 1492^2 patch: 801^2 ray-cast + map merge + hand-over + safety/pool + 373^2 heuristic",
+           "cycles_per_s": 1.0 / dt, "ms_per_cycle": dt * 1e3, "h2d_bytes_per_cycle": 801 * 801}
+    ctx.close()
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import ga_ref_py as gr
+        if gr.available():
+            gr.init(dim)
+            gr.cart_reset(dim)
+            gr.set_heuristic_config(early_exit=False, max_extra_nodes=1 << 30, unknown_cost_w=0.0)
+            L = gr.lib()
+            ts = []
+            for k in range(6):
+                wo = cycles[k] - origin - 400
+                t0 = time.perf_counter()
+                pm = gr.raytrace(wins[k])
+                gr.cartograph(pm, wo[0], wo[1])
+                gr.cart_pass_local_map(wo[0], wo[1], 801)
+                gr.process_safety_patch()
+                gr.calc_astar_grid()
+                L.gar_calc_distance_heuristic(goal[0], goal[1], goal[0], goal[1], 0, 0)
+                ts.append(time.perf_counter() - t0)
+            out["cpu_reference_ms_per_cycle"] = 1e3 * float(np.median(ts[1:]))
+            out["cpu_reference_sample"] = "5 cycles of the same chain through the reference's own code, 1 core, median"
+    return out
+
+
 def run_collision_leg(env, args, ga):
     """BASELINE metric M3 (collision checks/s) on environment 0 (4096^2 patch, 3-disk footprint):
     (a) pose checks through ga_check_poses: host pose arrays in, first-hit index per segment out, one
@@ -366,6 +432,7 @@ def main():
     ap.add_argument("--ref-procs", type=int, default=64, help="planner processes of the reference arm (capped by the host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-collision", action="store_true", help="skip the collision-checks/s leg")
+    ap.add_argument("--no-replan", action="store_true", help="skip the unknown-environment cycle leg")
     ap.add_argument("--batch", type=int, default=32, help="queries of the batched-heuristic leg (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -463,6 +530,7 @@ def main():
     e2e_dev_ms, e2e_wall_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
     collision = run_collision_leg(envs[0], args, ga_b200) if (rank == 0 and not args.no_collision) else None
+    replan = run_replan_leg(ga_b200, local_rank, args) if (rank == 0 and not args.no_replan) else None
     sampler.stop_flag = True
 
     # max over ranks
@@ -507,6 +575,8 @@ def main():
             line["batch"] = batch
         if collision:
             line["collision"] = collision
+        if replan:
+            line["replan_cycle"] = replan
         if not args.no_cpu_baseline:
             # bounded sample of the same step on the host: a 2048^2 patch seeded like environment 0
             dt, n, kind = cpu_reference_steps(2048, [20240], envs[0]["cc"].disk_r_c_)
