@@ -36,7 +36,7 @@ enum
   HC_HEAD = 0,      // ring consumer cursor
   HC_TAIL = 1,      // ring producer cursor
   HC_PENDING = 2,   // tiles queued or running
-  HC_CLOSED = 3,    // closed-cell count, HC_CLOSED + 1: terminal-cell count (finish kernels)
+  HC_CLOSED = 3,    // closed-cell count (finish kernel A)
   HC_VISITS = 8,    // statistics: tile visits, sweeps, visits that improved a cell
   HC_INNER = 9,
   HC_IMPROVING = 10,
@@ -79,8 +79,9 @@ struct heur_args  // finish kernel
   int32_t* parent;
   double* dist;
   uint8_t* flags;
-  int* closed;        // [2] counters of this grid: closed cells, terminal cells
-  int* tlist;         // [ncell / 4 + 1024] finish A: the terminal cells (parent in another 32x32 block)
+  int* closed;        // closed-cell counter of this grid
+  int* tlist;         // [blocks][FIN_SLOTS] finish A: the terminal cells of each 32x32 block (parent in another block)
+  int* tcount;        // [blocks] how many
   unsigned* scratch;  // [ncell] finish A: displacement of the block's terminal cell and (straight, diagonal) steps to it
   int2* tot;          // [ncell] finish B: (straight, diagonal) steps of a terminal cell to the root
   int dim, goal;
@@ -635,6 +636,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
 // ---------------------------------------------------------------------------------------------
 #define FB 32            // finish block edge
 #define FS (FB + 2)      // staged edge incl. halo
+#define FIN_SLOTS 128    // terminal-list slots per block: only its 124 border cells can have their parent outside
 
 // scratch word of a cell: displacement of its block's terminal cell (dx + 32, dy + 32: 6 bits each),
 // straight steps to it (10 bits), diagonal steps (10 bits)
@@ -644,6 +646,26 @@ __device__ __forceinline__ unsigned fin_pack(int dx, int dy, int cs, int cd)
 }
 __device__ __forceinline__ int fin_target(unsigned s, int cell, int dim) { return cell + ((int)((s >> 6) & 63) - 32) * dim + (int)(s & 63) - 32; }
 
+// bit i set: candidate of motion index i reproduces g(n) bit for bit.  Predecessor offsets
+// p = n - motion_[i] (a_star.hpp:52-54): (dx, dy) = (-1,0) (0,-1) (1,0) (0,1) (1,1) (1,-1) (-1,1) (-1,-1)
+template <bool PROX, bool UNK>
+__device__ __forceinline__ unsigned fin_match(const double* sg, const double* sb, const uint8_t* su, const int me, const double gn,
+                                              const double ln1, const double ln2, const double unk_w)
+{
+  constexpr int off[8] = { -1, -FS, 1, FS, FS + 1, -FS + 1, FS - 1, -FS - 1 };
+  unsigned match = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+  {
+    const int q = me + off[i];
+    double cand = sg[q] + (i < 4 ? ln1 : ln2);
+    if (PROX) cand = cand + sb[q];
+    if (UNK) cand = cand + (su[q] ? unk_w : 0.0);
+    match |= (cand == gn ? 1u : 0u) << i;
+  }
+  return match;
+}
+
 __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single, const heur_args* many)
 {
   __shared__ double sg[FS * FS];
@@ -651,13 +673,16 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
   __shared__ uint8_t su[FS * FS];
   __shared__ short lp[FB * FB];  // -1: terminal (parent outside the block, root, or not closed); else parent's local index | step type << 10
   __shared__ int s_cnt[2][FB];   // per warp: closed cells, terminal cells
-  __shared__ int s_base;
   const heur_args& a = many ? many[blockIdx.y] : single;
   const int dim = a.dim, nbx = (dim + FB - 1) / FB;
   if ((int)blockIdx.x >= nbx * nbx) return;  // batches of unequal grids
   const int bx = blockIdx.x % nbx, by = blockIdx.x / nbx;
   const int ox = bx * FB - 1, oy = by * FB - 1;
   const double w_prox = a.w_prox, unk_w = a.unk_w;
+  int any_prox = 0;
+  // the cell's own movement cost: issued with the staging loads, one memory round trip for both
+  const int own_x = bx * FB + (int)(threadIdx.x % FB), own_y = by * FB + (int)(threadIdx.x / FB);
+  const double m_own = (own_x < dim && own_y < dim) ? __ldg(a.mc + (size_t)own_y * dim + own_x) : 0.0;
   for (int i = threadIdx.x; i < FS * FS; i += FB * FB)
   {
     const int x = ox + i % FS, y = oy + i / FS;
@@ -673,8 +698,9 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     sg[i] = gv;
     sb[i] = bv;
     su[i] = u;
+    any_prox |= (bv != 0.0);
   }
-  __syncthreads();
+  const int has_prox = __syncthreads_or(any_prox);
   const int lx = threadIdx.x % FB, ly = threadIdx.x / FB, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nx = ox + 1 + lx, ny = oy + 1 + ly;
   const int me = (ly + 1) * FS + lx + 1;
@@ -694,26 +720,25 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     }
     else
     {
-      const double m = __ldg(a.mc + n);
-      const double ln1 = a.L1 * m, ln2 = a.L2 * m;
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
+      const double ln1 = a.L1 * m_own, ln2 = a.L2 * m_own;
+      // all eight candidates, branch-free (a +inf / off-grid predecessor gives +inf or NaN: no match);
+      // the prox and unknown terms only where the block has any (adding 0.0 changes nothing)
+      unsigned match;
+      if (has_prox) match = (unk_w != 0) ? fin_match<true, true>(sg, sb, su, me, gn, ln1, ln2, unk_w)
+                                         : fin_match<true, false>(sg, sb, su, me, gn, ln1, ln2, unk_w);
+      else match = (unk_w != 0) ? fin_match<false, true>(sg, sb, su, me, gn, ln1, ln2, unk_w)
+                                : fin_match<false, false>(sg, sb, su, me, gn, ln1, ln2, unk_w);
+      if (match)
       {
-        const int dx = -c_mdx[i], dy = -c_mdy[i];  // predecessor p = n - motion_[i]
-        const int q = me + dy * FS + dx;
-        const double gq = sg[q];
-        if (!(gq < INFINITY)) continue;  // off-grid halo cells are +inf as well
-        double cand = gq + (i < 4 ? ln1 : ln2);
-        cand = cand + sb[q];
-        cand = cand + (su[q] ? unk_w : 0.0);
-        if (cand == gn)
-        {
-          par = (ny + dy) * dim + (nx + dx);
-          if (su[q]) fl |= GA_H_UNKNOWN;  // NodeDisc::is_unknown_ = unknown-ness of the parent, :253,268
-          const int plx = lx + dx, ply = ly + dy;
-          if (plx >= 0 && ply >= 0 && plx < FB && ply < FB) lpar = (ply * FB + plx) | (i < 4 ? 0 : 1024);
-          break;
-        }
+        const int i = __ffs(match) - 1;  // canonical parent: smallest motion index
+        // predecessor offset p = n - motion_[i]: dx + 1, dy + 1 packed two bits per index
+        constexpr unsigned DXC = (0u << 0) | (1u << 2) | (2u << 4) | (1u << 6) | (2u << 8) | (2u << 10) | (0u << 12) | (0u << 14);
+        constexpr unsigned DYC = (1u << 0) | (0u << 2) | (1u << 4) | (2u << 6) | (2u << 8) | (0u << 10) | (2u << 12) | (0u << 14);
+        const int dx = (int)((DXC >> (2 * i)) & 3u) - 1, dy = (int)((DYC >> (2 * i)) & 3u) - 1;
+        par = (ny + dy) * dim + (nx + dx);
+        if (su[me + dy * FS + dx]) fl |= GA_H_UNKNOWN;  // NodeDisc::is_unknown_ = unknown-ness of the parent, :253,268
+        const int plx = lx + dx, ply = ly + dy;
+        if (plx >= 0 && ply >= 0 && plx < FB && ply < FB) lpar = (ply * FB + plx) | (i < 4 ? 0 : 1024);
       }
     }
   }
@@ -746,12 +771,12 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     s_cnt[1][lane] = incl - nt;  // exclusive offset of the warp
     if (lane == 31)
     {
-      if (tot_c) atomicAdd(a.closed, tot_c);
-      s_base = incl ? atomicAdd(a.closed + 1, incl) : 0;
+      if (tot_c) atomicAdd(a.closed, tot_c);  // no return value: fire and forget
+      a.tcount[blockIdx.x] = incl;            // the block's slice of the terminal list (no atomic round trip)
     }
   }
   __syncthreads();
-  if (term) a.tlist[s_base + s_cnt[1][warp] + __popc(m_term & ((1u << lane) - 1u))] = n;
+  if (term) a.tlist[blockIdx.x * FIN_SLOTS + s_cnt[1][warp] + __popc(m_term & ((1u << lane) - 1u))] = n;
   // chain walk inside the block (shared memory, one load per hop)
   int cur = threadIdx.x, cs = 0, cd = 0;
   for (int v = lpar; v >= 0; v = lp[cur])
@@ -764,13 +789,12 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
 }
 
 // one thread per terminal cell: terminal -> parent -> that block's terminal -> ... -> root
-__global__ void __launch_bounds__(128) heur_finish_b_kernel(heur_args single, const heur_args* many)
+__global__ void __launch_bounds__(FIN_SLOTS) heur_finish_b_kernel(heur_args single, const heur_args* many)
 {
   const heur_args& a = many ? many[blockIdx.y] : single;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= __ldcg(a.closed + 1)) return;
-  const int dim = a.dim, goal = a.goal;
-  const int c = a.tlist[i];
+  const int dim = a.dim, goal = a.goal, nbx = (dim + FB - 1) / FB;
+  if ((int)blockIdx.x >= nbx * nbx || (int)threadIdx.x >= a.tcount[blockIdx.x]) return;  // one CTA = one finish-A block's terminals
+  const int c = a.tlist[blockIdx.x * FIN_SLOTS + threadIdx.x];
   int cur = c, cs = 0, cd = 0;
   for (;;)
   {
@@ -851,7 +875,7 @@ int ga_heur_alloc(ga_ctx* c)
   GA_CUDA(c, cudaMalloc(&c->d_hctl, sizeof(int) * HC_WORDS));
   GA_CUDA(c, cudaMemsetAsync(c->d_hctl, 0, sizeof(int) * HC_WORDS, c->stream));
   GA_CUDA(c, cudaMalloc(&c->d_hcls, na));
-  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * (na + na / 4 + 1024)));  // scratch words + terminal list (terminals are block-border cells: < 1/8 of the grid)
+  GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * (na + (size_t)((c->astar_dim + 31) / 32) * ((c->astar_dim + 31) / 32) * 129)));  // scratch words + per-block terminal slots and counts
   GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
   GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS * sizeof(sweep_tile))));
@@ -894,6 +918,7 @@ static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed,
   a->closed = closed;
   a->scratch = reinterpret_cast<unsigned*>(c->d_jump);
   a->tlist = c->d_jump + (size_t)c->astar_dim * c->astar_dim;
+  a->tcount = a->tlist + (size_t)((c->astar_dim + FB - 1) / FB) * ((c->astar_dim + FB - 1) / FB) * FIN_SLOTS;
   a->tot = reinterpret_cast<int2*>(c->d_cnt);
   a->dim = c->astar_dim;
   a->goal = G->goal;
@@ -911,7 +936,9 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
   GA_CUDA(c, cudaMemsetAsync(q.ctl, 0, sizeof(int) * HC_WORDS, c->stream));  // ring cursors, pending count, statistics
   {
     ga_launch_scope ls(c, GA_K_HEUR_INIT);
-    heur_init_kernel<<<dim3(c->sm_count * 4 / (n > 4 ? 4 : 1), n), 256, 0, c->stream>>>(G0, dG, q);
+    // two cells per thread for one grid (latency bound otherwise), fewer blocks per grid in large batches
+    const int per_grid = n > 4 ? c->sm_count : (max_dim * max_dim + 511) / 512;
+    heur_init_kernel<<<dim3(per_grid, n), 256, 0, c->stream>>>(G0, dG, q);
   }
   GA_CUDA(c, cudaGetLastError());
   {
@@ -926,7 +953,7 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
     ga_launch_scope ls(c, GA_K_HEUR_FINISH, 3);
     const int nb = (max_dim + FB - 1) / FB, cells = (max_dim * max_dim + 255) / 256;
     heur_finish_a_kernel<<<dim3(nb * nb, n), FB * FB, 0, c->stream>>>(a0, dA);
-    heur_finish_b_kernel<<<dim3((max_dim * max_dim / 8 + 1024 + 127) / 128, n), 128, 0, c->stream>>>(a0, dA);
+    heur_finish_b_kernel<<<dim3(nb * nb, n), FIN_SLOTS, 0, c->stream>>>(a0, dA);
     heur_finish_c_kernel<<<dim3(cells, n), 256, 0, c->stream>>>(a0, dA);
   }
   GA_CUDA(c, cudaGetLastError());
