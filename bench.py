@@ -37,7 +37,7 @@ BYTES_PER_CELL_HEUR = 39.0   # read 1+1+8+8, write 8+8+4+1 per asta
 BYTES_PER_CELL_SAFETY = 2.0 + 1.0 / 16
 # dram__bytes_read.sum + dram__bytes_write.sum of one heur_sweep_kernel launch on the 1024^2 grid of
 # this workload, from the `ncu --set full` capture summarised in profiles/ (None until captured)
-NCU_TRAFFIC_BYTES = 17978112 + 694784  # profiles/r1_ncu_full_summary.csv (18.7 MB: the planes finish writes are not this kernel's, improved cells stay in L2)
+NCU_TRAFFIC_BYTES = 17968128 + 267520  # profiles/r1_ncu_full_summary.csv (18.2 MB: the planes finish writes are not this kernel's, improved cells stay in L2)
 
 
 def load_peaks():
@@ -518,7 +518,7 @@ def main():
     # library's stream (kept out of the run `value` comes from: the event records cost a little)
     timed(step_resident, args.steps, True)
     kt = {}
-    for k, name in ((_abi.K_PACK, "pack"), (_abi.K_DILATE, "dilate_pool"), (_abi.K_HEUR_INIT, "heur_init"),
+    for k, name in ((_abi.K_DILATE, "safety"), (_abi.K_HEUR_INIT, "heur_init"),
                     (_abi.K_HEUR_RELAX, "heur_relax"), (_abi.K_HEUR_FINISH, "heur_finish")):
         ms = n = 0
         for e in envs:
@@ -548,7 +548,7 @@ def main():
     if rank == 0:
         adim = PATCH_DIM // 4
         relax_ms, relax_n = kt["heur_relax"]
-        dil_ms, dil_n = kt["dilate_pool"]
+        dil_ms, dil_n = kt["safety"]
         # dominant kernel = the wavefront relaxation; algorithmic bytes = 39 B x astar cells of one grid per launch
         alg_bytes = BYTES_PER_CELL_HEUR * adim * adim
         achieved = alg_bytes / (relax_ms / max(relax_n, 1) * 1e-3) / 1e9
@@ -567,9 +567,9 @@ def main():
                                      "worker warps busy; see `batch` for the same kernel fed with independent grids",
                              "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": relax_ms / max(relax_n, 1)},
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
-                "dilate_roofline": {"achieved": BYTES_PER_CELL_SAFETY * PATCH_DIM * PATCH_DIM /
-                                    ((kt["pack"][0] + dil_ms) / max(dil_n, 1) * 1e-3) / 1e9, "unit": "GB/s",
-                                    "note": "pack + dilate_pool kernels, 2+1/16 B per gm cell"},
+                "safety_roofline": {"achieved": BYTES_PER_CELL_SAFETY * PATCH_DIM * PATCH_DIM /
+                                    (dil_ms / max(dil_n, 1) * 1e-3) / 1e9, "unit": "GB/s",
+                                    "note": "safety_kernel (threshold + dilation + pool fused), 2+1/16 B per gm cell"},
                 "clocks": sampler.result()}
         if batch:
             line["batch"] = batch
