@@ -68,6 +68,10 @@ struct heur_queue
   int* ctl;
   unsigned poll_ns;  // back-off of an idle worker between two looks at its ring slot
   unsigned early;    // publish once after this many changing sweeps (0 = only when converged)
+  unsigned linger;   // SM cycles a converged tile stays staged waiting for the next publication (0 = release at once)
+  unsigned prefetch; // 1: a tile the wave reaches for the first time queues its idle neighbours before sweeping
+  unsigned refresh;  // a running visit picks up new halo values between sweeps: 1 = state word read during the sweep, 2 = waited for before it
+  unsigned round;    // 1: the four sweeps run in lock step (sweep_round), 0: one after the other
 };
 
 struct heur_args  // finish kernel
@@ -206,6 +210,7 @@ __global__ void heur_init_kernel(heur_grid single, const heur_grid* many, heur_q
 #define SW_P 33                    // shared-memory pitch (doubles)
 #define SW_WARPS 6                 // workers per CTA (one CTA per SM: 6 x 33.5 KB of shared memory)
 #define SW_FULL 0xFFFFFFFFu
+#define SW_EARLY_ALL 255           // heur_queue::early: publish after every changing sweep
 
 struct sweep_tile
 {
@@ -328,11 +333,46 @@ __device__ __forceinline__ int sweep_once(sweep_tile& S, const int lane, const i
   return ch;
 }
 
+// One ROUND: the four sweeps in lock step, one line step of each per iteration.  The four chains are
+// independent instruction streams (each carries its own line in registers), so their shuffle / fp64
+// latencies overlap: a round costs about 1.5 sweeps instead of 4.  Any interleaving of relaxations
+// is admissible -- every stored value is the exact candidate of a value some neighbour held, values
+// only fall, and the loop ends on a round that stores nothing, i.e. on the fixed point.  Where two
+// chains meet in one cell in the same step (row s x column s) the later store may put the larger of
+// two improvements back; the next round repairs it (and reports a change now).
+template <bool PROX, bool UNK>
+__device__ __forceinline__ int sweep_round(sweep_tile& S, const int lane, const double w_prox, const double unk_w, const double L1,
+                                           const double L2)
+{
+  double a0 = S.g[lane], a1 = S.g[lane * SW_P], a2 = S.g[31 * SW_P + lane], a3 = S.g[lane * SW_P + 31];
+  int changed = 0;
+#pragma unroll 2
+  for (int k = 0; k < SW_O; ++k)
+  {
+    const int sf = k + 1, sb = SW_O - k;
+    double o0, o1, o2, o3;
+    const double n0 = sweep_step<0, PROX, UNK>(S, lane, sf - 1, sf, a0, w_prox, unk_w, L1, L2, &o0);  // rows, downwards
+    const double n1 = sweep_step<1, PROX, UNK>(S, lane, sf - 1, sf, a1, w_prox, unk_w, L1, L2, &o1);  // columns, rightwards
+    const double n2 = sweep_step<0, PROX, UNK>(S, lane, sb + 1, sb, a2, w_prox, unk_w, L1, L2, &o2);  // rows, upwards
+    const double n3 = sweep_step<1, PROX, UNK>(S, lane, sb + 1, sb, a3, w_prox, unk_w, L1, L2, &o3);  // columns, leftwards
+    const bool i0 = n0 < o0, i1 = n1 < o1, i2 = n2 < o2, i3 = n3 < o3;
+    if (i0) S.g[sf * SW_P + lane] = n0;
+    if (i1) S.g[lane * SW_P + sf] = n1;
+    if (i2) S.g[sb * SW_P + lane] = n2;
+    if (i3) S.g[lane * SW_P + sb] = n3;
+    changed |= (int)(i0 | i1 | i2 | i3);
+    a0 = n0; a1 = n1; a2 = n2; a3 = n3;
+  }
+  changed = __any_sync(SW_FULL, changed);
+  __syncwarp();
+  return changed;
+}
+
 struct sweep_visit  // what a visit needs to publish its results
 {
   double* gp;
   int* state;
-  int dim, tiles_x, gi, tx, ty, ox, oy;
+  int dim, tiles_x, gi, tile, tx, ty, ox, oy;
 };
 
 // write back the owned cells that improved since the last publication, activate the neighbour tiles
@@ -401,24 +441,157 @@ __device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V
   return __reduce_max_sync(SW_FULL, c);
 }
 
-// relax the staged tile to its fixed point; publishes early once (after `early` changing sweeps,
-// 0 = never) so that the tiles downstream start while this one is still confirming convergence
+// A neighbour published into the halo while this visit was running (state word DIRTY): take the
+// mark back and re-read the halo ring only -- the owned cells are written by nobody else and the
+// static planes have not changed.  Replaces release + ring + pop + a full re-stage on the chain a
+// corrected value travels along.
+__device__ __forceinline__ int sweep_refresh_halo(sweep_tile& S, const sweep_visit& V, const int lane)
+{
+  if (lane == 0)
+  {
+    int old_state;  // acquire: the marker's cost-plane writes are visible to the loads below
+    asm volatile("atom.acquire.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old_state) : "l"(V.state + V.tile), "r"((int)T_RUNNING) : "memory");
+    (void)old_state;
+  }
+  __syncwarp();
+  const int dim = V.dim, g_ = V.ox + lane;   // lane = x for the two rows
+  const int h_ = V.oy + lane;                // lane = y for the two columns
+  const int cx = min(max(g_, 0), dim - 1), cy = min(max(h_, 0), dim - 1);
+  const int y0 = V.oy, y1 = V.oy + 31, x0 = V.ox, x1 = V.ox + 31;
+  const double v_t = __ldcg(V.gp + (size_t)max(y0, 0) * dim + cx), v_b = __ldcg(V.gp + (size_t)min(y1, dim - 1) * dim + cx);
+  const double v_l = __ldcg(V.gp + (size_t)cy * dim + max(x0, 0)), v_r = __ldcg(V.gp + (size_t)cy * dim + min(x1, dim - 1));
+  const bool x_in = g_ >= 0 && g_ < dim, y_in = h_ >= 0 && h_ < dim;
+  const double n_t = (x_in && y0 >= 0) ? v_t : INFINITY, n_b = (x_in && y1 < dim) ? v_b : INFINITY;
+  const double n_l = (y_in && x0 >= 0) ? v_l : INFINITY, n_r = (y_in && x1 < dim) ? v_r : INFINITY;
+  // the side the news came from = the one with the smallest improved halo value; the next sweep
+  // runs away from it (same numbering as the first sweep of a visit)
+  const unsigned none = 0xFFFFFFFFu;
+  const unsigned k_t = n_t < S.g[lane] ? __float_as_uint(__double2float_rd(n_t)) : none;
+  const unsigned k_l = n_l < S.g[lane * SW_P] ? __float_as_uint(__double2float_rd(n_l)) : none;
+  const unsigned k_b = n_b < S.g[31 * SW_P + lane] ? __float_as_uint(__double2float_rd(n_b)) : none;
+  const unsigned k_r = n_r < S.g[lane * SW_P + 31] ? __float_as_uint(__double2float_rd(n_r)) : none;
+  __syncwarp();  // corner cells are read by two lanes: all reads before the writes
+  S.g[lane] = n_t;
+  S.g[31 * SW_P + lane] = n_b;
+  S.g[lane * SW_P] = n_l;
+  S.g[lane * SW_P + 31] = n_r;
+  const unsigned m_t = __reduce_min_sync(SW_FULL, k_t), m_l = __reduce_min_sync(SW_FULL, k_l);
+  const unsigned m_b = __reduce_min_sync(SW_FULL, k_b), m_r = __reduce_min_sync(SW_FULL, k_r);
+  int d = -1;
+  unsigned best = none;
+  if (m_t < best) { best = m_t; d = 0; }
+  if (m_l < best) { best = m_l; d = 1; }
+  if (m_b < best) { best = m_b; d = 2; }
+  if (m_r < best) { best = m_r; d = 3; }
+  __syncwarp();
+  return d;  // -1: no halo cell got smaller
+}
+
+// The wave has reached this tile for the first time: queue the idle neighbours NOW, so that idle
+// workers stage them (3 us) while this tile runs its first sweep; they then wait a moment for the
+// publication (`linger`) instead of being activated, popped and staged after it.
+__device__ __forceinline__ void sweep_prefetch(const sweep_visit& V, const heur_queue& q, const int lane, int* n_act, int* n_unused)
+{
+  int unused = 0;
+  if (lane < 8)
+  {
+    unused = 1;
+    const int nx = V.tx + c_ndx[lane], ny = V.ty + c_ndy[lane];
+    if (nx >= 0 && ny >= 0 && nx < V.tiles_x && ny < V.tiles_x)
+    {
+      const int nt = ny * V.tiles_x + nx;
+      if (atomicCAS(V.state + nt, T_IDLE, T_QUEUED) == T_IDLE)
+      {
+        q_push(q, ((V.gi << 20) | nt) + 1);
+        unused = 0;
+      }
+    }
+  }
+  __syncwarp();
+  *n_act += 8;
+  *n_unused += __reduce_add_sync(SW_FULL, unused);
+}
+
+// relax the staged tile to its fixed point.  Publication: once after `early` changing sweeps (0 =
+// never) plus the final one by the caller, or after every changing sweep (SW_EARLY_ALL).  With
+// `refresh` a neighbour's publication is picked up between sweeps; with `linger` (SM cycles; needs
+// SW_EARLY_ALL, everything is published then) the converged tile stays staged that long waiting for
+// the next one.
 template <bool PROX, bool UNK>
 __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
-                                               int d, const bool must_run, const double w_prox, const double unk_w, const double L1,
-                                               const double L2, int* n_sweeps, int* n_act, int* n_unused)
+                                               int d, const bool must_run, const bool fresh, const double w_prox, const double unk_w,
+                                               const double L1, const double L2, int* n_sweeps, int* n_act, int* n_unused, int* n_reserved)
 {
-  *n_sweeps = 0;
-  if (!must_run && !halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2)) return 0;
-  int streak = 0, n = 0, n_changing = 0;
-  while (streak < 4)
+  int n = 0, n_changing = 0, n_pub = 0;
+  bool run = must_run || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+  bool prefetch = q.prefetch && fresh;
+  for (;;)
   {
-    const int ch = sweep_once<PROX, UNK>(S, lane, d, w_prox, unk_w, L1, L2);
-    streak = ch ? 1 : streak + 1;  // a sweep is idempotent: after a changing one, three clean others suffice
-    n_changing += ch;
-    d = (d + 1) & 3;
-    ++n;
-    if (ch && n_changing == (int)q.early) sweep_publish<false>(S, V, q, lane, n_act, n_unused);
+    if (run)
+    {
+      if (prefetch)
+      {
+        sweep_prefetch(V, q, lane, n_act, n_unused);
+        prefetch = false;
+      }
+      int streak = 0;
+      while (streak < 4)
+      {
+        int st = ld_volatile(V.state + V.tile);  // issued here, looked at after the sweep
+        if (q.refresh == 2 && st == T_DIRTY)      // (2: waits for the word before the sweep as well)
+        {
+          const int dn = sweep_refresh_halo(S, V, lane);
+          if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
+          {
+            streak = 0;
+            d = dn;
+          }
+          st = T_RUNNING;
+        }
+        int ch;
+        if (q.round)
+        {
+          ch = sweep_round<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+          streak = ch ? 1 : 4;  // a clean round has looked at every cell from all eight sides
+          n += 4;
+        }
+        else
+        {
+          ch = sweep_once<PROX, UNK>(S, lane, d, w_prox, unk_w, L1, L2);
+          streak = ch ? 1 : streak + 1;  // a sweep is idempotent: after a changing one, three clean others suffice
+          d = (d + 1) & 3;
+          ++n;
+        }
+        n_changing += ch;
+        if (ch && (n_changing == (int)q.early || q.early == SW_EARLY_ALL))
+        {
+          if (n_pub++ > 0)  // publications beyond the reserved two: top the pending counts up first
+          {
+            if (lane == 0) atomicAdd(q.ctl + HC_PENDING, 8);
+            *n_reserved += 8;
+          }
+          sweep_publish<false>(S, V, q, lane, n_act, n_unused);
+        }
+        if (st == T_DIRTY && q.refresh)
+        {
+          const int dn = sweep_refresh_halo(S, V, lane);
+          if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
+          {
+            streak = 0;
+            d = dn;
+          }
+        }
+      }
+    }
+    if (q.linger == 0 || q.early != SW_EARLY_ALL) break;
+    const long long t_end = clock64() + (long long)q.linger;
+    int st;
+    do st = ld_volatile(V.state + V.tile);
+    while (st != T_DIRTY && __all_sync(SW_FULL, clock64() < t_end));
+    if (st != T_DIRTY) break;
+    const int dn = sweep_refresh_halo(S, V, lane);
+    run = dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+    if (run) d = dn;
   }
   *n_sweeps = n;
   return n_changing > 0;
@@ -429,7 +602,7 @@ __device__ __forceinline__ void cp_async8(const unsigned dst_smem, const void* s
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst_smem), "l"(src));
 }
 
-#define SW_RESERVE 16  // pending counts reserved per visit: two publications x 8 neighbours
+#define SW_RESERVE 24  // pending counts reserved per visit: (two publications + the prefetch) x 8 neighbours
 
 __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid single, const heur_grid* many, heur_queue q)
 {
@@ -462,7 +635,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
 #undef HG
     const int tx = tile % tiles_x, ty = tile / tiles_x;
     const int ox = tx * SW_O - 1, oy = ty * SW_O - 1;
-    V.gp = gp; V.state = state; V.dim = dim; V.tiles_x = tiles_x; V.tx = tx; V.ty = ty; V.ox = ox; V.oy = oy;
+    V.gp = gp; V.state = state; V.tile = tile; V.dim = dim; V.tiles_x = tiles_x; V.tx = tx; V.ty = ty; V.ox = ox; V.oy = oy;
     // ---- stage the 32x32 block (lane = x); every address is clamped into the grid so that all
     //      loads are unconditional and in flight together; out-of-grid cells are fixed up after.
     const int gx = ox + lane;
@@ -507,6 +680,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     const int r_lo = max(0, -oy), r_hi = min(32, dim - oy);  // staged rows inside the grid
     const unsigned vm = x_in ? ((r_hi >= 32 ? 0xFFFFFFFFu : ((1u << r_hi) - 1u)) & ~((1u << r_lo) - 1u)) : 0u;
     unsigned uc = 0, bc = 0;
+    bool reached = false;  // some owned cell already has a cost: the wave has been here before
     {
       double v_g[32];
       uint8_t v_c[32];
@@ -526,6 +700,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
         const int idx = r * SW_P + lane;
         S.g[idx] = gv;
         S.w[idx] = gv;
+        if (r >= 1 && r <= SW_O) reached |= gv < INFINITY;
         uc |= (unsigned)(v_c[r] & 1) << r;
         bc |= (unsigned)((v_c[r] >> 1) & 1) << r;
       }
@@ -575,16 +750,17 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     __syncwarp();
     const long long t2 = clock64();
 
-    int any, n_sweeps = 0, n_act = 0, n_unused = 0;
+    const bool fresh = !__any_sync(SW_FULL, reached && lane >= 1 && lane <= SW_O);
+    int any, n_sweeps = 0, n_act = 0, n_unused = 0, n_reserved = SW_RESERVE;
     if (has_prox)
     {
-      if (unk_w != 0) any = sweep_tile_loop<true, true>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
-      else any = sweep_tile_loop<true, false>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
+      if (unk_w != 0) any = sweep_tile_loop<true, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+      else any = sweep_tile_loop<true, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
     }
     else
     {
-      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
-      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused);
+      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
     }
     const long long t3 = clock64();
 
@@ -595,7 +771,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
       atomicAdd(q.ctl + HC_INNER, n_sweeps);
       if (any) atomicAdd(q.ctl + HC_IMPROVING, 1);
       // release the tile: re-queue it if a neighbour wrote into our halo meanwhile
-      int dec = (SW_RESERVE - n_act) + n_unused + 1;
+      int dec = (n_reserved - n_act) + n_unused + 1;
       if (atomicCAS(state + tile, T_RUNNING, T_IDLE) == T_DIRTY)
       {
         atomicExch(state + tile, T_QUEUED);
@@ -882,10 +1058,14 @@ int ga_heur_alloc(ga_ctx* c)
   // development knobs (read once per patch): workers per SM, idle back-off, early publication
   c->sw_warps = SW_WARPS;
   c->sw_poll_ns = 20;
-  c->sw_early = 1;
+  c->sw_early = c->sw_round = c->sw_refresh = c->sw_linger = c->sw_prefetch = -1;  // chosen per launch (queue_knobs)
   if (const char* s = getenv("GA_SW_WARPS")) c->sw_warps = atoi(s) >= 1 && atoi(s) <= SW_WARPS ? atoi(s) : SW_WARPS;
   if (const char* s = getenv("GA_POLL_NS")) c->sw_poll_ns = atoi(s);
   if (const char* s = getenv("GA_SW_EARLY")) c->sw_early = atoi(s);
+  if (const char* s = getenv("GA_SW_ROUND")) c->sw_round = atoi(s);
+  if (const char* s = getenv("GA_SW_REFRESH")) c->sw_refresh = atoi(s);
+  if (const char* s = getenv("GA_SW_LINGER")) c->sw_linger = atoi(s);
+  if (const char* s = getenv("GA_SW_PREFETCH")) c->sw_prefetch = atoi(s);
   return GA_OK;
 }
 
@@ -930,6 +1110,20 @@ static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed,
 }
 
 // init -> sweep relaxation -> finish A/B/C for n grids (descriptors in device memory when n > 1)
+// Scheduling mode of the sweep kernel.  Few grids (latency mode): the machine is mostly idle, so
+// every changing sweep is published at once, neighbours are staged ahead of the wave and converged
+// tiles stay staged for a moment.  Many grids (throughput mode): no speculative work, the four sweeps
+// of a tile run in lock step.  GA_SW_* (development) override either.
+static void queue_knobs(const ga_ctx* c, int n_grids, heur_queue* q)
+{
+  const bool lat = n_grids <= 4;
+  q->early = c->sw_early >= 0 ? (unsigned)c->sw_early : (lat ? SW_EARLY_ALL : 1u);
+  q->round = c->sw_round >= 0 ? (unsigned)c->sw_round : (lat ? 0u : 1u);
+  q->refresh = c->sw_refresh >= 0 ? (unsigned)c->sw_refresh : (lat ? 2u : 1u);
+  q->linger = c->sw_linger >= 0 ? (unsigned)c->sw_linger : (lat ? 8000u : 0u);
+  q->prefetch = c->sw_prefetch >= 0 ? (unsigned)c->sw_prefetch : (lat ? 1u : 0u);
+}
+
 static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& a0, const heur_grid* dG, const heur_args* dA,
                         const heur_queue& q, int max_dim, size_t total_tiles)
 {
@@ -977,7 +1171,7 @@ extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, i
   q.mask = (unsigned)c->hring_cap - 1;
   q.ctl = c->d_hctl;
   q.poll_ns = (unsigned)c->sw_poll_ns;
-  q.early = (unsigned)c->sw_early;
+  queue_knobs(c, 1, &q);
   const int rc = launch_build(c, 1, G, a, nullptr, nullptr, q, dim, (size_t)c->n_tiles);
   if (rc != GA_OK) return rc;
   if (n_closed)
@@ -1052,7 +1246,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
   q.mask = cap - 1;
   q.ctl = c->d_hctl;
   q.poll_ns = (unsigned)c->sw_poll_ns;
-  q.early = (unsigned)c->sw_early;
+  queue_knobs(c, n, &q);
   const int rc = launch_build(c, n, hG[0], hA[0], dG, dA, q, max_dim, total_tiles);
   if (rc != GA_OK) return rc;
   // the other contexts' streams continue after the batch

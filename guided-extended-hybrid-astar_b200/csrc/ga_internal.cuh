@@ -89,7 +89,8 @@ struct ga_ctx
   int32_t* d_jump = nullptr;      // finish scratch: block-local (terminal, steps) per cell
   int32_t* d_cnt = nullptr;       // finish scratch: (n_straight, n_diag) of terminal cells to the root
   int heur_epoch = 0;             // build counter (stamps the per-tile prox flags)
-  int sw_warps = 6, sw_poll_ns = 20, sw_early = 1;  // sweep kernel knobs (GA_SW_WARPS / GA_POLL_NS / GA_SW_EARLY)
+  int sw_warps = 6, sw_poll_ns = 20;  // sweep kernel knobs (GA_SW_WARPS / GA_POLL_NS)
+  int sw_early = -1, sw_round = -1, sw_refresh = -1, sw_linger = -1, sw_prefetch = -1;  // -1 = per launch (queue_knobs)
   int* d_bring = nullptr;         // batch ring (leading context of ga_build_heuristic_batch)
   int bring_cap = 0;
   void* d_bdesc = nullptr;        // batch descriptors + closed counters
