@@ -278,7 +278,9 @@ __device__ __forceinline__ double sweep_step(const sweep_tile& S, const int lane
     c1 = c1 + (((um >> lm) & 1u) ? unk_w : 0.0);
     c2 = c2 + (((um >> lp) & 1u) ? unk_w : 0.0);
   }
-  return dmin(dmin(old, c0), dmin(c1, c2));
+  // candidates are >= 0, +inf or NaN (0/0 in h_prox_arr_, a_star.cpp:492-497); a NaN's bit pattern is
+  // above +inf's as an unsigned integer whatever its sign, so it never wins: fmin's result on the integer pipe
+  return umin_f64(umin_f64(old, c0), umin_f64(c1, c2));
 }
 
 // one sweep over the 30 owned lines; dir = +1 / -1: line order.  Returns 1 if this lane improved a cell.
@@ -375,43 +377,17 @@ struct sweep_visit  // what a visit needs to publish its results
   int dim, tiles_x, gi, tile, tx, ty, ox, oy;
 };
 
-// write back the owned cells that improved since the last publication, activate the neighbour tiles
-// whose halo they are.  FINAL: the neighbour in front (smallest improved border value) is taken
-// over by this worker when it is idle -- no ring hand-off on the critical chain; returns its entry.
+// second half of a publication: kk = (lanes 0..7: W, E, N, S, NW, NE, SW, SE) the smallest improved
+// border value towards that neighbour, 0xFFFFFFFF = nothing; `stored` = this lane wrote to the cost
+// plane.  FINAL: the neighbour in front (smallest improved border value) is taken over by this
+// worker when it is idle -- no ring hand-off on the critical chain; returns its entry.
 // n_act / n_unused: pending-count bookkeeping (reserved at the start of the visit).
 template <bool FINAL>
-__device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
-                                             int* n_act, int* n_unused)
+__device__ __forceinline__ int sweep_notify(const sweep_visit& V, const heur_queue& q, const int lane, const unsigned kk,
+                                            const bool stored, int* n_act, int* n_unused)
 {
-  unsigned col_key = 0xFFFFFFFFu, kn = 0xFFFFFFFFu, ks = 0xFFFFFFFFu;
-  const bool own_x = lane >= 1 && lane <= SW_O;
-  const int gx = V.ox + lane;
-  double* grow = V.gp + (size_t)(V.oy + 1) * V.dim + gx;
-#pragma unroll 10
-  for (int r = 1; r <= SW_O; ++r, grow += V.dim)
-  {
-    const int idx = r * SW_P + lane;
-    const double v = S.g[idx];
-    const bool st = own_x & (v < S.w[idx]);
-    const unsigned kb = st ? __float_as_uint(__double2float_rd(v)) : 0xFFFFFFFFu;
-    if (st) __stcg(grow, v);
-    if (st) S.w[idx] = v;
-    col_key = min(col_key, kb);
-    if (r == 1) kn = kb;
-    if (r == SW_O) ks = kb;
-  }
-  // per direction (W, E, N, S, NW, NE, SW, SE) the smallest improved border value
-  unsigned kk = 0xFFFFFFFFu;
-  {
-    const unsigned k_w = __shfl_sync(SW_FULL, col_key, 1), k_e = __shfl_sync(SW_FULL, col_key, SW_O);
-    const unsigned k_n = __reduce_min_sync(SW_FULL, kn), k_s = __reduce_min_sync(SW_FULL, ks);
-    const unsigned k_nw = __shfl_sync(SW_FULL, kn, 1), k_ne = __shfl_sync(SW_FULL, kn, SW_O);
-    const unsigned k_sw = __shfl_sync(SW_FULL, ks, 1), k_se = __shfl_sync(SW_FULL, ks, SW_O);
-    kk = lane == 0 ? k_w : lane == 1 ? k_e : lane == 2 ? k_n : lane == 3 ? k_s : lane == 4 ? k_nw : lane == 5 ? k_ne
-       : lane == 6 ? k_sw : lane == 7 ? k_se : 0xFFFFFFFFu;
-  }
-  // the stores above are visible before any neighbour is told to look and before the tile is released
-  if (__any_sync(SW_FULL, col_key != 0xFFFFFFFFu)) asm volatile("fence.acq_rel.gpu;" ::: "memory");
+  // the stores are visible before any neighbour is told to look and before the tile is released
+  if (__any_sync(SW_FULL, stored)) asm volatile("fence.acq_rel.gpu;" ::: "memory");
   __syncwarp();
   if (!__any_sync(SW_FULL, kk != 0xFFFFFFFFu)) return 0;
   int nt = -1;
@@ -439,6 +415,66 @@ __device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V
   *n_act += __popc(want);
   *n_unused += __reduce_add_sync(SW_FULL, unused);
   return __reduce_max_sync(SW_FULL, c);
+}
+
+__device__ __forceinline__ unsigned sweep_dir_keys(const int lane, const unsigned k_w, const unsigned k_e, const unsigned kn, const unsigned ks)
+{
+  const unsigned k_n = __reduce_min_sync(SW_FULL, kn), k_s = __reduce_min_sync(SW_FULL, ks);
+  const unsigned k_nw = __shfl_sync(SW_FULL, kn, 1), k_ne = __shfl_sync(SW_FULL, kn, SW_O);
+  const unsigned k_sw = __shfl_sync(SW_FULL, ks, 1), k_se = __shfl_sync(SW_FULL, ks, SW_O);
+  return lane == 0 ? k_w : lane == 1 ? k_e : lane == 2 ? k_n : lane == 3 ? k_s : lane == 4 ? k_nw : lane == 5 ? k_ne
+       : lane == 6 ? k_sw : lane == 7 ? k_se : 0xFFFFFFFFu;
+}
+
+// write back the owned cells that improved since the last publication, activate the neighbour tiles
+// whose halo they are
+template <bool FINAL>
+__device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
+                                             int* n_act, int* n_unused)
+{
+  unsigned col_key = 0xFFFFFFFFu, kn = 0xFFFFFFFFu, ks = 0xFFFFFFFFu;
+  const bool own_x = lane >= 1 && lane <= SW_O;
+  const int gx = V.ox + lane;
+  double* grow = V.gp + (size_t)(V.oy + 1) * V.dim + gx;
+#pragma unroll 10
+  for (int r = 1; r <= SW_O; ++r, grow += V.dim)
+  {
+    const int idx = r * SW_P + lane;
+    const double v = S.g[idx];
+    const bool st = own_x & (v < S.w[idx]);
+    const unsigned kb = st ? __float_as_uint(__double2float_rd(v)) : 0xFFFFFFFFu;
+    if (st) __stcg(grow, v);
+    if (st) S.w[idx] = v;
+    col_key = min(col_key, kb);
+    if (r == 1) kn = kb;
+    if (r == SW_O) ks = kb;
+  }
+  const unsigned k_w = __shfl_sync(SW_FULL, col_key, 1), k_e = __shfl_sync(SW_FULL, col_key, SW_O);
+  const unsigned kk = sweep_dir_keys(lane, k_w, k_e, kn, ks);
+  return sweep_notify<FINAL>(V, q, lane, kk, col_key != 0xFFFFFFFFu, n_act, n_unused);
+}
+
+// the border cells only (rows 1 / 30 with lane = x, columns 1 / 30 with lane = y): all a neighbour
+// needs, a third of the latency.  The interior goes out with the visit's final publication.
+__device__ __forceinline__ void sweep_publish_border(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
+                                                     int* n_act, int* n_unused)
+{
+  const unsigned none = 0xFFFFFFFFu;
+  const bool own = lane >= 1 && lane <= SW_O;
+  const int i_n = 1 * SW_P + lane, i_s = SW_O * SW_P + lane, i_w = lane * SW_P + 1, i_e = lane * SW_P + SW_O;
+  const double v_n = S.g[i_n], v_s = S.g[i_s], v_w = S.g[i_w], v_e = S.g[i_e];
+  const bool s_n = own && v_n < S.w[i_n], s_s = own && v_s < S.w[i_s], s_w = own && v_w < S.w[i_w], s_e = own && v_e < S.w[i_e];
+  __syncwarp();  // a corner cell is looked at by two lanes: both before either marks it written
+  double* g00 = V.gp + (size_t)V.oy * V.dim + V.ox;
+  if (s_n) { __stcg(g00 + (size_t)1 * V.dim + lane, v_n); S.w[i_n] = v_n; }
+  if (s_s) { __stcg(g00 + (size_t)SW_O * V.dim + lane, v_s); S.w[i_s] = v_s; }
+  if (s_w) { __stcg(g00 + (size_t)lane * V.dim + 1, v_w); S.w[i_w] = v_w; }
+  if (s_e) { __stcg(g00 + (size_t)lane * V.dim + SW_O, v_e); S.w[i_e] = v_e; }
+  const unsigned kn = s_n ? __float_as_uint(__double2float_rd(v_n)) : none, ks = s_s ? __float_as_uint(__double2float_rd(v_s)) : none;
+  const unsigned kw = s_w ? __float_as_uint(__double2float_rd(v_w)) : none, ke = s_e ? __float_as_uint(__double2float_rd(v_e)) : none;
+  const unsigned k_w = __reduce_min_sync(SW_FULL, kw), k_e = __reduce_min_sync(SW_FULL, ke);
+  const unsigned kk = sweep_dir_keys(lane, k_w, k_e, kn, ks);
+  sweep_notify<false>(V, q, lane, kk, s_n || s_s || s_w || s_e, n_act, n_unused);
 }
 
 // A neighbour published into the halo while this visit was running (state word DIRTY): take the
@@ -523,75 +559,84 @@ __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit&
                                                const double L1, const double L2, int* n_sweeps, int* n_act, int* n_unused, int* n_reserved)
 {
   int n = 0, n_changing = 0, n_pub = 0;
-  bool run = must_run || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+  const bool run0 = must_run || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+  const bool can_linger = q.linger != 0 && q.early == SW_EARLY_ALL;  // everything is published when the tile waits
+  if (!run0 && !can_linger) return 0;
   bool prefetch = q.prefetch && fresh;
+  bool may_linger = can_linger && !run0;  // armed by a changing sweep, spent by one wait
+  // directions swept without a change since the last change (a sweep is idempotent, so a changing
+  // one counts for its own direction); 15 = fixed point.  prim = the next sweep's direction: round
+  // robin, restarted away from the side the news came from after a halo refresh.
+  unsigned mask = run0 ? 0u : 15u;
+  int prim = d, last_ch = 0;
   for (;;)
   {
-    if (run)
+    int st = ld_volatile(V.state + V.tile);  // refresh 1: looked at after the sweep, 2: waited for now
+    if (q.refresh == 2)
     {
-      if (prefetch)
+      if (st != T_DIRTY && may_linger && !last_ch)
       {
-        sweep_prefetch(V, q, lane, n_act, n_unused);
-        prefetch = false;
+        // the last sweep was clean (or the tile was staged ahead of the wave): news first, the
+        // confirming sweeps later -- nobody waits for those
+        const long long t_end = clock64() + (long long)q.linger;
+        do st = ld_volatile(V.state + V.tile);
+        while (st != T_DIRTY && __all_sync(SW_FULL, clock64() < t_end));
+        may_linger = false;
       }
-      int streak = 0;
-      while (streak < 4)
+      if (st == T_DIRTY)
       {
-        int st = ld_volatile(V.state + V.tile);  // issued here, looked at after the sweep
-        if (q.refresh == 2 && st == T_DIRTY)      // (2: waits for the word before the sweep as well)
+        const int dn = sweep_refresh_halo(S, V, lane);
+        if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
         {
-          const int dn = sweep_refresh_halo(S, V, lane);
-          if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
-          {
-            streak = 0;
-            d = dn;
-          }
-          st = T_RUNNING;
+          mask = 0;
+          prim = dn;
         }
-        int ch;
-        if (q.round)
-        {
-          ch = sweep_round<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
-          streak = ch ? 1 : 4;  // a clean round has looked at every cell from all eight sides
-          n += 4;
-        }
-        else
-        {
-          ch = sweep_once<PROX, UNK>(S, lane, d, w_prox, unk_w, L1, L2);
-          streak = ch ? 1 : streak + 1;  // a sweep is idempotent: after a changing one, three clean others suffice
-          d = (d + 1) & 3;
-          ++n;
-        }
-        n_changing += ch;
-        if (ch && (n_changing == (int)q.early || q.early == SW_EARLY_ALL))
-        {
-          if (n_pub++ > 0)  // publications beyond the reserved two: top the pending counts up first
-          {
-            if (lane == 0) atomicAdd(q.ctl + HC_PENDING, 8);
-            *n_reserved += 8;
-          }
-          sweep_publish<false>(S, V, q, lane, n_act, n_unused);
-        }
-        if (st == T_DIRTY && q.refresh)
-        {
-          const int dn = sweep_refresh_halo(S, V, lane);
-          if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
-          {
-            streak = 0;
-            d = dn;
-          }
-        }
+        st = T_RUNNING;
       }
     }
-    if (q.linger == 0 || q.early != SW_EARLY_ALL) break;
-    const long long t_end = clock64() + (long long)q.linger;
-    int st;
-    do st = ld_volatile(V.state + V.tile);
-    while (st != T_DIRTY && __all_sync(SW_FULL, clock64() < t_end));
-    if (st != T_DIRTY) break;
-    const int dn = sweep_refresh_halo(S, V, lane);
-    run = dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
-    if (run) d = dn;
+    if (mask == 15u) break;
+    if (prefetch)
+    {
+      sweep_prefetch(V, q, lane, n_act, n_unused);
+      prefetch = false;
+    }
+    int ch;
+    if (q.round)
+    {
+      ch = sweep_round<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+      mask = ch ? 0u : 15u;  // a clean round has looked at every cell from all eight sides
+      n += 4;
+    }
+    else
+    {
+      d = prim;
+      ch = sweep_once<PROX, UNK>(S, lane, d, w_prox, unk_w, L1, L2);
+      mask = ch ? (1u << d) : (mask | (1u << d));
+      prim = (d + 1) & 3;  // round robin (trying the perpendiculars before the way back measured slower)
+      ++n;
+    }
+    n_changing += ch;
+    last_ch = ch;
+    if (ch) may_linger = can_linger;
+    if (ch && (n_changing == (int)q.early || q.early == SW_EARLY_ALL))
+    {
+      if (n_pub++ > 0)  // publications beyond the reserved two: top the pending counts up first
+      {
+        if (lane == 0) atomicAdd(q.ctl + HC_PENDING, 8);
+        *n_reserved += 8;
+      }
+      if (q.early == SW_EARLY_ALL) sweep_publish_border(S, V, q, lane, n_act, n_unused);
+      else sweep_publish<false>(S, V, q, lane, n_act, n_unused);
+    }
+    if (q.refresh == 1 && st == T_DIRTY)
+    {
+      const int dn = sweep_refresh_halo(S, V, lane);
+      if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
+      {
+        mask = 0;
+        prim = dn;
+      }
+    }
   }
   *n_sweeps = n;
   return n_changing > 0;
