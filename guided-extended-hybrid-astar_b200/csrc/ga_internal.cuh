@@ -39,10 +39,11 @@ struct ga_ctx
   int sm_count = 148;
 
   // ---- parameters
-  bool have_cp = false, have_ep = false, have_ap = false;
+  bool have_cp = false, have_ep = false, have_ap = false, have_pp = false;
   ga_collision_params cp{};
   ga_expand_params ep{};
   ga_astar_params ap{};
+  ga_prox_params pp{};
   ga_se se{};
   int nb_yaws = 0;
   double yaw_res_coll_rad = 0.0;

@@ -24,6 +24,11 @@ class ExpandParams(C.Structure):
                 ("nb_steer", C.c_int)]
 
 
+class ProxParams(C.Structure):
+    _fields_ = [("lf", C.c_double), ("lb", C.c_double), ("width", C.c_double), ("con2star", C.c_double),
+                ("h_prox_cost", C.c_double), ("interp_res", C.c_double)]
+
+
 class AstarParams(C.Structure):
     _fields_ = [("astar_movement_cost", C.c_double), ("astar_prox_cost", C.c_double),
                 ("astar_lane_movement_cost", C.c_double), ("unknown_cost_w", C.c_double),
@@ -55,7 +60,7 @@ for _s in (0, 1):
     GRID_DTYPES[GRID_HEUR_FLAGS + _s] = np.uint8
 
 K_PACK, K_DILATE, K_HEUR_INIT, K_HEUR_RELAX, K_HEUR_FINISH, K_COLLISION, K_EXPAND, K_DT, \
-    K_POTENTIAL, K_CARTOGRAPH, K_RAYTRACE, K_COUNT = range(12)
+    K_POTENTIAL, K_CARTOGRAPH, K_RAYTRACE, K_PROX, K_COUNT = range(13)
 DT_FIXEDPOINT, DT_IPPFLOAT = 0, 1
 H_CLOSED, H_UNKNOWN = 1, 2
 
@@ -84,6 +89,9 @@ SYMBOLS = {
     "ga_cart_dim": (C.c_int, [_P]),
     "ga_raytrace": (C.c_int, [_P, C.c_void_p, C.c_void_p]),
     "ga_cartograph_raytraced": (C.c_int, [_P, C.c_int, C.c_int]),
+    "ga_set_prox_params": (C.c_int, [_P, C.POINTER(ProxParams)]),
+    "ga_prox_of_corners": (C.c_int, [_P, C.c_void_p, C.c_int, C.c_void_p]),
+    "ga_path_prox_costs": (C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "ga_build_heuristic": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ga_build_heuristic_batch": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "ga_potential_sites": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.POINTER(C.c_int)]),

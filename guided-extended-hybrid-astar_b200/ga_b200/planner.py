@@ -385,6 +385,39 @@ class GridMapSim:
         return out
 
 
+class HybridAStar:
+    """The grid reads of the reference's HybridAStar that score sampled poses
+    (LIB/src/hybridastar_planning_lib/hybrid_a_star_lib.cpp:265-289, 588-594, 670-676; pybind:
+    wrapper_hybrid_a_star_lib.cpp) on top of ga_prox_*: AStar::h_prox_arr_ stays on the device, a whole
+    batch of analytic-expansion candidates is scored per call."""
+
+    def __init__(self, ctx, vehicle, h_prox_cost=5.0, interp_res=0.1):
+        self.ctx, self.vehicle = ctx, vehicle
+        self.h_prox_cost_, self.interp_res_ = float(h_prox_cost), float(interp_res)  # params.yml:8, config.yml:22
+        p = _abi.ProxParams(vehicle.lf_, vehicle.lb_, vehicle.width_, CON2STAR, self.h_prox_cost_, self.interp_res_)
+        ctx.check(ctx.lib.ga_set_prox_params(ctx.h, C.byref(p)))
+
+    def getProxOfCornersBatch(self, poses):
+        """poses [n, 3] (x, y, yaw) in metres / rad -> getProxOfCorners(pose * con2star_) per pose"""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+        out = np.zeros(len(poses), np.float64)
+        self.ctx.check(self.ctx.lib.ga_prox_of_corners(self.ctx.h, _abi.ptr(poses), len(poses), _abi.ptr(out)))
+        return out
+
+    def getProxOfCorners(self, pose):
+        return float(self.getProxOfCornersBatch([pose])[0])
+
+    def getPathProxCosts(self, poses, path_offsets):
+        """the prox_cost term of getRSPathCosts / getRAPathCosts for every path of a ragged batch"""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+        off = np.ascontiguousarray(path_offsets, np.int32)
+        if len(off) < 1 or off[-1] != len(poses):
+            raise ValueError("path_offsets must end at len(poses)")
+        out = np.zeros(len(off) - 1, np.float64)
+        self.ctx.check(self.ctx.lib.ga_path_prox_costs(self.ctx.h, _abi.ptr(poses), _abi.ptr(off), len(off) - 1, _abi.ptr(out)))
+        return out
+
+
 class NodeDisc:
     """data_structures2.hpp:47-67"""
     __slots__ = ("pos", "cost_", "cost_dist_", "parent_index_", "is_unknown_")

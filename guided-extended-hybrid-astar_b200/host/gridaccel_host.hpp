@@ -405,6 +405,38 @@ private:
   Context& ctx_;
 };
 
+// The grid reads of HybridAStar that score sampled poses (hybrid_a_star_lib.cpp:265-289, 588-594,
+// 670-676): AStar::h_prox_arr_ stays on the device, whole batches of analytic-expansion candidates
+// are scored per call.
+class HybridAStar
+{
+public:
+  HybridAStar(Context& ctx, const Vehicle& veh, double h_prox_cost = 5.0, double interp_res = 0.1) : ctx_(ctx)
+  {
+    const ga_prox_params p{ veh.lf_, veh.lb_, veh.width_, 1.0 / 0.625 /* grid_tf::con2star_ */, h_prox_cost, interp_res };
+    ctx_.check(ga_set_prox_params(ctx_.handle(), &p));
+  }
+  // getProxOfCorners(pose * grid_tf::con2star_) for n poses, xyyaw = n x (x, y, yaw) in metres / rad
+  void getProxOfCorners(const double* xyyaw, int n, double* out) { ctx_.check(ga_prox_of_corners(ctx_.handle(), xyyaw, n, out)); }
+  double getProxOfCorners(const Pose<double>& pose)  // hybrid_a_star_lib.cpp:265, pose in metres
+  {
+    const double p[3] = { pose.x, pose.y, pose.yaw };
+    double v = 0;
+    getProxOfCorners(p, 1, &v);
+    return v;
+  }
+  // the prox_cost term of getRSPathCosts / getRAPathCosts for every path of a ragged batch
+  std::vector<double> getPathProxCosts(const std::vector<double>& xyyaw, const std::vector<int>& path_offsets)
+  {
+    std::vector<double> out(path_offsets.empty() ? 0 : path_offsets.size() - 1);
+    if (!out.empty()) ctx_.check(ga_path_prox_costs(ctx_.handle(), xyyaw.data(), path_offsets.data(), (int)out.size(), out.data()));
+    return out;
+  }
+
+private:
+  Context& ctx_;
+};
+
 // Cartographing (LIB/include/cartographing_lib/cartographing.hpp:19-41): the accumulated map of the
 // unknown-environment loop, device-resident.  Same member names; the map itself is fetched on demand.
 class Cartographing

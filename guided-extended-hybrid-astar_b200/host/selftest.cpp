@@ -146,6 +146,15 @@ int main()
   for (const auto& s : succ) n_valid += s.valid;
   EXPECT(n_valid > 0);
 
+  // proximity scoring: the potential field above left h_prox_arr_ on the device
+  HybridAStar hy(ctx, veh);
+  const double v0 = hy.getProxOfCorners(Pose<double>(70.0, 60.0, 0.3));
+  EXPECT(v0 >= 0.0 && v0 <= 1.0);
+  const std::vector<double> path_poses = { 70.0, 60.0, 0.3, 70.1, 60.0, 0.3, 70.2, 60.1, 0.31 };
+  const std::vector<double> costs = hy.getPathProxCosts(path_poses, { 0, 1, 1, 3 });
+  EXPECT(costs.size() == 3 && costs[1] == 0.0);
+  EXPECT(costs[0] == v0 * 5.0 * 0.1);
+
   std::printf("host selftest ok: %zu closed cells, path %zu cells, %d valid successors, %lld kernel launches\n", cs.size(),
               path.first.size(), n_valid, ga_launch_count(ctx.handle()));
   return 0;

@@ -208,6 +208,32 @@ GA_API int ga_set_expand_params(ga_ctx* ctx, const ga_expand_params* p);
 GA_API int ga_expand_stride(const ga_ctx* ctx);
 GA_API int ga_expand(ga_ctx* ctx, const ga_node* nodes, int n_nodes, ga_succ* out);
 
+/* ---- proximity scoring of sampled poses ----------------------------- */
+
+typedef struct
+{
+  double lf, lb, width; /* Vehicle::lf_, lb_, width_ (vehicle.cpp:16-27): the corner offsets, metres */
+  double con2star;      /* grid_tf::con2star_: metres -> astar cells */
+  double h_prox_cost;   /* HybridAStar::h_prox_cost_ */
+  double interp_res;    /* HybridAStar::interp_res_ (sampling distance of the analytic paths) */
+} ga_prox_params;
+
+GA_API int ga_set_prox_params(ga_ctx* ctx, const ga_prox_params* p);
+
+/* HybridAStar::getProxOfCorners(pose * grid_tf::con2star_) (hybrid_a_star_lib.cpp:265-289, with
+ * util::getBilinInterp, util2.cpp:41-52): poses = n x (x, y, yaw) in metres / rad, patch frame;
+ * out[i] = the largest bilinear sample of h_prox_arr_ under the four vehicle corners.  Cell indices
+ * are clamped into the grid (the reference clamps at 0 only and reads past the array beyond the
+ * last row / column).  fp64; sin / cos are the device's, so results agree with the host's to ~1e-15
+ * relative, not bit for bit. */
+GA_API int ga_prox_of_corners(ga_ctx* ctx, const double* poses, int n, double* out);
+
+/* The prox-cost loops of getRAPathCosts / getRSPathCosts (hybrid_a_star_lib.cpp:588-594, 670-676)
+ * for n_paths sampled paths at once: path i owns poses[path_offsets[i] .. path_offsets[i+1])
+ * (ragged, may be empty; path_offsets[0] = 0), out[i] = sum in list order of
+ * getProxOfCorners(pose * con2star_) * h_prox_cost_ * interp_res_. */
+GA_API int ga_path_prox_costs(ga_ctx* ctx, const double* poses, const int* path_offsets, int n_paths, double* out);
+
 /* ---- heuristic grid ------------------------------------------------------------------------- */
 
 typedef struct
@@ -285,7 +311,8 @@ typedef enum
   GA_K_POTENTIAL = 8,
   GA_K_CARTOGRAPH = 9, /* window merge / patch-to-patch copy of the accumulated map */
   GA_K_RAYTRACE = 10,  /* simulated lidar ray-cast */
-  GA_K_COUNT = 11
+  GA_K_PROX = 11,      /* corner proximity of sampled poses / paths */
+  GA_K_COUNT = 12
 } ga_kernel_id;
 
 GA_API int ga_prof_enable(ga_ctx* ctx, int on);

@@ -1014,3 +1014,84 @@ int gao_voronoi_potential_field(const gao_pot_params* p, const uint8_t* astar_gr
   free(mask);
   return 1;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * proximity scoring of sampled poses
+ * ------------------------------------------------------------------------------------------- */
+
+/* libstdc++ 13 <cmath> __lerp (what std::lerp in util1.cpp:179,185 resolves to) */
+static double gao_lerp(double a, double b, double t)
+{
+  if ((a <= 0 && b >= 0) || (a >= 0 && b <= 0)) return t * b + (1 - t) * a;
+  if (t == 1) return b;
+  {
+    const double x = a + t * (b - a);
+    return (t > 1) == (b > a) ? (b < x ? x : b) : (b > x ? x : b);
+  }
+}
+
+/* util::bilinearInterpolation, util1.cpp:152-200 */
+double gao_bilinear(double q11, double q12, double q21, double q22, int x1, int x2, int y1, int y2, double x, double y)
+{
+  const int x2x1 = x2 - x1, y2y1 = y2 - y1;
+  const double yy1 = y - y1, xx1 = x - x1;
+  double result;
+  if (abs(x2x1) == 0 && abs(y2y1) < 0.0001) result = q11;
+  else if (abs(x2x1) == 0) result = gao_lerp(q11, q12, yy1 / y2y1);
+  else if (abs(y2y1) < 0.0001) result = gao_lerp(q11, q21, xx1 / x2x1);
+  else
+  {
+    const double x2x = (double)x2 - x, y2y = y2 - y;
+    result = 1.0 / (x2x1 * y2y1) * (q11 * x2x * y2y + q21 * xx1 * y2y + q12 * x2x * yy1 + q22 * xx1 * yy1);
+  }
+  if (isnan(result)) result = 0.0;
+  return result;
+}
+
+/* util::getBilinInterp, util2.cpp:41-52.  The reference clamps the indices at 0 only; a point
+ * beyond the last row / column reads past its array -- here (as in the CUDA path) the indices
+ * are clamped into the grid, which is the same for every point the reference may legally ask. */
+double gao_bilin_at(double x, double y, const double* grid, int dim)
+{
+  const int hi = dim - 1;
+  int x1 = (int)x, x2 = (int)ceil(x), y1 = (int)y, y2 = (int)ceil(y);
+  x1 = x1 < 0 ? 0 : x1 > hi ? hi : x1;
+  x2 = x2 < 0 ? 0 : x2 > hi ? hi : x2;
+  y1 = y1 < 0 ? 0 : y1 > hi ? hi : y1;
+  y2 = y2 < 0 ? 0 : y2 > hi ? hi : y2;
+  return gao_bilinear(grid[(size_t)y1 * dim + x1], grid[(size_t)y2 * dim + x1], grid[(size_t)y1 * dim + x2],
+                      grid[(size_t)y2 * dim + x2], x1, x2, y1, y2, x, y);
+}
+
+/* HybridAStar::getProxOfCorners(pose * con2star_), hybrid_a_star_lib.cpp:265-289: the corners
+ * (vehicle.cpp:24-27, METRES) are rotated and added to the pose in ASTAR CELLS, as the reference does */
+double gao_prox_of_corners(const double* grid, int dim, const gao_prox_params* p, double x_m, double y_m, double yaw)
+{
+  const double cos_yaw = cos(yaw), sin_yaw = sin(yaw);
+  const double ox = x_m * p->con2star, oy = y_m * p->con2star;
+  const double cx[4] = { p->lf, p->lf, -p->lb, -p->lb };
+  const double cy[4] = { -p->width / 2, p->width / 2, -p->width / 2, p->width / 2 };
+  double best = 0;
+  int k;
+  for (k = 0; k < 4; ++k)
+  {
+    const double x = (cx[k] * cos_yaw - cy[k] * sin_yaw) + ox, y = (cx[k] * sin_yaw + cy[k] * cos_yaw) + oy;
+    const double v = gao_bilin_at(x, y, grid, dim);
+    if (k == 0 || best < v) best = v;
+  }
+  return isnan(best) ? 0.0 : best;
+}
+
+/* the prox_cost loops of getRAPathCosts / getRSPathCosts, hybrid_a_star_lib.cpp:588-594, 670-676 */
+void gao_path_prox_costs(const double* grid, int dim, const gao_prox_params* p, const double* poses, const int* offsets,
+                         int n_paths, double* out)
+{
+  int i, j;
+  for (i = 0; i < n_paths; ++i)
+  {
+    double prox_cost = 0;
+    for (j = offsets[i]; j < offsets[i + 1]; ++j)
+      prox_cost += gao_prox_of_corners(grid, dim, p, poses[3 * j], poses[3 * j + 1], poses[3 * j + 2]) * p->h_prox_cost * p->interp_res;
+    out[i] = prox_cost;
+  }
+}

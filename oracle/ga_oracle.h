@@ -229,6 +229,14 @@ int gao_voronoi_potential_field(const gao_pot_params* p, const uint8_t* astar_gr
 void gao_costmap_value(const gao_pot_params* p, float d_obs, float d_vor, double* h_prox,
                        double* motion_res);
 
+/* ---- proximity scoring of sampled poses ---- */
+double gao_bilinear(double q11, double q12, double q21, double q22, int x1, int x2, int y1, int y2, double x, double y);
+double gao_bilin_at(double x, double y, const double* grid, int dim);
+typedef struct { double lf, lb, width, con2star, h_prox_cost, interp_res; } gao_prox_params;
+double gao_prox_of_corners(const double* grid, int dim, const gao_prox_params* p, double x_m, double y_m, double yaw);
+void gao_path_prox_costs(const double* grid, int dim, const gao_prox_params* p, const double* poses, const int* offsets,
+                         int n_paths, double* out);
+
 #ifdef __cplusplus
 }
 #endif

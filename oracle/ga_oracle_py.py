@@ -70,6 +70,13 @@ def lib():
                                                  C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         _lib.gao_turn_on_rear_axis.argtypes = [C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_int]
         _lib.gao_steering_inputs.argtypes = [C.c_double, C.c_int, C.c_void_p]
+        _lib.gao_bilinear.argtypes = [C.c_double] * 4 + [C.c_int] * 4 + [C.c_double] * 2
+        _lib.gao_bilinear.restype = C.c_double
+        _lib.gao_bilin_at.argtypes = [C.c_double, C.c_double, C.c_void_p, C.c_int]
+        _lib.gao_bilin_at.restype = C.c_double
+        _lib.gao_prox_of_corners.argtypes = [C.c_void_p, C.c_int, C.c_void_p] + [C.c_double] * 3
+        _lib.gao_prox_of_corners.restype = C.c_double
+        _lib.gao_path_prox_costs.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         _lib.gao_costmap_value.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         _lib.gao_check_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
     return _lib
@@ -129,6 +136,37 @@ def cartograph(cart, local_map, ox, oy):
 def copy_patch_to_patch(prev, prev_o, nxt, o):
     lib().gao_copy_patch_to_patch(_p(prev), prev.shape[0], int(prev_o[0]), int(prev_o[1]), _p(nxt), nxt.shape[0],
                                   int(o[0]), int(o[1]))
+
+
+class ProxParams(C.Structure):
+    _fields_ = [(k, C.c_double) for k in ("lf", "lb", "width", "con2star", "h_prox_cost", "interp_res")]
+
+
+def bilinear(q11, q12, q21, q22, x1, x2, y1, y2, x, y):
+    return lib().gao_bilinear(q11, q12, q21, q22, x1, x2, y1, y2, x, y)
+
+
+def bilin_at(x, y, grid):
+    grid = np.ascontiguousarray(grid, np.float64)
+    return lib().gao_bilin_at(x, y, _p(grid), grid.shape[0])
+
+
+def prox_of_corners(grid, params, poses):
+    """poses [n, 3] in metres / rad -> getProxOfCorners(pose * con2star_) per pose"""
+    grid = np.ascontiguousarray(grid, np.float64)
+    p = ProxParams(*params)
+    return np.array([lib().gao_prox_of_corners(_p(grid), grid.shape[0], C.byref(p), float(x), float(y), float(w))
+                     for x, y, w in np.asarray(poses, np.float64).reshape(-1, 3)], np.float64)
+
+
+def path_prox_costs(grid, params, poses, offsets):
+    grid = np.ascontiguousarray(grid, np.float64)
+    poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    p = ProxParams(*params)
+    out = np.zeros(len(offsets) - 1, np.float64)
+    lib().gao_path_prox_costs(_p(grid), grid.shape[0], C.byref(p), _p(poses), _p(offsets), len(offsets) - 1, _p(out))
+    return out
 
 
 GM_DIM = 801

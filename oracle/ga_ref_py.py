@@ -75,6 +75,13 @@ def lib():
         L.gar_check_segments.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_int, C.c_void_p]
         L.gar_move_car_some_steps.argtypes = [C.c_double] * 5 + [C.c_int, C.c_double] + [C.c_void_p] * 3 + [C.c_int]
         L.gar_turn_on_rear_axis.argtypes = [C.c_double] * 5 + [C.c_void_p, C.c_int]
+        L.gar_bilinear.argtypes = [C.c_double] * 4 + [C.c_int] * 4 + [C.c_double] * 2
+        L.gar_bilinear.restype = C.c_double
+        L.gar_bilin_interp.argtypes = [C.c_double] * 2
+        L.gar_bilin_interp.restype = C.c_double
+        L.gar_prox_of_corners.argtypes = [C.c_double] * 3
+        L.gar_prox_of_corners.restype = C.c_double
+        L.gar_con2star.restype = C.c_double
     return _lib
 
 
@@ -229,6 +236,25 @@ def cart_get():
 
 def con2gm():
     return lib().gar_con2gm()
+
+
+def con2star():
+    return lib().gar_con2star()
+
+
+def bilinear(q11, q12, q21, q22, x1, x2, y1, y2, x, y):
+    """util::bilinearInterpolation (util1.cpp:152-200)"""
+    return lib().gar_bilinear(q11, q12, q21, q22, x1, x2, y1, y2, x, y)
+
+
+def bilin_interp(x, y):
+    """util::getBilinInterp on AStar::h_prox_arr_ (set_grid(5, ...))"""
+    return lib().gar_bilin_interp(x, y)
+
+
+def prox_of_corners(x, y, yaw):
+    """HybridAStar::getProxOfCorners composed from the reference's parts; pose in astar cells"""
+    return lib().gar_prox_of_corners(x, y, yaw)
 
 
 GM_DIM = 801  # gridmap_sim.hpp:17

@@ -376,4 +376,31 @@ int gar_cart_get(uint8_t* dst, size_t bytes)
 }
 double gar_con2gm() { return grid_tf::con2gm_; }
 
+// ---- proximity scoring.  util::bilinearInterpolation / util::getBilinInterp,
+// Vehicle's corners, Point::rotatePreCalc and AStar::h_prox_arr_ are the reference's own;
+// HybridAStar::getProxOfCorners itself (hybrid_a_star_lib.cpp:265-289) lives in a TU that needs the
+// Reeds-Shepp / spline side of the planner and is not built here, so its 15 lines are composed
+// below from those parts, statement by statement.
+double gar_bilinear(double q11, double q12, double q21, double q22, int x1, int x2, int y1, int y2, double x, double y)
+{
+  return util::bilinearInterpolation(q11, q12, q21, q22, x1, x2, y1, y2, x, y);
+}
+double gar_bilin_interp(double x, double y) { return util::getBilinInterp(x, y, AStar::h_prox_arr_); }
+double gar_prox_of_corners(double x, double y, double yaw)  // pose in astar cells (pose * con2star_)
+{
+  const double cos_yaw = cos(yaw), sin_yaw = sin(yaw);
+  const Point<double> offset(x, y);
+  const Point<double> f_r = Vehicle::f_r_corner_.rotatePreCalc(cos_yaw, sin_yaw) + offset;
+  const Point<double> f_l = Vehicle::f_l_corner_.rotatePreCalc(cos_yaw, sin_yaw) + offset;
+  const Point<double> r_r = Vehicle::r_r_corner_.rotatePreCalc(cos_yaw, sin_yaw) + offset;
+  const Point<double> r_l = Vehicle::r_l_corner_.rotatePreCalc(cos_yaw, sin_yaw) + offset;
+  const double v_1 = util::getBilinInterp(f_r.x, f_r.y, AStar::h_prox_arr_);
+  const double v_2 = util::getBilinInterp(f_l.x, f_l.y, AStar::h_prox_arr_);
+  const double v_3 = util::getBilinInterp(r_r.x, r_r.y, AStar::h_prox_arr_);
+  const double v_4 = util::getBilinInterp(r_l.x, r_l.y, AStar::h_prox_arr_);
+  const double max_value = std::max({ v_1, v_2, v_3, v_4 });
+  return std::isnan(max_value) ? 0.0 : max_value;
+}
+double gar_con2star() { return grid_tf::con2star_; }
+
 }  // extern "C"

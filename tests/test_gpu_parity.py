@@ -521,3 +521,43 @@ def test_unknown_environment_cycle(planner, oracle):
         assert np.array_equal(cc.patch_safety_arr_, want), cyc
         assert np.array_equal(astar.astar_grid_, oracle.pool_max(want)), cyc
     assert (cart != 127).mean() > 0.05
+
+
+def test_prox_scoring_matches_oracle(planner, oracle):
+    """ga_prox_of_corners / ga_path_prox_costs (HybridAStar::getProxOfCorners and the prox-cost loops of
+    getRSPathCosts / getRAPathCosts) against the oracle pinned on the reference's util::getBilinInterp:
+    a prox field built by the potential-field kernel's own format (zeros, NaN cells), poses on cell
+    centres (no-interpolation branches), poses whose corners leave the grid (clamped on both sides),
+    ragged paths with empty ones, an empty batch.  1e-12 relative: device sin / cos."""
+    ctx, cc, astar = planner
+    dim = 1492
+    cc.initialize(dim)
+    ad = astar.astar_dim_
+    rng = np.random.default_rng(99)
+    grid = rng.random((ad, ad)) * (rng.random((ad, ad)) < 0.6)
+    grid[rng.integers(0, ad, 20), rng.integers(0, ad, 20)] = np.nan
+    ctx.upload(_abi.GRID_H_PROX, grid)
+    hy = ga_b200.HybridAStar(ctx, cc.vehicle, 5.0, 0.1)
+    params = (cc.vehicle.lf_, cc.vehicle.lb_, cc.vehicle.width_, 1 / ga_b200.ASTAR_RES, 5.0, 0.1)
+    n = 50000
+    span = ad * ga_b200.ASTAR_RES
+    poses = np.stack([(rng.random(n) * 1.1 - 0.05) * span, (rng.random(n) * 1.1 - 0.05) * span,
+                      (rng.random(n) - 0.5) * 4 * np.pi], 1)
+    poses[:2000, :2] = np.round(poses[:2000, :2] / ga_b200.ASTAR_RES) * ga_b200.ASTAR_RES
+    poses[2000:2100, 2] = 0.0
+    got = hy.getProxOfCornersBatch(poses)
+    want = oracle.prox_of_corners(grid, params, poses)
+    np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-14)
+    assert hy.getProxOfCorners(poses[7]) == got[7]
+    cuts = np.sort(rng.integers(0, n + 1, 999))
+    cuts[100:110] = cuts[100]
+    offsets = np.concatenate([[0], np.sort(cuts), [n]]).astype(np.int32)
+    np.testing.assert_allclose(hy.getPathProxCosts(poses, offsets), oracle.path_prox_costs(grid, params, poses, offsets),
+                               rtol=1e-12, atol=1e-13)
+    assert len(hy.getProxOfCornersBatch(np.zeros((0, 3)))) == 0
+    assert np.array_equal(hy.getPathProxCosts(np.zeros((0, 3)), [0, 0, 0]), [0.0, 0.0])
+    with pytest.raises(ValueError):
+        hy.getPathProxCosts(poses, [0, 5])
+    with pytest.raises(ga_b200.GaError):
+        ctx.check(ctx.lib.ga_path_prox_costs(ctx.h, _abi.ptr(poses), _abi.ptr(np.array([0, 9, 4], np.int32)), 2,
+                                             _abi.ptr(np.zeros(2))))

@@ -98,3 +98,29 @@ def test_unknown_environment_rows(oracle):
     nxt = np.full((dim, dim), 127, np.uint8)
     oracle.copy_patch_to_patch(cart, [rnd(v * 6.4) for v in prev_utm], nxt, [rnd(v * 6.4) for v in utm])
     assert np.array_equal(nxt, g["cart_moved"])
+
+
+def _prox_golden():
+    import importlib.util
+    import os
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    spec = importlib.util.spec_from_file_location("make_ref_golden_prox", os.path.join(here, "make_ref_golden_prox.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    return gen, np.load(os.path.join(here, "ref_golden_prox.npz"))
+
+
+def test_prox_scoring_rows(oracle):
+    """tests/golden/ref_golden_prox.npz (the reference's own bilinear interpolation, corners and h_prox_arr_,
+    see make_ref_golden_prox.py) and the known answers of LIB/test/cpp/util_lib_test/test_util.cpp:342-440
+    against the oracle, bit for bit."""
+    kat = [((0, 0, 0, 0), (0.0, 0.0), 0.0), ((0, 0, 2, 2), (1.0, 0.0), 2.0), ((0, 0, 2, 2), (0.5, 0.5), 1.0),
+           ((0, 2, 0, 2), (0.0, 1.0), 2.0), ((0, 2, 0, 2), (1.0, 0.0), 0.0), ((0, 2, 0, 2), (0.5, 0.5), 1.0),
+           ((0, 1, 1, 2), (0.0, 0.0), 0.0), ((0, 1, 1, 2), (1.0, 1.0), 2.0), ((0, 1, 1, 2), (0.5, 0.5), 1.0)]
+    for q, (x, y), want in kat:
+        assert oracle.bilinear(*q, 0, 1, 0, 1, x, y) == want
+    gen, g = _prox_golden()
+    grid, poses, offsets = gen.inputs()
+    params = (gen.VEH[2], gen.VEH[3], gen.VEH[4], gen.CON2STAR, gen.H_PROX_COST, gen.INTERP_RES)
+    assert np.array_equal(oracle.prox_of_corners(grid, params, poses), g["prox"])
+    assert np.array_equal(oracle.path_prox_costs(grid, params, poses, offsets), g["costs"])

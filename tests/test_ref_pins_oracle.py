@@ -283,3 +283,59 @@ def test_raytracing_vs_reference():
     gt = np.zeros((801, 801), np.uint8)
     gt[400, 400] = 255  # the sensor cell itself: every list starts there
     assert np.array_equal(go.raytrace(gt), gr.raytrace(gt))
+
+
+# LIB/test/cpp/util_lib_test/test_util.cpp:342-440 (UtilFunctions.bilinearInterpolation): x1 = y1 = 0, x2 = y2 = 1
+BILINEAR_KAT = [((0, 0, 0, 0), (0.0, 0.0), 0.0),
+                ((0, 0, 2, 2), (0.0, 0.0), 0.0), ((0, 0, 2, 2), (0.0, 1.0), 0.0), ((0, 0, 2, 2), (1.0, 0.0), 2.0),
+                ((0, 0, 2, 2), (1.0, 1.0), 2.0), ((0, 0, 2, 2), (0.5, 0.5), 1.0),
+                ((0, 2, 0, 2), (0.0, 0.0), 0.0), ((0, 2, 0, 2), (0.0, 1.0), 2.0), ((0, 2, 0, 2), (1.0, 0.0), 0.0),
+                ((0, 2, 0, 2), (1.0, 1.0), 2.0), ((0, 2, 0, 2), (0.5, 0.5), 1.0),
+                ((0, 1, 1, 2), (0.0, 0.0), 0.0)]
+
+
+def _prox_grid(rng, dim):
+    g = rng.random((dim, dim))
+    g[rng.random((dim, dim)) < 0.3] = 0.0
+    g[3, 5] = np.nan  # 0/0 of setCostmapValue (a_star.cpp:492-497): interpolates to NaN -> 0
+    return g
+
+
+def test_prox_scoring_vs_reference():
+    """util::bilinearInterpolation / util::getBilinInterp (util1.cpp:152-200, util2.cpp:41-52) and the
+    composition of HybridAStar::getProxOfCorners (hybrid_a_star_lib.cpp:265-289) from the reference's own
+    parts against gao_bilinear / gao_bilin_at / gao_prox_of_corners: bit for bit (same glibc sin / cos)."""
+    for (q11, q12, q21, q22), (x, y), want in BILINEAR_KAT:
+        assert gr.bilinear(q11, q12, q21, q22, 0, 1, 0, 1, x, y) == want
+        assert go.bilinear(q11, q12, q21, q22, 0, 1, 0, 1, x, y) == want
+    rng = np.random.default_rng(31)
+    for _ in range(2000):  # every branch: no / x-only / y-only / full interpolation, NaN corners
+        q = rng.random(4) * rng.choice([1.0, -1.0, 0.0], 4)
+        if rng.random() < 0.05:
+            q[rng.integers(4)] = np.nan
+        x1, y1 = (int(v) for v in rng.integers(0, 50, 2))
+        x2, y2 = x1 + int(rng.integers(0, 2)), y1 + int(rng.integers(0, 2))
+        x, y = x1 + (rng.random() if x2 > x1 else 0.0), y1 + (rng.random() if y2 > y1 else 0.0)
+        a, b = gr.bilinear(*q, x1, x2, y1, y2, x, y), go.bilinear(*q, x1, x2, y1, y2, x, y)
+        assert a == b, (q, x1, x2, y1, y2, x, y, a, b)
+    dim = 1000
+    gr.init(dim, veh=VEH)
+    ad = gr.dims()[1]
+    grid = _prox_grid(rng, ad)
+    gr.set_grid(gr.H_PROX, grid)
+    for _ in range(500):
+        x, y = rng.random(2) * (ad - 1)
+        if rng.random() < 0.2:
+            x = float(int(x))
+        if rng.random() < 0.2:
+            y = float(int(y))
+        assert gr.bilin_interp(x, y) == go.bilin_at(x, y, grid)
+    c2s = gr.con2star()
+    params = (VEH[2], VEH[3], VEH[4], c2s, 5.0, 0.1)
+    # poses whose corners (up to 4.2 "cells" away: metres added to cells) stay inside the grid -- beyond it
+    # the reference reads past its array
+    lo, span = 6.0 / c2s, (ad - 13) / c2s
+    poses = np.stack([lo + rng.random(3000) * span, lo + rng.random(3000) * span, (rng.random(3000) - 0.5) * 4 * math.pi], 1)
+    want = np.array([gr.prox_of_corners(x * c2s, y * c2s, w) for x, y, w in poses])
+    got = go.prox_of_corners(grid, params, poses)
+    assert np.array_equal(want, got)
