@@ -408,12 +408,33 @@ def run_collision_leg(env, args, ga):
     poses = int(succ["n_poses"].sum())
     out.update({"expand_nodes_per_s": len(nodes) / dt, "expand_primitives_per_s": int((succ["n_poses"] > 0).sum()) / dt,
                 "expand_pose_checks_per_s": poses / dt, "expand_batch_nodes": len(nodes), "ushift": True})
+    # (c) proximity scoring of sampled analytic-expansion paths: host pose lists
+    #     in, one cost per path out; h_prox_arr_ stays on the device
+    adim = PATCH_DIM // 4
+    prox = rng.random((adim, adim)) * (rng.random((adim, adim)) < 0.5)
+    ctx.upload(_abi.GRID_H_PROX, prox)
+    hy = ga.HybridAStar(ctx, cc.vehicle)
+    n_paths, path_len = 8192, 128  # 12.8 m sampled at INTERP_RES = 0.1
+    pp = np.stack([rng.uniform(10, ext - 10, n_paths * path_len), rng.uniform(10, ext - 10, n_paths * path_len),
+                   rng.uniform(-3.14, 3.14, n_paths * path_len)], 1)
+    poff = np.arange(0, n_paths * path_len + 1, path_len, dtype=np.int32)
+    hy.getPathProxCosts(pp, poff)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        costs = hy.getPathProxCosts(pp, poff)
+    dt = (time.perf_counter() - t0) / reps
+    out.update({"prox_poses_per_s": len(pp) / dt, "prox_paths_per_launch": n_paths, "prox_path_len": path_len})
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import ga_ref_py as gr
         if gr.available():
             m = 200000
             gr.init(PATCH_DIM)
+            gr.set_grid(gr.H_PROX, prox)
+            t0 = time.perf_counter()
+            ref_costs = gr.path_prox_costs(pp[:m], poff[:m // path_len + 1])
+            out["cpu_reference_prox_poses_per_s"] = (m // path_len * path_len) / (time.perf_counter() - t0)
+            out["prox_max_diff_vs_reference"] = float(np.max(np.abs(ref_costs - costs[:len(ref_costs)])) / np.max(np.abs(ref_costs)))
             gr.set_grid(gr.SAFETY, ctx.download(_abi.GRID_SAFETY))
             t0 = time.perf_counter()
             gr.check_segments(x[:m], y[:m], yaw[:m], seg[:m // seg_len + 1])

@@ -82,6 +82,7 @@ def lib():
         L.gar_prox_of_corners.argtypes = [C.c_double] * 3
         L.gar_prox_of_corners.restype = C.c_double
         L.gar_con2star.restype = C.c_double
+        L.gar_path_prox_costs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p]
     return _lib
 
 
@@ -250,6 +251,15 @@ def bilinear(q11, q12, q21, q22, x1, x2, y1, y2, x, y):
 def bilin_interp(x, y):
     """util::getBilinInterp on AStar::h_prox_arr_ (set_grid(5, ...))"""
     return lib().gar_bilin_interp(x, y)
+
+
+def path_prox_costs(poses_m, offsets, h_prox_cost=5.0, interp_res=0.1):
+    """the prox_cost loop of getRSPathCosts / getRAPathCosts over a ragged batch; poses in metres"""
+    poses_m = np.ascontiguousarray(poses_m, np.float64).reshape(-1, 3)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    out = np.zeros(len(offsets) - 1, np.float64)
+    lib().gar_path_prox_costs(_p(poses_m), _p(offsets), len(offsets) - 1, h_prox_cost, interp_res, _p(out))
+    return out
 
 
 def prox_of_corners(x, y, yaw):

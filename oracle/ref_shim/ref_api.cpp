@@ -402,5 +402,17 @@ double gar_prox_of_corners(double x, double y, double yaw)  // pose in astar cel
   return std::isnan(max_value) ? 0.0 : max_value;
 }
 double gar_con2star() { return grid_tf::con2star_; }
+// the prox_cost loop of getRSPathCosts / getRAPathCosts (hybrid_a_star_lib.cpp:588-594) over a ragged batch
+void gar_path_prox_costs(const double* poses_m, const int* offsets, int n_paths, double h_prox_cost, double interp_res, double* out)
+{
+  for (int i = 0; i < n_paths; ++i)
+  {
+    double prox_cost = 0;
+    for (int j = offsets[i]; j < offsets[i + 1]; ++j)
+      prox_cost += gar_prox_of_corners(poses_m[3 * j] * grid_tf::con2star_, poses_m[3 * j + 1] * grid_tf::con2star_, poses_m[3 * j + 2]) *
+                   h_prox_cost * interp_res;
+    out[i] = prox_cost;
+  }
+}
 
 }  // extern "C"
