@@ -21,7 +21,6 @@ FULL_METRICS = [
     "dram__bytes_write.sum",
     "sm__throughput.avg.pct_of_peak_sustained_elapsed",
     "smsp__inst_executed.sum",
-    "dram__throughput.avg.pct_of_peak_sustained_elapsed",
     "sm__instruction_throughput.avg.pct_of_peak_sustained_active",
     "smsp__issue_active.avg.pct_of_peak_sustained_active",
     "sm__warps_active.avg.pct_of_peak_sustained_active",
