@@ -424,6 +424,20 @@ def run_collision_leg(env, args, ga):
         costs = hy.getPathProxCosts(pp, poff)
     dt = (time.perf_counter() - t0) / reps
     out.update({"prox_poses_per_s": len(pp) / dt, "prox_paths_per_launch": n_paths, "prox_path_len": path_len})
+    # (d) getValidClosePose step 3: 64 x 64 x 114 candidate poses per call
+    grid = ctx.download(_abi.GRID_ASTAR)
+    free = np.argwhere(grid == 0)
+    cyx = free[len(free) // 2]
+    ys, xs = np.mgrid[0:adim, 0:adim]
+    near = (np.sqrt((xs - cyx[1]) ** 2.0 + (ys - cyx[0]) ** 2.0) < 10.0) & (grid != 2)
+    cells = (ys[near] * adim + xs[near]).astype(np.int32)
+    center = (cyx[1] * 0.625 + 0.3, cyx[0] * 0.625 + 0.05, 0.4)
+    close = hy.getValidClosePose(center, cells)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        close = hy.getValidClosePose(center, cells)
+    dt = (time.perf_counter() - t0) / reps
+    out.update({"close_pose_ms": dt * 1e3, "close_pose_candidates": 64 * 64 * 114})
     if not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import ga_ref_py as gr
@@ -436,6 +450,11 @@ def run_collision_leg(env, args, ga):
             out["cpu_reference_prox_poses_per_s"] = (m // path_len * path_len) / (time.perf_counter() - t0)
             out["prox_max_diff_vs_reference"] = float(np.max(np.abs(ref_costs - costs[:len(ref_costs)])) / np.max(np.abs(ref_costs)))
             gr.set_grid(gr.SAFETY, ctx.download(_abi.GRID_SAFETY))
+            t0 = time.perf_counter()
+            ref_close = gr.valid_close_pose(center, cells)
+            out["cpu_reference_close_pose_ms"] = (time.perf_counter() - t0) * 1e3
+            out["close_pose_equal_to_reference"] = bool((ref_close is None) == (close is None) and
+                                                        (close is None or np.array_equal(ref_close, close)))
             t0 = time.perf_counter()
             gr.check_segments(x[:m], y[:m], yaw[:m], seg[:m // seg_len + 1])
             out["cpu_reference_pose_checks_per_s"] = m / (time.perf_counter() - t0)

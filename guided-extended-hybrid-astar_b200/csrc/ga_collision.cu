@@ -12,7 +12,7 @@
 #include <climits>
 #include <cmath>
 
-#include "ga_internal.cuh"
+#include "ga_prox.cuh"
 
 #define GA_CON2GM (1.0 / 0.15625)   // grid_tf::con2gm_  (transforms.hpp:73-74, params.hpp:8)
 #define GA_CON2STAR (1.0 / 0.625)   // grid_tf::con2star_ (transforms.hpp:76-77, params.hpp:7)
@@ -166,6 +166,141 @@ extern "C" int ga_check_poses(ga_ctx* c, const double* x, const double* y, const
   GA_CUDA(c, cudaMemcpyAsync(h + off_hit, d_hit, b_hit, cudaMemcpyDeviceToHost, c->stream));
   GA_CUDA(c, cudaStreamSynchronize(c->stream));
   memcpy(first_hit, h + off_hit, b_hit);
+  return GA_OK;
+}
+
+// ---- ga_valid_close_pose ------------------------------------------------------------------------
+// Step 3 of HybridAStar::getValidClosePose (hybrid_a_star_lib.cpp:1604-1668): 64 x 64 x 114 candidate
+// poses around the centre, cost = squared offset + 20 |yaw offset| + corner proximity, a candidate
+// counts when its astar cell is one of nodes_near_goal_ and its footprint is collision free.  The
+// reference walks them in order and takes a candidate when its cost is not ABOVE the best so far:
+// the result is the smallest cost, and among equal costs the LAST candidate in loop order.  Here:
+// one thread per candidate, a 64-bit atomic minimum over the cost bits (costs are >= 0, so the IEEE
+// order is the integer order), then an atomic maximum of the loop index over the candidates that hold it.
+
+#define CP_DXY_MAX 5.0        // dxy_max, :1613
+#define CP_ANGLE_W 20.0       // angle_weight, :1609
+#define CP_GM_RES 0.15625     // HybridAStar::gm_res_ = GM_RES (:34)
+
+struct close_pose_view
+{
+  coll_view cv;
+  prox_args pa;
+  const uint8_t* member;  // astar_dim^2 bytes: 1 = cell is in nodes_near_goal_
+  double cx, cy, cyaw, phi_res;
+  int nxy, nphi;          // dxy_max_idx, dphi_max_idx: loops run [-n, n)
+};
+
+__global__ void fill_u8_scatter_kernel(uint8_t* m, const int* __restrict__ cells, int n, int cells_total)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && cells[i] >= 0 && cells[i] < cells_total) m[cells[i]] = 1;
+}
+
+__device__ __forceinline__ bool close_pose_eval(const close_pose_view& v, int idx, unsigned long long* key)
+{
+  const int dphii = idx % (2 * v.nphi) - v.nphi;
+  const int r = idx / (2 * v.nphi);
+  const int dyi = r % (2 * v.nxy) - v.nxy, dxi = r / (2 * v.nxy) - v.nxy;
+  const double x_diff = dxi * CP_GM_RES, y_diff = dyi * CP_GM_RES, phi_diff = dphii * v.phi_res;
+  const double dist2 = x_diff * x_diff + y_diff * y_diff;
+  const double px = v.cx + x_diff, py = v.cy + y_diff, pyaw = v.cyaw + phi_diff;
+  const double prox_cost = prox_of_corners(px, py, pyaw, v.pa);
+  const double cost = dist2 * 1.0 + fabs(phi_diff) * CP_ANGLE_W + prox_cost * 1.0;
+  *key = (unsigned long long)__double_as_longlong(cost);
+  // grid_tf::utm2astar(pose.getPoint()).toInt() (std::round) -> AStar::calcIndex(size_t, size_t): a
+  // negative coordinate wraps there, which only matters when the sum lands on a real cell again
+  const long long ix = (long long)round(px * v.pa.p.con2star), iy = (long long)round(py * v.pa.p.con2star);
+  const long long index = iy * v.pa.dim + ix;
+  if (index < 0 || index >= (long long)v.pa.dim * v.pa.dim || !v.member[index]) return false;
+  return check_pose_dev(v.cv, px, py, pyaw, 0, nullptr) != 0;
+}
+
+__global__ void __launch_bounds__(256) close_pose_min_kernel(close_pose_view v, int n, unsigned long long* __restrict__ keys,
+                                                             unsigned long long* __restrict__ best)
+{
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long key = ~0ull;
+  if (idx < n)
+  {
+    unsigned long long k;
+    if (close_pose_eval(v, idx, &k)) key = k;
+    keys[idx] = key;
+  }
+  // warp minimum first: one atomic per warp
+  for (int o = 16; o > 0; o >>= 1)
+  {
+    const unsigned long long other = __shfl_xor_sync(0xFFFFFFFFu, key, o);
+    key = other < key ? other : key;
+  }
+  if ((threadIdx.x & 31) == 0 && key != ~0ull) atomicMin(best, key);
+}
+
+__global__ void __launch_bounds__(256) close_pose_arg_kernel(int n, const unsigned long long* __restrict__ keys,
+                                                             const unsigned long long* __restrict__ best, int* __restrict__ arg)
+{
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long b = *best;
+  if (idx < n && b != ~0ull && keys[idx] == b) atomicMax(arg, idx);
+}
+
+extern "C" int ga_valid_close_pose(ga_ctx* c, const double* center_pose, const int* near_cells, int n_near, double* out_pose,
+                                   int* found)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp, GA_ERR_STATE, "no patch / collision params");
+  GA_REQUIRE(c, c->have_pp, GA_ERR_STATE, "no prox params (call ga_set_prox_params)");
+  GA_REQUIRE(c, center_pose && out_pose && found && n_near >= 0 && (n_near == 0 || near_cells), GA_ERR_ARG, "bad arguments");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  close_pose_view v;
+  v.cv = make_view(c);
+  v.pa = prox_args{ c->d_prox, c->astar_dim, c->pp };
+  v.cx = center_pose[0];
+  v.cy = center_pose[1];
+  v.cyaw = center_pose[2];
+  v.phi_res = c->yaw_res_coll_rad;  // yaw_res_coll_ * TO_RAD, :1616
+  v.nxy = static_cast<int>(std::floor(CP_DXY_MAX) / CP_GM_RES);      // :1623
+  v.nphi = static_cast<int>(std::floor(GA_PI) / v.phi_res);          // :1624
+  const int n = 2 * v.nxy * 2 * v.nxy * 2 * v.nphi;
+  *found = 0;
+  if (n <= 0 || n_near == 0) return GA_OK;
+  const size_t cells = (size_t)c->astar_dim * c->astar_dim;
+  // staging layout: near_cells | member map | keys | best | arg
+  const size_t b_near = (sizeof(int) * (size_t)n_near + 255) & ~(size_t)255, b_mem = (cells + 255) & ~(size_t)255;
+  const size_t b_keys = sizeof(unsigned long long) * (size_t)n;
+  const int rc = ga_stage_reserve(c, b_near + b_mem + b_keys + 64);
+  if (rc) return rc;
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));  // staging buffer reuse
+  char* h = (char*)c->h_stage;
+  char* d = (char*)c->d_stage;
+  memcpy(h, near_cells, sizeof(int) * (size_t)n_near);
+  GA_CUDA(c, cudaMemcpyAsync(d, h, sizeof(int) * (size_t)n_near, cudaMemcpyHostToDevice, c->stream));
+  uint8_t* d_mem = (uint8_t*)(d + b_near);
+  unsigned long long* d_keys = (unsigned long long*)(d + b_near + b_mem);
+  unsigned long long* d_best = d_keys + n;
+  int* d_arg = (int*)(d_best + 1);
+  GA_CUDA(c, cudaMemsetAsync(d_mem, 0, cells, c->stream));
+  GA_CUDA(c, cudaMemsetAsync(d_best, 0xFF, 16, c->stream));  // best = all ones, arg = -1
+  v.member = d_mem;
+  {
+    ga_launch_scope ls(c, GA_K_COLLISION, 3);
+    fill_u8_scatter_kernel<<<(n_near + 255) / 256, 256, 0, c->stream>>>(d_mem, (const int*)d, n_near, (int)cells);
+    close_pose_min_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(v, n, d_keys, d_best);
+    close_pose_arg_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(n, d_keys, d_best, d_arg);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  int* h_arg = (int*)(h + b_near + b_mem + b_keys + 8);
+  GA_CUDA(c, cudaMemcpyAsync(h_arg, d_arg, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  const int idx = *h_arg;
+  if (idx < 0) return GA_OK;
+  // the winning pose, with the loop's own arithmetic (:1632-1640)
+  const int dphii = idx % (2 * v.nphi) - v.nphi, r = idx / (2 * v.nphi);
+  const int dyi = r % (2 * v.nxy) - v.nxy, dxi = r / (2 * v.nxy) - v.nxy;
+  out_pose[0] = v.cx + dxi * CP_GM_RES;
+  out_pose[1] = v.cy + dyi * CP_GM_RES;
+  out_pose[2] = v.cyaw + dphii * v.phi_res;
+  *found = 1;
   return GA_OK;
 }
 

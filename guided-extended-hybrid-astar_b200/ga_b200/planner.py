@@ -407,6 +407,17 @@ class HybridAStar:
     def getProxOfCorners(self, pose):
         return float(self.getProxOfCornersBatch([pose])[0])
 
+    def getValidClosePose(self, center_pose, near_cells, ego_pose=None):
+        """step 3 of HybridAStar::getValidClosePose (hybrid_a_star_lib.cpp:1604-1668): the cheapest
+        collision-free pose around center_pose whose astar cell is in near_cells (nodes_near_goal_ as
+        cell indices y * astar_dim + x); ego_pose (the reference's default) when there is none"""
+        c = np.ascontiguousarray(center_pose, np.float64)
+        cells = np.ascontiguousarray(near_cells, np.int32)
+        out, found = np.zeros(3, np.float64), C.c_int()
+        self.ctx.check(self.ctx.lib.ga_valid_close_pose(self.ctx.h, _abi.ptr(c), _abi.ptr(cells), len(cells), _abi.ptr(out),
+                                                        C.byref(found)))
+        return out if found.value else ego_pose
+
     def getPathProxCosts(self, poses, path_offsets):
         """the prox_cost term of getRSPathCosts / getRAPathCosts for every path of a ragged batch"""
         poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)

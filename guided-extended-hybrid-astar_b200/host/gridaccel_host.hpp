@@ -425,6 +425,16 @@ public:
     getProxOfCorners(p, 1, &v);
     return v;
   }
+  // step 3 of getValidClosePose (hybrid_a_star_lib.cpp:1604-1668): near_cells = AStar::calcIndex of the nodes of
+  // nodes_near_goal_; the reference's default (ego_pose) when no candidate qualifies
+  Pose<double> getValidClosePose(const Pose<double>& center_pose, const std::vector<int>& near_cells, const Pose<double>& ego_pose)
+  {
+    const double c[3] = { center_pose.x, center_pose.y, center_pose.yaw };
+    double out[3];
+    int found = 0;
+    ctx_.check(ga_valid_close_pose(ctx_.handle(), c, near_cells.data(), (int)near_cells.size(), out, &found));
+    return found ? Pose<double>(out[0], out[1], out[2]) : ego_pose;
+  }
   // the prox_cost term of getRSPathCosts / getRAPathCosts for every path of a ragged batch
   std::vector<double> getPathProxCosts(const std::vector<double>& xyyaw, const std::vector<int>& path_offsets)
   {

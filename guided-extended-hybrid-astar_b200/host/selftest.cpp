@@ -155,6 +155,15 @@ int main()
   EXPECT(costs.size() == 3 && costs[1] == 0.0);
   EXPECT(costs[0] == v0 * 5.0 * 0.1);
 
+  // close pose: the neighbourhood of a free cell; no cell list -> the ego pose comes back
+  std::vector<int> near_cells;
+  for (int dy = -6; dy <= 6; ++dy)
+    for (int dx = -6; dx <= 6; ++dx) near_cells.push_back((int)astar.calcIndex(112 + dx, 96 + dy));
+  const Pose<double> ego(1.0, 2.0, 0.5);
+  const Pose<double> cp = hy.getValidClosePose(Pose<double>(70.0, 60.0, 0.3), near_cells, ego);
+  EXPECT(std::fabs(cp.x - 70.0) <= 5.0 && std::fabs(cp.y - 60.0) <= 5.0);
+  EXPECT(hy.getValidClosePose(Pose<double>(70.0, 60.0, 0.3), {}, ego).x == 1.0);
+
   std::printf("host selftest ok: %zu closed cells, path %zu cells, %d valid successors, %lld kernel launches\n", cs.size(),
               path.first.size(), n_valid, ga_launch_count(ctx.handle()));
   return 0;

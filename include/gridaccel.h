@@ -234,6 +234,19 @@ GA_API int ga_prox_of_corners(ga_ctx* ctx, const double* poses, int n, double* o
  * getProxOfCorners(pose * con2star_) * h_prox_cost_ * interp_res_. */
 GA_API int ga_path_prox_costs(ga_ctx* ctx, const double* poses, const int* path_offsets, int n_paths, double* out);
 
+/* Step 3 of HybridAStar::getValidClosePose (hybrid_a_star_lib.cpp:1604-1668):
+ * the collision-free pose of smallest cost around center_pose = (x, y, yaw) in metres / rad, among
+ * the 64 x 64 x 114 offsets (gm_res_ steps within +-5 m, yaw_res_coll_ steps within +-3 rad) whose
+ * astar cell is one of near_cells (AStar::nodes_near_goal_ as indices y * astar_dim + x; steps 1-2,
+ * the heuristic sweep and the closest node, are ga_build_heuristic and host code).  cost = squared
+ * offset + 20 |yaw offset| + getProxOfCorners; equal costs resolve to the last candidate in the
+ * reference's loop order, as its `cost > min_cost` pruning does.  found = 0 (out_pose untouched)
+ * when no candidate qualifies -- the reference then returns the ego pose.  Needs
+ * ga_set_collision_params and ga_set_prox_params.  The proximity term carries the device's sin / cos
+ * (1e-15 relative), which can only change the winner between candidates whose costs differ by less. */
+GA_API int ga_valid_close_pose(ga_ctx* ctx, const double* center_pose, const int* near_cells, int n_near, double* out_pose,
+                               int* found);
+
 /* ---- heuristic grid ------------------------------------------------------------------------- */
 
 typedef struct

@@ -1095,3 +1095,45 @@ void gao_path_prox_costs(const double* grid, int dim, const gao_prox_params* p, 
     out[i] = prox_cost;
   }
 }
+
+/* step 3 of HybridAStar::getValidClosePose, hybrid_a_star_lib.cpp:1604-1668.  member = astar_dim^2
+ * bytes, 1 where the cell is one of AStar::nodes_near_goal_.  Returns 1 and the pose, or 0 (the
+ * reference then keeps the ego pose). */
+int gao_valid_close_pose(const uint8_t* safety, int patch_dim, const int* centers, int nb_disks, int yaw_res_deg,
+                         const double* prox, int astar_dim, const gao_prox_params* p, const uint8_t* member,
+                         const double* center, double* out_pose)
+{
+  const double angle_weight = 20.0, dist_weight = 1.0, prox_weight = 1.0;
+  const double dxy_max = 5.0, dphi_max = 3.14159265358979323846;
+  const double gm_res = 0.15625;                                      /* gm_res_ = GM_RES, :34 */
+  const double phi_res = yaw_res_deg * (3.14159265358979323846 / 180); /* yaw_res_coll_ * util::TO_RAD */
+  double min_cost = 1.7976931348623157e308;
+  int found_any = 0, dxi, dyi, dphii;
+  const int dxy_max_idx = (int)(floor(dxy_max) / gm_res);
+  const int dphi_max_idx = (int)(floor(dphi_max) / phi_res);
+  for (dxi = -dxy_max_idx; dxi < dxy_max_idx; ++dxi)
+    for (dyi = -dxy_max_idx; dyi < dxy_max_idx; ++dyi)
+      for (dphii = -dphi_max_idx; dphii < dphi_max_idx; ++dphii)
+      {
+        const double x_diff = dxi * gm_res, y_diff = dyi * gm_res, phi_diff = dphii * phi_res;
+        const double dist2 = x_diff * x_diff + y_diff * y_diff;
+        const double px = center[0] + x_diff, py = center[1] + y_diff, pyaw = center[2] + phi_diff;
+        const double prox_cost = gao_prox_of_corners(prox, astar_dim, p, px, py, pyaw);
+        const double cost = dist2 * dist_weight + fabs(phi_diff) * angle_weight + prox_cost * prox_weight;
+        long long ix, iy, index;
+        if (cost > min_cost) continue;
+        ix = (long long)round(px * p->con2star); /* Point<double>::toInt = std::round */
+        iy = (long long)round(py * p->con2star);
+        index = iy * astar_dim + ix;               /* calcIndex(size_t, size_t): wraps like this sum */
+        if (index < 0 || index >= (long long)astar_dim * astar_dim || !member[index]) continue;
+        if (gao_check_pose(safety, patch_dim, centers, nb_disks, yaw_res_deg, px, py, pyaw, 0))
+        {
+          out_pose[0] = px;
+          out_pose[1] = py;
+          out_pose[2] = pyaw;
+          min_cost = cost;
+          found_any = 1;
+        }
+      }
+  return found_any;
+}

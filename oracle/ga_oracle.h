@@ -236,6 +236,9 @@ typedef struct { double lf, lb, width, con2star, h_prox_cost, interp_res; } gao_
 double gao_prox_of_corners(const double* grid, int dim, const gao_prox_params* p, double x_m, double y_m, double yaw);
 void gao_path_prox_costs(const double* grid, int dim, const gao_prox_params* p, const double* poses, const int* offsets,
                          int n_paths, double* out);
+int gao_valid_close_pose(const uint8_t* safety, int patch_dim, const int* centers, int nb_disks, int yaw_res_deg,
+                         const double* prox, int astar_dim, const gao_prox_params* p, const uint8_t* member,
+                         const double* center, double* out_pose);
 
 #ifdef __cplusplus
 }

@@ -169,6 +169,23 @@ def path_prox_costs(grid, params, poses, offsets):
     return out
 
 
+def valid_close_pose(safety, centers, yaw_res_deg, prox, params, near_cells, center):
+    """step 3 of getValidClosePose; centers [nb_yaws, nb_disks, 2]; returns the pose or None"""
+    safety = np.ascontiguousarray(safety, np.uint8)
+    centers = np.ascontiguousarray(centers, np.int32)
+    prox = np.ascontiguousarray(prox, np.float64)
+    member = np.zeros(prox.shape[0] * prox.shape[0], np.uint8)
+    member[np.asarray(near_cells, np.int64)] = 1
+    p = ProxParams(*params)
+    c = np.ascontiguousarray(center, np.float64)
+    out = np.zeros(3, np.float64)
+    lib().gao_valid_close_pose.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p]
+    ok = lib().gao_valid_close_pose(_p(safety), safety.shape[0], _p(centers), centers.shape[-2], int(yaw_res_deg), _p(prox),
+                                    prox.shape[0], C.byref(p), _p(member), _p(c), _p(out))
+    return out if ok else None
+
+
 GM_DIM = 801
 
 

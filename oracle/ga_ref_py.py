@@ -82,6 +82,7 @@ def lib():
         L.gar_prox_of_corners.argtypes = [C.c_double] * 3
         L.gar_prox_of_corners.restype = C.c_double
         L.gar_con2star.restype = C.c_double
+        L.gar_valid_close_pose.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p]
         L.gar_path_prox_costs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p]
     return _lib
 
@@ -260,6 +261,15 @@ def path_prox_costs(poses_m, offsets, h_prox_cost=5.0, interp_res=0.1):
     out = np.zeros(len(offsets) - 1, np.float64)
     lib().gar_path_prox_costs(_p(poses_m), _p(offsets), len(offsets) - 1, h_prox_cost, interp_res, _p(out))
     return out
+
+
+def valid_close_pose(center, near_cells, yaw_res_coll=3.0):
+    """step 3 of HybridAStar::getValidClosePose composed from the reference's parts; the pose or None"""
+    c = np.ascontiguousarray(center, np.float64)
+    cells = np.ascontiguousarray(near_cells, np.int32)
+    out = np.zeros(3, np.float64)
+    ok = lib().gar_valid_close_pose(_p(c), _p(cells), len(cells), float(yaw_res_coll), _p(out))
+    return out if ok else None
 
 
 def prox_of_corners(x, y, yaw):

@@ -402,6 +402,52 @@ double gar_prox_of_corners(double x, double y, double yaw)  // pose in astar cel
   return std::isnan(max_value) ? 0.0 : max_value;
 }
 double gar_con2star() { return grid_tf::con2star_; }
+// step 3 of HybridAStar::getValidClosePose (hybrid_a_star_lib.cpp:1604-1668), composed like
+// getProxOfCorners above: the loop is restated, CollisionChecker::checkPose, AStar::calcIndex, grid_tf and
+// Point::toInt are the reference's.  near_cells = calcIndex of the nodes of AStar::nodes_near_goal_.
+int gar_valid_close_pose(const double* center, const int* near_cells, int n_near, double yaw_res_coll, double* out_pose)
+{
+  const Pose<double> center_pose = { center[0], center[1], center[2] };
+  const double angle_weight = 20.0, dist_weight = 1.0, prox_weight = 1.0;
+  const double dxy_max = 5.0, dphi_max = util::PI;
+  const double gm_res = GM_RES;
+  const double phi_res = yaw_res_coll * util::TO_RAD;
+  double min_cost = std::numeric_limits<double>::max();
+  int found_any = 0;
+  const int dxy_max_idx = static_cast<int>(std::floor(dxy_max) / gm_res);
+  const int dphi_max_idx = static_cast<int>(std::floor(dphi_max) / phi_res);
+  for (int dxi = -dxy_max_idx; dxi < dxy_max_idx; ++dxi)
+    for (int dyi = -dxy_max_idx; dyi < dxy_max_idx; ++dyi)
+      for (int dphii = -dphi_max_idx; dphii < dphi_max_idx; ++dphii)
+      {
+        const double x_diff = dxi * gm_res, y_diff = dyi * gm_res, phi_diff = dphii * phi_res;
+        const double dist2 = x_diff * x_diff + y_diff * y_diff;
+        const Pose<double> pose = { center_pose.x + x_diff, center_pose.y + y_diff, center_pose.yaw + phi_diff };
+        const Pose<double> ps = grid_tf::utm2astar(pose);
+        const double prox_cost = gar_prox_of_corners(ps.x, ps.y, ps.yaw);
+        const double cost = dist2 * dist_weight + std::abs(phi_diff) * angle_weight + prox_cost * prox_weight;
+        if (cost > min_cost) continue;
+        const Point<int> index2d = grid_tf::utm2astar(pose.getPoint()).toInt();
+        const size_t index = AStar::calcIndex(index2d.x, index2d.y);
+        bool found = false;
+        for (int k = 0; k < n_near; ++k)
+          if (index == (size_t)near_cells[k])
+          {
+            found = true;
+            break;
+          }
+        if (not found) continue;
+        if (CollisionChecker::checkPose(pose))
+        {
+          out_pose[0] = pose.x;
+          out_pose[1] = pose.y;
+          out_pose[2] = pose.yaw;
+          min_cost = cost;
+          found_any = 1;
+        }
+      }
+  return found_any;
+}
 // the prox_cost loop of getRSPathCosts / getRAPathCosts (hybrid_a_star_lib.cpp:588-594) over a ragged batch
 void gar_path_prox_costs(const double* poses_m, const int* offsets, int n_paths, double h_prox_cost, double interp_res, double* out)
 {

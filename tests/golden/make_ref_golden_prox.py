@@ -37,8 +37,27 @@ def inputs():
     return grid, poses, offsets
 
 
+CP_SEED, CP_CENTERS = 77, 8
+
+
+def close_pose_inputs(astar):
+    """centres (metres / rad) and their nodes_near_goal_ cell lists for the getValidClosePose rows: the
+    non-occupied cells closer than 10 cells to the centre cell (a_star.cpp:182-193)"""
+    rng = np.random.default_rng(CP_SEED)
+    ad = astar.shape[0]
+    free = np.argwhere(astar == 0)
+    picks = [free[i] for i in rng.integers(0, len(free), CP_CENTERS - 2)] + [np.array([2, 3]), np.array([ad - 3, ad - 2])]
+    ys, xs = np.mgrid[0:ad, 0:ad]
+    out = []
+    for cy, cx in picks:
+        near = (np.sqrt((xs - cx) ** 2.0 + (ys - cy) ** 2.0) < 10.0) & (astar != 2)
+        out.append(((cx * 0.625 + 0.1, cy * 0.625 + 0.2, float(rng.uniform(-3, 3))), (ys[near] * ad + xs[near]).astype(np.int32)))
+    return out
+
+
 if __name__ == "__main__":
     import ga_ref_py as gr
+    from ga_b200.synth import gen_map
     grid, poses, offsets = inputs()
     gr.init(PATCH_DIM, veh=VEH)
     assert gr.dims()[1] == ASTAR_DIM and gr.con2star() == CON2STAR
@@ -50,5 +69,14 @@ if __name__ == "__main__":
         for j in range(offsets[i], offsets[i + 1]):
             c += v[j] * H_PROX_COST * INTERP_RES  # hybrid_a_star_lib.cpp:592
         costs[i] = c
-    np.savez_compressed(os.path.join(HERE, "ref_golden_prox.npz"), prox=v, costs=costs)
+    # getValidClosePose step 3 on a synthetic map (safety patch through the reference's own processSafetyPatch)
+    gr.pass_local_map(gen_map(PATCH_DIM, CP_SEED), 0, 0)
+    gr.process_safety_patch()
+    gr.calc_astar_grid()
+    close = []
+    for center, cells in close_pose_inputs(gr.get_grid(gr.ASTAR)):
+        r = gr.valid_close_pose(center, cells)
+        close.append(np.concatenate([[0.0], np.zeros(3)]) if r is None else np.concatenate([[1.0], r]))
+    np.savez_compressed(os.path.join(HERE, "ref_golden_prox.npz"), prox=v, costs=costs, close=np.array(close))
+    print("close poses found:", int(np.array(close)[:, 0].sum()), "of", len(close))
     print("ref_golden_prox.npz: %d poses, %d paths, max %.3f" % (len(v), len(costs), v.max()))

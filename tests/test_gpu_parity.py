@@ -561,3 +561,46 @@ def test_prox_scoring_matches_oracle(planner, oracle):
     with pytest.raises(ga_b200.GaError):
         ctx.check(ctx.lib.ga_path_prox_costs(ctx.h, _abi.ptr(poses), _abi.ptr(np.array([0, 9, 4], np.int32)), 2,
                                              _abi.ptr(np.zeros(2))))
+
+
+def test_valid_close_pose_matches_oracle(planner, oracle):
+    """ga_valid_close_pose (step 3 of HybridAStar::getValidClosePose) against the oracle pinned on the
+    reference's parts: centres in the open, next to obstacles and at the patch border, with a zero prox
+    field (every cost ties eight ways: the LAST candidate in loop order must win), a random one, an empty
+    neighbourhood (-> the ego pose) and a neighbourhood that is entirely in collision."""
+    ctx, cc, astar = planner
+    dim = 1200
+    cc.initialize(dim)
+    cc.passLocalMap(ga_b200.gen_map(dim, 321), (0, 0), dim)
+    cc.processSafetyPatch()
+    grid, safety = astar.astar_grid_, cc.patch_safety_arr_
+    ad = grid.shape[0]
+    hy = ga_b200.HybridAStar(ctx, cc.vehicle, 5.0, 0.1)
+    params = (cc.vehicle.lf_, cc.vehicle.lb_, cc.vehicle.width_, 1 / ga_b200.ASTAR_RES, 5.0, 0.1)
+    rng = np.random.default_rng(11)
+    ys, xs = np.mgrid[0:ad, 0:ad]
+    free = np.argwhere(grid == 0)
+    picks = [free[i] for i in rng.integers(0, len(free), 5)] + [np.array([1, 2]), np.array([ad - 2, ad - 3])]
+    n_found = 0
+    for prox in (np.zeros((ad, ad)), rng.random((ad, ad)) * (rng.random((ad, ad)) < 0.5)):
+        ctx.upload(_abi.GRID_H_PROX, prox)
+        for cy, cx in picks:
+            near = (np.sqrt((xs - cx) ** 2.0 + (ys - cy) ** 2.0) < 10.0) & (grid != 2)
+            cells = (ys[near] * ad + xs[near]).astype(np.int32)
+            center = (cx * 0.625 + 0.3, cy * 0.625 + 0.05, float(rng.uniform(-3, 3)))
+            want = oracle.valid_close_pose(safety, cc.disk_centers_, 3, prox, params, cells, center)
+            got = hy.getValidClosePose(center, cells)
+            assert (want is None) == (got is None)
+            if want is not None:
+                n_found += 1
+                assert np.array_equal(got, want), (center, got, want)
+    assert n_found >= 6
+    ego = np.array([1.0, 2.0, 3.0])
+    assert hy.getValidClosePose((50.0, 50.0, 0.0), np.zeros(0, np.int32), ego) is ego
+    blocked = np.argwhere(grid == 2)
+    cy, cx = blocked[len(blocked) // 2]
+    cells = np.array([cy * ad + cx], np.int32)
+    center = (cx * 0.625 + 0.3, cy * 0.625 + 0.3, 0.0)
+    want = oracle.valid_close_pose(safety, cc.disk_centers_, 3, prox, params, cells, center)
+    got = hy.getValidClosePose(center, cells)
+    assert (want is None) == (got is None) and (want is None or np.array_equal(want, got))

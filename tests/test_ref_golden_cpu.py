@@ -124,3 +124,20 @@ def test_prox_scoring_rows(oracle):
     params = (gen.VEH[2], gen.VEH[3], gen.VEH[4], gen.CON2STAR, gen.H_PROX_COST, gen.INTERP_RES)
     assert np.array_equal(oracle.prox_of_corners(grid, params, poses), g["prox"])
     assert np.array_equal(oracle.path_prox_costs(grid, params, poses, offsets), g["costs"])
+
+
+def test_valid_close_pose_rows(oracle):
+    """the getValidClosePose rows of ref_golden_prox.npz (step 3 through the reference's own checkPose /
+    calcIndex / getBilinInterp on the reference's own safety patch) against the oracle chain
+    threshold -> dilation -> pool -> gao_valid_close_pose: the chosen poses bit for bit."""
+    gen, g = _prox_golden()
+    grid, _, _ = gen.inputs()
+    info, cen = oracle.calc_disks(gen.VEH[2] + gen.VEH[3], gen.VEH[4], gen.VEH[3])
+    safety = oracle.process_safety_patch(gen_map(gen.PATCH_DIM, gen.CP_SEED), 100, 130, info.disk_r_c)
+    astar = oracle.pool_max(safety)
+    params = (gen.VEH[2], gen.VEH[3], gen.VEH[4], gen.CON2STAR, gen.H_PROX_COST, gen.INTERP_RES)
+    for (center, cells), want in zip(gen.close_pose_inputs(astar), g["close"]):
+        got = oracle.valid_close_pose(safety, cen, 3, grid, params, cells, center)
+        assert (got is not None) == bool(want[0])
+        if got is not None:
+            assert np.array_equal(got, want[1:])

@@ -339,3 +339,42 @@ def test_prox_scoring_vs_reference():
     want = np.array([gr.prox_of_corners(x * c2s, y * c2s, w) for x, y, w in poses])
     got = go.prox_of_corners(grid, params, poses)
     assert np.array_equal(want, got)
+
+
+def _near_cells(astar, cx, cy, radius=10.0):
+    """what the sweep of getValidClosePose's step 1 leaves in nodes_near_goal_ (a_star.cpp:182-193): the
+    closed -- hence non-occupied -- cells closer than 10 cells to the sweep's start cell"""
+    ad = astar.shape[0]
+    ys, xs = np.mgrid[0:ad, 0:ad]
+    near = (np.sqrt((xs - cx) ** 2.0 + (ys - cy) ** 2.0) < radius) & (astar != 2)
+    return (ys[near] * ad + xs[near]).astype(np.int32)
+
+
+def test_valid_close_pose_vs_reference():
+    """step 3 of HybridAStar::getValidClosePose (hybrid_a_star_lib.cpp:1604-1668), composed in the shim from
+    the reference's own checkPose / calcIndex / getBilinInterp / grid_tf, against gao_valid_close_pose:
+    the chosen pose bit for bit, for centres in the open, next to obstacles, at the patch border (candidate
+    cells wrap in calcIndex) and with an empty neighbourhood."""
+    dim = 1000
+    patch, safety, astar = _env(dim, 77)
+    ad = astar.shape[0]
+    rng = np.random.default_rng(5)
+    prox = rng.random((ad, ad)) * (rng.random((ad, ad)) < 0.5)
+    gr.set_grid(gr.H_PROX, prox)
+    d = gr.disks()
+    params = (VEH[2], VEH[3], VEH[4], gr.con2star(), 5.0, 0.1)
+    free = np.argwhere(astar == 0)
+    picks = [free[i] for i in rng.integers(0, len(free), 6)] + [np.array([2, 3]), np.array([ad - 3, ad - 2])]
+    n_found = 0
+    for cy, cx in picks:
+        center = (cx * 0.625 + 0.1, cy * 0.625 + 0.2, float(rng.uniform(-3, 3)))
+        cells = _near_cells(astar, cx, cy)
+        want = gr.valid_close_pose(center, cells)
+        got = go.valid_close_pose(safety, d["centers"], 3, prox, params, cells, center)
+        assert (want is None) == (got is None)
+        if want is not None:
+            n_found += 1
+            assert np.array_equal(want, got), (center, want, got)
+    assert n_found >= 4
+    assert gr.valid_close_pose((100.0, 100.0, 0.0), np.zeros(0, np.int32)) is None
+    assert go.valid_close_pose(safety, d["centers"], 3, prox, params, np.zeros(0, np.int32), (100.0, 100.0, 0.0)) is None
