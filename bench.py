@@ -151,6 +151,20 @@ def step_e2e(env):
         ctx.check(lib.ga_download(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
 
 
+def step_e2e_async(env):
+    """step_e2e without the host waiting for the result: the caller syncs the context before it touches
+    the environment's buffers again"""
+    from ga_b200 import _abi
+    ctx = env["ctx"]
+    lib, h = ctx.lib, ctx.h
+    hp = env["h_patch"]
+    ctx.check(lib.ga_upload(h, _abi.GRID_PATCH, C.c_void_p(hp.data_ptr()), hp.numel()))
+    ctx.check(lib.ga_build_safety(h))
+    ctx.check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], None))
+    for gid, t in env["outs"].items():
+        ctx.check(lib.ga_download_async(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+
+
 def _ref_goal(patch):
     import ga_oracle_py as go
     thr = go.threshold(patch, 100, 130)
@@ -550,6 +564,29 @@ def main():
                 e["ctx"].prof_enable(False)
         return dev_ms, wall * 1e3, launches, cells
 
+    def timed_pipelined(steps):
+        """the e2e step with the N_ROT environments (one context, stream and pinned buffer set each) in
+        flight together: environment k's upload and downloads overlap the kernels of the others.  Every
+        step still copies its own patch in and its four result planes out inside the timed region."""
+        for i in range(args.warmup):
+            step_e2e_async(envs[i % N_ROT])
+        for e in envs:
+            e["ctx"].sync()
+        barrier()
+        sampler.active = True
+        t0 = time.perf_counter()
+        for i in range(steps):
+            e = envs[i % N_ROT]
+            if i >= N_ROT:
+                e["ctx"].sync()  # this environment's previous step is complete: its buffers are free again
+            step_e2e_async(e)
+        for e in envs:
+            e["ctx"].sync()
+        barrier()
+        wall = time.perf_counter() - t0
+        sampler.active = False
+        return wall * 1e3, sum(closed[i % N_ROT] for i in range(steps))
+
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -567,20 +604,22 @@ def main():
             n += n_
         kt[name] = (ms, n)
     # the steps are serialised on each context's stream; K steps' device time = sum of per-step event spans
-    e2e_dev_ms, e2e_wall_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
+    e2e_dev_ms, e2e_serial_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
+    e2e_wall_ms, e2e_cells = timed_pipelined(args.steps)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
     collision = run_collision_leg(envs[0], args, ga_b200) if (rank == 0 and not args.no_collision) else None
     replan = run_replan_leg(ga_b200, local_rank, args) if (rank == 0 and not args.no_replan) else None
     sampler.stop_flag = True
 
     # max over ranks
-    t = torch.tensor([dev_ms, e2e_wall_ms, float(cells), float(e2e_cells), float(launches)], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, e2e_wall_ms, float(cells), float(e2e_cells), float(launches), e2e_serial_ms], dtype=torch.float64,
+                     device="cuda")
     if world > 1:
         tmax = t.clone()
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone()
         dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        dev_ms, e2e_wall_ms = float(tmax[0]), float(tmax[1])
+        dev_ms, e2e_wall_ms, e2e_serial_ms = float(tmax[0]), float(tmax[1]), float(tmax[5])
         cells, e2e_cells, launches = float(tsum[2]), float(tsum[3]), int(tsum[4])
     value = cells / (dev_ms * 1e-3) / 1e6
     e2e_value = e2e_cells / (e2e_wall_ms * 1e-3) / 1e6
@@ -599,7 +638,11 @@ def main():
                            "disk_r_c": envs[0]["cc"].disk_r_c_, "l2": "inputs rotate over %d environments per rank (~130 MB each) > L2" % N_ROT,
                            "cells_closed_per_step": cells / args.steps / world},
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": PATCH_DIM * PATCH_DIM,
-                        "d2h_bytes_per_step": adim * adim * 21, "ms_per_step": e2e_wall_ms / args.steps},
+                        "d2h_bytes_per_step": adim * adim * 21, "ms_per_step": e2e_wall_ms / args.steps,
+                        "pipeline": "%d planner contexts in flight (one stream and pinned buffer set each): a step's copies "
+                                    "overlap the other contexts' kernels" % N_ROT,
+                        "serial_value": e2e_cells / (e2e_serial_ms * 1e-3) / 1e6,
+                        "serial_ms_per_step": e2e_serial_ms / args.steps},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "kernel": "heur_sweep_kernel", "achieved": achieved, "peak": hbm_peak,
                              "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES, "peak_source": peak_src,

@@ -376,6 +376,22 @@ extern "C" int ga_download(ga_ctx* c, int grid_id, void* dst, size_t bytes)
   return GA_OK;
 }
 
+// ga_download without the wait: dst (pinned host memory) is valid after ga_sync.  Lets a caller with
+// several contexts keep uploads, builds and downloads of different contexts in flight together.
+extern "C" int ga_download_async(ga_ctx* c, int grid_id, void* dst, size_t bytes)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, dst, GA_ERR_ARG, "null destination");
+  GA_REQUIRE(c, c->patch_dim > 0 || grid_id == GA_GRID_CART || grid_id == GA_GRID_PMAP, GA_ERR_STATE, "no patch (call ga_patch_reset)");
+  void* p;
+  size_t b;
+  GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");
+  GA_REQUIRE(c, b == bytes, GA_ERR_ARG, "size mismatch");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  GA_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+  return GA_OK;
+}
+
 // ---- measurement --------------------------------------------------------------------------------
 
 extern "C" int ga_prof_enable(ga_ctx* c, int on)

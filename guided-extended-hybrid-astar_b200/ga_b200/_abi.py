@@ -99,6 +99,7 @@ SYMBOLS = {
     "ga_build_potential": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, C.POINTER(C.c_int)]),
     "ga_upload": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),
     "ga_download": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),
+    "ga_download_async": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),
     "ga_grid_bytes": (C.c_int, [_P, C.c_int, C.POINTER(C.c_size_t)]),
     "ga_device_ptr": (C.c_int, [_P, C.c_int, C.POINTER(_P)]),
     "ga_patch_dim": (C.c_int, [_P]),

@@ -301,6 +301,10 @@ GA_API int ga_build_potential(ga_ctx* ctx, int ego_x, int ego_y, const int* vor_
 /* whole-grid host <-> device copies (bytes must equal the grid's size) */
 GA_API int ga_upload(ga_ctx* ctx, int grid_id, const void* src, size_t bytes);
 GA_API int ga_download(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
+/* ga_download without the wait: dst must be pinned host memory and is valid after ga_sync(ctx).
+ * With one context per planner this keeps the copies of one planner overlapped with the kernels of
+ * another (bench.py's pipelined e2e leg). */
+GA_API int ga_download_async(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
 GA_API int ga_grid_bytes(const ga_ctx* ctx, int grid_id, size_t* bytes);
 /* device address of a grid (for zero-copy consumers such as the bench's resident-input leg) */
 GA_API int ga_device_ptr(ga_ctx* ctx, int grid_id, void** dptr);

@@ -604,3 +604,41 @@ def test_valid_close_pose_matches_oracle(planner, oracle):
     want = oracle.valid_close_pose(safety, cc.disk_centers_, 3, prox, params, cells, center)
     got = hy.getValidClosePose(center, cells)
     assert (want is None) == (got is None) and (want is None or np.array_equal(want, got))
+
+
+def test_download_async_and_interleaved_contexts(oracle):
+    """ga_download_async + ga_sync return what ga_download returns, also when three contexts (one stream
+    each) have their uploads, builds and downloads in flight together (bench.py's pipelined e2e leg)."""
+    import torch
+    envs = []
+    for k in range(3):
+        ctx = ga_b200.GridContext(0)
+        cfg = ga_b200.LibConfig()
+        astar = ga_b200.AStar(ctx, cfg)
+        cc = ga_b200.CollisionChecker(ctx, ga_b200.Vehicle.from_config(ga_b200.VehConfig()), cfg)
+        cc.initialize(1024)
+        patch = torch.from_numpy(ga_b200.gen_map(1024, 900 + k)).pin_memory()
+        ctx.upload(_abi.GRID_PATCH, patch.numpy())
+        cc.processSafetyPatch()
+        goal = ga_b200.sample_free_cells(astar.astar_grid_, 1, 5 + k)[0]
+        outs = {gid: torch.empty(256 * 256, dtype=dt).pin_memory()
+                for gid, dt in ((_abi.GRID_HEUR_COST, torch.float64), (_abi.GRID_HEUR_PARENT, torch.int32))}
+        envs.append((ctx, astar, patch, goal, outs))
+    for rep in range(3):
+        for ctx, astar, patch, goal, outs in envs:
+            ctx.check(ctx.lib.ga_upload(ctx.h, _abi.GRID_PATCH, patch.data_ptr(), patch.numel()))
+            ctx.check(ctx.lib.ga_build_safety(ctx.h))
+            ctx.check(ctx.lib.ga_build_heuristic(ctx.h, 0, int(goal[0]), int(goal[1]), None))
+            for gid, t in outs.items():
+                ctx.check(ctx.lib.ga_download_async(ctx.h, gid, t.data_ptr(), t.numel() * t.element_size()))
+    for ctx, astar, patch, goal, outs in envs:
+        ctx.sync()
+        for gid, t in outs.items():
+            assert np.array_equal(t.numpy().reshape(256, 256), ctx.download(gid), equal_nan=True)
+        fp = oracle.heuristic_fixedpoint(oracle.HeurParams(256, 5.0, 3.0, 0.0, 0, 0, 0), astar.astar_grid_,
+                                         np.zeros((256, 256), np.uint8), np.full((256, 256), 5.0), np.zeros((256, 256)),
+                                         (int(goal[0]), int(goal[1])))
+        cost = outs[_abi.GRID_HEUR_COST].numpy().reshape(256, 256)
+        closed = (fp["flags"] & 1) != 0
+        assert np.array_equal(cost[closed], fp["cost"][closed])
+        ctx.close()
