@@ -642,3 +642,43 @@ def test_download_async_and_interleaved_contexts(oracle):
         closed = (fp["flags"] & 1) != 0
         assert np.array_equal(cost[closed], fp["cost"][closed])
         ctx.close()
+
+
+@pytest.mark.parametrize("knobs", [
+    dict(GA_SW_ROUND="0", GA_SW_EARLY="0", GA_SW_REFRESH="0", GA_SW_LINGER="0", GA_SW_PREFETCH="0"),   # plain: publish when converged
+    dict(GA_SW_ROUND="0", GA_SW_EARLY="1", GA_SW_REFRESH="1", GA_SW_LINGER="0", GA_SW_PREFETCH="0"),
+    dict(GA_SW_ROUND="1", GA_SW_EARLY="1", GA_SW_REFRESH="1", GA_SW_LINGER="0", GA_SW_PREFETCH="0"),   # throughput mode
+    dict(GA_SW_ROUND="1", GA_SW_EARLY="255", GA_SW_REFRESH="2", GA_SW_LINGER="8000", GA_SW_PREFETCH="1"),
+    dict(GA_SW_ROUND="0", GA_SW_EARLY="255", GA_SW_REFRESH="2", GA_SW_LINGER="8000", GA_SW_PREFETCH="1"),  # latency mode
+    dict(GA_SW_ROUND="0", GA_SW_EARLY="255", GA_SW_REFRESH="2", GA_SW_LINGER="100000", GA_SW_PREFETCH="1", GA_SW_WARPS="1"),
+    dict(GA_SW_ROUND="0", GA_SW_EARLY="3", GA_SW_REFRESH="2", GA_SW_LINGER="0", GA_SW_PREFETCH="1", GA_SW_WARPS="2"),
+])
+def test_heuristic_schedules_agree(oracle, knobs, monkeypatch):
+    """the sweep kernel's scheduling knobs (sweep order, when a tile publishes, in-place halo refresh, waiting,
+    staging ahead, worker count) only change WHEN cells are relaxed: every combination must give the oracle's
+    fixed point bit for bit, with prox and unknown-cell costs on (all four sweep_step variants)."""
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    dim, seed = 1492, 3
+    ctx = ga_b200.GridContext(0)
+    cfg = ga_b200.LibConfig(ASTAR_UNKNOWN_COST=2.5)
+    astar = ga_b200.AStar(ctx, cfg)
+    cc = ga_b200.CollisionChecker(ctx, ga_b200.Vehicle.from_config(ga_b200.VehConfig()), cfg)
+    cc.initialize(dim)
+    ctx.upload(_abi.GRID_PATCH, ga_b200.gen_map(dim, seed))
+    cc.processSafetyPatch()
+    rng = np.random.default_rng(seed)
+    grid, mc, prox, fence = _heur_inputs(astar, ctx, rng, True)
+    goal = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, seed)[0]
+    hp = oracle.HeurParams(astar.astar_dim_, 5.0, 3.0, 2.5, 0, 0, 0)
+    want = oracle.heuristic_fixedpoint(hp, grid, fence, mc, prox, goal)
+    for rep in range(3):
+        n = astar.calcDistanceHeuristic(goal, None, for_path=False)
+        cs = astar.closed_set_guidance_
+        assert n == want["n_closed"]
+        assert np.array_equal(cs.flags, want["flags"])
+        closed = (want["flags"] & 1) != 0
+        assert np.array_equal(cs.cost[closed], want["cost"][closed])
+        assert np.array_equal(cs.parent[closed], want["parent"][closed])
+        assert np.array_equal(cs.dist[closed], want["dist"][closed])
+    ctx.close()
