@@ -997,7 +997,11 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     }
   }
   __syncthreads();
-  if (term) a.tlist[blockIdx.x * FIN_SLOTS + s_cnt[1][warp] + __popc(m_term & ((1u << lane) - 1u))] = n;
+  if (term)
+  {
+    a.tlist[blockIdx.x * FIN_SLOTS + s_cnt[1][warp] + __popc(m_term & ((1u << lane) - 1u))] = n;
+    a.tot[n] = make_int2(-1, -1);  // "not known yet" for finish B's shortcut
+  }
   // chain walk inside the block (shared memory, one load per hop)
   int cur = threadIdx.x, cs = 0, cd = 0;
   for (int v = lpar; v >= 0; v = lp[cur])
@@ -1009,17 +1013,27 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
   if (in) a.scratch[n] = fin_pack(cur % FB - lx, cur / FB - ly, cs, cd);
 }
 
-// one thread per terminal cell: terminal -> parent -> that block's terminal -> ... -> root
+// one thread per terminal cell: terminal -> parent -> that block's terminal -> ... -> root.  A walk ends
+// early at a terminal whose total another thread has already written (the threads nearer the root
+// finish first), so the longest chain costs about half its hops.
 __global__ void __launch_bounds__(FIN_SLOTS) heur_finish_b_kernel(heur_args single, const heur_args* many)
 {
   const heur_args& a = many ? many[blockIdx.y] : single;
   const int dim = a.dim, goal = a.goal, nbx = (dim + FB - 1) / FB;
   if ((int)blockIdx.x >= nbx * nbx || (int)threadIdx.x >= a.tcount[blockIdx.x]) return;  // one CTA = one finish-A block's terminals
   const int c = a.tlist[blockIdx.x * FIN_SLOTS + threadIdx.x];
+  const long long* tot64 = reinterpret_cast<const long long*>(a.tot);
   int cur = c, cs = 0, cd = 0;
   for (;;)
   {
     const int p = __ldg(a.parent + cur);
+    const long long known = cur != c ? __ldcg(tot64 + cur) : -1;  // same dependency level as the parent load
+    if ((int)(known & 0xFFFFFFFFll) >= 0)
+    {
+      cs += (int)(known & 0xFFFFFFFFll);
+      cd += (int)(known >> 32);
+      break;
+    }
     const int d = p - cur;
     if (d == 1 || d == -1 || d == dim || d == -dim) ++cs; else ++cd;  // the step terminal -> parent
     if (p == goal) break;
@@ -1029,7 +1043,7 @@ __global__ void __launch_bounds__(FIN_SLOTS) heur_finish_b_kernel(heur_args sing
     cur = fin_target(s, p, dim);
     if (cur == goal) break;
   }
-  a.tot[c] = make_int2(cs, cd);
+  __stcg(reinterpret_cast<long long*>(a.tot) + c, ((long long)cd << 32) | (unsigned)cs);  // one 8-byte store: never seen half written
 }
 
 __global__ void __launch_bounds__(256) heur_finish_c_kernel(heur_args single, const heur_args* many)
