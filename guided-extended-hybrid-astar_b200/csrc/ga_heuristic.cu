@@ -208,17 +208,17 @@ __global__ void heur_init_kernel(heur_grid single, const heur_grid* many, heur_q
 // ---------------------------------------------------------------------------------------------
 #define SW_O 30                    // owned cells per tile edge
 #define SW_P 33                    // shared-memory pitch (doubles)
-#define SW_WARPS 6                 // workers per CTA (one CTA per SM: 6 x 33.5 KB of shared memory)
+#define SW_WARPS 8                 // workers per CTA (one CTA per SM: 8 x 25 KB of shared memory)
 #define SW_FULL 0xFFFFFFFFu
 #define SW_EARLY_ALL 255           // heur_queue::early: publish after every changing sweep
 
 struct sweep_tile
 {
   double g[32 * SW_P];   // cost plane, relaxed in place
-  double w[32 * SW_P];   // value last read from / written to global memory
   double mc[32 * SW_P];  // movement_cost_map_ of the cell (edge length factor of the DESTINATION); +inf = blocked
   double pb[32 * SW_P];  // h_prox_arr_ of the cell (x astar_prox_cost_ = prox_cost, term of the PREDECESSOR)
   unsigned urow[32], ucol[32];  // UNKNOWN masks: urow[y] bit x / ucol[x] bit y
+  unsigned dirty[32];           // dirty[y] bit x: cell improved since it was last written to global memory
 };
 
 // NaN-safe minimum (a NaN candidate, 0/0 in h_prox_arr_, never wins -- a_star.cpp:492-497)
@@ -292,6 +292,7 @@ __device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const 
   int s = dir > 0 ? 0 : 31;
   double a = S.g[s * ds + lane * dl];
   int changed = 0;
+  unsigned dm = S.dirty[lane];  // this lane keeps row `lane` of the dirty map, whichever way the sweep runs
 #pragma unroll 5
   for (int k = 0; k < SW_O; ++k)
   {
@@ -302,8 +303,15 @@ __device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const 
     const bool imp = nv < old;
     if (imp) S.g[s * ds + lane * dl] = nv;
     changed |= imp;
+    if (ORIENT == 0)
+    {
+      const unsigned b = __ballot_sync(SW_FULL, imp);  // lane = x, line = row s: the ballot IS row s's news
+      if (lane == s) dm |= b;
+    }
+    else dm |= (unsigned)imp << s;                     // lane = y, line = column s
     a = nv;
   }
+  S.dirty[lane] = dm;
   return changed;
 }
 
@@ -348,6 +356,7 @@ __device__ __forceinline__ int sweep_round(sweep_tile& S, const int lane, const 
 {
   double a0 = S.g[lane], a1 = S.g[lane * SW_P], a2 = S.g[31 * SW_P + lane], a3 = S.g[lane * SW_P + 31];
   int changed = 0;
+  unsigned dm = S.dirty[lane];
 #pragma unroll 2
   for (int k = 0; k < SW_O; ++k)
   {
@@ -363,8 +372,13 @@ __device__ __forceinline__ int sweep_round(sweep_tile& S, const int lane, const 
     if (i2) S.g[sb * SW_P + lane] = n2;
     if (i3) S.g[lane * SW_P + sb] = n3;
     changed |= (int)(i0 | i1 | i2 | i3);
+    const unsigned b0 = __ballot_sync(SW_FULL, i0), b2 = __ballot_sync(SW_FULL, i2);
+    if (lane == sf) dm |= b0;
+    if (lane == sb) dm |= b2;
+    dm |= ((unsigned)i1 << sf) | ((unsigned)i3 << sb);
     a0 = n0; a1 = n1; a2 = n2; a3 = n3;
   }
+  S.dirty[lane] = dm;
   changed = __any_sync(SW_FULL, changed);
   __syncwarp();
   return changed;
@@ -441,14 +455,16 @@ __device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V
   {
     const int idx = r * SW_P + lane;
     const double v = S.g[idx];
-    const bool st = own_x & (v < S.w[idx]);
+    const bool st = own_x & ((S.dirty[r] >> lane) & 1u);
     const unsigned kb = st ? __float_as_uint(__double2float_rd(v)) : 0xFFFFFFFFu;
     if (st) __stcg(grow, v);
-    if (st) S.w[idx] = v;
     col_key = min(col_key, kb);
     if (r == 1) kn = kb;
     if (r == SW_O) ks = kb;
   }
+  __syncwarp();
+  S.dirty[lane] = 0;
+  __syncwarp();
   const unsigned k_w = __shfl_sync(SW_FULL, col_key, 1), k_e = __shfl_sync(SW_FULL, col_key, SW_O);
   const unsigned kk = sweep_dir_keys(lane, k_w, k_e, kn, ks);
   return sweep_notify<FINAL>(V, q, lane, kk, col_key != 0xFFFFFFFFu, n_act, n_unused);
@@ -463,13 +479,16 @@ __device__ __forceinline__ void sweep_publish_border(sweep_tile& S, const sweep_
   const bool own = lane >= 1 && lane <= SW_O;
   const int i_n = 1 * SW_P + lane, i_s = SW_O * SW_P + lane, i_w = lane * SW_P + 1, i_e = lane * SW_P + SW_O;
   const double v_n = S.g[i_n], v_s = S.g[i_s], v_w = S.g[i_w], v_e = S.g[i_e];
-  const bool s_n = own && v_n < S.w[i_n], s_s = own && v_s < S.w[i_s], s_w = own && v_w < S.w[i_w], s_e = own && v_e < S.w[i_e];
-  __syncwarp();  // a corner cell is looked at by two lanes: both before either marks it written
+  const unsigned d_n = S.dirty[1], d_s = S.dirty[SW_O], d_y = S.dirty[lane];  // rows 1 / 30 (lane = x), row `lane` (lane = y)
+  const bool s_n = own && ((d_n >> lane) & 1u), s_s = own && ((d_s >> lane) & 1u);
+  const bool s_w = own && ((d_y >> 1) & 1u), s_e = own && ((d_y >> SW_O) & 1u);
+  __syncwarp();  // every lane has read the map before the published cells are taken out of it
+  S.dirty[lane] = (lane == 1 || lane == SW_O) ? 0u : (d_y & ~((1u << 1) | (1u << SW_O)));
   double* g00 = V.gp + (size_t)V.oy * V.dim + V.ox;
-  if (s_n) { __stcg(g00 + (size_t)1 * V.dim + lane, v_n); S.w[i_n] = v_n; }
-  if (s_s) { __stcg(g00 + (size_t)SW_O * V.dim + lane, v_s); S.w[i_s] = v_s; }
-  if (s_w) { __stcg(g00 + (size_t)lane * V.dim + 1, v_w); S.w[i_w] = v_w; }
-  if (s_e) { __stcg(g00 + (size_t)lane * V.dim + SW_O, v_e); S.w[i_e] = v_e; }
+  if (s_n) __stcg(g00 + (size_t)1 * V.dim + lane, v_n);
+  if (s_s) __stcg(g00 + (size_t)SW_O * V.dim + lane, v_s);
+  if (s_w) __stcg(g00 + (size_t)lane * V.dim + 1, v_w);
+  if (s_e) __stcg(g00 + (size_t)lane * V.dim + SW_O, v_e);
   const unsigned kn = s_n ? __float_as_uint(__double2float_rd(v_n)) : none, ks = s_s ? __float_as_uint(__double2float_rd(v_s)) : none;
   const unsigned kw = s_w ? __float_as_uint(__double2float_rd(v_w)) : none, ke = s_e ? __float_as_uint(__double2float_rd(v_e)) : none;
   const unsigned k_w = __reduce_min_sync(SW_FULL, kw), k_e = __reduce_min_sync(SW_FULL, ke);
@@ -744,7 +763,6 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
         const double gv = ((vm >> r) & 1u) ? v_g[r] : INFINITY;
         const int idx = r * SW_P + lane;
         S.g[idx] = gv;
-        S.w[idx] = gv;
         if (r >= 1 && r <= SW_O) reached |= gv < INFINITY;
         uc |= (unsigned)(v_c[r] & 1) << r;
         bc |= (unsigned)((v_c[r] >> 1) & 1) << r;
@@ -759,6 +777,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     const int glx = goal % dim - ox, gly = goal / dim - oy;
     if (lane == glx && gly >= 0 && gly < 32) bc |= 1u << gly;
     const bool must_run = glx >= 1 && glx <= SW_O && gly >= 1 && gly <= SW_O;  // the root's tile is not a fixed point of its old halo
+    S.dirty[lane] = 0;
     if (unk_w != 0)
     {
       S.ucol[lane] = uc;
