@@ -102,6 +102,22 @@ __constant__ int c_ndy[8] = { 0, 0, -1, 1, -1, -1, 1, 1 };
 
 __device__ __forceinline__ int ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
 
+#ifdef SW_TRACE  // development: per-tile event log (tools/trace_wave.py); never defined in the shipped build
+__device__ unsigned long long g_trace[1 << 20];
+__device__ unsigned g_trace_n;
+__device__ __forceinline__ void trace_ev(int lane, int tile, int ev, int arg)
+{
+  if (lane != 0) return;
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  const unsigned i = atomicAdd(&g_trace_n, 1u);
+  if (i < (1u << 20)) g_trace[i] = (t << 24) | ((unsigned long long)(tile & 0xFFF) << 12) | ((unsigned long long)(ev & 15) << 8) | (arg & 255);
+}
+#define TRACE(lane, tile, ev, arg) trace_ev(lane, tile, ev, arg)
+#else
+#define TRACE(lane, tile, ev, arg) ((void)0)
+#endif
+
 // The ring is a ticket queue: a consumer takes the next ticket (atomicAdd on the head cursor) and
 // spins on ITS slot only, a producer takes the next position (atomicAdd on the tail cursor) and
 // stores the entry there.  Idle CTAs therefore poll distinct addresses and a pushed tile is picked
@@ -114,20 +130,14 @@ __device__ __forceinline__ void q_push(const heur_queue& q, int entry)
 }
 
 // mark tile t of grid gi as needing a (re)run; the caller's writes to g are already fenced.
+// The state word is two bits -- T_QUEUED = "news", T_RUNNING = "a worker has it", T_DIRTY = both -- so ONE
+// atomic OR does every transition: idle -> queued (and we push it), running -> dirty, the rest unchanged.
 // The caller has already counted the tile in HC_PENDING; returns 1 if the count was NOT consumed.
 __device__ __forceinline__ int tile_activate(const heur_queue& q, int* state, int gi, int t)
 {
-  for (;;)
-  {
-    const int old = atomicCAS(state + t, T_IDLE, T_QUEUED);
-    if (old == T_IDLE)
-    {
-      q_push(q, ((gi << 20) | t) + 1);
-      return 0;
-    }
-    if (old == T_QUEUED || old == T_DIRTY) return 1;
-    if (atomicCAS(state + t, T_RUNNING, T_DIRTY) == T_RUNNING) return 1;  // else it just finished: retry
-  }
+  if (atomicOr(state + t, (int)T_QUEUED) != T_IDLE) return 1;
+  q_push(q, ((gi << 20) | t) + 1);
+  return 0;
 }
 
 // blocks until this worker's ticket is served (returns the entry) or all work is done (returns -1).
@@ -579,6 +589,7 @@ __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit&
 {
   int n = 0, n_changing = 0, n_pub = 0;
   const bool run0 = must_run || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+  TRACE(lane, V.tile, 2, (int)run0 | ((int)fresh << 1));
   const bool can_linger = q.linger != 0 && q.early == SW_EARLY_ALL;  // everything is published when the tile waits
   if (!run0 && !can_linger) return 0;
   bool prefetch = q.prefetch && fresh;
@@ -597,15 +608,19 @@ __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit&
       {
         // the last sweep was clean (or the tile was staged ahead of the wave): news first, the
         // confirming sweeps later -- nobody waits for those
+        TRACE(lane, V.tile, 6, 0);
         const long long t_end = clock64() + (long long)q.linger;
         do st = ld_volatile(V.state + V.tile);
         while (st != T_DIRTY && __all_sync(SW_FULL, clock64() < t_end));
         may_linger = false;
+        TRACE(lane, V.tile, 8, st == T_DIRTY);
       }
       if (st == T_DIRTY)
       {
         const int dn = sweep_refresh_halo(S, V, lane);
-        if (dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2))
+        const bool news = dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+        TRACE(lane, V.tile, 5, (dn + 1) | ((int)news << 3));
+        if (news)
         {
           mask = 0;
           prim = dn;
@@ -634,6 +649,7 @@ __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit&
       prim = (d + 1) & 3;  // round robin (trying the perpendiculars before the way back measured slower)
       ++n;
     }
+    TRACE(lane, V.tile, 3, d | (ch << 2));
     n_changing += ch;
     last_ch = ch;
     if (ch) may_linger = can_linger;
@@ -646,6 +662,7 @@ __device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit&
       }
       if (q.early == SW_EARLY_ALL) sweep_publish_border(S, V, q, lane, n_act, n_unused);
       else sweep_publish<false>(S, V, q, lane, n_act, n_unused);
+      TRACE(lane, V.tile, 4, 0);
     }
     if (q.refresh == 1 && st == T_DIRTY)
     {
@@ -699,6 +716,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
 #undef HG
     const int tx = tile % tiles_x, ty = tile / tiles_x;
     const int ox = tx * SW_O - 1, oy = ty * SW_O - 1;
+    TRACE(lane, tile, 1, 0);
     V.gp = gp; V.state = state; V.tile = tile; V.dim = dim; V.tiles_x = tiles_x; V.tx = tx; V.ty = ty; V.ox = ox; V.oy = oy;
     // ---- stage the 32x32 block (lane = x); every address is clamped into the grid so that all
     //      loads are unconditional and in flight together; out-of-grid cells are fixed up after.
@@ -829,6 +847,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     const long long t3 = clock64();
 
     if (any) cont = sweep_publish<true>(S, V, q, lane, &n_act, &n_unused);
+    TRACE(lane, tile, 7, any);
     if (lane == 0)
     {
       atomicAdd(q.ctl + HC_VISITS, 1);
@@ -1354,3 +1373,22 @@ extern "C" int ga_heur_stats(ga_ctx* c, long long* out7)
   memcpy(out7 + 3, w + HC_CYC, 4 * sizeof(long long));
   return GA_OK;
 }
+
+#ifdef SW_TRACE
+extern "C" __attribute__((visibility("default"))) int ga_heur_trace(ga_ctx* c, unsigned long long* out, unsigned cap, unsigned* n, int reset)
+{
+  cudaStreamSynchronize(c->stream);
+  unsigned cnt = 0;
+  cudaMemcpyFromSymbol(&cnt, g_trace_n, sizeof cnt);
+  if (cnt > (1u << 20)) cnt = 1u << 20;
+  if (cnt > cap) cnt = cap;
+  if (out && cnt) cudaMemcpyFromSymbol(out, g_trace, sizeof(unsigned long long) * cnt);
+  *n = cnt;
+  if (reset)
+  {
+    const unsigned z = 0;
+    cudaMemcpyToSymbol(g_trace_n, &z, sizeof z);
+  }
+  return 0;
+}
+#endif
