@@ -94,6 +94,7 @@ extern "C" int ga_destroy(ga_ctx* c)
   free_grids(c);
   ga_cart_free(c);
   ga_rt_free(c);
+  ga_reforder_free(c);
   if (c->d_centers) cudaFree(c->d_centers);
   if (c->d_stage) cudaFree(c->d_stage);
   if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -372,6 +373,29 @@ extern "C" int ga_download(ga_ctx* c, int grid_id, void* dst, size_t bytes)
   GA_REQUIRE(c, b == bytes, GA_ERR_ARG, "size mismatch");
   GA_CUDA(c, cudaSetDevice(c->device));
   GA_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return GA_OK;
+}
+
+// a w x h window of an astar-sized grid (row pitch = astar_dim) into a dense host array
+extern "C" int ga_download_window(ga_ctx* c, int grid_id, int x0, int y0, int w, int h, void* dst)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, dst, GA_ERR_ARG, "null destination");
+  GA_REQUIRE(c, c->patch_dim > 0, GA_ERR_STATE, "no patch (call ga_patch_reset)");
+  void* p;
+  size_t b;
+  GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");
+  const size_t na = (size_t)c->astar_dim * c->astar_dim;
+  GA_REQUIRE(c, na > 0 && b % na == 0 && grid_id != GA_GRID_PATCH && grid_id != GA_GRID_SAFETY && grid_id != GA_GRID_CART &&
+                    grid_id != GA_GRID_PMAP && grid_id != GA_GRID_OBSTACLE_DIST && grid_id != GA_GRID_VORONOI_DIST,
+             GA_ERR_ARG, "not an astar-sized grid");
+  GA_REQUIRE(c, x0 >= 0 && y0 >= 0 && w > 0 && h > 0 && x0 + w <= c->astar_dim && y0 + h <= c->astar_dim, GA_ERR_ARG,
+             "window outside the grid");
+  const size_t el = b / na;
+  GA_CUDA(c, cudaSetDevice(c->device));
+  GA_CUDA(c, cudaMemcpy2DAsync(dst, (size_t)w * el, static_cast<char*>(p) + ((size_t)y0 * c->astar_dim + x0) * el,
+                               (size_t)c->astar_dim * el, (size_t)w * el, (size_t)h, cudaMemcpyDeviceToHost, c->stream));
   GA_CUDA(c, cudaStreamSynchronize(c->stream));
   return GA_OK;
 }

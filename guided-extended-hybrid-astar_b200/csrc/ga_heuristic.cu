@@ -1152,17 +1152,6 @@ int ga_heur_alloc(ga_ctx* c)
   GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
   GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS * sizeof(sweep_tile))));
-  // development knobs (read once per patch): workers per SM, idle back-off, early publication
-  c->sw_warps = SW_WARPS;
-  c->sw_poll_ns = 20;
-  c->sw_early = c->sw_round = c->sw_refresh = c->sw_linger = c->sw_prefetch = -1;  // chosen per launch (queue_knobs)
-  if (const char* s = getenv("GA_SW_WARPS")) c->sw_warps = atoi(s) >= 1 && atoi(s) <= SW_WARPS ? atoi(s) : SW_WARPS;
-  if (const char* s = getenv("GA_POLL_NS")) c->sw_poll_ns = atoi(s);
-  if (const char* s = getenv("GA_SW_EARLY")) c->sw_early = atoi(s);
-  if (const char* s = getenv("GA_SW_ROUND")) c->sw_round = atoi(s);
-  if (const char* s = getenv("GA_SW_REFRESH")) c->sw_refresh = atoi(s);
-  if (const char* s = getenv("GA_SW_LINGER")) c->sw_linger = atoi(s);
-  if (const char* s = getenv("GA_SW_PREFETCH")) c->sw_prefetch = atoi(s);
   return GA_OK;
 }
 
@@ -1276,6 +1265,114 @@ extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, i
     GA_CUDA(c, cudaMemcpyAsync(n_closed, c->d_hctl + HC_CLOSED, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     GA_CUDA(c, cudaStreamSynchronize(c->stream));
   }
+  return GA_OK;
+}
+
+// scheduling knobs of the sweep kernel (tests: every schedule gives the same fixed point); -1 = automatic
+extern "C" int ga_set_heur_knobs(ga_ctx* c, const int* k7)
+{
+  if (!c || !k7) return GA_ERR_ARG;
+  c->sw_warps = k7[0] >= 1 && k7[0] <= SW_WARPS ? k7[0] : SW_WARPS;
+  c->sw_poll_ns = k7[1] >= 0 ? k7[1] : 20;
+  c->sw_early = k7[2];
+  c->sw_round = k7[3];
+  c->sw_refresh = k7[4];
+  c->sw_linger = k7[5];
+  c->sw_prefetch = k7[6];
+  return GA_OK;
+}
+
+extern "C" int ga_build_heuristic_ex(ga_ctx* c, int slot, const ga_heur_query* q, int* n_closed)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, q != nullptr, GA_ERR_ARG, "query is NULL");
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_ap, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, slot == 0 || slot == 1, GA_ERR_ARG, "slot must be 0 (guidance) or 1 (path)");
+  const int dim = c->astar_dim;
+  GA_REQUIRE(c, q->goal_x >= 0 && q->goal_y >= 0 && q->goal_x < dim && q->goal_y < dim, GA_ERR_ARG, "goal outside the astar grid");
+  if (!(q->flags & GA_HEUR_REFORDER))
+  {
+    GA_REQUIRE(c, (q->flags & GA_HEUR_EARLY_EXIT) == 0, GA_ERR_ARG,
+               "GA_HEUR_EARLY_EXIT is a property of the reference's closing order: combine it with GA_HEUR_REFORDER");
+    if (c->near_slot == slot) c->near_slot = -1;
+    return ga_build_heuristic(c, slot, q->goal_x, q->goal_y, n_closed);
+  }
+  GA_REQUIRE(c, q->start_x >= 0 && q->start_y >= 0 && q->start_x < dim && q->start_y < dim, GA_ERR_ARG,
+             "start outside the astar grid");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int rc = ga_heur_reforder_build(c, slot, q, n_closed);
+  if (rc != GA_OK) return rc;
+  if (q->flags & GA_HEUR_ONLY_NEAR)
+  {
+    c->near_slot = slot;
+    c->near_start[0] = q->start_x;
+    c->near_start[1] = q->start_y;
+  }
+  else if (c->near_slot == slot)
+    c->near_slot = -1;
+  return GA_OK;
+}
+
+// AStar::nodes_near_goal_ (a_star.cpp:182-193)
+extern "C" int ga_heur_near_nodes(ga_ctx* c, int slot, int start_x, int start_y, int* ids, double* dist, int cap, int* n)
+{
+  if (!c || !n) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0, GA_ERR_STATE, "no patch");
+  GA_REQUIRE(c, slot == 0 || slot == 1, GA_ERR_ARG, "slot must be 0 or 1");
+  if (c->near_slot == slot && c->near_start[0] == start_x && c->near_start[1] == start_y)
+  {
+    const int32_t* rid;
+    const double* rd;
+    int rn;
+    ga_heur_reforder_near(c, &rid, &rd, &rn);
+    *n = rn;
+    for (int i = 0; i < rn && i < cap; ++i)
+    {
+      if (ids) ids[i] = rid[i];
+      if (dist) dist[i] = rd[i];
+    }
+    return GA_OK;
+  }
+  // derive the list from the slot's flag plane: the 19 x 19 box around the start holds every cell with dist < 10
+  const int dim = c->astar_dim;
+  const int x0 = start_x - 9 < 0 ? 0 : start_x - 9, y0 = start_y - 9 < 0 ? 0 : start_y - 9;
+  const int x1 = start_x + 9 >= dim ? dim - 1 : start_x + 9, y1 = start_y + 9 >= dim ? dim - 1 : start_y + 9;
+  int cnt = 0;
+  if (x1 >= x0 && y1 >= y0)
+  {
+    const int w = x1 - x0 + 1, hgt = y1 - y0 + 1;
+    uint8_t box[19 * 19];
+    GA_CUDA(c, cudaSetDevice(c->device));
+    GA_CUDA(c, cudaMemcpy2DAsync(box, (size_t)w, c->d_hflags[slot] + (size_t)y0 * dim + x0, (size_t)dim, (size_t)w, (size_t)hgt,
+                                 cudaMemcpyDeviceToHost, c->stream));
+    GA_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int y = 0; y < hgt; ++y)
+      for (int x = 0; x < w; ++x)
+      {
+        if (!(box[y * w + x] & GA_H_CLOSED)) continue;
+        const double xd = (x0 + x) - start_x, yd = (y0 + y) - start_y;
+        const double d = fabs(sqrt(xd * xd + yd * yd));
+        if (!(d < 10)) continue;
+        if (cnt < cap)
+        {
+          if (ids) ids[cnt] = (y0 + y) * dim + (x0 + x);
+          if (dist) dist[cnt] = d;
+        }
+        ++cnt;
+      }
+  }
+  *n = cnt;
+  return GA_OK;
+}
+
+extern "C" int ga_heur_closing_order(ga_ctx* c, int* ids, int cap, int* n)
+{
+  if (!c || !n) return GA_ERR_ARG;
+  const int32_t* o;
+  int cnt;
+  ga_heur_reforder_order(c, &o, &cnt);
+  *n = cnt;
+  for (int i = 0; i < cnt && i < cap; ++i) ids[i] = o[i];
   return GA_OK;
 }
 

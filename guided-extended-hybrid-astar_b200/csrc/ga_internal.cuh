@@ -90,13 +90,17 @@ struct ga_ctx
   int32_t* d_jump = nullptr;      // finish scratch: block-local (terminal, steps) per cell
   int32_t* d_cnt = nullptr;       // finish scratch: (n_straight, n_diag) of terminal cells to the root
   int heur_epoch = 0;             // build counter (stamps the per-tile prox flags)
-  int sw_warps = 6, sw_poll_ns = 20;  // sweep kernel knobs (GA_SW_WARPS / GA_POLL_NS)
+  int sw_warps = 8, sw_poll_ns = 20;  // sweep kernel knobs (ga_set_heur_knobs; 8 = SW_WARPS)
   int sw_early = -1, sw_round = -1, sw_refresh = -1, sw_linger = -1, sw_prefetch = -1;  // -1 = per launch (queue_knobs)
   int* d_bring = nullptr;         // batch ring (leading context of ga_build_heuristic_batch)
   int bring_cap = 0;
   void* d_bdesc = nullptr;        // batch descriptors + closed counters
   size_t bdesc_cap = 0;
   cudaEvent_t ev_batch = nullptr; // stream ordering between the contexts of a batch
+  struct ga_reforder_state* reforder = nullptr;  // host side of GA_HEUR_REFORDER (ga_heur_reforder.cu)
+  int near_slot = -1;             // slot whose nodes_near_goal_ list the last REFORDER build recorded
+  int near_start[2] = { -1, -1 };
+  bool heur_host_valid[2] = { false, false };
 
   // ---- staging (pinned host + device) for pose batches
   void* h_stage = nullptr;
@@ -144,5 +148,9 @@ int ga_stage_reserve(ga_ctx* ctx, size_t bytes);
 // implemented per subsystem
 int ga_heur_alloc(ga_ctx* ctx);
 void ga_heur_free(ga_ctx* ctx);
+int ga_heur_reforder_build(ga_ctx* ctx, int slot, const ga_heur_query* q, int* n_closed);
+void ga_heur_reforder_near(const ga_ctx* ctx, const int32_t** ids, const double** dist, int* n);
+void ga_heur_reforder_order(const ga_ctx* ctx, const int32_t** ids, int* n);
+void ga_reforder_free(ga_ctx* ctx);
 void ga_cart_free(ga_ctx* ctx);
 void ga_rt_free(ga_ctx* ctx);

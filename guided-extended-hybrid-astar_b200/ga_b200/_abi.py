@@ -38,6 +38,13 @@ class AstarParams(C.Structure):
                 ("vor_dim", C.c_int), ("dt_variant", C.c_int)]
 
 
+class HeurQuery(C.Structure):
+    _fields_ = [("goal_x", C.c_int), ("goal_y", C.c_int), ("start_x", C.c_int), ("start_y", C.c_int),
+                ("flags", C.c_uint), ("max_extra_nodes", C.c_uint)]
+
+
+HEUR_FIXEDPOINT, HEUR_REFORDER, HEUR_EARLY_EXIT, HEUR_ONLY_NEAR = 0, 1, 2, 4
+
 NODE_DTYPE = np.dtype([("x", "f8"), ("y", "f8"), ("yaw", "f8"), ("motion_res", "f8"),
                        ("with_rear_axis", "i4"), ("pad_", "i4")])
 SUCC_DTYPE = np.dtype([("x", "f8"), ("y", "f8"), ("yaw", "f8"), ("xi", "i4"), ("yi", "i4"),
@@ -100,6 +107,7 @@ SYMBOLS = {
     "ga_upload": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),
     "ga_download": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),
     "ga_download_async": (C.c_int, [_P, C.c_int, _P, C.c_size_t]),
+    "ga_download_window": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "ga_grid_bytes": (C.c_int, [_P, C.c_int, C.POINTER(C.c_size_t)]),
     "ga_device_ptr": (C.c_int, [_P, C.c_int, C.POINTER(_P)]),
     "ga_patch_dim": (C.c_int, [_P]),
@@ -109,6 +117,12 @@ SYMBOLS = {
     "ga_prof_get": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
     "ga_launch_count": (C.c_longlong, [_P]),
     "ga_heur_stats": (C.c_int, [_P, C.POINTER(C.c_longlong)]),
+    "ga_set_heur_knobs": (C.c_int, [_P, _P]),
+    "ga_build_heuristic_ex": (C.c_int, [_P, C.c_int, C.POINTER(HeurQuery), C.POINTER(C.c_int)]),
+    "ga_heur_near_nodes": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.POINTER(C.c_int)]),
+    "ga_heur_closing_order": (C.c_int, [_P, _P, C.c_int, C.POINTER(C.c_int)]),
+    "ga_heur_reforder_host": (C.c_int, [C.POINTER(AstarParams), C.c_int, _P, _P, _P, _P, C.POINTER(HeurQuery), _P, _P, _P,
+                                        _P, _P, C.POINTER(C.c_int)]),
 }
 
 _lib = None

@@ -467,6 +467,29 @@ class ClosedSet:
         return np.flatnonzero(self.flags.ravel() & _abi.H_CLOSED)
 
 
+def heuristic_reference_order_host(cfg, grid, fence, mc, prox, goal, start, get_only_near=False):
+    """ga_heur_reforder_host: the library's GA_HEUR_REFORDER replay on host planes (no device)."""
+    lib = _abi.load()
+    d = grid.shape[0]
+    ap = _abi.AstarParams(cfg.astar_movement_cost_, cfg.astar_prox_cost_, cfg.astar_lane_movement_cost_,
+                          float(cfg.ASTAR_UNKNOWN_COST), cfg.alpha_, cfg.do_max_, cfg.do_min_, cfg.MOTION_RES_MIN,
+                          cfg.MOTION_RES_MAX, float(cfg.MIN_DIST_VAL), float(cfg.MAX_DIST_VAL), int(cfg.VOR_DIM),
+                          int(cfg.DT_VARIANT))
+    flags = _abi.HEUR_REFORDER | (_abi.HEUR_EARLY_EXIT if cfg.HEURISTIC_EARLY_EXIT else 0) | \
+        (_abi.HEUR_ONLY_NEAR if get_only_near else 0)
+    q = _abi.HeurQuery(int(goal[0]), int(goal[1]), int(start[0]), int(start[1]), flags, int(cfg.MAX_EXTRA_NODES_ASTAR))
+    g, f = np.ascontiguousarray(grid, np.uint8), np.ascontiguousarray(fence, np.uint8)
+    m, p = np.ascontiguousarray(mc, np.float64), np.ascontiguousarray(prox, np.float64)
+    cost, dist = np.empty((d, d)), np.empty((d, d))
+    parent, fl, order = np.empty((d, d), np.int32), np.empty((d, d), np.uint8), np.empty(d * d, np.int32)
+    n = C.c_int()
+    rc = lib.ga_heur_reforder_host(C.byref(ap), d, _abi.ptr(g), _abi.ptr(f), _abi.ptr(m), _abi.ptr(p), C.byref(q),
+                                   _abi.ptr(cost), _abi.ptr(dist), _abi.ptr(parent), _abi.ptr(fl), _abi.ptr(order), C.byref(n))
+    if rc != 0:
+        raise _abi.GaError("ga_heur_reforder_host failed: %d" % rc)
+    return dict(n_closed=n.value, cost=cost, dist=dist, parent=parent, flags=fl, order=order[:n.value].copy())
+
+
 class AStar:
     """Mirror of the reference's AStar grid builder (a_star.hpp:32-140)."""
 
@@ -521,14 +544,56 @@ class AStar:
                                                        _abi.ptr(v) if len(v) else None, len(v), C.byref(had)))
         return bool(had.value)
 
-    def calcDistanceHeuristic(self, goal_pos, start_pos=None, for_path=True, get_only_near=False):
-        """a_star.cpp:110-295.  Fixed-point mode: every cell reachable from the goal is closed; the
-        start cell only steers the reference's early exit and is not needed."""
+    def astar_params(self):
+        c = self.cfg
+        return _abi.AstarParams(c.astar_movement_cost_, c.astar_prox_cost_, c.astar_lane_movement_cost_,
+                                float(c.ASTAR_UNKNOWN_COST), c.alpha_, c.do_max_, c.do_min_, c.MOTION_RES_MIN,
+                                c.MOTION_RES_MAX, float(c.MIN_DIST_VAL), float(c.MAX_DIST_VAL), int(c.VOR_DIM),
+                                int(c.DT_VARIANT))
+
+    def calcDistanceHeuristic(self, goal_pos, start_pos=None, for_path=True, get_only_near=False, reference_order=None):
+        """a_star.cpp:110-295.  reference_order=False (default without a start cell): the GPU fixed point --
+        every cell reachable from the goal is closed, the start cell is not needed.  reference_order=True
+        (default when start_pos is given): the reference's own closing order with its early exit
+        (cfg.HEURISTIC_EARLY_EXIT, cfg.MAX_EXTRA_NODES_ASTAR) and get_only_near -- bit-exact planes and
+        nodes_near_goal_ (GA_HEUR_REFORDER, replayed on the host by the library)."""
         slot = 1 if for_path else 0
         n = C.c_int()
-        self.ctx.check(self.ctx.lib.ga_build_heuristic(self.ctx.h, slot, int(goal_pos[0]), int(goal_pos[1]), C.byref(n)))
+        if reference_order is None:
+            reference_order = start_pos is not None
+        if not reference_order:
+            if get_only_near and start_pos is None:
+                raise ValueError("get_only_near needs the start cell")
+            self.ctx.check(self.ctx.lib.ga_build_heuristic(self.ctx.h, slot, int(goal_pos[0]), int(goal_pos[1]), C.byref(n)))
+        else:
+            if start_pos is None:
+                raise ValueError("the reference's closing order depends on the start cell")
+            flags = _abi.HEUR_REFORDER | (_abi.HEUR_EARLY_EXIT if self.cfg.HEURISTIC_EARLY_EXIT else 0) | \
+                (_abi.HEUR_ONLY_NEAR if get_only_near else 0)
+            q = _abi.HeurQuery(int(goal_pos[0]), int(goal_pos[1]), int(start_pos[0]), int(start_pos[1]), flags,
+                               int(self.cfg.MAX_EXTRA_NODES_ASTAR))
+            self.ctx.check(self.ctx.lib.ga_build_heuristic_ex(self.ctx.h, slot, C.byref(q), C.byref(n)))
         self.closed_sets_[slot] = None
+        self.near_query_ = (slot, start_pos) if get_only_near else None
         return n.value
+
+    @property
+    def nodes_near_goal_(self):
+        """a_star.hpp:82: (dist, cell id) of the closed cells within 10 cells of the start of the last
+        get_only_near build."""
+        if getattr(self, "near_query_", None) is None:
+            return []
+        slot, start = self.near_query_
+        ids, dist, n = np.zeros(400, np.int32), np.zeros(400), C.c_int()
+        self.ctx.check(self.ctx.lib.ga_heur_near_nodes(self.ctx.h, slot, int(start[0]), int(start[1]), _abi.ptr(ids),
+                                                       _abi.ptr(dist), 400, C.byref(n)))
+        return list(zip(dist[:n.value].tolist(), ids[:n.value].tolist()))
+
+    def closing_order(self):
+        cap = self.astar_dim_ ** 2
+        ids, n = np.zeros(cap, np.int32), C.c_int()
+        self.ctx.check(self.ctx.lib.ga_heur_closing_order(self.ctx.h, _abi.ptr(ids), cap, C.byref(n)))
+        return ids[:n.value].copy()
 
     @staticmethod
     def calcDistanceHeuristicBatch(astars, goals, for_path=True):

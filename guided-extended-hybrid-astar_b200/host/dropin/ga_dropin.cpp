@@ -1,0 +1,794 @@
+// ga_dropin.cpp -- bodies of the drop-in static classes (ga_dropin.hpp): every grid computation is a call into
+// libgridaccel.so.  Host code here is what the reference also runs on the host around its grids: the footprint
+// model (fp64 trig, once), the motion-primitive rollout (glibc, it defines the search state), the Fortune sweep
+// (the reference's own VoronoiDiagramGenerator), lane-graph and geofence rasterisation.
+#include "ga_dropin.hpp"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+namespace ga_dropin
+{
+namespace
+{
+ga_ctx* g_ctx = nullptr;
+unsigned g_heur_mode = GA_HEUR_REFORDER;
+Stats g_stats;
+}  // namespace
+
+ga_ctx* ctx()
+{
+  if (!g_ctx)
+  {
+    if (ga_abi_version() != GA_ABI_VERSION) throw std::runtime_error("gridaccel: ABI version mismatch");
+    int dev = 0;
+    if (const char* s = std::getenv("GA_DEVICE")) dev = std::atoi(s);
+    if (ga_create(dev, &g_ctx) != GA_OK)
+      throw std::runtime_error("gridaccel: ga_create failed -- no usable CUDA device (there is no CPU path)");
+  }
+  return g_ctx;
+}
+void check(int rc)
+{
+  if (rc != GA_OK) throw std::runtime_error(std::string("gridaccel: ") + ga_last_error(g_ctx));
+}
+void setHeuristicMode(unsigned flags) { g_heur_mode = flags & GA_HEUR_REFORDER; }
+unsigned heuristicMode() { return g_heur_mode; }
+Stats& stats() { return g_stats; }
+
+namespace
+{
+constexpr int NB_STEER = 13;  // HybridAStar::NB_STEER (hybrid_a_star_lib.hpp:48)
+double g_turn_on_point_angle = 90.0;  // config.yml TURN_ON_POINT_ANGLE (read in CollisionChecker::initialize)
+
+// All primitives of one expanded node, rolled out on the host and checked on the device in one launch.
+struct Fan
+{
+  bool valid = false;
+  double parent[3] = { 0, 0, 0 }, arc_l = 0, motion_res = 0;
+  std::vector<MotionPrimitive> prims;
+  std::vector<double> key;  // steer (move fan) or delta_angle (rear-axis fan)
+  std::vector<int> dir;
+  std::vector<int> first_hit;
+  int last = -1;  // primitive handed out last (checkPathCollision is asked about it next)
+};
+Fan g_move_fan, g_ra_fan;
+std::vector<double> g_x, g_y, g_yaw;
+std::vector<int> g_seg;
+
+void check_fan(Fan& f)
+{
+  g_x.clear();
+  g_y.clear();
+  g_yaw.clear();
+  g_seg.assign(1, 0);
+  for (const MotionPrimitive& p : f.prims)
+  {
+    g_x.insert(g_x.end(), p.x_list_.begin(), p.x_list_.end());
+    g_y.insert(g_y.end(), p.y_list_.begin(), p.y_list_.end());
+    g_yaw.insert(g_yaw.end(), p.yaw_list_.begin(), p.yaw_list_.end());
+    g_seg.push_back((int)g_x.size());
+  }
+  f.first_hit.assign(f.prims.size(), -1);
+  if (!g_x.empty())
+    check(ga_check_poses(ctx(), g_x.data(), g_y.data(), g_yaw.data(), (int)g_x.size(), g_seg.data(), (int)f.prims.size(), 0,
+                         f.first_hit.data()));
+  g_stats.poses_checked += g_x.size();
+  ++g_stats.expansions_prefetched;
+}
+
+inline bool same_list(const std::vector<double>& a, const std::vector<double>& b)
+{
+  return a.size() == b.size() && (a.empty() || std::memcmp(a.data(), b.data(), a.size() * sizeof(double)) == 0);
+}
+// index of the fan primitive whose pose lists are exactly (x, y, yaw), or -1
+int match_fan(const Fan& f, const std::vector<double>& x, const std::vector<double>& y, const std::vector<double>& yaw)
+{
+  if (!f.valid) return -1;
+  auto is = [&](int k) {
+    const MotionPrimitive& p = f.prims[(size_t)k];
+    return same_list(p.x_list_, x) && same_list(p.y_list_, y) && same_list(p.yaw_list_, yaw);
+  };
+  if (f.last >= 0 && is(f.last)) return f.last;
+  for (int k = 0; k < (int)f.prims.size(); ++k)
+    if (is(k)) return k;
+  return -1;
+}
+}  // namespace
+}  // namespace ga_dropin
+
+using namespace ga_dropin;
+
+// =====================================================================================================
+// Vehicle (LIB/src/collision_checker_lib/vehicle.cpp)
+// =====================================================================================================
+void Vehicle::setPose(const Pose<double>& pose) { pose_utm_ = pose; }
+
+void Vehicle::initialize(double max_steer, double w_b, double l_f, double l_b, double width, bool is_ushift)  // :11-32
+{
+  max_steer_ = max_steer;
+  w_b_ = w_b;
+  lf_ = l_f;
+  lb_ = l_b;
+  length_ = l_f + l_b;
+  width_ = width;
+  is_ushift_ = is_ushift;
+  max_curvature_ = tan(max_steer_) / w_b_;
+  f_r_corner_ = Point<double>(lf_, -width_ / 2);
+  f_l_corner_ = Point<double>(lf_, width_ / 2);
+  r_r_corner_ = Point<double>(-lb_, -width_ / 2);
+  r_l_corner_ = Point<double>(-lb_, width_ / 2);
+  geo_center_ = (lb_ + lf_) / 2 - lb_;
+  vehicle_vertices_ = { f_l_corner_, f_r_corner_, r_r_corner_, r_l_corner_, f_l_corner_ };
+  vis_vehicle_vertices_ = vehicle_vertices_;
+  g_move_fan.valid = g_ra_fan.valid = false;
+}
+
+void Vehicle::move(Pose<double>& pose, double distance, double steer)  // :34-43, one Euler step of the bicycle model
+{
+  pose.x += distance * cos(pose.yaw);
+  pose.y += distance * sin(pose.yaw);
+  pose.yaw += distance * tan(steer) / w_b_;
+  pose.yaw = util::constrainAngleMinPIPlusPi(pose.yaw);
+}
+
+namespace
+{
+MotionPrimitive roll_out(const Pose<double>& pose, double arc_l, double motion_res, int direction, double steer)  // :100-122
+{
+  const auto n = static_cast<size_t>(round(arc_l / motion_res));
+  MotionPrimitive mp = MotionPrimitive(n);
+  Pose<double> p = pose;
+  for (size_t i = 0; i < n; ++i)
+  {
+    Vehicle::move(p, motion_res * direction, steer);
+    mp.x_list_.push_back(p.x);
+    mp.y_list_.push_back(p.y);
+    mp.yaw_list_.push_back(p.yaw);
+    mp.dir_list_.push_back(direction);
+    mp.delta_list_.push_back(steer);
+  }
+  return mp;
+}
+
+MotionPrimitive rotate_on_axis(const Pose<double>& pose, double delta_angle, double yaw_res_coll)  // :45-98
+{
+  MotionPrimitive mp;
+  double yaw = pose.yaw;
+  const double goal_yaw = util::constrainAngleMinPIPlusPi(yaw + delta_angle);
+  const double step = yaw_res_coll * util::TO_RAD;
+  mp.yaw_list_.reserve((size_t)ceil(std::abs(delta_angle) / step));
+  double margin;
+  do
+  {
+    yaw = util::constrainAngleMinPIPlusPi(yaw + util::sgn(delta_angle) * step);
+    mp.yaw_list_.push_back(yaw);
+    margin = std::abs(util::getAngleDiff(yaw, goal_yaw));
+  } while (margin >= step);
+  if (mp.yaw_list_.back() != goal_yaw) mp.yaw_list_.back() = goal_yaw;
+  mp.nb_elements_ = mp.yaw_list_.size();
+  mp.x_list_.resize(mp.nb_elements_, pose.x);
+  mp.y_list_.resize(mp.nb_elements_, pose.y);
+  mp.dir_list_.resize(mp.nb_elements_, 1);
+  mp.delta_list_.resize(mp.nb_elements_, delta_angle > 0 ? util::PI / 2.0 : -util::PI / 2.0);
+  return mp;
+}
+}  // namespace
+
+MotionPrimitive Vehicle::move_car_some_steps(const Pose<double>& pose, double arc_l, double motion_res, int direction,
+                                             double steer)
+{
+  Fan& f = g_move_fan;
+  const bool same = f.valid && f.parent[0] == pose.x && f.parent[1] == pose.y && f.parent[2] == pose.yaw &&
+                    f.arc_l == arc_l && f.motion_res == motion_res;
+  if (!same)
+  {
+    // the fan HybridAStar::setNeighbors is about to ask for (hybrid_a_star_lib.cpp:492-510): calcSteeringInputs'
+    // 13 steers (:115-129) x directions {+1, -1}
+    f.prims.clear();
+    f.key.clear();
+    f.dir.clear();
+    const double delta_steer = (2 * max_steer_) / static_cast<double>(NB_STEER - 1);
+    const int side = NB_STEER / 2;
+    for (int i = -side; i <= side; ++i)
+      for (const int d : { 1, -1 })
+      {
+        const double st = i * delta_steer;
+        f.prims.push_back(roll_out(pose, arc_l, motion_res, d, st));
+        f.key.push_back(st);
+        f.dir.push_back(d);
+      }
+    f.parent[0] = pose.x;
+    f.parent[1] = pose.y;
+    f.parent[2] = pose.yaw;
+    f.arc_l = arc_l;
+    f.motion_res = motion_res;
+    f.valid = true;
+    f.last = -1;
+    g_ra_fan.valid = false;
+    check_fan(f);
+  }
+  for (int k = 0; k < (int)f.prims.size(); ++k)
+    if (f.dir[(size_t)k] == direction && f.key[(size_t)k] == steer)
+    {
+      f.last = k;
+      return f.prims[(size_t)k];
+    }
+  f.last = -1;  // a primitive outside the fan: rolled out alone, checked by its own launch
+  return roll_out(pose, arc_l, motion_res, direction, steer);
+}
+
+MotionPrimitive Vehicle::turn_on_rear_axis(const Pose<double>& pose, double delta_angle, double yaw_res_coll)
+{
+  Fan& f = g_ra_fan;
+  const bool same = f.valid && f.parent[0] == pose.x && f.parent[1] == pose.y && f.parent[2] == pose.yaw &&
+                    f.motion_res == yaw_res_coll;
+  if (!same)
+  {
+    // the rotations setNeighbors tries (hybrid_a_star_lib.cpp:512-533), same loop arithmetic
+    f.prims.clear();
+    f.key.clear();
+    f.dir.clear();
+    const double a = g_turn_on_point_angle * util::TO_RAD;
+    if (a > 1e-6)
+      for (double d = -2 * util::PI + a; d <= 2 * util::PI - a; d += a)
+      {
+        if (d == 0) continue;
+        f.prims.push_back(rotate_on_axis(pose, d, yaw_res_coll));
+        f.key.push_back(d);
+        f.dir.push_back(1);
+      }
+    f.parent[0] = pose.x;
+    f.parent[1] = pose.y;
+    f.parent[2] = pose.yaw;
+    f.motion_res = yaw_res_coll;
+    f.valid = true;
+    f.last = -1;
+    check_fan(f);
+  }
+  for (int k = 0; k < (int)f.prims.size(); ++k)
+    if (f.key[(size_t)k] == delta_angle)
+    {
+      f.last = k;
+      return f.prims[(size_t)k];
+    }
+  f.last = -1;
+  return rotate_on_axis(pose, delta_angle, yaw_res_coll);
+}
+
+// ---- host mirrors of the astar-side maps that still have to reach the device ------------------------------
+namespace
+{
+bool g_maps_dirty = false;  // host movement cost / geofence / carried-over h_prox, motion_res not yet on the device
+int g_vor_dt_variant = GA_DT_IPPFLOAT;  // the reference's Docker OpenCV is built WITH_IPP
+
+void flush_maps()
+{
+  if (!g_maps_dirty) return;
+  ga_ctx* c = ctx();
+  const int d = ga_astar_dim(c);
+  if (d != AStar::astar_dim_ || d <= 0) return;  // device grids get their size with CollisionChecker::resetPatch
+  const size_t n = (size_t)d * d;
+  auto full = [d](const auto& grid) { return grid.getDims() == std::pair<int, int>(d, d); };
+  if (full(AStar::movement_cost_map_)) check(ga_upload(c, GA_GRID_MOVEMENT_COST, AStar::movement_cost_map_.getPtr(), n * 8));
+  if (full(AStar::restr_geofence_grid_)) check(ga_upload(c, GA_GRID_GEOFENCE, AStar::restr_geofence_grid_.getPtr(), n));
+  if (full(AStar::h_prox_arr_)) check(ga_upload(c, GA_GRID_H_PROX, AStar::h_prox_arr_.getPtr(), n * 8));
+  if (full(AStar::motion_res_map_)) check(ga_upload(c, GA_GRID_MOTION_RES, AStar::motion_res_map_.getPtr(), n * 8));
+  check(ga_sync(c));
+  g_maps_dirty = false;
+}
+}  // namespace
+
+// =====================================================================================================
+// CollisionChecker (LIB/src/collision_checker_lib/collision_checking.cpp)
+// =====================================================================================================
+void CollisionChecker::initialize(size_t patch_dim, const std::string& path2config)  // :12-31
+{
+  YAML::Node config = YAML::LoadFile(path2config);
+  yaw_res_coll_ = config["YAW_RES_COLL"].as<int>();
+  yaw_res_coll_rad_ = yaw_res_coll_ * util::TO_RAD;
+  nb_disc_yaws_ = 360 / yaw_res_coll_;
+  safety_distance_m_ = config["SAFETY_DISTANCE_M"].as<double>();
+  search_dist_ = config["SEARCH_DIST"].as<double>();
+  search_dist_cells_ = search_dist_ * grid_tf::con2gm_;
+  min_thresh_ = config["MIN_THRESH"].as<int>();
+  max_thresh_ = config["MAX_THRESH"].as<int>();
+  len_per_disk_ = config["LEN_PER_DISK"].as<double>();
+  double_disk_rows_ = config["DOUBLE_DISK_ROWS"].as<bool>();
+  max_patch_ins_dist_ = config["MAX_PATCH_INS_DIST"].as<double>();
+  try
+  {
+    g_turn_on_point_angle = config["TURN_ON_POINT_ANGLE"].as<double>();
+  }
+  catch (const std::exception&)
+  {
+  }
+  calculateDisks();  // the device needs the footprint model before the first reset sizes the grids
+  resetPatch(patch_dim);
+}
+
+double CollisionChecker::getDiskRadius(double length, double width, unsigned int nb_disks)  // :44-47
+{
+  return sqrt(((length * length) / (nb_disks * nb_disks) + (width * width)) / 4);
+}
+
+std::vector<double> CollisionChecker::getDiskPositions(double radius, unsigned int nb_disks, double width, double lb)  // :57-70
+{
+  std::vector<double> positions;
+  const double dist = 2 * sqrt((radius * radius) - (width * width) / 4);
+  const double first = dist / 2 - lb;
+  for (unsigned int i = 0; i < nb_disks; ++i) positions.push_back(first + i * dist);
+  return positions;
+}
+
+// :75-145 -- footprint disks and the per-yaw centre LUT in fp64 on the host, exactly as the reference fills
+// disk_centers_ (Point::rotate, * con2gm_, toInt = std::round); the LUT and the dilation radius go to the device
+void CollisionChecker::calculateDisks()
+{
+  const unsigned int eff_nb = ceil(Vehicle::length_ / len_per_disk_);
+  const int rows = double_disk_rows_ ? 2 : 1;
+  nb_disks_ = rows * eff_nb;
+  const double eff_width = Vehicle::width_ / rows;
+  const double radius = getDiskRadius(Vehicle::length_, eff_width, eff_nb);
+  const std::vector<double> x_pos = getDiskPositions(radius, eff_nb, eff_width, Vehicle::lb_);
+  disk_r_ = radius + safety_distance_m_;
+  disk_r_c_ = static_cast<int>(ceil(disk_r_ * grid_tf::con2gm_));
+  disk_diameter_c_ = 2 * disk_r_c_ + 1;
+
+  disk_centers_.resize_and_reset(nb_disks_, nb_disc_yaws_, Point<int>(0, 0));
+  std::vector<int> lut((size_t)nb_disc_yaws_ * nb_disks_ * 2);
+  for (unsigned int yi = 0; yi < nb_disc_yaws_; ++yi)
+  {
+    const double yaw = yi * yaw_res_coll_rad_;
+    unsigned int k = 0;
+    for (const double xp : x_pos)
+    {
+      for (int r = 0; r < rows; ++r)
+      {
+        const double y_off = double_disk_rows_ ? (r == 0 ? eff_width / 2.0 : -eff_width / 2.0) : 0.0;
+        const Point<double> centre = Point<double>(xp, y_off).rotate(yaw);
+        const Point<int> cell = (centre * grid_tf::con2gm_).toInt();
+        disk_centers_(yi, k) = cell;
+        lut[((size_t)yi * nb_disks_ + k) * 2] = cell.x;
+        lut[((size_t)yi * nb_disks_ + k) * 2 + 1] = cell.y;
+        ++k;
+      }
+    }
+  }
+  const ga_collision_params p{ (int)min_thresh_, (int)max_thresh_, disk_r_c_, (int)yaw_res_coll_, (int)nb_disks_,
+                               (int)ceil(grid_tf::star2gm_) };
+  check(ga_set_collision_params(ctx(), &p, lut.data()));
+  g_move_fan.valid = g_ra_fan.valid = false;
+}
+
+std::vector<Point<double>> CollisionChecker::returnDiskPositions(double yaw)  // :320-331
+{
+  std::vector<Point<double>> points;
+  points.reserve(nb_disks_);
+  const int yaw_idx = getYawIdx(yaw);
+  for (unsigned int d = 0; d < nb_disks_; ++d) points.push_back(grid_tf::grid2utm(disk_centers_(yaw_idx, d).toDouble()));
+  return points;
+}
+
+void CollisionChecker::resetPatch(size_t patch_dim)  // :37-42; sizes the astar-side device grids too (ga_patch_reset)
+{
+  patch_dim_ = patch_dim;
+  AStar::pushParams();
+  check(ga_patch_reset(ctx(), (int)patch_dim));  // every device grid back to its initial value
+  host_patch_stale_ = host_safety_stale_ = true;
+  g_move_fan.valid = g_ra_fan.valid = false;
+  g_maps_dirty = true;  // the host mirrors (lane costs, geofence, carried-over potential field) are authoritative
+  flush_maps();
+}
+
+void CollisionChecker::processSafetyPatch()  // :193-224 (+ the 4x4 pooling of AStar::calcAstarGridCuda, fused)
+{
+  check(ga_build_safety(ctx()));
+  host_safety_stale_ = true;
+  g_move_fan.valid = g_ra_fan.valid = false;
+}
+
+void CollisionChecker::syncPatch()
+{
+  patch_arr_.resize_and_reset(patch_dim_, patch_dim_, SENSOR_UNKNOWN);
+  check(ga_download(ctx(), GA_GRID_PATCH, patch_arr_.getPtr(), patch_dim_ * patch_dim_));
+  host_patch_stale_ = false;
+}
+void CollisionChecker::syncSafetyPatch()
+{
+  patch_safety_arr_.resize_and_reset(patch_dim_, patch_dim_, UNKNOWN);
+  check(ga_download(ctx(), GA_GRID_SAFETY, patch_safety_arr_.getPtr(), patch_dim_ * patch_dim_));
+  host_safety_stale_ = false;
+}
+
+void CollisionChecker::insertMinipatches(const std::map<std::pair<int, int>, Minipatch>& minipatches,
+                                         const Point<double>& ego_utm, bool only_nearest, bool only_new)  // :147-174
+{
+  for (const auto& [patch_idx, minipatch] : minipatches)
+  {
+    if (only_new and !minipatch.is_new_) continue;
+    if (only_nearest && minipatch.center_.dist2(ego_utm) > max_patch_ins_dist_) continue;
+    const auto origin_grid = grid_tf::utm2grid_round(grid_tf::utm2patch_utm(minipatch.origin_));
+    passLocalMap(minipatch.patch_, origin_grid, minipatch.width_);
+  }
+}
+
+void CollisionChecker::passLocalMap(const py::array_t<uint8_t>& local_map, const Point<int>& origin, int dim)
+{
+  passLocalMapData(local_map.data(), origin, dim);
+}
+void CollisionChecker::passLocalMap(const Vec2DFlat<uint8_t>& local_map, const Point<int>& origin, int dim)
+{
+  passLocalMapData(const_cast<Vec2DFlat<uint8_t>&>(local_map).getPtr(), origin, dim);  // the const getPtr() of Vec2DFlat does not compile
+}
+// :269-313 -- only the window crosses PCIe; the clipping rules are applied by ga_patch_insert
+void CollisionChecker::passLocalMapData(const unsigned char* local_map, const Point<int>& origin, int dim)
+{
+  check(ga_patch_insert(ctx(), local_map, origin.x, origin.y, dim));
+  check(ga_sync(ctx()));
+  host_patch_stale_ = true;
+}
+
+int CollisionChecker::getYawIdx(double yaw)  // :333-337
+{
+  const int yaw_idx = static_cast<int>(util::constrainAngleZero2Pi(yaw) / yaw_res_coll_rad_);
+  return std::min(yaw_idx, static_cast<int>(nb_disc_yaws_ - 1));
+}
+
+namespace
+{
+int first_hit(const double* x, const double* y, const double* yaw, int n, int variant)
+{
+  const int seg[2] = { 0, n };
+  int hit = -1;
+  check(ga_check_poses(ctx(), x, y, yaw, n, seg, 1, variant, &hit));
+  g_stats.poses_checked += (unsigned long long)n;
+  return hit;
+}
+}  // namespace
+
+// :344-387 take CELL coordinates; the centre of the cell maps back to the same cell and yaw bin on the device
+bool CollisionChecker::checkGrid(const Pose<int>& pose)
+{
+  if (pose.x < 0 || pose.y < 0) return false;  // every disk lookup of :351-354 would be off-map or the pose is
+  const double x = (pose.x + 0.5) * grid_tf::gm2con_, y = (pose.y + 0.5) * grid_tf::gm2con_;
+  const double yaw = (pose.yaw + 0.5) * yaw_res_coll_rad_;
+  return first_hit(&x, &y, &yaw, 1, 0) < 0;
+}
+bool CollisionChecker::checkGridVariant(const Pose<int>& pose)
+{
+  if (pose.x < 0 || pose.y < 0)
+  {
+    // a negative cell cannot be expressed in metres (truncation toward zero): resolve the few lookups on a host copy
+    if (host_safety_stale_) syncSafetyPatch();
+    for (unsigned int d = 0; d < nb_disks_; ++d)
+    {
+      const Point<int> c = disk_centers_(pose.yaw, d) + Point<int>(pose.x, pose.y);
+      if (c.x < 0 || c.y < 0 || c.x >= (int)patch_dim_ || c.y >= (int)patch_dim_) continue;
+      if (patch_safety_arr_(c.y, c.x) == OCC) return false;
+    }
+    return true;
+  }
+  const double x = (pose.x + 0.5) * grid_tf::gm2con_, y = (pose.y + 0.5) * grid_tf::gm2con_;
+  const double yaw = (pose.yaw + 0.5) * yaw_res_coll_rad_;
+  return first_hit(&x, &y, &yaw, 1, 1) < 0;
+}
+bool CollisionChecker::checkPose(const Pose<double>& pose) { return first_hit(&pose.x, &pose.y, &pose.yaw, 1, 0) < 0; }
+bool CollisionChecker::checkPoseVariant(const Pose<double>& pose) { return first_hit(&pose.x, &pose.y, &pose.yaw, 1, 1) < 0; }
+
+int CollisionChecker::getPathCollisionIndex(const std::vector<double>& x_list, const std::vector<double>& y_list,
+                                            const std::vector<double>& yaw_list)  // :440-452
+{
+  if (x_list.empty()) return -1;
+  ++g_stats.path_checks_direct;
+  return first_hit(x_list.data(), y_list.data(), yaw_list.data(), (int)x_list.size(), 0);
+}
+
+bool CollisionChecker::checkPathCollision(const std::vector<double>& x_list, const std::vector<double>& y_list,
+                                          const std::vector<double>& yaw_list)  // :418-431
+{
+  // a primitive of the fan the last expansion rolled out: its answer came back with that launch
+  for (Fan* f : { &g_move_fan, &g_ra_fan })
+  {
+    const int k = f->last >= 0 ? match_fan(*f, x_list, y_list, yaw_list) : -1;
+    if (k >= 0)
+    {
+      ++g_stats.path_checks_cached;
+      return f->first_hit[(size_t)k] < 0;
+    }
+  }
+  return getPathCollisionIndex(x_list, y_list, yaw_list) < 0;
+}
+
+// =====================================================================================================
+// AStar (LIB/src/hybridastar_planning_lib/a_star.cpp)
+// =====================================================================================================
+
+namespace ga_dropin
+{
+void setDistanceTransformVariant(int ga_dt_variant)
+{
+  g_vor_dt_variant = ga_dt_variant;
+  AStar::pushParams();
+}
+}  // namespace ga_dropin
+
+void AStar::pushParams()
+{
+  ga_astar_params p{};
+  p.astar_movement_cost = astar_movement_cost_;
+  p.astar_prox_cost = astar_prox_cost_;
+  p.astar_lane_movement_cost = astar_lane_movement_cost_;
+  p.unknown_cost_w = unknown_cost_w_;
+  p.alpha = alpha_;
+  p.do_max = do_max_;
+  p.do_min = do_min_;
+  p.motion_res_min = motion_res_min_;
+  p.motion_res_max = motion_res_max_;
+  p.dist_val_min = dist_val_min_;
+  p.dist_val_max = dist_val_max_;
+  p.vor_dim = (int)VOR_DIM;
+  p.dt_variant = g_vor_dt_variant;
+  check(ga_set_astar_params(ctx(), &p));
+  params_pushed_ = true;
+}
+
+void AStar::initialize(int patch_dim, const Point<double>& patch_origin_utm, const std::string& path2config)  // :11-53
+{
+  path2config_ = path2config;
+  YAML::Node config = YAML::LoadFile(path2config_);
+  patch_origin_astar_ = (patch_origin_utm * grid_tf::con2star_).toInt();
+  patch_dim_ = patch_dim;
+  unknown_cost_w_ = config["ASTAR_UNKNOWN_COST"].as<double>();
+  astar_dim_ = std::floor(static_cast<double>(patch_dim_) * GM_RES / ASTAR_RES);
+  heuristic_early_exit_ = config["HEURISTIC_EARLY_EXIT"].as<bool>();
+  max_extra_nodes_ = config["MAX_EXTRA_NODES_ASTAR"].as<unsigned int>();
+  motion_res_min_ = config["MOTION_RES_MIN"].as<double>();
+  motion_res_max_ = config["MOTION_RES_MAX"].as<double>();
+  dist_val_min_ = config["MIN_DIST_VAL"].as<double>();
+  dist_val_max_ = config["MAX_DIST_VAL"].as<double>();
+  init_structs(patch_dim);
+  // Pooling::init: the 4 x 4 max is part of the fused safety kernel, nothing to set up
+}
+
+void AStar::init_structs(int patch_dim)  // :55-68
+{
+  patch_dim_ = patch_dim;
+  astar_dim_ = std::floor(static_cast<double>(patch_dim_) * GM_RES / ASTAR_RES);
+  astar_grid_.resize_and_reset(astar_dim_, astar_dim_, CollisionChecker::UNKNOWN);
+  h_prox_arr_.resize_and_reset(astar_dim_, astar_dim_, 0.0);
+  motion_res_map_.resize_and_reset(astar_dim_, astar_dim_, motion_res_max_);
+  restr_geofence_grid_.resize_and_reset(astar_dim_, astar_dim_, 0);
+  movement_cost_map_.resize_and_reset(astar_dim_, astar_dim_, astar_movement_cost_);
+  astar_grid_stale_ = true;
+  g_maps_dirty = true;
+}
+
+// :70-99 -- incl. the carry-over of h_prox_arr_ / motion_res_map_ across a patch move (saveTemp + copyPatch2Patch on
+// the host mirrors; they reach the device once CollisionChecker::resetPatch has resized its grids)
+void AStar::reinit(const Point<double>& patch_origin_utm, int patch_dim)
+{
+  patch_dim_ = patch_dim;
+  astar_dim_ = std::floor(static_cast<double>(patch_dim_) * GM_RES / ASTAR_RES);
+  patch_origin_utm_ = patch_origin_utm;
+  astar_grid_.resize_and_reset(astar_dim_, astar_dim_, CollisionChecker::UNKNOWN);
+  astar_grid_stale_ = true;
+  obstacle_dist_.resize_and_reset(VOR_DIM, VOR_DIM, CollisionChecker::FREE);
+  voronoi_dist_.resize_and_reset(VOR_DIM, VOR_DIM, CollisionChecker::FREE);
+
+  util::saveTemp(h_prox_arr_, temp_h_prox_arr_, 0.0);
+  h_prox_arr_.resize_and_reset(astar_dim_, astar_dim_, 0.0);
+  util::saveTemp(motion_res_map_, temp_motion_res_map_, motion_res_max_);
+  motion_res_map_.resize_and_reset(astar_dim_, astar_dim_, motion_res_max_);
+  movement_cost_map_.resize_and_reset(astar_dim_, astar_dim_, astar_movement_cost_);
+
+  processGeofence();
+
+  const Point<int> next_origin_astar = (patch_origin_utm * grid_tf::con2star_).toInt();
+  util::copyPatch2Patch(patch_origin_astar_, next_origin_astar, h_prox_arr_, temp_h_prox_arr_);
+  util::copyPatch2Patch(patch_origin_astar_, next_origin_astar, motion_res_map_, temp_motion_res_map_);
+  patch_origin_astar_ = next_origin_astar;
+
+  closed_set_path_.clear();
+  closed_set_guidance_.clear();
+  g_maps_dirty = true;
+}
+
+size_t AStar::calcIndex(size_t x_ind, size_t y_ind) { return y_ind * astar_dim_ + x_ind; }  // :303-316
+size_t AStar::calcIndex(const NodeDisc& node) { return calcIndex(node.pos.x, node.pos.y); }
+
+Point<int> AStar::reverse2DIndex(int idx, int dim)  // :515-519
+{
+  const int first = idx % dim;
+  return { first, (idx - first) / dim };
+}
+
+Point<int> AStar::getCurrentMapOrigin(const Point<int>& ego_pos, size_t dim)  // :527-531
+{
+  const int offset = std::floor(dim / 2);
+  return { std::max(ego_pos.x - offset, 0), std::max(ego_pos.y - offset, 0) };
+}
+
+// :536-542 -- Pooling::execute is fused into processSafetyPatch's kernel: astar_grid_ on the device is current; the
+// host copy the reference's callers (GUI) read follows here (astar_dim^2 bytes)
+void AStar::calcAstarGridCuda() { syncAstarGrid(); }
+
+void AStar::syncAstarGrid()
+{
+  astar_grid_.resize_and_reset(astar_dim_, astar_dim_, CollisionChecker::UNKNOWN);
+  check(ga_download(ctx(), GA_GRID_ASTAR, astar_grid_.getPtr(), (size_t)astar_dim_ * astar_dim_));
+  astar_grid_stale_ = false;
+}
+void AStar::syncDistanceGrids()
+{
+  obstacle_dist_.resize_and_reset(VOR_DIM, VOR_DIM, 0.0f);
+  voronoi_dist_.resize_and_reset(VOR_DIM, VOR_DIM, 0.0f);
+  check(ga_download(ctx(), GA_GRID_OBSTACLE_DIST, obstacle_dist_.getPtr(), VOR_DIM * VOR_DIM * sizeof(float)));
+  check(ga_download(ctx(), GA_GRID_VORONOI_DIST, voronoi_dist_.getPtr(), VOR_DIM * VOR_DIM * sizeof(float)));
+}
+
+// :440-479 -- both distance transforms and setCostmapValue run on the device; the Fortune sweep between them is the
+// reference's own serial fp64 code (deps_lib/VoronoiDiagramGenerator.cpp) on the host
+void AStar::calcVoronoiPotentialField(const Point<int>& ego_index)
+{
+  pushParams();  // alpha_, do_max_, do_min_ are plain statics the caller may have changed
+  flush_maps();
+  ga_ctx* c = ctx();
+  static std::vector<int> sites(2 * VOR_DIM * VOR_DIM);
+  int n_sites = 0;
+  check(ga_potential_sites(c, ego_index.x, ego_index.y, sites.data(), (int)(VOR_DIM * VOR_DIM), &n_sites));
+  std::vector<int> vor;
+  if (n_sites > 0)
+  {
+    std::vector<cv::Point> indices((size_t)n_sites);  // cv::findNonZero order (row-major), a_star.cpp:457-459
+    for (int i = 0; i < n_sites; ++i) indices[(size_t)i] = cv::Point(sites[2 * (size_t)i], sites[2 * (size_t)i + 1]);
+    static Vec2DFlat<float> marks;
+    marks.resize_and_reset(VOR_DIM, VOR_DIM, 0.0f);
+    vdg::VoronoiDiagramGenerator::generateVoronoi_wrapper(indices, marks, VOR_DIM - 1, VOR_DIM - 1, do_min_, CollisionChecker::OCC);
+    const float* m = marks.getPtr();
+    for (int y = 0; y < (int)VOR_DIM; ++y)
+      for (int x = 0; x < (int)VOR_DIM; ++x)
+        if (m[(size_t)y * VOR_DIM + x] == (float)CollisionChecker::OCC)
+        {
+          vor.push_back(x);
+          vor.push_back(y);
+        }
+  }
+  int had = 0;
+  check(ga_build_potential(c, ego_index.x, ego_index.y, vor.empty() ? nullptr : vor.data(), (int)(vor.size() / 2), &had));
+  if (!had) return;  // no obstacle in the window: the old field stays (:462-465)
+  // the window of h_prox_arr_ / motion_res_map_ that changed, back into the host mirrors the search reads
+  const Point<int> o = getCurrentMapOrigin(ego_index, VOR_DIM);
+  static std::vector<double> win(VOR_DIM * VOR_DIM);
+  for (const int id : { (int)GA_GRID_H_PROX, (int)GA_GRID_MOTION_RES })
+  {
+    check(ga_download_window(c, id, o.x, o.y, (int)VOR_DIM, (int)VOR_DIM, win.data()));
+    Vec2DFlat<double>& dst = id == GA_GRID_H_PROX ? h_prox_arr_ : motion_res_map_;
+    for (size_t y = 0; y < VOR_DIM; ++y)
+      std::memcpy(dst.getPtr() + (size_t)(o.y + (int)y) * astar_dim_ + o.x, win.data() + y * VOR_DIM, VOR_DIM * sizeof(double));
+  }
+}
+
+// :110-295
+void AStar::calcDistanceHeuristic(const Point<int>& goal_pos, const Point<int>& start_pos, bool for_path, bool get_only_near)
+{
+  pushParams();
+  flush_maps();
+  ga_ctx* c = ctx();
+  const int slot = for_path ? 1 : 0;
+  std::unordered_map<size_t, NodeDisc>& cs = for_path ? closed_set_path_ : closed_set_guidance_;
+  ga_heur_query q{};
+  q.goal_x = goal_pos.x;
+  q.goal_y = goal_pos.y;
+  q.start_x = start_pos.x;
+  q.start_y = start_pos.y;
+  q.max_extra_nodes = max_extra_nodes_;
+  q.flags = GA_HEUR_FIXEDPOINT;
+  if (heuristicMode() & GA_HEUR_REFORDER)
+    q.flags = GA_HEUR_REFORDER | (heuristic_early_exit_ ? GA_HEUR_EARLY_EXIT : 0) | (get_only_near ? GA_HEUR_ONLY_NEAR : 0);
+  int n = 0;
+  check(ga_build_heuristic_ex(c, slot, &q, &n));
+  const size_t cells = (size_t)astar_dim_ * astar_dim_;
+  ClosedPlanes& p = cs.planes;
+  p.dim = astar_dim_;
+  p.cost.resize(cells);
+  p.dist.resize(cells);
+  p.parent.resize(cells);
+  p.flags.resize(cells);
+  check(ga_download(c, GA_GRID_HEUR_COST + slot, p.cost.data(), cells * 8));
+  check(ga_download(c, GA_GRID_HEUR_DIST + slot, p.dist.data(), cells * 8));
+  check(ga_download(c, GA_GRID_HEUR_PARENT + slot, p.parent.data(), cells * 4));
+  check(ga_download(c, GA_GRID_HEUR_FLAGS + slot, p.flags.data(), cells));
+  p.n_closed = (size_t)n;
+
+  nodes_near_goal_.clear();
+  if (get_only_near)
+  {
+    int ids[400];
+    double dist[400];
+    int cnt = 0;
+    check(ga_heur_near_nodes(c, slot, start_pos.x, start_pos.y, ids, dist, 400, &cnt));
+    for (int i = 0; i < cnt && i < 400; ++i) nodes_near_goal_.emplace_back(dist[i], cs.at((size_t)ids[i]));
+  }
+}
+
+int AStar::findValidNeighborIndex(int start_idx, const std::unordered_map<size_t, NodeDisc>& heuristic)  // :351-378
+{
+  for (const int cand : { start_idx + 1, start_idx - 1, start_idx + astar_dim_, start_idx - astar_dim_ })
+    if (cand >= 0 && heuristic.contains((size_t)cand)) return cand;
+  std::cout << "No node around the ego/start position was in heuristic, this should never be the case" << std::endl;
+  return -1;
+}
+
+std::pair<std::vector<int>, std::vector<int>> AStar::getAstarPath(int x_index, int y_index)  // :386-421
+{
+  std::vector<int> x_list, y_list;
+  size_t idx = calcIndex(x_index, y_index);
+  if (!closed_set_guidance_.contains(idx))
+  {
+    const int index = findValidNeighborIndex(static_cast<int>(idx), closed_set_guidance_);
+    if (index == -1) return { x_list, y_list };
+    idx = static_cast<size_t>(index);
+  }
+  const ClosedPlanes& p = closed_set_guidance_.planes;
+  for (int cur = (int)idx; cur != -1; cur = p.parent[(size_t)cur])
+  {
+    x_list.push_back(cur % astar_dim_);
+    y_list.push_back(cur / astar_dim_);
+  }
+  return { x_list, y_list };
+}
+
+void AStar::resetMovementMap()  // :544-547
+{
+  movement_cost_map_.resize_and_reset(astar_dim_, astar_dim_, astar_movement_cost_);
+  g_maps_dirty = true;
+}
+
+// :553-602 -- cells along the lane-graph edges (Bresenham, 3 x 3 brush) get the lane movement cost
+void AStar::setMovementMap(const LaneGraph::edges_t& edges)
+{
+  auto brush = [](const Point<int>& from, const Point<int>& to) {
+    for (const auto& point : util::drawline(from, to))
+      for (const auto& p_diff : patch_coords_)
+      {
+        const Point<int> q = point + p_diff;
+        if (q.x < 0 or q.x >= astar_dim_ or q.y < 0 or q.y >= astar_dim_) continue;
+        movement_cost_map_(q) = astar_lane_movement_cost_;
+      }
+  };
+  for (const auto& edge : edges)
+  {
+    const auto& [n1_opt, node_center, n3_opt] = edge;
+    const Point<int> p_center = (node_center.point_utm_patch * grid_tf::con2star_).toInt();
+    if (n1_opt) brush(p_center, ((*n1_opt).point_utm_patch * grid_tf::con2star_).toInt());
+    if (n3_opt) brush(p_center, ((*n3_opt).point_utm_patch * grid_tf::con2star_).toInt());
+  }
+  g_maps_dirty = true;
+}
+
+// :607-652 -- restricted-area polygon rasterised into restr_geofence_grid_ (the reference's loop bounds, including
+// its inner loop starting at min_x)
+void AStar::processGeofence()
+{
+  restr_geofence_grid_.resize_and_reset(astar_dim_, astar_dim_, 0);
+  int min_x = astar_dim_, min_y = astar_dim_, max_x = 0, max_y = 0;
+  for (auto& point : restr_geofence_.vertices)
+  {
+    const Point<int> pa = ((point - patch_origin_utm_) * grid_tf::con2star_).toInt();
+    min_x = std::min(min_x, pa.x);
+    min_y = std::min(min_y, pa.y);
+    max_x = std::max(max_x, pa.x);
+    max_y = std::max(max_y, pa.y);
+  }
+  for (int x_idx = min_x; x_idx < max_x; ++x_idx)
+    for (int y_idx = min_x; y_idx < max_y; ++y_idx)
+    {
+      if (x_idx < 0 || y_idx < 0 || x_idx >= astar_dim_ || y_idx >= astar_dim_) continue;  // the reference writes out of bounds here
+      const Point<int> pa(x_idx, y_idx);
+      const Point<double> p_utm = pa.toDouble() * grid_tf::star2con_ + patch_origin_utm_;
+      if (util::point_in_poly(restr_geofence_, p_utm)) restr_geofence_grid_(pa) = 1;
+    }
+  g_maps_dirty = true;
+}

@@ -276,6 +276,39 @@ GA_API int ga_set_astar_params(ga_ctx* ctx, const ga_astar_params* p);
  * receives the number of reachable cells. */
 GA_API int ga_build_heuristic(ga_ctx* ctx, int slot, int goal_x, int goal_y, int* n_closed);
 
+/* AStar::calcDistanceHeuristic(goal_pos, start_pos, for_path, get_only_near) with the reference's full
+ * signature (a_star.cpp:110-113) and the two config.yml switches it reads (HEURISTIC_EARLY_EXIT,
+ * MAX_EXTRA_NODES_ASTAR, a_star.cpp:31-32).
+ *   flags = 0 (GA_HEUR_FIXEDPOINT): the GPU fixed point, exactly ga_build_heuristic; start / early exit /
+ *           max_extra_nodes do not apply (every reachable cell is closed);
+ *   GA_HEUR_REFORDER: the reference's own closing order -- closed-set membership under early exit, cost_,
+ *           cost_dist_, parent_index_, is_unknown_ equal the reference's bit for bit (needed for identical
+ *           Hybrid A* node sequences).  The order is one serial chain of heap operations and is
+ *           replayed on the host (csrc/ga_heur_reforder.cu); inputs come from and results return to the device.
+ *   GA_HEUR_EARLY_EXIT / GA_HEUR_ONLY_NEAR: HEURISTIC_EARLY_EXIT / get_only_near (REFORDER only).
+ * ga_heur_near_nodes = AStar::nodes_near_goal_ (a_star.cpp:182-193) of the last build of `slot`: closed cells
+ * closer than 10 cells to (start_x, start_y), as ids y * astar_dim + x with their distances; in closing order
+ * after a REFORDER build with GA_HEUR_ONLY_NEAR for the same start, in row-major order otherwise (derived from
+ * the slot's planes).  ga_heur_closing_order = the cells of the last REFORDER build in the order they were
+ * closed (the reference does not expose it; tests and diagnostics do). */
+enum { GA_HEUR_FIXEDPOINT = 0, GA_HEUR_REFORDER = 1, GA_HEUR_EARLY_EXIT = 2, GA_HEUR_ONLY_NEAR = 4 };
+typedef struct
+{
+  int goal_x, goal_y;
+  int start_x, start_y;
+  unsigned flags;
+  unsigned max_extra_nodes; /* config.yml MAX_EXTRA_NODES_ASTAR */
+} ga_heur_query;
+GA_API int ga_build_heuristic_ex(ga_ctx* ctx, int slot, const ga_heur_query* q, int* n_closed);
+GA_API int ga_heur_near_nodes(ga_ctx* ctx, int slot, int start_x, int start_y, int* ids, double* dist, int cap, int* n);
+GA_API int ga_heur_closing_order(ga_ctx* ctx, int* ids, int cap, int* n);
+/* the GA_HEUR_REFORDER replay alone, on caller-owned HOST planes (dim x dim each; no context, no device): for
+ * callers that keep host mirrors of astar_grid_ / movement_cost_map_ / h_prox_arr_ anyway.  order (may be NULL)
+ * receives the closing order (up to dim * dim ids). */
+GA_API int ga_heur_reforder_host(const ga_astar_params* ap, int dim, const uint8_t* grid, const uint8_t* fence,
+                                 const double* movement_cost, const double* h_prox, const ga_heur_query* q, double* cost,
+                                 double* cost_dist, int32_t* parent, uint8_t* flags, int32_t* order, int* n_closed);
+
 /* The same for n independent queries at once (BASELINE config 5: batches of start/goal queries,
  * one heuristic grid per query; the reference needs one process per planner for this because all
  * of AStar's state is static, a_star.hpp:65-134).  ctxs[i] = the i-th query's context (all on one
@@ -305,6 +338,9 @@ GA_API int ga_download(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
  * With one context per planner this keeps the copies of one planner overlapped with the kernels of
  * another (bench.py's pipelined e2e leg). */
 GA_API int ga_download_async(ga_ctx* ctx, int grid_id, void* dst, size_t bytes);
+/* a w x h window at (x0, y0) of an astar_dim^2 grid into a dense w x h host array (e.g. the 200 x 200 window of
+ * h_prox_arr_ / motion_res_map_ that calcVoronoiPotentialField just rewrote, a_star.cpp:440-479) */
+GA_API int ga_download_window(ga_ctx* ctx, int grid_id, int x0, int y0, int w, int h, void* dst);
 GA_API int ga_grid_bytes(const ga_ctx* ctx, int grid_id, size_t* bytes);
 /* device address of a grid (for zero-copy consumers such as the bench's resident-input leg) */
 GA_API int ga_device_ptr(ga_ctx* ctx, int grid_id, void** dptr);
@@ -340,6 +376,10 @@ GA_API int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches
  * line sweeps summed over visits, visits that improved a cell, SM cycles summed over
  * visits spent waiting for a tile / staging / sweeping / publishing } (syncs the stream) */
 GA_API int ga_heur_stats(ga_ctx* ctx, long long* out7);
+/* scheduling of the sweep kernel, k7 = { workers per SM (1..8), idle back-off ns, early publications, lock-step
+ * rounds, in-place halo refresh, linger ns, stage-ahead }; -1 = chosen per launch.  Every setting yields the same
+ * fixed point (tests/test_gpu_parity.py::test_heuristic_schedules_agree); this exists for that test and for tuning. */
+GA_API int ga_set_heur_knobs(ga_ctx* ctx, const int* k7);
 /* launches of ALL library kernels since ga_create / ga_prof_reset (always counted) */
 GA_API long long ga_launch_count(const ga_ctx* ctx);
 

@@ -75,7 +75,7 @@ def _share_dir(cfg):
 class Planner:
     """One planner process-wide (static state in the library)."""
 
-    def __init__(self, arm, is_ushift=False, timeout_ms=10**9, config=None, is_sim=True):
+    def __init__(self, arm, is_ushift=False, timeout_ms=10**9, config=None, is_sim=True, dt_variant=1):
         self.arm = arm
         path = LIBS[arm]
         if not os.path.exists(path):
@@ -108,6 +108,9 @@ class Planner:
         self._ck(L.gap_init(_share_dir(cfg).encode(), v["max_steer"], v["wb"], v["lf"], v["lb"], v["width"],
                             int(bool(is_ushift)), _p(p), int(min(timeout_ms, 2**31 - 1)), int(is_sim)))
         self.init_s = time.perf_counter() - t0
+        # cv::distanceTransform arithmetic: 1 = IPP float (OpenCV built WITH_IPP, the reference's Docker image), 0 = 16.16
+        L.gap_set_dt_variant.argtypes = [C.c_int]
+        self._ck(L.gap_set_dt_variant(int(dt_variant)))
         self.origin = np.zeros(2)
         self.patch_dim = 0
 
@@ -311,7 +314,7 @@ def main():
         r = run_scenario(pl, a.scenario, trace=not a.no_trace)
         _flatten("", r, out)
         if a.heuristic:
-            for w, nm in ((0, "guid_"), (1, "path_")):
+            for w, nm in ((0, "hg_"), (1, "hp_")):
                 _flatten(nm, pl.heuristic(w), out)
             out["h_prox"] = pl.get_map(1)
             out["motion_res"] = pl.get_map(2)
@@ -322,8 +325,7 @@ def main():
         for i, r in enumerate(rs):
             _flatten("q%d_" % i, r, out)
     np.savez_compressed(a.out, **out)
-    brief = {k: (v.tolist() if v.size < 4 else v.shape) for k, v in out.items() if not k.startswith(("q", "path_", "guid_"))
-             or k in ("path_cost",)}
+    brief = {k: (v.tolist() if v.size < 4 else v.shape) for k, v in out.items() if not k.startswith(("q", "hp_", "hg_"))}
     print(brief)
 
 

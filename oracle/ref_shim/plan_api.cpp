@@ -372,6 +372,35 @@ int gap_get_heuristic(int which, double* cost, double* dist, int32_t* parent, ui
 
 int gap_astar_dim() { return AStar::astar_dim_; }
 
+#ifdef GA_DROPIN_HPP
+// arm B switches: heuristic mode (0 = the reference's closing order, 1 = GPU fixed point), DT arithmetic, counters
+int gap_b200_set_mode(int fixedpoint)
+{
+  ga_dropin::setHeuristicMode(fixedpoint ? GA_HEUR_FIXEDPOINT : GA_HEUR_REFORDER);
+  return 0;
+}
+int gap_set_dt_variant(int v)
+{
+  GAP_TRY({ ga_dropin::setDistanceTransformVariant(v); })
+}
+int gap_b200_stats(unsigned long long* out4)
+{
+  const ga_dropin::Stats& s = ga_dropin::stats();
+  out4[0] = s.expansions_prefetched;
+  out4[1] = s.path_checks_cached;
+  out4[2] = s.path_checks_direct;
+  out4[3] = s.poses_checked;
+  return 0;
+}
+long long gap_b200_launches() { return ga_launch_count(ga_dropin::ctx()); }
+#else
+int gap_set_dt_variant(int v)
+{
+  cv::shim_dt_variant = v;
+  return 0;
+}
+#endif
+
 // dense copies of the planner-side maps: 0 astar_grid_ (u8), 1 h_prox_arr_ (f64), 2 motion_res_map_ (f64),
 // 3 movement_cost_map_ (f64), 4 patch_safety_arr_ (u8, patch_dim^2)
 int gap_get_map(int which, void* dst)

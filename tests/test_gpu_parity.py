@@ -294,7 +294,7 @@ def test_heuristic_vs_reference_order(planner, oracle, with_prox):
         ctx.upload(_abi.GRID_MOVEMENT_COST, mc)
     goal = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, 5)[0]
     start = ga_b200.sample_free_cells(np.where(fence == 1, 2, grid), 1, 6)[0]
-    astar.calcDistanceHeuristic(goal, start, for_path=True)
+    astar.calcDistanceHeuristic(goal, start, for_path=True, reference_order=False)
     cs = astar.closed_set_path_
     import ga_oracle_py as go
     hp = go.HeurParams(astar.astar_dim_, 5.0, 3.0, 0.0, 0, 10000, 0)
@@ -644,23 +644,24 @@ def test_download_async_and_interleaved_contexts(oracle):
         ctx.close()
 
 
+# ga_set_heur_knobs: { workers per SM, idle back-off ns, early publications, lock-step rounds, halo refresh, linger ns, stage-ahead }
 @pytest.mark.parametrize("knobs", [
-    dict(GA_SW_ROUND="0", GA_SW_EARLY="0", GA_SW_REFRESH="0", GA_SW_LINGER="0", GA_SW_PREFETCH="0"),   # plain: publish when converged
-    dict(GA_SW_ROUND="0", GA_SW_EARLY="1", GA_SW_REFRESH="1", GA_SW_LINGER="0", GA_SW_PREFETCH="0"),
-    dict(GA_SW_ROUND="1", GA_SW_EARLY="1", GA_SW_REFRESH="1", GA_SW_LINGER="0", GA_SW_PREFETCH="0"),   # throughput mode
-    dict(GA_SW_ROUND="1", GA_SW_EARLY="255", GA_SW_REFRESH="2", GA_SW_LINGER="8000", GA_SW_PREFETCH="1"),
-    dict(GA_SW_ROUND="0", GA_SW_EARLY="255", GA_SW_REFRESH="2", GA_SW_LINGER="8000", GA_SW_PREFETCH="1"),  # latency mode
-    dict(GA_SW_ROUND="0", GA_SW_EARLY="255", GA_SW_REFRESH="2", GA_SW_LINGER="100000", GA_SW_PREFETCH="1", GA_SW_WARPS="1"),
-    dict(GA_SW_ROUND="0", GA_SW_EARLY="3", GA_SW_REFRESH="2", GA_SW_LINGER="0", GA_SW_PREFETCH="1", GA_SW_WARPS="2"),
+    (8, 20, 0, 0, 0, 0, 0),            # plain: publish when converged
+    (8, 20, 1, 0, 1, 0, 0),
+    (8, 20, 1, 1, 1, 0, 0),            # throughput mode
+    (8, 20, 255, 1, 2, 8000, 1),
+    (8, 20, 255, 0, 2, 8000, 1),       # latency mode
+    (1, 20, 255, 0, 2, 100000, 1),     # one worker per SM
+    (2, 20, 3, 0, 2, 0, 1),
 ])
-def test_heuristic_schedules_agree(oracle, knobs, monkeypatch):
+def test_heuristic_schedules_agree(oracle, knobs):
     """the sweep kernel's scheduling knobs (sweep order, when a tile publishes, in-place halo refresh, waiting,
     staging ahead, worker count) only change WHEN cells are relaxed: every combination must give the oracle's
     fixed point bit for bit, with prox and unknown-cell costs on (all four sweep_step variants)."""
-    for k, v in knobs.items():
-        monkeypatch.setenv(k, v)
     dim, seed = 1492, 3
     ctx = ga_b200.GridContext(0)
+    k7 = np.array(knobs, np.int32)
+    ctx.check(ctx.lib.ga_set_heur_knobs(ctx.h, _abi.ptr(k7)))
     cfg = ga_b200.LibConfig(ASTAR_UNKNOWN_COST=2.5)
     astar = ga_b200.AStar(ctx, cfg)
     cc = ga_b200.CollisionChecker(ctx, ga_b200.Vehicle.from_config(ga_b200.VehConfig()), cfg)

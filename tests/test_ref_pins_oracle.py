@@ -126,6 +126,15 @@ def _heur_compare(dim, seed, early_exit, max_extra, unk_w, prox, only_near=False
     assert got["n_closed"] == ref["n_closed"]
     for k in ("cost", "dist", "parent", "flags"):
         assert np.array_equal(got[k], ref[k]), k
+    # the PRODUCT's GA_HEUR_REFORDER replay (libgridaccel.so, host entry point: no device needed)
+    import ga_b200
+    from ga_b200.planner import heuristic_reference_order_host
+    cfg = ga_b200.LibConfig(ASTAR_UNKNOWN_COST=unk_w, HEURISTIC_EARLY_EXIT=early_exit, MAX_EXTRA_NODES_ASTAR=max_extra)
+    prod = heuristic_reference_order_host(cfg, grid, fence, mc, px, (gx, gy), (sx, sy), get_only_near=only_near)
+    assert prod["n_closed"] == ref["n_closed"]
+    for k in ("cost", "dist", "parent", "flags"):
+        assert np.array_equal(prod[k], ref[k]), "product replay: " + k
+    assert np.array_equal(prod["order"], got["order"])
     return ref, got, grid, mc, px, (gx, gy), (sx, sy)
 
 
