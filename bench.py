@@ -1,19 +1,27 @@
 #!/usr/bin/env python
 """bench.py -- headline measurement of the B200 grid backend (BASELINE.json configs[1]).
 
-Workload ("synthetic-4096"): synthetic 4096 x 4096 occupancy patch (SURVEY.md 8(d) gen_map, seed
-20240 + i) -> threshold + 21x21 disk dilation + 4x4 max-pool (ga_build_safety) -> obstacle-aware
-2D heuristic grid from a goal cell (ga_build_heuristic) on the 1024 x 1024 astar grid.
-One step = one such environment build.  metric = heuristic-grid Mcells/s = astar cells closed by
-the heuristic / step time (the dilation + pool that feed it are inside the step).
+Workload ("synthetic-4096"): one ENVIRONMENT BUILD of the planner on a synthetic 4096 x 4096 occupancy patch
+(SURVEY.md 8(d) gen_map, seed 20240 + i), in the reference's call order (planning.py:756-783, hybrid_a_star_lib.cpp:1225-1234):
+  passLocalMap(801^2 sensor window)  ->  processSafetyPatch (threshold + 21x21 disk dilation, whole patch) + 4x4 max-pool
+  ->  calcVoronoiPotentialField(ego) (two distance transforms + setCostmapValue on the 200^2 window; the Fortune sweep
+  between them is the reference's host code in BOTH arms)  ->  calcDistanceHeuristic(goal, ego) on the 1024 x 1024
+  astar grid, with the proximity term the real planner carries (PROX instantiation).
+One step = one such build.  metric = heuristic-grid Mcells/s = astar cells closed by the heuristic / step time.
 
-value : inputs resident in HBM, device-timed with CUDA events on the library's stream.
-e2e   : same step through the reference-facing host API with HOST buffers: pinned patch -> H2D,
-        build, D2H of the closed-set planes (cost, cost_dist, parent, flags) the serial search reads.
-N > 1 : one process per GPU (torchrun), every rank builds its own environments (independent
-        queries, no data-path collective), value = all ranks' cells / max-over-ranks time.
---impl reference : the reference's own CPU code for the same step (oracle/_ref when built, else
-        the oracle port), timed on the host cores.
+value : inputs resident in HBM (patch, window, sweep end points), device-timed with CUDA events on the library's stream:
+        safety + pool, potential field, heuristic (GPU fixed point: every reachable cell closed).
+e2e   : the same build through the host API with HOST buffers, as the drop-in planner classes issue it: pinned 801^2
+        window -> ga_patch_insert (H2D), safety, ga_potential_sites (D2H), Fortune sweep on the host, ga_build_potential
+        (H2D), heuristic, D2H of what the serial search reads (h_prox / motion_res windows + the four closed-set planes).
+        e2e.lean_* : the same with the packed 1-byte plane instead of the four planes (planner that takes its per-successor
+        costs from ga_expand's epilogue).
+N > 1 : one process per GPU (torchrun), every rank builds its own environments (independent queries, no data-path
+        collective), value = all ranks' cells / max-over-ranks time.
+plan  : metric M1, plan queries/s: the reference's serial Hybrid A* (hybrid_a_star_lib.cpp, unmodified) on the drop-in
+        classes over this library, P planner processes per GPU, next to the pure reference planner on the host cores.
+--impl reference : the reference's own CPU code for the same step at the SAME patch size (oracle/_ref), one planner
+        process per host core, per-stage times and both heuristic configurations (shipped early exit / whole grid).
 """
 import argparse
 import ctypes as C
@@ -21,6 +29,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -28,16 +37,54 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "guided-extended-hybrid-astar_b200"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 PATCH_DIM = 4096
+WIN_DIM = 801        # sensor window of one cycle (simulation.py:53)
+VOR_DIM = 200
 N_ROT = 4            # distinct environments rotated through so consecutive steps never share L2 contents
 METRIC = "heuristic_grid_mcells_per_s"
 UNIT = "Mcells/s"
 BYTES_PER_CELL_HEUR = 39.0   # read 1+1+8+8, write 8+8+4+1 per astar cell
 BYTES_PER_CELL_SAFETY = 2.0 + 1.0 / 16
-# dram__bytes_read.sum + dram__bytes_write.sum of one heur_sweep_kernel launch on the 1024^2 grid of
-# this workload, from the `ncu --set full` capture summarised in profiles/ (None until captured)
-NCU_TRAFFIC_BYTES = 17946900 + 148480  # profiles/r1_ncu_full_summary.csv (18.1 MB: the planes finish writes are not this kernel's, improved cells stay in L2)
+# dram__bytes_read.sum + dram__bytes_write.sum of one heur_sweep_kernel launch on the 1024^2 grid of this workload,
+# from the `ncu --set full` capture summarised in profiles/ (None until captured for this round's kernel)
+NCU_TRAFFIC_BYTES = 17946900 + 148480
+
+
+def cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def pick_points(grid, seed):
+    """ego and goal astar cells of an environment, from the pooled grid (bit-identical in both arms): the ego keeps
+    110 cells from every border (Voronoi window), the goal is any free cell at least a third of the
+    grid away."""
+    ad = grid.shape[0]
+    rng = np.random.default_rng(seed)
+    ys, xs = np.nonzero(grid == 0)
+    inner = (xs >= 110) & (xs < ad - 110) & (ys >= 110) & (ys < ad - 110)
+    k = rng.integers(0, int(inner.sum()))
+    ego = (int(xs[inner][k]), int(ys[inner][k]))
+    far = np.hypot(xs - ego[0], ys - ego[1]) > ad / 3
+    k = rng.integers(0, int(far.sum()))
+    return ego, (int(xs[far][k]), int(ys[far][k]))
+
+
+def host_sweep(sites):
+    """the Fortune sweep between the two distance transforms (deps_lib/VoronoiDiagramGenerator.cpp): serial fp64 host
+    code that stays the reference's in both arms; here through oracle/_ref (the reference's own TU)."""
+    import ga_ref_py as gr
+    if len(sites) == 0:
+        return np.zeros((0, 2), np.int32)
+    return np.ascontiguousarray(gr.voronoi_endpoints(sites, VOR_DIM, 3.0), np.int32).reshape(-1, 2)
 
 
 def load_peaks():
@@ -113,7 +160,8 @@ class ClockSampler(threading.Thread):
 
 
 def make_env(ga, device, seed, torch):
-    """one planner context with its 4096^2 patch resident, plus pinned host buffers for e2e"""
+    """one planner context with its 4096^2 patch resident, the cycle's 801^2 sensor window in pinned host memory,
+    ego / goal cells, the sweep end points of its potential window, and pinned result buffers for e2e"""
     from ga_b200 import _abi
     ctx = ga.GridContext(device)
     cfg = ga.LibConfig()
@@ -121,140 +169,226 @@ def make_env(ga, device, seed, torch):
     cc = ga.CollisionChecker(ctx, ga.Vehicle.from_config(ga.VehConfig()), cfg)
     cc.initialize(PATCH_DIM)
     patch = ga.gen_map(PATCH_DIM, seed)
-    h_patch = torch.from_numpy(patch).pin_memory()
-    ctx.upload(_abi.GRID_PATCH, h_patch.numpy())
+    ctx.upload(_abi.GRID_PATCH, patch)
     cc.processSafetyPatch()
     grid = astar.astar_grid_
-    goal = ga.sample_free_cells(grid, 1, seed + 1)[0]
+    ego, goal = pick_points(grid, seed + 1)
     adim = astar.astar_dim_
+    # the window the sensor delivers this cycle: 801^2 cells around the ego (same content as the patch there)
+    wo = (min(max(ego[0] * 4 - WIN_DIM // 2, 0), PATCH_DIM - WIN_DIM), min(max(ego[1] * 4 - WIN_DIM // 2, 0), PATCH_DIM - WIN_DIM))
+    h_win = torch.from_numpy(np.ascontiguousarray(patch[wo[1]:wo[1] + WIN_DIM, wo[0]:wo[0] + WIN_DIM])).pin_memory()
+    sites = astar.potentialSites(ego)
+    vor = host_sweep(sites)
+    astar.calcVoronoiPotentialField(ego, vor)
     outs = {gid: torch.empty((adim, adim), dtype=dt).pin_memory() for gid, dt in
             ((_abi.GRID_HEUR_COST, torch.float64), (_abi.GRID_HEUR_DIST, torch.float64),
              (_abi.GRID_HEUR_PARENT, torch.int32), (_abi.GRID_HEUR_FLAGS, torch.uint8))}
-    return dict(ctx=ctx, cc=cc, astar=astar, patch=patch, h_patch=h_patch, goal=(int(goal[0]), int(goal[1])), outs=outs)
+    wins = {gid: torch.empty((VOR_DIM, VOR_DIM), dtype=torch.float64).pin_memory() for gid in (_abi.GRID_H_PROX, _abi.GRID_MOTION_RES)}
+    h_sites = np.empty((VOR_DIM * VOR_DIM, 2), np.int32)
+    return dict(ctx=ctx, cc=cc, astar=astar, patch=patch, h_win=h_win, win_origin=wo, ego=ego, goal=goal, vor=vor,
+                n_sites=len(sites), outs=outs, wins=wins, h_sites=h_sites,
+                vor_origin=(max(ego[0] - VOR_DIM // 2, 0), max(ego[1] - VOR_DIM // 2, 0)))
 
 
 def step_resident(env, n_closed=None):
-    lib, h = env["ctx"].lib, env["ctx"].h
-    env["ctx"].check(lib.ga_build_safety(h))
-    env["ctx"].check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], n_closed))
-
-
-def step_e2e(env):
+    """device-resident build: safety + pool, potential field (end points of the sweep given), heuristic with prox"""
     from ga_b200 import _abi
     ctx = env["ctx"]
     lib, h = ctx.lib, ctx.h
-    hp = env["h_patch"]
-    ctx.check(lib.ga_upload(h, _abi.GRID_PATCH, C.c_void_p(hp.data_ptr()), hp.numel()))
+    v = env["vor"]
     ctx.check(lib.ga_build_safety(h))
-    ctx.check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], None))
-    for gid, t in env["outs"].items():
-        ctx.check(lib.ga_download(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+    ctx.check(lib.ga_build_potential(h, env["ego"][0], env["ego"][1], _abi.ptr(v) if len(v) else None, len(v), None))
+    ctx.check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], n_closed))
 
 
-def step_e2e_async(env):
-    """step_e2e without the host waiting for the result: the caller syncs the context before it touches
-    the environment's buffers again"""
+def _e2e_front(env, sweep_s):
+    """window in, safety, sites out, host sweep, potential field, heuristic -- everything up to the result copies"""
     from ga_b200 import _abi
     ctx = env["ctx"]
     lib, h = ctx.lib, ctx.h
-    hp = env["h_patch"]
-    ctx.check(lib.ga_upload(h, _abi.GRID_PATCH, C.c_void_p(hp.data_ptr()), hp.numel()))
+    hw = env["h_win"]
+    ctx.check(lib.ga_patch_insert(h, C.c_void_p(hw.data_ptr()), env["win_origin"][0], env["win_origin"][1], WIN_DIM))
     ctx.check(lib.ga_build_safety(h))
+    n = C.c_int()
+    ctx.check(lib.ga_potential_sites(h, env["ego"][0], env["ego"][1], _abi.ptr(env["h_sites"]), VOR_DIM * VOR_DIM, C.byref(n)))
+    t0 = time.perf_counter()
+    v = host_sweep(env["h_sites"][:n.value])
+    sweep_s[0] += time.perf_counter() - t0
+    ctx.check(lib.ga_build_potential(h, env["ego"][0], env["ego"][1], _abi.ptr(v) if len(v) else None, len(v), None))
     ctx.check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], None))
-    for gid, t in env["outs"].items():
-        ctx.check(lib.ga_download_async(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
 
 
-def _ref_goal(patch):
-    import ga_oracle_py as go
-    thr = go.threshold(patch, 100, 130)
-    free = np.argwhere(thr[::4, ::4] == 0)
-    return int(free[len(free) // 2][1]), int(free[len(free) // 2][0])
+def step_e2e(env, sweep_s, wait=True, lean=False):
+    from ga_b200 import _abi
+    ctx = env["ctx"]
+    lib, h = ctx.lib, ctx.h
+    _e2e_front(env, sweep_s)
+    ox, oy = env["vor_origin"]
+    for gid, t in env["wins"].items():  # the window of h_prox_arr_ / motion_res_map_ the search reads cell by cell
+        ctx.check(lib.ga_download_window(h, gid, ox, oy, VOR_DIM, VOR_DIM, C.c_void_p(t.data_ptr())))
+    if lean:
+        t = env["outs"][_abi.GRID_HEUR_FLAGS]
+        ctx.check(lib.ga_download_async(h, _abi.GRID_HEUR_PACKED, C.c_void_p(t.data_ptr()), t.numel()))
+    else:
+        for gid, t in env["outs"].items():
+            ctx.check(lib.ga_download_async(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+    if wait:
+        ctx.sync()
 
 
-def cpu_reference_steps(dim, seeds, disk_r_c):
-    """the same step on the host cores, one thread (the reference keeps all planner state in static
-    members: one planner per process).  oracle/_ref (the reference's own translation units) when it
-    was built, else the plain-C oracle port.  Returns (seconds, cells closed, kind)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+E2E_H2D = WIN_DIM * WIN_DIM          # + the sweep's end points (a few KB, counted per run)
+E2E_D2H_FULL = 2 * VOR_DIM * VOR_DIM * 8 + (PATCH_DIM // 4) ** 2 * 21
+E2E_D2H_LEAN = 2 * VOR_DIM * VOR_DIM * 8 + (PATCH_DIM // 4) ** 2
+
+
+def cpu_reference_steps(dim, seeds, full_grid=True, repeats=1):
+    """the same environment build through the reference's OWN code (oracle/_ref: collision_checking.cpp, a_star.cpp,
+    VoronoiDiagramGenerator.cpp ... compiled unmodified; cv::dilate / distanceTransform / cuDNN pooling restated in
+    oracle/ref_shim), one thread -- the reference keeps its planner state in static members, one planner per process.
+    full_grid: HEURISTIC_EARLY_EXIT off, the whole reachable grid as the GPU builds; else the shipped config.yml
+    (early exit, MAX_EXTRA_NODES_ASTAR 10000).  Returns dict(seconds, cells, stage seconds)."""
     import ga_b200
-    import ga_oracle_py as go
     import ga_ref_py as gr
-    total, cells = 0.0, 0
-    if gr.available():
-        gr.init(dim)
-        gr.set_heuristic_config(early_exit=False, max_extra_nodes=1 << 30, unknown_cost_w=0.0)  # whole reachable grid, as the GPU builds
-        L = gr.lib()
-        for seed in seeds:
-            patch = ga_b200.gen_map(dim, seed)
-            goal = _ref_goal(patch)
-            t0 = time.perf_counter()
-            gr.set_grid(gr.PATCH, patch)       # CollisionChecker::patch_arr_
-            gr.process_safety_patch()          # collision_checking.cpp:193-224
-            gr.calc_astar_grid()               # a_star.cpp:536-542 (CPU max in place of cuDNN)
-            n = L.gar_calc_distance_heuristic(goal[0], goal[1], goal[0], goal[1], 0, 0)  # a_star.cpp:110-295
-            total += time.perf_counter() - t0
-            cells += n
-        return total, cells, "reference"
+    if not gr.available():
+        raise RuntimeError("oracle/_ref/libga_ref.so is not built")
+    gr.init(dim)
+    if full_grid:
+        gr.set_heuristic_config(early_exit=False, max_extra_nodes=1 << 30, unknown_cost_w=0.0)
+    else:
+        gr.set_heuristic_config(early_exit=True, max_extra_nodes=10000, unknown_cost_w=0.0)
+    st = dict(insert=0.0, dilate=0.0, pool=0.0, potential=0.0, heuristic=0.0)
+    cells = 0
     for seed in seeds:
         patch = ga_b200.gen_map(dim, seed)
-        goal = _ref_goal(patch)
-        t0 = time.perf_counter()
-        safety = go.process_safety_patch(patch, 100, 130, disk_r_c)
-        grid = go.pool_max(safety)
-        ad = grid.shape[0]
-        hp = go.HeurParams(ad, 5.0, 3.0, 0.0, 0, 1 << 30, 0)
-        res = go.heuristic_reforder(hp, grid, np.zeros((ad, ad), np.uint8), np.full((ad, ad), 5.0), np.zeros((ad, ad)), goal, goal)
-        total += time.perf_counter() - t0
-        cells += res["n_closed"]
-    return total, cells, "port"
+        gr.set_grid(gr.PATCH, patch)
+        gr.process_safety_patch()
+        gr.calc_astar_grid()
+        ego, goal = pick_points(gr.get_grid(gr.ASTAR), seed + 1)
+        wo = (min(max(ego[0] * 4 - WIN_DIM // 2, 0), dim - WIN_DIM), min(max(ego[1] * 4 - WIN_DIM // 2, 0), dim - WIN_DIM))
+        win = np.ascontiguousarray(patch[wo[1]:wo[1] + WIN_DIM, wo[0]:wo[0] + WIN_DIM])
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            gr.pass_local_map(win, wo[0], wo[1])            # collision_checking.cpp:269-313
+            t1 = time.perf_counter()
+            gr.process_safety_patch()                       # :193-224
+            t2 = time.perf_counter()
+            gr.calc_astar_grid()                            # a_star.cpp:536-542 (CPU max in place of cuDNN)
+            t3 = time.perf_counter()
+            gr.calc_voronoi_potential_field(ego, 1)         # :440-479, incl. the Fortune sweep
+            t4 = time.perf_counter()
+            r = gr.calc_distance_heuristic(goal, ego, for_path=False)  # :110-295
+            t5 = time.perf_counter()
+            for k, d in zip(("insert", "dilate", "pool", "potential", "heuristic"), (t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4)):
+                st[k] += d
+            cells += r["n_closed"]
+    return dict(seconds=sum(st.values()), cells=cells, stages=st)
 
 
 def _ref_worker(a):
-    dim, seeds, r_c = a
-    return cpu_reference_steps(dim, seeds, r_c)  # (seconds inside the reference's calls, cells, kind)
+    dim, seeds, full_grid = a
+    return cpu_reference_steps(dim, seeds, full_grid)
 
 
 def run_reference(args, rank):
-    """--impl reference: the reference's own CPU implementation of the step, one planner process per
-    host core (its only way to use more than one core), each step = cores x one 2048^2 sample."""
+    """--impl reference: the reference's own CPU implementation of the step at the same patch size, one planner
+    process per host core (its only way to use more than one core); each step = cores x one environment build."""
     if rank != 0:
         return
     import multiprocessing as mp
-    import ga_b200
-    dim = args.ref_dim
-    if dim <= 0:
-        # bounded sample: the whole --steps/--warmup run stays within ~2 minutes of host time
-        budget = 120.0 / (args.steps + args.warmup)
-        dim = 2048 if budget >= 0.9 else 1024 if budget >= 0.25 else 512
-    veh = ga_b200.Vehicle.from_config(ga_b200.VehConfig())
-    _, _, r_c, _ = ga_b200.calc_disks(veh, ga_b200.LibConfig())
+    dim = args.ref_dim if args.ref_dim > 0 else PATCH_DIM
+    # the whole --steps/--warmup run has to end within a few minutes: ~1.5 s per 4096^2 build
+    est = {4096: 1.6, 2048: 0.4, 1024: 0.1}.get(dim, 1.6)
+    if args.ref_dim <= 0 and est * (args.steps + args.warmup) > 420:
+        dim = 2048 if 0.4 * (args.steps + args.warmup) <= 420 else 1024
     cores = max(1, min(len(os.sched_getaffinity(0)), args.ref_procs))
     ctx = mp.get_context("spawn")
     with ctx.Pool(cores) as pool:
-        def one_step(i):
-            # the processes run concurrently; the step lasts as long as the slowest planner's calls
-            # (map generation and process start-up are not the reference's work and stay outside)
-            out = pool.map(_ref_worker, [(dim, [20240 + (i * cores + w) % 64], r_c) for w in range(cores)])
-            return max(o[0] for o in out), sum(o[1] for o in out), out[0][2]
+        def one_step(i, full):
+            # the processes run concurrently; the step lasts as long as the slowest planner's calls (map generation
+            # and process start-up are not the reference's work and stay outside)
+            out = pool.map(_ref_worker, [(dim, [20240 + (i * cores + w) % 64], full) for w in range(cores)])
+            return max(o["seconds"] for o in out), sum(o["cells"] for o in out), out[0]["stages"]
         for i in range(args.warmup):
-            one_step(i)
-        total, cells, kind = 0.0, 0, "port"
+            one_step(i, True)
+        total, cells = 0.0, 0
+        stages = None
         for i in range(args.steps):
-            dt, n, kind = one_step(args.warmup + i)
+            dt, n, stg = one_step(args.warmup + i, True)
             total += dt
             cells += n
+            stages = stg if stages is None else {k: stages[k] + stg[k] for k in stg}
+        # the shipped configuration (early exit after the ego cell + 10 000 nodes) on a few builds, beside it
+        ship_t, ship_n, ship_stg = 0.0, 0, None
+        for i in range(min(args.steps, 3)):
+            dt, n, stg = one_step(1000 + i, False)
+            ship_t += dt
+            ship_n += n
+            ship_stg = stg if ship_stg is None else {k: ship_stg[k] + stg[k] for k in stg}
     val = cells / total / 1e6
-    sample = "%d step(s); one step = %d planner processes x (threshold + dilate + pool + heuristic) on a %dx%d patch" % (
-        args.steps, cores, dim, dim)
+    ms = lambda d, n: {k + "_ms": 1e3 * v / n for k, v in d.items()}
+    sample = "%d step(s); one step = %d planner processes x one environment build (window insert + threshold + dilate + pool " \
+             "+ potential field incl. Fortune sweep + heuristic, whole reachable grid) on a %dx%d patch" % (args.steps, cores, dim, dim)
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic-4096", "patch_dim": PATCH_DIM, "astar_dim": PATCH_DIM // 4,
-                       "sample_patch_dim": dim},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+                       "sample_patch_dim": dim, "same_config": dim == PATCH_DIM},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample,
+                             "cpu_model": cpu_model(),
+                             "stages_per_build_one_process": ms(stages, args.steps),
+                             "dilate_share": stages["dilate"] / max(sum(stages.values()), 1e-12),
+                             "shipped_config": {"note": "HEURISTIC_EARLY_EXIT True, MAX_EXTRA_NODES_ASTAR 10000 (config.yml:47-49)",
+                                                "value": ship_n / max(ship_t, 1e-12) / 1e6, "ms_per_step": 1e3 * ship_t / max(min(args.steps, 3), 1),
+                                                "cells_per_build": ship_n / max(min(args.steps, 3), 1) / cores,
+                                                "stages_per_build_one_process": ms(ship_stg, max(min(args.steps, 3), 1))}},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def run_plan_leg(args, local_rank, rank):
+    """metric M1, plan queries/s (BASELINE config 5's unit): independent start/goal queries on synthetic 2048^2 maps.
+    Arm B = the reference's unmodified hybrid_a_star_lib.cpp on the drop-in classes over libgridaccel.so
+    (oracle/_ref/libga_planb.so), P planner processes on this rank's GPU; on rank 0 also arm A = the pure reference
+    planner, P processes on the host cores.  One planner per process (static state), so processes, not threads.
+    A query = recalculateEnv (pool + potential field + guidance heuristic) + hybridAStarPlanning's search; the shipped
+    2000 ms timeout applies.  queries/s = queries / the slowest process's summed query time."""
+    import ga_plan_py as gp
+    if not (os.path.exists(gp.LIBS["b200"]) and os.path.exists(gp.LIBS["ref"])):
+        return {"unavailable": "oracle/_ref plan libraries not built (need /root/reference at build time)"}
+    procs, nq = args.plan_procs, args.plan_queries
+    tmp = tempfile.mkdtemp(prefix="ga_plan_")
+
+    def run_arm(arm, tag):
+        ps = []
+        env = dict(os.environ, GA_DEVICE=str(local_rank))
+        for w in range(procs):
+            out = os.path.join(tmp, "%s_%d_%d.npz" % (tag, rank, w))
+            cmd = [sys.executable, os.path.join(ROOT, "oracle", "ga_plan_py.py"), "--arm", arm, "--synthetic", "2048",
+                   "--seed", str(50000 + rank * 64 + w), "--queries", str(nq), "--no-trace", "--timeout-ms", "2000", "--out", out]
+            ps.append((subprocess.Popen(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE), out))
+        tot, found, exp, env_ms, search_ms, n = [], 0, 0, 0.0, 0.0, 0
+        for p, out in ps:
+            err = p.communicate()[1]
+            if p.returncode != 0:
+                return {"error": err.decode()[-400:]}
+            z = np.load(out)
+            k = int(z["n_queries"])
+            tot.append(sum(float(z["q%d_query_ms" % i]) for i in range(k)))
+            for i in range(k):
+                found += int(z["q%d_found" % i])
+                exp += int(z["q%d_n_closed" % i])
+                env_ms += float(z["q%d_env_ms" % i])
+                search_ms += float(z["q%d_search_ms" % i])
+            n += k
+        return {"queries_per_s": n / (max(tot) * 1e-3), "queries": n, "processes": procs, "found": found,
+                "expanded_nodes": exp, "env_ms_per_query": env_ms / n, "search_ms_per_query": search_ms / n}
+
+    out = {"workload": "%d planner processes x %d queries on synthetic 2048^2 maps (one map per process), shipped config" % (procs, nq),
+           "b200": run_arm("b200", "b")}
+    if rank == 0 and not args.no_cpu_baseline:
+        out["cpu_reference"] = run_arm("ref", "a")
+        out["cpu_reference"]["cores"] = procs
+    return out
 
 
 def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak):
@@ -362,23 +496,26 @@ def run_replan_leg(ga, device, args):
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import ga_ref_py as gr
         if gr.available():
-            gr.init(dim)
-            gr.cart_reset(dim)
-            gr.set_heuristic_config(early_exit=False, max_extra_nodes=1 << 30, unknown_cost_w=0.0)
-            L = gr.lib()
-            ts = []
-            for k in range(6):
-                wo = cycles[k] - origin - 400
-                t0 = time.perf_counter()
-                pm = gr.raytrace(wins[k])
-                gr.cartograph(pm, wo[0], wo[1])
-                gr.cart_pass_local_map(wo[0], wo[1], 801)
-                gr.process_safety_patch()
-                gr.calc_astar_grid()
-                L.gar_calc_distance_heuristic(goal[0], goal[1], goal[0], goal[1], 0, 0)
-                ts.append(time.perf_counter() - t0)
-            out["cpu_reference_ms_per_cycle"] = 1e3 * float(np.median(ts[1:]))
-            out["cpu_reference_sample"] = "5 cycles of the same chain through the reference's own code, 1 core, median"
+            for tag, early in (("", False), ("_shipped_config", True)):
+                gr.init(dim)
+                gr.cart_reset(dim)
+                gr.set_heuristic_config(early_exit=early, max_extra_nodes=10000 if early else 1 << 30, unknown_cost_w=0.0)
+                L = gr.lib()
+                ts = []
+                for k in range(6):
+                    wo = cycles[k] - origin - 400
+                    ego = ((cycles[k][0] - origin[0]) // 4, (cycles[k][1] - origin[1]) // 4)
+                    t0 = time.perf_counter()
+                    pm = gr.raytrace(wins[k])
+                    gr.cartograph(pm, wo[0], wo[1])
+                    gr.cart_pass_local_map(wo[0], wo[1], 801)
+                    gr.process_safety_patch()
+                    gr.calc_astar_grid()
+                    L.gar_calc_distance_heuristic(goal[0], goal[1], int(ego[0]), int(ego[1]), 0, 0)
+                    ts.append(time.perf_counter() - t0)
+                out["cpu_reference_ms_per_cycle" + tag] = 1e3 * float(np.median(ts[1:]))
+            out["cpu_reference_sample"] = "5 cycles of the same chain through the reference's own code, 1 core, median; whole " \
+                                          "reachable grid (as the GPU builds) and the shipped early-exit configuration"
     return out
 
 
@@ -482,11 +619,14 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ref-dim", type=int, default=0, help="patch size of the bounded CPU sample (reference arm); 0 = from --steps")
+    ap.add_argument("--ref-dim", type=int, default=0, help="patch size of the reference arm (0 = 4096, shrunk only if --steps makes the run too long)")
     ap.add_argument("--ref-procs", type=int, default=64, help="planner processes of the reference arm (capped by the host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-collision", action="store_true", help="skip the collision-checks/s leg")
     ap.add_argument("--no-replan", action="store_true", help="skip the unknown-environment cycle leg")
+    ap.add_argument("--no-plan", action="store_true", help="skip the plan queries/s leg")
+    ap.add_argument("--plan-procs", type=int, default=4, help="planner processes per GPU of the plan leg (fixed per GPU: weak scaling)")
+    ap.add_argument("--plan-queries", type=int, default=6, help="queries per planner process of the plan leg")
     ap.add_argument("--batch", type=int, default=128, help="queries of the batched-heuristic leg (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -521,7 +661,7 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    # cells closed per environment (fixed by the map), also the parity hook of smoke()
+    # cells closed per environment (fixed by the map)
     closed = []
     for e in envs:
         n = C.c_int()
@@ -539,8 +679,8 @@ def main():
         launches0 = sum(e["ctx"].launch_count() for e in envs)
         sampler.active = True
         t0 = time.perf_counter()
-        # steps run back to back on the device: step i+1's stream waits for step i's end event, so the
-        # span first-start .. last-end is exactly K serialised steps without any host synchronisation
+        # steps run back to back on the device: step i+1's stream waits for step i's end event, so the span
+        # first-start .. last-end is exactly K serialised steps
         first = last = None
         for i in range(steps):
             e = envs[i % N_ROT]
@@ -564,63 +704,78 @@ def main():
                 e["ctx"].prof_enable(False)
         return dev_ms, wall * 1e3, launches, cells
 
-    def timed_pipelined(steps):
-        """the e2e step with the N_ROT environments (one context, stream and pinned buffer set each) in
-        flight together: environment k's upload and downloads overlap the kernels of the others.  Every
-        step still copies its own patch in and its four result planes out inside the timed region."""
+    def timed_e2e(steps, pipelined, lean):
+        """host-clocked: every step copies its window in and its results out inside the timed region.  pipelined: the
+        N_ROT planner contexts (one stream and pinned buffer set each) are in flight together, a context is synced
+        only before its buffers are reused, so one step's copies overlap the other contexts' kernels."""
+        sweep_s = [0.0]
         for i in range(args.warmup):
-            step_e2e_async(envs[i % N_ROT])
-        for e in envs:
-            e["ctx"].sync()
+            step_e2e(envs[i % N_ROT], sweep_s, wait=True, lean=lean)
         barrier()
+        sweep_s = [0.0]
         sampler.active = True
         t0 = time.perf_counter()
         for i in range(steps):
             e = envs[i % N_ROT]
-            if i >= N_ROT:
-                e["ctx"].sync()  # this environment's previous step is complete: its buffers are free again
-            step_e2e_async(e)
+            if pipelined and i >= N_ROT:
+                e["ctx"].sync()
+            step_e2e(e, sweep_s, wait=not pipelined, lean=lean)
         for e in envs:
             e["ctx"].sync()
         barrier()
         wall = time.perf_counter() - t0
         sampler.active = False
-        return wall * 1e3, sum(closed[i % N_ROT] for i in range(steps))
+        return wall * 1e3, sum(closed[i % N_ROT] for i in range(steps)), sweep_s[0] * 1e3
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     dev_ms, wall_ms, launches, cells = timed(step_resident, args.steps, False)
-    # per-kernel device time: the same K steps once more with CUDA events around every launch on the
-    # library's stream (kept out of the run `value` comes from: the event records cost a little)
+    # per-kernel device time: the same K steps once more with CUDA events around every launch on the library's
+    # stream (kept out of the run `value` comes from: the event records cost a little)
     timed(step_resident, args.steps, True)
     kt = {}
-    for k, name in ((_abi.K_DILATE, "safety"), (_abi.K_HEUR_INIT, "heur_init"),
-                    (_abi.K_HEUR_RELAX, "heur_relax"), (_abi.K_HEUR_FINISH, "heur_finish")):
+    for k, name in ((_abi.K_DILATE, "safety"), (_abi.K_DT, "distance_transforms"), (_abi.K_POTENTIAL, "costmap"),
+                    (_abi.K_HEUR_INIT, "heur_init"), (_abi.K_HEUR_RELAX, "heur_relax"), (_abi.K_HEUR_FINISH, "heur_finish")):
         ms = n = 0
         for e in envs:
             m_, n_ = e["ctx"].prof_get(k)
             ms += m_
             n += n_
         kt[name] = (ms, n)
-    # the steps are serialised on each context's stream; K steps' device time = sum of per-step event spans
-    e2e_dev_ms, e2e_serial_ms, _, e2e_cells = timed(step_e2e, args.steps, False)
-    e2e_wall_ms, e2e_cells = timed_pipelined(args.steps)
+    e2e_steps = max(20, args.steps // 2)
+    e2e_serial_ms, e2e_serial_cells, _ = timed_e2e(e2e_steps, False, False)
+    e2e_wall_ms, e2e_cells, sweep_ms = timed_e2e(e2e_steps, True, False)
+    lean_wall_ms, lean_cells, _ = timed_e2e(e2e_steps, True, True)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
     collision = run_collision_leg(envs[0], args, ga_b200) if (rank == 0 and not args.no_collision) else None
     replan = run_replan_leg(ga_b200, local_rank, args) if (rank == 0 and not args.no_replan) else None
     sampler.stop_flag = True
+    for e in envs[1:]:
+        e["ctx"].sync()
+    plan = None
+    if not args.no_plan:
+        if world > 1:
+            dist.barrier()
+        plan = run_plan_leg(args, local_rank, rank)
 
-    # max over ranks
-    t = torch.tensor([dev_ms, e2e_wall_ms, float(cells), float(e2e_cells), float(launches), e2e_serial_ms], dtype=torch.float64,
-                     device="cuda")
+    # max over ranks of the times, sum over ranks of the work
+    plan_qps = plan["b200"].get("queries_per_s", 0.0) if plan and "b200" in plan else 0.0
+    plan_t = (plan["b200"]["queries"] / plan_qps) if plan_qps else 0.0
+    plan_q = float(plan["b200"]["queries"]) if plan_qps else 0.0
+    batch_ms = batch["ms_per_batch"] if batch else 0.0
+    t = torch.tensor([dev_ms, e2e_wall_ms, float(cells), float(e2e_cells), float(launches), e2e_serial_ms, lean_wall_ms,
+                      float(lean_cells), plan_t, plan_q, batch_ms, float(args.batch if batch else 0)], dtype=torch.float64, device="cuda")
     if world > 1:
         tmax = t.clone()
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone()
         dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        dev_ms, e2e_wall_ms, e2e_serial_ms = float(tmax[0]), float(tmax[1]), float(tmax[5])
-        cells, e2e_cells, launches = float(tsum[2]), float(tsum[3]), int(tsum[4])
+        dev_ms, e2e_wall_ms, e2e_serial_ms, lean_wall_ms, plan_t, batch_ms = (float(tmax[i]) for i in (0, 1, 5, 6, 8, 10))
+        cells, e2e_cells, launches, lean_cells, plan_q = float(tsum[2]), float(tsum[3]), int(tsum[4]), float(tsum[7]), float(tsum[9])
+        batch_n = float(tsum[11])
+    else:
+        batch_n = float(args.batch if batch else 0)
     value = cells / (dev_ms * 1e-3) / 1e6
     e2e_value = e2e_cells / (e2e_wall_ms * 1e-3) / 1e6
 
@@ -631,40 +786,59 @@ def main():
         # dominant kernel = the wavefront relaxation; algorithmic bytes = 39 B x astar cells of one grid per launch
         alg_bytes = BYTES_PER_CELL_HEUR * adim * adim
         achieved = alg_bytes / (relax_ms / max(relax_n, 1) * 1e-3) / 1e9
+        n_vor = int(np.mean([len(e["vor"]) for e in envs]))
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": "synthetic-4096", "patch_dim": PATCH_DIM, "astar_dim": adim,
+                           "step": "safety + pool (4096^2) -> potential field (200^2 window, PROX) -> heuristic (1024^2, fixed point)",
                            "disk_r_c": envs[0]["cc"].disk_r_c_, "l2": "inputs rotate over %d environments per rank (~130 MB each) > L2" % N_ROT,
-                           "cells_closed_per_step": cells / args.steps / world},
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": PATCH_DIM * PATCH_DIM,
-                        "d2h_bytes_per_step": adim * adim * 21, "ms_per_step": e2e_wall_ms / args.steps,
-                        "pipeline": "%d planner contexts in flight (one stream and pinned buffer set each): a step's copies "
-                                    "overlap the other contexts' kernels" % N_ROT,
-                        "serial_value": e2e_cells / (e2e_serial_ms * 1e-3) / 1e6,
-                        "serial_ms_per_step": e2e_serial_ms / args.steps},
+                           "cells_closed_per_step": cells / args.steps / world, "voronoi_end_points": n_vor,
+                           "potential_sites": int(np.mean([e["n_sites"] for e in envs]))},
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": E2E_H2D + 8 * n_vor,
+                        "d2h_bytes_per_step": E2E_D2H_FULL + 8 * int(np.mean([e["n_sites"] for e in envs])),
+                        "ms_per_step": e2e_wall_ms / e2e_steps, "steps": e2e_steps,
+                        "what": "801^2 window in (ga_patch_insert), safety, sites out, Fortune sweep on the host, potential field, "
+                                "heuristic, h_prox / motion_res windows + four closed-set planes out",
+                        "pipeline": "%d planner contexts in flight (one stream and pinned buffer set each)" % N_ROT,
+                        "host_sweep_ms_per_step": sweep_ms / e2e_steps,
+                        "serial_value": e2e_serial_cells / (e2e_serial_ms * 1e-3) / 1e6,
+                        "serial_ms_per_step": e2e_serial_ms / e2e_steps,
+                        "lean_value": lean_cells / (lean_wall_ms * 1e-3) / 1e6, "lean_ms_per_step": lean_wall_ms / e2e_steps,
+                        "lean_d2h_bytes_per_step": E2E_D2H_LEAN,
+                        "lean_what": "the packed 1-byte plane (GA_GRID_HEUR_PACKED) instead of the four planes: a planner that "
+                                     "takes per-successor costs from ga_expand's epilogue"},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "kernel": "heur_sweep_kernel", "achieved": achieved, "peak": hbm_peak,
                              "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES, "peak_source": peak_src,
-                             "note": "dependency-depth bound, not bandwidth bound: one grid's wavefront keeps ~5% of the "
+                             "note": "dependency-depth bound, not bandwidth bound: one grid's wavefront keeps a few % of the "
                                      "worker warps busy; see `batch` for the same kernel fed with independent grids",
                              "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": relax_ms / max(relax_n, 1)},
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
                 "safety_roofline": {"achieved": BYTES_PER_CELL_SAFETY * PATCH_DIM * PATCH_DIM /
-                                    (dil_ms / max(dil_n, 1) * 1e-3) / 1e9, "unit": "GB/s",
+                                    (dil_ms / max(dil_n, 1) * 1e-3) / 1e9, "unit": "GB/s", "peak": hbm_peak,
+                                    "frac": BYTES_PER_CELL_SAFETY * PATCH_DIM * PATCH_DIM / (dil_ms / max(dil_n, 1) * 1e-3) / 1e9 / hbm_peak,
                                     "note": "safety_kernel (threshold + dilation + pool fused), 2+1/16 B per gm cell"},
                 "clocks": sampler.result()}
         if batch:
+            batch["grids_per_s_all_ranks"] = batch_n / (batch_ms * 1e-3)
             line["batch"] = batch
         if collision:
             line["collision"] = collision
         if replan:
             line["replan_cycle"] = replan
+        if plan:
+            if plan_t:
+                plan["queries_per_s_all_ranks"] = plan_q / plan_t
+            line["plan"] = plan
         if not args.no_cpu_baseline:
-            # bounded sample of the same step on the host: a 2048^2 patch seeded like environment 0
-            dt, n, kind = cpu_reference_steps(2048, [20240], envs[0]["cc"].disk_r_c_)
-            line["cpu_baseline"] = {"value": n / dt / 1e6, "unit": UNIT, "cores": 1, "kind": kind,
-                                    "sample": "1 step (threshold + dilate + pool + heuristic) on a 2048x2048 patch, seed 20240 (%.1f s)" % dt}
+            # bounded sample of the same step on the host, one core: two builds at the full patch size
+            r = cpu_reference_steps(PATCH_DIM, [20240], full_grid=True, repeats=2)
+            line["cpu_baseline"] = {"value": r["cells"] / r["seconds"] / 1e6, "unit": UNIT, "cores": 1, "kind": "reference",
+                                    "cpu_model": cpu_model(),
+                                    "stages_ms_per_build": {k: 1e3 * v / 2 for k, v in r["stages"].items()},
+                                    "sample": "2 environment builds on the 4096x4096 patch of seed 20240 through the reference's own "
+                                              "code, whole reachable grid (%.1f s)" % r["seconds"]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -674,5 +848,4 @@ def main():
 
 
 if __name__ == "__main__":
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
     main()

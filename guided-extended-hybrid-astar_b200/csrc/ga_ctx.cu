@@ -77,7 +77,7 @@ static void free_grids(ga_ctx* c)
                     (void**)&c->d_astar,   (void**)&c->d_fence,  (void**)&c->d_mc,        (void**)&c->d_prox,
                     (void**)&c->d_mres,    (void**)&c->d_odist,  (void**)&c->d_vdist,     (void**)&c->d_hcost[0],
                     (void**)&c->d_hcost[1], (void**)&c->d_hdist[0], (void**)&c->d_hdist[1], (void**)&c->d_hparent[0],
-                    (void**)&c->d_hparent[1], (void**)&c->d_hflags[0], (void**)&c->d_hflags[1] };
+                    (void**)&c->d_hparent[1], (void**)&c->d_hflags[0], (void**)&c->d_hflags[1], (void**)&c->d_hpacked };
   for (void** p : ptrs)
   {
     if (*p) cudaFree(*p);
@@ -228,6 +228,13 @@ extern "C" int ga_set_astar_params(ga_ctx* c, const ga_astar_params* p)
   GA_REQUIRE(c, p, GA_ERR_ARG, "null argument");
   GA_REQUIRE(c, p->vor_dim >= 8 && p->vor_dim <= 200, GA_ERR_ARG, "vor_dim out of range [8,200]");
   GA_REQUIRE(c, p->dt_variant == GA_DT_FIXEDPOINT || p->dt_variant == GA_DT_IPPFLOAT, GA_ERR_ARG, "dt_variant");
+  // every edge of the heuristic relaxation must cost more than nothing: with zero-cost edges g(n) == g(p) holds both
+  // ways, parent pointers could form cycles and the fixed point would not be unique
+  GA_REQUIRE(c, p->astar_movement_cost > 0 && p->astar_movement_cost < INFINITY, GA_ERR_ARG,
+             "astar_movement_cost must be positive and finite");
+  GA_REQUIRE(c, p->astar_lane_movement_cost > 0 && p->astar_lane_movement_cost < INFINITY, GA_ERR_ARG,
+             "astar_lane_movement_cost must be positive and finite");
+  GA_REQUIRE(c, p->astar_prox_cost >= 0 && p->unknown_cost_w >= 0, GA_ERR_ARG, "prox / unknown cost weights must be >= 0");
   c->ap = *p;
   c->have_ap = true;
   return GA_OK;
@@ -238,6 +245,36 @@ extern "C" int ga_set_astar_params(ga_ctx* c, const ga_astar_params* p)
 __global__ void fill_f64_kernel(double* p, size_t n, double v)
 {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+static int alloc_grids(ga_ctx* c, int patch_dim, int astar_dim)
+{
+  const size_t np = (size_t)patch_dim * patch_dim;
+  const size_t na = (size_t)astar_dim * astar_dim;
+  c->patch_dim = patch_dim;
+  c->astar_dim = astar_dim;
+  {
+    const size_t nv = (size_t)c->ap.vor_dim * c->ap.vor_dim;
+    GA_CUDA(c, cudaMalloc(&c->d_patch, np));
+    GA_CUDA(c, cudaMalloc(&c->d_safety, np));
+    GA_CUDA(c, cudaMalloc(&c->d_astar, na));
+    GA_CUDA(c, cudaMalloc(&c->d_fence, na));
+    GA_CUDA(c, cudaMalloc(&c->d_mc, na * 8));
+    GA_CUDA(c, cudaMalloc(&c->d_prox, na * 8));
+    GA_CUDA(c, cudaMalloc(&c->d_mres, na * 8));
+    GA_CUDA(c, cudaMalloc(&c->d_odist, nv * 4));
+    GA_CUDA(c, cudaMalloc(&c->d_vdist, nv * 4));
+    c->vor_alloc = c->ap.vor_dim;
+    GA_CUDA(c, cudaMalloc(&c->d_hpacked, na));
+    for (int s = 0; s < 2; ++s)
+    {
+      GA_CUDA(c, cudaMalloc(&c->d_hcost[s], na * 8));
+      GA_CUDA(c, cudaMalloc(&c->d_hdist[s], na * 8));
+      GA_CUDA(c, cudaMalloc(&c->d_hparent[s], na * 4));
+      GA_CUDA(c, cudaMalloc(&c->d_hflags[s], na));
+    }
+  }
+  return ga_heur_alloc(c);
 }
 
 extern "C" int ga_patch_reset(ga_ctx* c, int patch_dim)
@@ -253,28 +290,14 @@ extern "C" int ga_patch_reset(ga_ctx* c, int patch_dim)
   {
     GA_CUDA(c, cudaStreamSynchronize(c->stream));
     free_grids(c);
-    c->patch_dim = patch_dim;
-    c->astar_dim = astar_dim;
-    const size_t nv = (size_t)c->ap.vor_dim * c->ap.vor_dim;
-    GA_CUDA(c, cudaMalloc(&c->d_patch, np));
-    GA_CUDA(c, cudaMalloc(&c->d_safety, np));
-    GA_CUDA(c, cudaMalloc(&c->d_astar, na));
-    GA_CUDA(c, cudaMalloc(&c->d_fence, na));
-    GA_CUDA(c, cudaMalloc(&c->d_mc, na * 8));
-    GA_CUDA(c, cudaMalloc(&c->d_prox, na * 8));
-    GA_CUDA(c, cudaMalloc(&c->d_mres, na * 8));
-    GA_CUDA(c, cudaMalloc(&c->d_odist, nv * 4));
-    GA_CUDA(c, cudaMalloc(&c->d_vdist, nv * 4));
-    c->vor_alloc = c->ap.vor_dim;
-    for (int s = 0; s < 2; ++s)
+    const int rc = alloc_grids(c, patch_dim, astar_dim);
+    if (rc != GA_OK)
     {
-      GA_CUDA(c, cudaMalloc(&c->d_hcost[s], na * 8));
-      GA_CUDA(c, cudaMalloc(&c->d_hdist[s], na * 8));
-      GA_CUDA(c, cudaMalloc(&c->d_hparent[s], na * 4));
-      GA_CUDA(c, cudaMalloc(&c->d_hflags[s], na));
+      // a half-built context must not look sized: the next reset allocates from scratch
+      free_grids(c);
+      c->patch_dim = c->astar_dim = c->vor_alloc = 0;
+      return rc;
     }
-    int rc = ga_heur_alloc(c);
-    if (rc) return rc;
   }
   const size_t nv = (size_t)c->ap.vor_dim * c->ap.vor_dim;
   GA_CUDA(c, cudaMemsetAsync(c->d_patch, GA_SENSOR_UNKNOWN, np, c->stream));
@@ -303,6 +326,35 @@ extern "C" int ga_patch_dim(const ga_ctx* c) { return c ? c->patch_dim : GA_ERR_
 extern "C" int ga_astar_dim(const ga_ctx* c) { return c ? c->astar_dim : GA_ERR_ARG; }
 extern "C" int ga_cart_dim(const ga_ctx* c) { return c ? c->cart_dim : GA_ERR_ARG; }
 
+// GA_GRID_HEUR_PACKED: one byte per cell for consumers that only need membership and the parent chain
+// (getAstarPath, findValidNeighborIndex, OUT_OF_HEURISTIC tests): bits 0-3 = index i of motion_ (a_star.hpp:50-52)
+// with parent = cell - motion_[i], 8 = root, 15 = none; bit 4 = in the closed set; bit 5 = is_unknown_
+__global__ void heur_pack_kernel(const int32_t* __restrict__ parent, const uint8_t* __restrict__ flags, uint8_t* __restrict__ out,
+                                 int dim)
+{
+  const int n = dim * dim;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x)
+  {
+    const uint8_t f = flags[c];
+    unsigned code = 15;
+    if (f & GA_H_CLOSED)
+    {
+      const int p = parent[c];
+      if (p == -1)
+        code = 8;
+      else if (p >= 0)
+      {
+        const int dx = c % dim - p % dim, dy = c / dim - p / dim;  // motion_[i] = (dx, dy)
+        // { 1, 0 }, { 0, 1 }, { -1, 0 }, { 0, -1 }, { -1, -1 }, { -1, 1 }, { 1, -1 }, { 1, 1 }
+        const int key = (dy + 1) * 3 + (dx + 1);
+        const unsigned lut[9] = { 4, 3, 6, 2, 15, 0, 5, 1, 7 };
+        code = (dx >= -1 && dx <= 1 && dy >= -1 && dy <= 1) ? lut[key] : 15;
+      }
+    }
+    out[c] = (uint8_t)(code | ((f & GA_H_CLOSED) ? 16u : 0u) | ((f & GA_H_UNKNOWN) ? 32u : 0u));
+  }
+}
+
 static int grid_lookup(const ga_ctx* c, int id, void** p, size_t* bytes)
 {
   const size_t np = (size_t)c->patch_dim * c->patch_dim;
@@ -325,6 +377,7 @@ static int grid_lookup(const ga_ctx* c, int id, void** p, size_t* bytes)
     case GA_GRID_HEUR_DIST: case GA_GRID_HEUR_DIST + 1: *p = c->d_hdist[id - GA_GRID_HEUR_DIST]; *bytes = na * 8; return 0;
     case GA_GRID_HEUR_PARENT: case GA_GRID_HEUR_PARENT + 1: *p = c->d_hparent[id - GA_GRID_HEUR_PARENT]; *bytes = na * 4; return 0;
     case GA_GRID_HEUR_FLAGS: case GA_GRID_HEUR_FLAGS + 1: *p = c->d_hflags[id - GA_GRID_HEUR_FLAGS]; *bytes = na; return 0;
+    case GA_GRID_HEUR_PACKED: case GA_GRID_HEUR_PACKED + 1: *p = c->d_hpacked; *bytes = na; return 0;
     default: return -1;
   }
 }
@@ -355,6 +408,20 @@ extern "C" int ga_upload(ga_ctx* c, int grid_id, const void* src, size_t bytes)
   size_t b;
   GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");
   GA_REQUIRE(c, b == bytes, GA_ERR_ARG, "size mismatch");
+  if (grid_id == GA_GRID_MOVEMENT_COST || grid_id == GA_GRID_H_PROX)
+  {
+    // the heuristic relaxation needs strictly positive movement costs and non-negative proximity costs (NaN is
+    // kept: the reference's 0/0 of setCostmapValue, a_star.cpp:492-502)
+    const double* v = static_cast<const double*>(src);
+    const size_t n = bytes / sizeof(double);
+    bool ok = true;
+    if (grid_id == GA_GRID_MOVEMENT_COST)
+      for (size_t i = 0; i < n && ok; ++i) ok = v[i] > 0 && v[i] < INFINITY;
+    else
+      for (size_t i = 0; i < n && ok; ++i) ok = !(v[i] < 0);
+    GA_REQUIRE(c, ok, GA_ERR_ARG,
+               grid_id == GA_GRID_MOVEMENT_COST ? "movement costs must be positive and finite" : "proximity costs must not be negative");
+  }
   GA_CUDA(c, cudaSetDevice(c->device));
   GA_CUDA(c, cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, c->stream));
   // pageable sources are staged by the driver before the call returns; pinned ones are the
@@ -372,6 +439,12 @@ extern "C" int ga_download(ga_ctx* c, int grid_id, void* dst, size_t bytes)
   GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");
   GA_REQUIRE(c, b == bytes, GA_ERR_ARG, "size mismatch");
   GA_CUDA(c, cudaSetDevice(c->device));
+  if (grid_id == GA_GRID_HEUR_PACKED || grid_id == GA_GRID_HEUR_PACKED + 1)
+  {
+    const int slot = grid_id - GA_GRID_HEUR_PACKED;
+    ga_launch_scope ls(c, GA_K_HEUR_FINISH);
+    heur_pack_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(c->d_hparent[slot], c->d_hflags[slot], c->d_hpacked, c->astar_dim);
+  }
   GA_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
   GA_CUDA(c, cudaStreamSynchronize(c->stream));
   return GA_OK;
@@ -412,6 +485,12 @@ extern "C" int ga_download_async(ga_ctx* c, int grid_id, void* dst, size_t bytes
   GA_REQUIRE(c, grid_lookup(c, grid_id, &p, &b) == 0, GA_ERR_ARG, "unknown grid id");
   GA_REQUIRE(c, b == bytes, GA_ERR_ARG, "size mismatch");
   GA_CUDA(c, cudaSetDevice(c->device));
+  if (grid_id == GA_GRID_HEUR_PACKED || grid_id == GA_GRID_HEUR_PACKED + 1)
+  {
+    const int slot = grid_id - GA_GRID_HEUR_PACKED;
+    ga_launch_scope ls(c, GA_K_HEUR_FINISH);
+    heur_pack_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(c->d_hparent[slot], c->d_hflags[slot], c->d_hpacked, c->astar_dim);
+  }
   GA_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
   return GA_OK;
 }

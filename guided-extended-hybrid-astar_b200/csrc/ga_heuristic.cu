@@ -1041,8 +1041,10 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     a.tot[n] = make_int2(-1, -1);  // "not known yet" for finish B's shortcut
   }
   // chain walk inside the block (shared memory, one load per hop)
-  int cur = threadIdx.x, cs = 0, cd = 0;
-  for (int v = lpar; v >= 0; v = lp[cur])
+  // (hop cap: parent pointers cannot form a cycle while every edge weight is positive -- ga_set_astar_params and
+  // ga_upload enforce that -- the cap keeps a corrupted plane from hanging the kernel)
+  int cur = threadIdx.x, cs = 0, cd = 0, hops = 0;
+  for (int v = lpar; v >= 0 && hops < FB * FB; v = lp[cur], ++hops)
   {
     cd += v >> 10;
     cs += 1 - (v >> 10);
@@ -1062,9 +1064,10 @@ __global__ void __launch_bounds__(FIN_SLOTS) heur_finish_b_kernel(heur_args sing
   const int c = a.tlist[blockIdx.x * FIN_SLOTS + threadIdx.x];
   const long long* tot64 = reinterpret_cast<const long long*>(a.tot);
   int cur = c, cs = 0, cd = 0;
-  for (;;)
+  for (int hops = 0; hops < nbx * nbx * 4 + 8; ++hops)  // a chain crosses every block at most a few times
   {
     const int p = __ldg(a.parent + cur);
+    if (p < 0) break;  // no parent (cannot happen for a terminal of a consistent plane)
     const long long known = cur != c ? __ldcg(tot64 + cur) : -1;  // same dependency level as the parent load
     if ((int)(known & 0xFFFFFFFFll) >= 0)
     {

@@ -68,6 +68,7 @@ struct ga_ctx
   double* d_hdist[2] = { nullptr, nullptr };
   int32_t* d_hparent[2] = { nullptr, nullptr };
   uint8_t* d_hflags[2] = { nullptr, nullptr };
+  uint8_t* d_hpacked = nullptr;  // GA_GRID_HEUR_PACKED scratch (filled on demand by ga_download)
 
   // ---- accumulated map (Cartographing::patch_arr_ / temp_patch_)
   uint8_t* d_cart = nullptr;

@@ -231,6 +231,7 @@ extern "C" int ga_potential_sites(ga_ctx* c, int ego_x, int ego_y, int* xy, int 
   if (!c) return GA_ERR_ARG;
   GA_REQUIRE(c, c->patch_dim > 0 && c->have_ap, GA_ERR_STATE, "no patch / params");
   GA_REQUIRE(c, n_sites && cap >= 0 && (cap == 0 || xy), GA_ERR_ARG, "bad arguments");
+  GA_REQUIRE(c, c->ap.vor_dim == c->vor_alloc, GA_ERR_STATE, "vor_dim changed after the last ga_patch_reset: reset the patch first");
   int ox, oy;
   GA_REQUIRE(c, window_origin(c, ego_x, ego_y, &ox, &oy) == 0, GA_ERR_ARG, "potential window leaves the astar grid");
   GA_CUDA(c, cudaSetDevice(c->device));
@@ -266,6 +267,7 @@ extern "C" int ga_build_potential(ga_ctx* c, int ego_x, int ego_y, const int* vo
   if (!c) return GA_ERR_ARG;
   GA_REQUIRE(c, c->patch_dim > 0 && c->have_ap, GA_ERR_STATE, "no patch / params");
   GA_REQUIRE(c, n_vor >= 0 && (n_vor == 0 || vor_xy), GA_ERR_ARG, "bad arguments");
+  GA_REQUIRE(c, c->ap.vor_dim == c->vor_alloc, GA_ERR_STATE, "vor_dim changed after the last ga_patch_reset: reset the patch first");
   int ox, oy;
   GA_REQUIRE(c, window_origin(c, ego_x, ego_y, &ox, &oy) == 0, GA_ERR_ARG, "potential window leaves the astar grid");
   GA_CUDA(c, cudaSetDevice(c->device));

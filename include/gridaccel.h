@@ -74,7 +74,12 @@ typedef enum
   GA_GRID_HEUR_COST = 16,     /* f64 astar_dim^2   NodeDisc::cost_        (+inf = not in set) */
   GA_GRID_HEUR_DIST = 18,     /* f64 astar_dim^2   NodeDisc::cost_dist_                      */
   GA_GRID_HEUR_PARENT = 20,   /* i32 astar_dim^2   NodeDisc::parent_index_ (-1 root, -2 none) */
-  GA_GRID_HEUR_FLAGS = 22     /* u8  astar_dim^2   bit0 in closed set, bit1 is_unknown_       */
+  GA_GRID_HEUR_FLAGS = 22,    /* u8  astar_dim^2   bit0 in closed set, bit1 is_unknown_       */
+  /* download only: one byte per cell for callers that need membership and the parent chain but take costs from
+   * the device (getAstarPath a_star.cpp:386-421, findValidNeighborIndex :351-378, calcCost's OUT_OF_HEURISTIC test
+   * hybrid_a_star_lib.cpp:242-247): bits 0-3 = i with parent = cell - motion_[i] (a_star.hpp:50-52), 8 = root,
+   * 15 = none; bit 4 = closed; bit 5 = is_unknown_.  1 B/cell over PCIe instead of 21. */
+  GA_GRID_HEUR_PACKED = 24
 } ga_grid_id;
 
 enum { GA_H_CLOSED = 1, GA_H_UNKNOWN = 2 };

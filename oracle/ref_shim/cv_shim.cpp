@@ -5,6 +5,9 @@
 //   the plain-C oracle (gao_ellipse_rows / gao_distance_transform), dilate is a max over the
 //   kernel's in-image support written out below (row runs of the kernel, border ignored).
 #include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <new>
 
 #include "ga_oracle.h"
 #include "opencv2/imgproc.hpp"
@@ -12,6 +15,48 @@
 namespace cv
 {
 int shim_dt_variant = 0;
+
+// Matrix storage: uninitialised, and recycled through a small free list -- cv::Mat gets the same from malloc, which
+// hands a just-freed block back without touching the kernel.  (A value-initialised std::vector per temporary made the
+// element-wise ops of processSafetyPatch cost more in page faults than in arithmetic.)
+namespace
+{
+struct pool_t
+{
+  std::vector<std::pair<size_t, uchar*>> free_list;
+  ~pool_t()
+  {
+    for (auto& e : free_list) std::free(e.second);
+  }
+};
+pool_t& pool()
+{
+  static thread_local pool_t p;
+  return p;
+}
+}  // namespace
+std::shared_ptr<uchar> shim_alloc(size_t bytes)
+{
+  pool_t& p = pool();
+  uchar* buf = nullptr;
+  for (size_t i = 0; i < p.free_list.size(); ++i)
+    if (p.free_list[i].first == bytes)
+    {
+      buf = p.free_list[i].second;
+      p.free_list.erase(p.free_list.begin() + (long)i);
+      break;
+    }
+  if (!buf) buf = static_cast<uchar*>(std::malloc(bytes ? bytes : 1));
+  if (!buf) throw std::bad_alloc();
+  return std::shared_ptr<uchar>(buf, [bytes](uchar* q) {
+    pool_t& pp = pool();
+    if (pp.free_list.size() < 24)
+      pp.free_list.emplace_back(bytes, q);
+    else
+      std::free(q);
+  });
+}
+
 
 static void need_u8(const Mat& m, const char* who)
 {
@@ -33,8 +78,7 @@ Mat& Mat::setTo(double value, const Mat& mask)
   {
     uchar* d = ptr<uchar>(y);
     const uchar* m = mask.ptr<uchar>(y);
-    for (int x = 0; x < cols; ++x)
-      if (m[x]) d[x] = v;
+    for (int x = 0; x < cols; ++x) d[x] = m[x] ? v : d[x];  // select, not a branch: vectorises like OpenCV's copyMask
   }
   return *this;
 }
@@ -80,34 +124,47 @@ Mat operator-(double s, const Mat& m)
   {
     uchar* o = out.ptr<uchar>(y);
     const uchar* p = m.ptr<uchar>(y);
-    for (int x = 0; x < m.cols; ++x) o[x] = (uchar)std::clamp(s - (double)p[x], 0.0, 255.0);
+    if (s == std::floor(s) && s >= 0 && s <= 255)
+    {
+      const int si = (int)s;  // saturate_cast<uchar>(s - p) for an integral scalar: plain integer arithmetic (SIMD)
+      for (int x = 0; x < m.cols; ++x) o[x] = (uchar)(si > p[x] ? si - p[x] : 0);
+    }
+    else
+      for (int x = 0; x < m.cols; ++x) o[x] = (uchar)std::clamp(std::nearbyint(s - (double)p[x]), 0.0, 255.0);
   }
   return out;
 }
 
+// cv::compare(u8 Mat, scalar): the operator is chosen once, the row loops are byte compares (SIMD), as in OpenCV.
+// A u8 value compared with a scalar: v < t  <=>  v < ceil(t), v > t  <=>  v > floor(t) -- integer thresholds.
 void compare(const Mat& src, double value, Mat& dst, int cmpop)
 {
   need_u8(src, "compare");
   dst.create(src.rows, src.cols, CV_8UC1);
+  // reduce every operator to "lo <= v <= hi" on bytes (possibly negated): two byte compares per cell
+  const double fl = std::floor(value), ce = std::ceil(value);
+  int lo = 0, hi = 255;
+  bool negate = false;
+  switch (cmpop)
+  {
+    case CMP_EQ: lo = hi = (fl == value && value >= 0 && value <= 255) ? (int)value : -1; break;
+    case CMP_GT: lo = (int)std::clamp(fl + 1, 0.0, 256.0); break;
+    case CMP_GE: lo = (int)std::clamp(ce, 0.0, 256.0); break;
+    case CMP_LT: hi = (int)std::clamp(ce - 1, -1.0, 255.0); break;
+    case CMP_LE: hi = (int)std::clamp(fl, -1.0, 255.0); break;
+    default: lo = hi = (fl == value && value >= 0 && value <= 255) ? (int)value : -1; negate = true; break;
+  }
+  const bool none = lo > 255 || hi < 0 || lo > hi;
+  const uchar l8 = (uchar)std::clamp(lo, 0, 255), h8 = (uchar)std::clamp(hi, 0, 255);
+  const uchar yes = negate ? 0 : 255, no = negate ? 255 : 0;
   for (int y = 0; y < src.rows; ++y)
   {
-    const uchar* s = src.ptr<uchar>(y);
-    uchar* d = dst.ptr<uchar>(y);
-    for (int x = 0; x < src.cols; ++x)
-    {
-      const double v = s[x];
-      bool r = false;
-      switch (cmpop)
-      {
-        case CMP_EQ: r = v == value; break;
-        case CMP_GT: r = v > value; break;
-        case CMP_GE: r = v >= value; break;
-        case CMP_LT: r = v < value; break;
-        case CMP_LE: r = v <= value; break;
-        default: r = v != value; break;
-      }
-      d[x] = r ? 255 : 0;
-    }
+    const uchar* __restrict s = src.ptr<uchar>(y);
+    uchar* __restrict d = dst.ptr<uchar>(y);
+    if (none)
+      std::memset(d, no, (size_t)src.cols);
+    else
+      for (int x = 0; x < src.cols; ++x) d[x] = (s[x] >= l8 && s[x] <= h8) ? yes : no;
   }
 }
 
@@ -143,43 +200,54 @@ Mat getStructuringElement(int shape, Size ksize, Point anchor)
 
 // cv::dilate for a kernel whose rows are single centred runs (every MORPH_ELLIPSE kernel is): out-of-image taps
 // are ignored, i.e. the image is padded with 0.  In OpenCV's complexity class so that timing the reference through
-// this shim is fair: one horizontal running maximum (van Herk / Gil-Werman, ~3 comparisons per pixel whatever the
-// width) per DISTINCT run width -- 7 for the 21 x 21 disk -- into a plane each, then one vertical pass that takes
+// this shim is fair: one horizontal running maximum per DISTINCT run width -- 7 for the 21 x 21 disk -- into a plane
+// each (built by window doubling, SIMD byte maxima, see hmax_rows), then one vertical pass that takes
 // the maximum over the kernel rows of the plane belonging to each row's width (byte maxima, auto-vectorised).
 // Kernels with other row shapes fall back to a plain scan (not used by the reference).
-static void hmax_row(const uchar* in, uchar* out, int W, int hw, std::vector<uchar>& fwd, std::vector<uchar>& bwd)
+// Horizontal running maxima of one row for several half widths at once.  Windows are built by doubling:
+// M_1 = row, M_2[i] = max(M_1[i], M_1[i+1]), M_4[i] = max(M_2[i], M_2[i+2]) ... and a window of k cells starting at i
+// is max(M_p[i], M_p[i + k - p]) with p the largest power of two <= k.  Every pass is an element-wise byte maximum of
+// two shifted arrays, which the compiler turns into SIMD (pmaxub) -- the same cost class as OpenCV's row filters.
+struct hmax_scratch
 {
-  if (hw == 0)
+  std::vector<uchar> m[6];  // M_1 .. M_32, padded
+};
+static void hmax_rows(const uchar* in, int W, const std::vector<int>& half_widths, std::vector<uchar*>& out_rows, hmax_scratch& sc)
+{
+  const int P = 64;               // zero padding on both sides (>= the largest half width, keeps every index in range)
+  const int L = W + 2 * P;
+  for (auto& v : sc.m)
+    if ((int)v.size() != L) v.assign((size_t)L, 0);
+  uchar* __restrict m1 = sc.m[0].data();
+  std::memset(m1, 0, (size_t)P);
+  std::memcpy(m1 + P, in, (size_t)W);
+  std::memset(m1 + P + W, 0, (size_t)P);
+  int top = 0;                    // highest level built
+  int kmax = 1;
+  for (int hw : half_widths) kmax = std::max(kmax, 2 * hw + 1);
+  for (int lv = 1, p = 2; p <= kmax && lv < 6; ++lv, p <<= 1)
   {
-    std::memcpy(out, in, (size_t)W);
-    return;
+    const uchar* __restrict a = sc.m[lv - 1].data();
+    uchar* __restrict d = sc.m[lv].data();
+    const int sh = p >> 1, n = L - p + 1;
+    for (int i = 0; i < n; ++i) d[i] = std::max(a[i], a[i + sh]);
+    for (int i = n; i < L; ++i) d[i] = 0;
+    top = lv;
   }
-  const int k = 2 * hw + 1, P = hw;                 // window, zero padding on both sides
-  const int n = ((W + 2 * P + k - 1) / k) * k;      // padded length, a whole number of blocks
-  fwd.assign((size_t)n, 0);
-  bwd.assign((size_t)n, 0);
-  // padded signal p[i] = in[i - P]
-  for (int b0 = 0; b0 < n; b0 += k)
+  for (size_t v = 0; v < half_widths.size(); ++v)
   {
-    uchar m = 0;
-    for (int i = b0; i < b0 + k; ++i)
+    const int hw = half_widths[v], k = 2 * hw + 1;
+    int lv = 0, p = 1;
+    while (lv < top && p * 2 <= k)
     {
-      const int x = i - P;
-      const uchar v = (x >= 0 && x < W) ? in[x] : 0;
-      m = std::max(m, v);
-      fwd[(size_t)i] = m;
+      ++lv;
+      p <<= 1;
     }
-    m = 0;
-    for (int i = b0 + k - 1; i >= b0; --i)
-    {
-      const int x = i - P;
-      const uchar v = (x >= 0 && x < W) ? in[x] : 0;
-      m = std::max(m, v);
-      bwd[(size_t)i] = m;
-    }
+    const uchar* __restrict a = sc.m[lv].data() + (P - hw);
+    const uchar* __restrict b = a + (k - p);
+    uchar* __restrict d = out_rows[v];
+    for (int x = 0; x < W; ++x) d[x] = std::max(a[x], b[x]);
   }
-  // window of output x covers padded [x, x + k - 1]
-  for (int x = 0; x < W; ++x) out[x] = std::max(bwd[(size_t)x], fwd[(size_t)(x + k - 1)]);
 }
 
 void dilate(const Mat& src, Mat& dst, const Mat& kernel)
@@ -227,10 +295,20 @@ void dilate(const Mat& src, Mat& dst, const Mat& kernel)
   std::vector<int> widths;
   for (int hw : row_hw)
     if (hw >= 0 && std::find(widths.begin(), widths.end(), hw) == widths.end()) widths.push_back(hw);
-  std::vector<std::vector<uchar>> plane(widths.size(), std::vector<uchar>((size_t)H * W));
-  std::vector<uchar> fwd, bwd;
+  std::vector<std::shared_ptr<uchar>> plane_mem;
+  std::vector<uchar*> plane;
   for (size_t v = 0; v < widths.size(); ++v)
-    for (int y = 0; y < H; ++y) hmax_row(in.ptr<uchar>(y), plane[v].data() + (size_t)y * W, W, widths[v], fwd, bwd);
+  {
+    plane_mem.push_back(shim_alloc((size_t)H * W));
+    plane.push_back(plane_mem.back().get());
+  }
+  hmax_scratch sc;
+  std::vector<uchar*> rows(widths.size());
+  for (int y = 0; y < H; ++y)
+  {
+    for (size_t v = 0; v < widths.size(); ++v) rows[v] = plane[v] + (size_t)y * W;
+    hmax_rows(in.ptr<uchar>(y), W, widths, rows, sc);
+  }
   std::vector<int> row_plane((size_t)kh, -1);
   for (int j = 0; j < kh; ++j)
     if (row_hw[(size_t)j] >= 0)
@@ -243,7 +321,7 @@ void dilate(const Mat& src, Mat& dst, const Mat& kernel)
     {
       const int yy = y + j - ay;
       if (row_plane[(size_t)j] < 0 || yy < 0 || yy >= H) continue;
-      const uchar* __restrict p = plane[(size_t)row_plane[(size_t)j]].data() + (size_t)yy * W;
+      const uchar* __restrict p = plane[(size_t)row_plane[(size_t)j]] + (size_t)yy * W;
       for (int x = 0; x < W; ++x) d[x] = std::max(d[x], p[x]);
     }
   }

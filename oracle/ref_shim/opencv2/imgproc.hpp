@@ -46,13 +46,15 @@ enum { DIST_MASK_3 = 3, DIST_MASK_5 = 5 };
 template <typename T>
 using Ptr = std::shared_ptr<T>;
 
+std::shared_ptr<uchar> shim_alloc(size_t bytes);
+
 class Mat
 {
 public:
   int rows = 0, cols = 0, type_ = CV_8UC1;
   size_t step = 0;  // bytes per row
   uchar* data = nullptr;
-  std::shared_ptr<std::vector<uchar>> own;
+  std::shared_ptr<uchar> own;  // pooled, uninitialised storage (shim_alloc): temporaries are recycled as malloc does for OpenCV
 
   Mat() = default;
   Mat(int r, int c, int type) { create(r, c, type); }
@@ -64,12 +66,12 @@ public:
   void create(int r, int c, int type)
   {
     if (data && rows == r && cols == c && type_ == type) return;  // cv::Mat::create keeps a matching buffer
-    own = std::make_shared<std::vector<uchar>>((size_t)r * c * esz(type));
+    own = shim_alloc((size_t)r * c * esz(type));
     rows = r;
     cols = c;
     type_ = type;
     step = (size_t)c * esz(type);
-    data = own->data();
+    data = own.get();
   }
   template <typename T>
   T* ptr(int y) { return reinterpret_cast<T*>(data + (size_t)y * step); }

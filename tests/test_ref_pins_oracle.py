@@ -387,3 +387,29 @@ def test_valid_close_pose_vs_reference():
     assert n_found >= 4
     assert gr.valid_close_pose((100.0, 100.0, 0.0), np.zeros(0, np.int32)) is None
     assert go.valid_close_pose(safety, d["centers"], 3, prox, params, np.zeros(0, np.int32), (100.0, 100.0, 0.0)) is None
+
+
+def test_shim_dilate_is_in_opencvs_cost_class():
+    """the cv::dilate stand-in behind the reference's processSafetyPatch (oracle/ref_shim/cv_shim.cpp) is what the CPU
+    baseline of bench.py times: it has to be bit-identical to OpenCV and must not be slower than OpenCV by more than a
+    small factor, or the reported speed-ups would be inflated by checker code (round-1 verdict)."""
+    cv2 = pytest.importorskip("cv2")
+    import time
+    dim = 2048
+    gr.init(dim, veh=VEH)
+    patch = gen_map(dim, 20240)
+    gr.set_grid(gr.PATCH, patch)
+    gr.process_safety_patch()  # warm: buffers
+    t0 = time.perf_counter()
+    gr.process_safety_patch()
+    t_shim = time.perf_counter() - t0
+    thr = np.where(patch < 100, 0, np.where(patch > 130, 2, 1)).astype(np.uint8)
+    k = cv2.getStructuringElement(cv2.MORPH_ELLIPSE, (21, 21))
+    cv2.setNumThreads(1)
+    cv2.dilate(thr, k)
+    t0 = time.perf_counter()
+    want = cv2.dilate(thr, k)
+    t_cv = time.perf_counter() - t0
+    assert np.array_equal(gr.get_grid(gr.SAFETY), want)
+    # whole processSafetyPatch (8 element-wise passes + the dilation) against cv2.dilate alone
+    assert t_shim < 4.0 * t_cv + 0.02, (t_shim, t_cv)
