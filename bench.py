@@ -358,9 +358,29 @@ def run_plan_leg(args, local_rank, rank):
     procs, nq = args.plan_procs, args.plan_queries
     tmp = tempfile.mkdtemp(prefix="ga_plan_")
 
+    # Several planner PROCESSES on one GPU only run concurrently under CUDA MPS (otherwise the driver time-slices whole
+    # contexts and every launch waits for a slice).  One MPS control daemon per rank, restricted to the rank's GPU.
+    mps_env = None
+    if not args.no_mps and procs > 1:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = vis.split(",")[local_rank] if vis else str(local_rank)
+        cand = dict(os.environ, CUDA_VISIBLE_DEVICES=phys, CUDA_MPS_PIPE_DIRECTORY=os.path.join(tmp, "mps_pipe"),
+                    CUDA_MPS_LOG_DIRECTORY=os.path.join(tmp, "mps_log"))
+        os.makedirs(cand["CUDA_MPS_PIPE_DIRECTORY"], exist_ok=True)
+        os.makedirs(cand["CUDA_MPS_LOG_DIRECTORY"], exist_ok=True)
+        try:
+            r = subprocess.run(["nvidia-cuda-mps-control", "-d"], env=cand, capture_output=True, timeout=20)
+            if r.returncode == 0:
+                mps_env = cand
+        except (OSError, subprocess.TimeoutExpired):
+            mps_env = None
+
     def run_arm(arm, tag):
         ps = []
-        env = dict(os.environ, GA_DEVICE=str(local_rank))
+        if arm == "b200" and mps_env is not None:
+            env = dict(mps_env, GA_DEVICE="0")
+        else:
+            env = dict(os.environ, GA_DEVICE=str(local_rank))
         for w in range(procs):
             out = os.path.join(tmp, "%s_%d_%d.npz" % (tag, rank, w))
             cmd = [sys.executable, os.path.join(ROOT, "oracle", "ga_plan_py.py"), "--arm", arm, "--synthetic", "2048",
@@ -385,6 +405,12 @@ def run_plan_leg(args, local_rank, rank):
 
     out = {"workload": "%d planner processes x %d queries on synthetic 2048^2 maps (one map per process), shipped config" % (procs, nq),
            "b200": run_arm("b200", "b")}
+    out["b200"]["mps"] = mps_env is not None
+    if mps_env is not None:
+        try:
+            subprocess.run(["nvidia-cuda-mps-control"], input=b"quit\n", env=mps_env, capture_output=True, timeout=20)
+        except (OSError, subprocess.TimeoutExpired):
+            pass
     if rank == 0 and not args.no_cpu_baseline:
         out["cpu_reference"] = run_arm("ref", "a")
         out["cpu_reference"]["cores"] = procs
@@ -627,6 +653,8 @@ def main():
     ap.add_argument("--no-plan", action="store_true", help="skip the plan queries/s leg")
     ap.add_argument("--plan-procs", type=int, default=4, help="planner processes per GPU of the plan leg (fixed per GPU: weak scaling)")
     ap.add_argument("--plan-queries", type=int, default=6, help="queries per planner process of the plan leg")
+    ap.add_argument("--no-mps", action="store_true", help="plan leg: do not start a CUDA MPS daemon for the planner processes")
+    ap.add_argument("--plan-only", action="store_true", help="run only the plan leg (development)")
     ap.add_argument("--batch", type=int, default=128, help="queries of the batched-heuristic leg (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -637,6 +665,9 @@ def main():
 
     if args.impl == "reference":
         run_reference(args, rank)
+        return
+    if args.plan_only:
+        print(json.dumps(run_plan_leg(args, local_rank, rank)), flush=True)
         return
 
     import torch

@@ -82,6 +82,50 @@ __device__ __forceinline__ int check_pose_dev(const coll_view& v, double x, doub
   return 1;
 }
 
+// The same check for a pose whose coordinates may be off by a rounding error (device libm against glibc in a
+// rolled-out primitive): when x * con2gm, y * con2gm or yaw / res lies within eps of an integer the pose could fall
+// into either neighbouring cell / yaw bin; every combination is evaluated and *ambiguous is set when they disagree.
+__device__ __forceinline__ int check_cell_dev(const coll_view& v, int gx, int gy, int yi, int variant)
+{
+  const int* cen = v.centers + (size_t)yi * v.nb_disks * 2;
+  for (int k = 0; k < v.nb_disks; ++k)
+  {
+    const int px = cen[2 * k] + gx, py = cen[2 * k + 1] + gy;
+    if (px >= v.patch_dim || py >= v.patch_dim || px < 0 || py < 0)
+    {
+      if (variant) continue;
+      return 0;
+    }
+    if (v.safety[(size_t)py * v.patch_dim + px] == GA_OCC) return 0;
+  }
+  return 1;
+}
+
+__device__ __forceinline__ int check_pose_robust(const coll_view& v, double x, double y, double yaw, int variant, double eps,
+                                                 int* ambiguous)
+{
+  const double fx = x * GA_CON2GM, fy = y * GA_CON2GM;
+  const double fa = angle_0_2pi(yaw) / v.yaw_res_rad;
+  const int gx = (int)fx, gy = (int)fy;
+  int yi = (int)fa;
+  yi = yi < v.nb_yaws - 1 ? yi : v.nb_yaws - 1;
+  const int r0 = check_cell_dev(v, gx, gy, yi, variant);
+  const bool nx = fabs(fx - rint(fx)) < eps, ny = fabs(fy - rint(fy)) < eps, na = fabs(fa - rint(fa)) < eps;
+  if (nx | ny | na)
+  {
+    const int gx2 = (int)rint(fx) == gx ? gx - 1 : (int)rint(fx);
+    const int gy2 = (int)rint(fy) == gy ? gy - 1 : (int)rint(fy);
+    int ya = (int)rint(fa) == (int)fa ? (int)fa - 1 : (int)rint(fa);
+    ya = ya < 0 ? v.nb_yaws - 1 : (ya > v.nb_yaws - 1 ? v.nb_yaws - 1 : ya);
+    for (int m = 1; m < 8; ++m)
+    {
+      if (((m & 1) && !nx) || ((m & 2) && !ny) || ((m & 4) && !na)) continue;
+      if (check_cell_dev(v, (m & 1) ? gx2 : gx, (m & 2) ? gy2 : gy, (m & 4) ? ya : yi, variant) != r0) *ambiguous = 1;
+    }
+  }
+  return r0;
+}
+
 // ---- ga_check_poses ---------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256)
@@ -114,6 +158,60 @@ __global__ void fix_first_hit_kernel(int* p, int n)
   if (i < n && p[i] == INT_MAX) p[i] = -1;
 }
 
+// ---- low-latency path of ga_check_poses ----------------------------------------------------------
+// The serial search asks about ONE expansion at a time (26-32 primitives, <= a few hundred poses) and waits for the
+// answer, so a call costs latency, not throughput.  For such batches
+//   - the poses travel INSIDE the kernel's parameter block (up to 25 KB, sm_70+ accepts 32 KB): they reach the SM with
+//     the launch itself, no copy-engine operation and no PCIe read round trip;
+//   - one CTA does everything: one warp per segment (looping), lanes take 32 poses at a time in list order, the first
+//     ballot with a set bit gives the first colliding index -- no init / fix-up kernels, no atomics;
+//   - the answers are written to host memory the device maps, followed by a ticket word; the host spins on that word
+//     instead of entering the driver (cudaStreamSynchronize costs several microseconds by itself).
+template <int CAP>
+struct ll_params
+{
+  double x[CAP], y[CAP], yaw[CAP];
+  unsigned short seg[CAP / 4 + 2];
+  int n_seg, variant;
+  unsigned ticket;
+};
+struct ll_host  // mapped pinned memory
+{
+  int hit[1024];
+  volatile unsigned ticket;
+};
+
+template <int CAP>
+__global__ void __launch_bounds__(256) check_fan_kernel(coll_view v, const __grid_constant__ ll_params<CAP> p, ll_host* out)
+{
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int seg = warp; seg < p.n_seg; seg += 8)
+  {
+    const int s0 = p.seg[seg], s1 = p.seg[seg + 1];
+    int first = -1;
+    for (int base = s0; base < s1 && first < 0; base += 32)
+    {
+      const int i = base + lane;
+      int bad = 0;
+      if (i < s1) bad = !check_pose_dev(v, p.x[i], p.y[i], p.yaw[i], p.variant, nullptr);
+      const unsigned m = __ballot_sync(0xFFFFFFFFu, bad);
+      if (m) first = base - s0 + __ffs(m) - 1;
+    }
+    if (lane == 0) out->hit[seg] = first;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    __threadfence_system();
+    out->ticket = p.ticket;
+  }
+}
+
+template <int CAP>
+static int check_fan_launch(ga_ctx* c, const double* x, const double* y, const double* yaw, int n_poses, const int* seg_off,
+                            int n_seg, int variant, int* first_hit);
+
 static coll_view make_view(const ga_ctx* c)
 {
   coll_view v;
@@ -126,6 +224,52 @@ static coll_view make_view(const ga_ctx* c)
   return v;
 }
 
+template <int CAP>
+static int check_fan_launch(ga_ctx* c, const double* x, const double* y, const double* yaw, int n_poses, const int* seg_off,
+                            int n_seg, int variant, int* first_hit)
+{
+  if (!c->h_ll)
+  {
+    GA_CUDA(c, cudaHostAlloc(&c->h_ll, sizeof(ll_host), cudaHostAllocMapped));
+    GA_CUDA(c, cudaHostGetDevicePointer(&c->d_ll, c->h_ll, 0));
+    static_cast<ll_host*>(c->h_ll)->ticket = 0;
+  }
+  static_assert(sizeof(ll_params<CAP>) + sizeof(coll_view) + 16 < 32764, "kernel parameter block too large");
+  ll_params<CAP> p;
+  memcpy(p.x, x, sizeof(double) * (size_t)n_poses);
+  memcpy(p.y, y, sizeof(double) * (size_t)n_poses);
+  memcpy(p.yaw, yaw, sizeof(double) * (size_t)n_poses);
+  for (int s = 0; s <= n_seg; ++s) p.seg[s] = (unsigned short)seg_off[s];
+  p.n_seg = n_seg;
+  p.variant = variant;
+  p.ticket = ++c->ll_ticket;
+  if (p.ticket == 0) p.ticket = ++c->ll_ticket;
+  ll_host* hb = static_cast<ll_host*>(c->h_ll);
+  {
+    ga_launch_scope ls(c, GA_K_COLLISION);
+    check_fan_kernel<CAP><<<1, 256, 0, c->stream>>>(make_view(c), p, static_cast<ll_host*>(c->d_ll));
+  }
+  GA_CUDA(c, cudaGetLastError());
+  // wait for the ticket word; look at the stream now and then so that a failed launch cannot hang the caller
+  for (unsigned long long spins = 0; hb->ticket != p.ticket; ++spins)
+  {
+    if ((spins & 0xFFFFF) == 0xFFFFF)
+    {
+      const cudaError_t q = cudaStreamQuery(c->stream);
+      if (q != cudaErrorNotReady && hb->ticket != p.ticket)
+      {
+        if (q == cudaSuccess) break;  // finished: the store is visible after the stream is idle
+        return ga_fail(c, GA_ERR_CUDA, "%s: %s", __func__, cudaGetErrorString(q));
+      }
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+  memcpy(first_hit, hb->hit, sizeof(int) * (size_t)n_seg);
+  return GA_OK;
+}
+
 extern "C" int ga_check_poses(ga_ctx* c, const double* x, const double* y, const double* yaw, int n_poses,
                               const int* seg_off, int n_seg, int variant, int* first_hit)
 {
@@ -136,6 +280,8 @@ extern "C" int ga_check_poses(ga_ctx* c, const double* x, const double* y, const
   if (n_seg == 0) return GA_OK;
   GA_REQUIRE(c, seg_off[0] == 0 && seg_off[n_seg] == n_poses, GA_ERR_ARG, "seg_off must span [0, n_poses]");
   GA_CUDA(c, cudaSetDevice(c->device));
+  if (n_poses <= 256 && n_seg <= 64) return check_fan_launch<256>(c, x, y, yaw, n_poses, seg_off, n_seg, variant, first_hit);
+  if (n_poses <= 1024 && n_seg <= 256) return check_fan_launch<1024>(c, x, y, yaw, n_poses, seg_off, n_seg, variant, first_hit);
   // staging layout: x | y | yaw | seg_off | first_hit
   const size_t b_pose = sizeof(double) * (size_t)n_poses;
   const size_t b_seg = sizeof(int) * (size_t)(n_seg + 1);
@@ -320,12 +466,84 @@ struct expand_view
 
 // one thread per (node, primitive); primitives in the reference's order: steer-major,
 // direction +1 then -1 (direction_inputs_, hybrid_a_star_lib.hpp:50), then the rear-axis deltas
+// successor epilogue (optional): the grid reads the serial search makes per successor, done where the grids live
+struct expand_epilogue
+{
+  const double* hcost;   // closed-set cost_ plane of the chosen slot
+  const double* hdist;   // cost_dist_ plane
+  const uint8_t* hflags;
+  const double* mc;      // movement_cost_map_
+  const double* mres;    // motion_res_map_
+  ga_succ_cost* out;     // per (node, primitive), nullptr = no epilogue
+  double* parent_prox;   // per node
+  prox_args pa;          // h_prox_arr_ + vehicle corners
+};
+
+// completion signal of an asynchronous launch: the last CTA to finish writes the ticket into mapped host memory
+struct expand_done
+{
+  unsigned* counter;          // device memory, zero between launches
+  volatile unsigned* flag;    // mapped host memory (nullptr: synchronous launch, nothing to signal)
+  unsigned ticket;
+};
+
+__device__ __forceinline__ void expand_one(const coll_view& v, const expand_view& e, const expand_epilogue& ep,
+                                           const ga_node* __restrict__ nodes, ga_succ* __restrict__ out, long long t);
+
 __global__ void __launch_bounds__(128)
-expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int n_nodes, ga_succ* __restrict__ out)
+expand_kernel(coll_view v, expand_view e, expand_epilogue ep, const ga_node* __restrict__ nodes, int n_nodes,
+              ga_succ* __restrict__ out, expand_done done)
 {
   const int stride = 2 * e.nb_steer + e.n_ra;
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (t >= (long long)n_nodes * stride) return;
+  if (t < (long long)n_nodes * stride) expand_one(v, e, ep, nodes, out, t);
+  if (done.flag)
+  {
+    __threadfence_system();  // this thread's results are visible to the host before the CTA reports
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+      if (atomicAdd(done.counter, 1u) == gridDim.x - 1)
+      {
+        *done.counter = 0;
+        __threadfence_system();
+        *done.flag = done.ticket;
+      }
+    }
+  }
+}
+
+// kernel-parameter variant for the few nodes of one search step (the nodes travel with the launch)
+#define GA_EXPAND_ASYNC_MAX 32
+struct expand_nodes_param
+{
+  ga_node n[GA_EXPAND_ASYNC_MAX];
+};
+__global__ void __launch_bounds__(128)
+expand_param_kernel(coll_view v, expand_view e, const __grid_constant__ expand_nodes_param nodes, int n_nodes,
+                    ga_succ* __restrict__ out, expand_done done)
+{
+  const int stride = 2 * e.nb_steer + e.n_ra;
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  expand_epilogue ep{};
+  if (t < (long long)n_nodes * stride) expand_one(v, e, ep, nodes.n, out, t);
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    if (atomicAdd(done.counter, 1u) == gridDim.x - 1)
+    {
+      *done.counter = 0;
+      __threadfence_system();
+      *done.flag = done.ticket;
+    }
+  }
+}
+
+__device__ __forceinline__ void expand_one(const coll_view& v, const expand_view& e, const expand_epilogue& ep,
+                                           const ga_node* __restrict__ nodes, ga_succ* __restrict__ out, long long t)
+{
+  const int stride = 2 * e.nb_steer + e.n_ra;
   const int node = (int)(t / stride);
   const int k = (int)(t % stride);
   const ga_node nd = nodes[node];
@@ -335,10 +553,13 @@ expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int
   s.n_poses = 0;
   s.valid = 0;
   s.near_cell_edge = 0;
-  for (int i = 0; i < 6; ++i) s.pad_[i] = 0;
+  s.collision_free = 0;
+  s.collision_ambiguous = 0;
+  for (int i = 0; i < 4; ++i) s.pad_[i] = 0;
 
   double x = nd.x, y = nd.y, yaw = nd.yaw;
   double margin = 1.0, m;
+  int amb = 0;
   if (k < 2 * e.nb_steer)
   {
     // calcNextNode (hybrid_a_star_lib.cpp:427-483)
@@ -360,9 +581,11 @@ expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int
       {
         ok = check_pose_dev(v, x, y, yaw, 0, &m);
         margin = fmin(margin, m);
+        if (m < GA_EDGE_EPS) check_pose_robust(v, x, y, yaw, 0, GA_EDGE_EPS, &amb);
       }
     }
     s.n_poses = n;
+    s.collision_free = (uint8_t)ok;
     if (n > 0)
     {
       // mapCont2Disc (:410-417)
@@ -396,6 +619,7 @@ expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int
       {
         ok = check_pose_dev(v, x, y, prev_yaw, 0, &m);
         margin = fmin(margin, m);
+        if (m < GA_EDGE_EPS) check_pose_robust(v, x, y, prev_yaw, 0, GA_EDGE_EPS, &amb);
       }
       yaw = angle_mpi_pi(yaw + sg * res);
       prev_yaw = yaw;
@@ -408,9 +632,11 @@ expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int
     {
       ok = check_pose_dev(v, x, y, goal_yaw, 0, &m);
       margin = fmin(margin, m);
+      if (m < GA_EDGE_EPS) check_pose_robust(v, x, y, goal_yaw, 0, GA_EDGE_EPS, &amb);
     }
     const double fa = goal_yaw * e.yaw_res_inv;
     s.n_poses = n;
+    s.collision_free = (uint8_t)ok;
     s.yaw = goal_yaw;
     s.xi = (int)(x * GA_CON2STAR);
     s.yi = (int)(y * GA_CON2STAR);
@@ -419,27 +645,37 @@ expand_kernel(coll_view v, expand_view e, const ga_node* __restrict__ nodes, int
     s.valid = (uint8_t)ok;
   }
   s.near_cell_edge = (uint8_t)(margin < GA_EDGE_EPS);
+  s.collision_ambiguous = (uint8_t)amb;
   out[t] = s;
+  if (ep.out)
+  {
+    // calcCost's heuristic lookup (hybrid_a_star_lib.cpp:242-250), getPathCosts' movement weight (:324), the
+    // successor's own motion resolution (:1483), getDistance2goal's cost_dist_ (:781-798)
+    ga_succ_cost c;
+    c.heur_cost = GA_OUT_OF_HEURISTIC;
+    c.heur_dist = GA_OUT_OF_HEURISTIC;
+    c.movement_cost = 0.0;
+    c.motion_res = 0.0;
+    const bool on_grid = s.n_poses > 0 && (-1 < s.xi && s.xi < e.astar_dim) && (-1 < s.yi && s.yi < e.astar_dim);
+    if (on_grid)
+    {
+      const size_t cell = (size_t)s.yi * e.astar_dim + s.xi;
+      if (ep.hflags[cell] & GA_H_CLOSED)
+      {
+        c.heur_cost = ep.hcost[cell];
+        c.heur_dist = ep.hdist[cell];
+      }
+      c.movement_cost = ep.mc[cell];
+      c.motion_res = ep.mres[cell];
+    }
+    ep.out[t] = c;
+    // getProxOfCorners(parent pose * con2star_) (:335-336): one value per node, the same for all its primitives
+    if (k == 0) ep.parent_prox[node] = prox_of_corners(nd.x, nd.y, nd.yaw, ep.pa);
+  }
 }
 
-extern "C" int ga_expand(ga_ctx* c, const ga_node* nodes, int n_nodes, ga_succ* out)
+static expand_view make_expand_view(const ga_ctx* c)
 {
-  if (!c) return GA_ERR_ARG;
-  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp && c->have_ep, GA_ERR_STATE, "no patch / params");
-  GA_REQUIRE(c, n_nodes >= 0 && (n_nodes == 0 || (nodes && out)), GA_ERR_ARG, "bad arguments");
-  if (n_nodes == 0) return GA_OK;
-  GA_CUDA(c, cudaSetDevice(c->device));
-  const int stride = 2 * c->ep.nb_steer + c->n_ra;
-  const size_t b_in = sizeof(ga_node) * (size_t)n_nodes;
-  const size_t b_out = sizeof(ga_succ) * (size_t)n_nodes * stride;
-  const size_t off_out = (b_in + 63) & ~(size_t)63;
-  int rc = ga_stage_reserve(c, off_out + b_out);
-  if (rc) return rc;
-  GA_CUDA(c, cudaStreamSynchronize(c->stream));
-  char* h = (char*)c->h_stage;
-  char* d = (char*)c->d_stage;
-  memcpy(h, nodes, b_in);
-  GA_CUDA(c, cudaMemcpyAsync(d, h, b_in, cudaMemcpyHostToDevice, c->stream));
   expand_view e;
   memcpy(e.steer, c->steer, sizeof(e.steer));
   memcpy(e.ra_delta, c->ra_delta, sizeof(e.ra_delta));
@@ -450,15 +686,194 @@ extern "C" int ga_expand(ga_ctx* c, const ga_node* nodes, int n_nodes, ga_succ* 
   e.nb_steer = c->ep.nb_steer;
   e.n_ra = c->n_ra;
   e.astar_dim = c->astar_dim;
+  return e;
+}
+
+static int expand_impl(ga_ctx* c, const ga_node* nodes, int n_nodes, ga_succ* out, int slot, ga_succ_cost* out_cost,
+                       double* out_parent_prox)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp && c->have_ep, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, n_nodes >= 0 && (n_nodes == 0 || (nodes && out)), GA_ERR_ARG, "bad arguments");
+  const bool epi = out_cost != nullptr;
+  if (epi)
+  {
+    GA_REQUIRE(c, slot == 0 || slot == 1, GA_ERR_ARG, "slot must be 0 (guidance) or 1 (path)");
+    GA_REQUIRE(c, out_parent_prox != nullptr, GA_ERR_ARG, "out_parent_prox is NULL");
+    GA_REQUIRE(c, c->have_pp, GA_ERR_STATE, "ga_set_prox_params first (vehicle corners of getProxOfCorners)");
+  }
+  if (n_nodes == 0) return GA_OK;
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int stride = 2 * c->ep.nb_steer + c->n_ra;
+  const size_t b_in = sizeof(ga_node) * (size_t)n_nodes;
+  const size_t b_out = sizeof(ga_succ) * (size_t)n_nodes * stride;
+  const size_t b_cost = epi ? sizeof(ga_succ_cost) * (size_t)n_nodes * stride : 0;
+  const size_t b_prox = epi ? sizeof(double) * (size_t)n_nodes : 0;
+  const size_t off_out = (b_in + 63) & ~(size_t)63;
+  const size_t off_cost = (off_out + b_out + 63) & ~(size_t)63;
+  const size_t off_prox = (off_cost + b_cost + 63) & ~(size_t)63;
+  int rc = ga_stage_reserve(c, off_prox + b_prox);
+  if (rc) return rc;
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  char* h = (char*)c->h_stage;
+  char* d = (char*)c->d_stage;
+  memcpy(h, nodes, b_in);
+  GA_CUDA(c, cudaMemcpyAsync(d, h, b_in, cudaMemcpyHostToDevice, c->stream));
+  const expand_view e = make_expand_view(c);
+  expand_epilogue ep{};
+  if (epi)
+  {
+    ep.hcost = c->d_hcost[slot];
+    ep.hdist = c->d_hdist[slot];
+    ep.hflags = c->d_hflags[slot];
+    ep.mc = c->d_mc;
+    ep.mres = c->d_mres;
+    ep.out = (ga_succ_cost*)(d + off_cost);
+    ep.parent_prox = (double*)(d + off_prox);
+    ep.pa.grid = c->d_prox;
+    ep.pa.dim = c->astar_dim;
+    ep.pa.p = c->pp;
+  }
   {
     ga_launch_scope ls(c, GA_K_EXPAND);
     const long long threads = (long long)n_nodes * stride;
-    expand_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, c->stream>>>(make_view(c), e, (const ga_node*)d, n_nodes,
-                                                                            (ga_succ*)(d + off_out));
+    expand_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, c->stream>>>(make_view(c), e, ep, (const ga_node*)d, n_nodes,
+                                                                            (ga_succ*)(d + off_out), expand_done{});
   }
   GA_CUDA(c, cudaGetLastError());
-  GA_CUDA(c, cudaMemcpyAsync(h + off_out, d + off_out, b_out, cudaMemcpyDeviceToHost, c->stream));
+  // results are contiguous in the staging area: one copy back
+  GA_CUDA(c, cudaMemcpyAsync(h + off_out, d + off_out, (off_prox + b_prox) - off_out, cudaMemcpyDeviceToHost, c->stream));
   GA_CUDA(c, cudaStreamSynchronize(c->stream));
   memcpy(out, h + off_out, b_out);
+  if (epi)
+  {
+    memcpy(out_cost, h + off_cost, b_cost);
+    memcpy(out_parent_prox, h + off_prox, b_prox);
+  }
+  return GA_OK;
+}
+
+extern "C" int ga_expand(ga_ctx* c, const ga_node* nodes, int n_nodes, ga_succ* out)
+{
+  return expand_impl(c, nodes, n_nodes, out, 0, nullptr, nullptr);
+}
+
+extern "C" int ga_expand_ex(ga_ctx* c, const ga_node* nodes, int n_nodes, int slot, ga_succ* out, ga_succ_cost* out_cost,
+                            double* out_parent_prox)
+{
+  if (c && !out_cost) return ga_fail(c, GA_ERR_ARG, "%s: %s", __func__, "out_cost is NULL (use ga_expand)");
+  return expand_impl(c, nodes, n_nodes, out, slot, out_cost, out_parent_prox);
+}
+
+// ---- asynchronous expansion (submit / collect) ------------------------------------------------------
+// For a caller that knows which nodes it will expand NEXT (the successors it has just created): the launch returns at
+// once, the results arrive in mapped host memory while the caller goes on with its own work, and are picked up when
+// the node is actually expanded.  Nodes travel in the kernel's parameter block, results are written straight to host
+// memory, completion is a ticket word the host polls: no copy-engine operation and no driver call on the wait side.
+#define GA_ASYNC_RING 4
+struct expand_async_state
+{
+  ga_succ* h_out[GA_ASYNC_RING];  // mapped pinned, GA_EXPAND_ASYNC_MAX * stride entries each
+  ga_succ* d_out[GA_ASYNC_RING];
+  volatile unsigned* h_flag;      // GA_ASYNC_RING ticket words (mapped)
+  unsigned* d_flag;
+  unsigned* d_counter;            // GA_ASYNC_RING CTA counters (device)
+  unsigned ticket[GA_ASYNC_RING];
+  int n_nodes[GA_ASYNC_RING];
+  int stride;
+  unsigned next_ticket;
+  int next_slot;
+};
+
+void ga_expand_async_free(ga_ctx* c)
+{
+  expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
+  if (!a) return;
+  for (int i = 0; i < GA_ASYNC_RING; ++i)
+    if (a->h_out[i]) cudaFreeHost(a->h_out[i]);
+  if (a->h_flag) cudaFreeHost((void*)a->h_flag);
+  if (a->d_counter) cudaFree(a->d_counter);
+  delete a;
+  c->expand_async = nullptr;
+}
+
+extern "C" int ga_expand_submit(ga_ctx* c, const ga_node* nodes, int n_nodes, int* ticket)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp && c->have_ep, GA_ERR_STATE, "no patch / params");
+  GA_REQUIRE(c, nodes && ticket && n_nodes >= 1 && n_nodes <= GA_EXPAND_ASYNC_MAX, GA_ERR_ARG, "1 .. 32 nodes per submission");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  const int stride = 2 * c->ep.nb_steer + c->n_ra;
+  expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
+  if (a && a->stride != stride)
+  {
+    GA_CUDA(c, cudaStreamSynchronize(c->stream));
+    ga_expand_async_free(c);
+    a = nullptr;
+  }
+  if (!a)
+  {
+    a = new expand_async_state();
+    memset(a, 0, sizeof(*a));
+    c->expand_async = a;
+    a->stride = stride;
+    for (int i = 0; i < GA_ASYNC_RING; ++i)
+    {
+      GA_CUDA(c, cudaHostAlloc((void**)&a->h_out[i], sizeof(ga_succ) * GA_EXPAND_ASYNC_MAX * (size_t)stride, cudaHostAllocMapped));
+      GA_CUDA(c, cudaHostGetDevicePointer((void**)&a->d_out[i], a->h_out[i], 0));
+    }
+    GA_CUDA(c, cudaHostAlloc((void**)&a->h_flag, sizeof(unsigned) * GA_ASYNC_RING, cudaHostAllocMapped));
+    GA_CUDA(c, cudaHostGetDevicePointer((void**)&a->d_flag, (void*)a->h_flag, 0));
+    for (int i = 0; i < GA_ASYNC_RING; ++i) a->h_flag[i] = 0;
+    GA_CUDA(c, cudaMalloc(&a->d_counter, sizeof(unsigned) * GA_ASYNC_RING));
+    GA_CUDA(c, cudaMemsetAsync(a->d_counter, 0, sizeof(unsigned) * GA_ASYNC_RING, c->stream));
+  }
+  const int slot = a->next_slot;
+  // the slot's previous submission must have been collected or at least be complete before it is reused
+  if (a->ticket[slot] && a->h_flag[slot] != a->ticket[slot]) GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  a->next_slot = (slot + 1) % GA_ASYNC_RING;
+  unsigned tk = ++a->next_ticket;
+  if (tk == 0) tk = ++a->next_ticket;
+  a->ticket[slot] = tk;
+  a->n_nodes[slot] = n_nodes;
+  expand_nodes_param p;
+  memcpy(p.n, nodes, sizeof(ga_node) * (size_t)n_nodes);
+  expand_done done{ a->d_counter + slot, a->d_flag + slot, tk };
+  {
+    ga_launch_scope ls(c, GA_K_EXPAND);
+    const int threads = n_nodes * stride;
+    expand_param_kernel<<<(threads + 127) / 128, 128, 0, c->stream>>>(make_view(c), make_expand_view(c), p, n_nodes, a->d_out[slot], done);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  *ticket = (int)((tk << 2) | (unsigned)slot);
+  return GA_OK;
+}
+
+extern "C" int ga_expand_collect(ga_ctx* c, int ticket, ga_succ* out, int* n_nodes)
+{
+  if (!c) return GA_ERR_ARG;
+  expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
+  GA_REQUIRE(c, a != nullptr && out != nullptr, GA_ERR_STATE, "nothing was submitted");
+  const int slot = ticket & 3;
+  const unsigned tk = (unsigned)ticket >> 2;
+  GA_REQUIRE(c, (a->ticket[slot] & 0x3FFFFFFFu) == tk, GA_ERR_ARG, "stale ticket: the ring slot was reused (at most 4 submissions in flight)");
+  const unsigned want = a->ticket[slot];
+  for (unsigned long long spins = 0; a->h_flag[slot] != want; ++spins)
+  {
+    if ((spins & 0xFFFFF) == 0xFFFFF)
+    {
+      const cudaError_t q = cudaStreamQuery(c->stream);
+      if (q != cudaErrorNotReady && a->h_flag[slot] != want)
+      {
+        if (q == cudaSuccess) break;
+        return ga_fail(c, GA_ERR_CUDA, "%s: %s", __func__, cudaGetErrorString(q));
+      }
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+  memcpy(out, a->h_out[slot], sizeof(ga_succ) * (size_t)a->n_nodes[slot] * a->stride);
+  if (n_nodes) *n_nodes = a->n_nodes[slot];
   return GA_OK;
 }

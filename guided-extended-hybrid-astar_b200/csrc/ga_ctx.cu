@@ -95,9 +95,11 @@ extern "C" int ga_destroy(ga_ctx* c)
   ga_cart_free(c);
   ga_rt_free(c);
   ga_reforder_free(c);
+  ga_expand_async_free(c);
   if (c->d_centers) cudaFree(c->d_centers);
   if (c->d_stage) cudaFree(c->d_stage);
   if (c->h_stage) cudaFreeHost(c->h_stage);
+  if (c->h_ll) cudaFreeHost(c->h_ll);
   for (auto& r : c->prof)
   {
     cudaEventDestroy(r.e0);

@@ -108,6 +108,10 @@ struct ga_ctx
   size_t h_stage_bytes = 0;
   void* d_stage = nullptr;
   size_t d_stage_bytes = 0;
+  void* h_ll = nullptr;  // mapped pinned buffer of the low-latency ga_check_poses path (host / device view)
+  void* d_ll = nullptr;
+  unsigned ll_ticket = 0;
+  void* expand_async = nullptr;  // ring of ga_expand_submit (ga_collision.cu)
 
   // ---- measurement
   bool prof_on = false;
@@ -153,5 +157,6 @@ int ga_heur_reforder_build(ga_ctx* ctx, int slot, const ga_heur_query* q, int* n
 void ga_heur_reforder_near(const ga_ctx* ctx, const int32_t** ids, const double** dist, int* n);
 void ga_heur_reforder_order(const ga_ctx* ctx, const int32_t** ids, int* n);
 void ga_reforder_free(ga_ctx* ctx);
+void ga_expand_async_free(ga_ctx* ctx);
 void ga_cart_free(ga_ctx* ctx);
 void ga_rt_free(ga_ctx* ctx);

@@ -49,8 +49,11 @@ NODE_DTYPE = np.dtype([("x", "f8"), ("y", "f8"), ("yaw", "f8"), ("motion_res", "
                        ("with_rear_axis", "i4"), ("pad_", "i4")])
 SUCC_DTYPE = np.dtype([("x", "f8"), ("y", "f8"), ("yaw", "f8"), ("xi", "i4"), ("yi", "i4"),
                        ("yawi", "i4"), ("n_poses", "i4"), ("valid", "u1"),
-                       ("near_cell_edge", "u1"), ("pad_", "u1", (6,))])
-assert NODE_DTYPE.itemsize == 40 and SUCC_DTYPE.itemsize == 48
+                       ("near_cell_edge", "u1"), ("collision_free", "u1"), ("collision_ambiguous", "u1"),
+                       ("pad_", "u1", (4,))])
+SUCC_COST_DTYPE = np.dtype([("heur_cost", "f8"), ("heur_dist", "f8"), ("movement_cost", "f8"), ("motion_res", "f8")])
+OUT_OF_HEURISTIC = 999999999.0
+assert NODE_DTYPE.itemsize == 40 and SUCC_DTYPE.itemsize == 48 and SUCC_COST_DTYPE.itemsize == 32
 
 # ga_grid_id
 GRID_PATCH, GRID_SAFETY, GRID_ASTAR, GRID_GEOFENCE, GRID_MOVEMENT_COST, GRID_H_PROX, \
@@ -89,6 +92,9 @@ SYMBOLS = {
     "ga_set_expand_params": (C.c_int, [_P, C.POINTER(ExpandParams)]),
     "ga_expand_stride": (C.c_int, [_P]),
     "ga_expand": (C.c_int, [_P, _P, C.c_int, _P]),
+    "ga_expand_submit": (C.c_int, [_P, _P, C.c_int, C.POINTER(C.c_int)]),
+    "ga_expand_collect": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int)]),
+    "ga_expand_ex": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P, _P]),
     "ga_set_astar_params": (C.c_int, [_P, C.POINTER(AstarParams)]),
     "ga_cart_reset": (C.c_int, [_P, C.c_int]),
     "ga_cartograph": (C.c_int, [_P, C.c_void_p, C.c_int, C.c_int, C.c_int]),

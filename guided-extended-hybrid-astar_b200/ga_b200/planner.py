@@ -329,6 +329,18 @@ class CollisionChecker:
         self.ctx.check(self.ctx.lib.ga_expand(self.ctx.h, _abi.ptr(nodes), len(nodes), _abi.ptr(out)))
         return out
 
+    def expandNodesWithCosts(self, nodes, for_path=True):
+        """ga_expand_ex: successors plus the grid reads the search makes per successor (heuristic cost_ / cost_dist_
+        of closed_set_path_ or closed_set_guidance_, movement_cost_map_, motion_res_map_) and getProxOfCorners of every
+        parent pose -- the planes stay on the device.  Needs HybridAStar(ctx, vehicle) (prox parameters)."""
+        nodes = np.ascontiguousarray(nodes, _abi.NODE_DTYPE)
+        out = np.zeros((len(nodes), self.expand_stride_), _abi.SUCC_DTYPE)
+        cost = np.zeros((len(nodes), self.expand_stride_), _abi.SUCC_COST_DTYPE)
+        prox = np.zeros(len(nodes))
+        self.ctx.check(self.ctx.lib.ga_expand_ex(self.ctx.h, _abi.ptr(nodes), len(nodes), 1 if for_path else 0, _abi.ptr(out),
+                                                 _abi.ptr(cost), _abi.ptr(prox)))
+        return out, cost, prox
+
 
 class Cartographing:
     """Mirror of the reference's Cartographing (LIB/include/cartographing_lib/cartographing.hpp:19-41,

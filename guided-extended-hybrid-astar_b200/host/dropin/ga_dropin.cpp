@@ -5,6 +5,7 @@
 #include "ga_dropin.hpp"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -95,7 +96,142 @@ int match_fan(const Fan& f, const std::vector<double>& x, const std::vector<doub
     if (is(k)) return k;
   return -1;
 }
+
+// ---- look-ahead: the fans of the nodes the search will expand next ----------------------------------------------
+// Every node the search expands (except the first) is a successor it created earlier.  When a node's fan has been
+// answered, its collision-free successors are handed to ga_expand_submit: the device rolls out and checks THEIR fans
+// while the host goes on with the search; the answers are waiting in host memory when one of them is popped.  The
+// device rollout uses its own libm (last-bit differences), so an answer is only trusted when no pose came within
+// 1e-9 cells / yaw bins of a boundary (ga_succ::near_cell_edge); the others are re-checked from the host's poses.
+struct PoseKey
+{
+  uint64_t x, y, yaw;
+  bool operator==(const PoseKey& o) const { return x == o.x && y == o.y && yaw == o.yaw; }
+};
+struct PoseKeyHash
+{
+  size_t operator()(const PoseKey& k) const
+  {
+    uint64_t h = k.x * 0x9E3779B97F4A7C15ull;
+    h ^= (k.y + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (k.yaw + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    return (size_t)h;
+  }
+};
+struct FanAnswers
+{
+  double motion_res;
+  int8_t ans[2 * NB_STEER];  // 0 collides, 1 free, 2 ask again (near a cell / yaw-bin edge)
+};
+std::unordered_map<PoseKey, FanAnswers, PoseKeyHash> g_lookahead;
+struct Pending
+{
+  bool in_flight = false;
+  int ticket = 0, n = 0;
+  PoseKey key[2 * NB_STEER];
+  double motion_res[2 * NB_STEER];
+} g_pending;
+bool g_lookahead_on = true;
+bool g_expand_params_set = false;
+double g_expand_arc_l = 0, g_yaw_res_deg = 10.0;
+std::vector<ga_succ> g_succ;
+
+inline PoseKey key_of(double x, double y, double yaw)
+{
+  PoseKey k;
+  std::memcpy(&k.x, &x, 8);
+  std::memcpy(&k.y, &y, 8);
+  std::memcpy(&k.yaw, &yaw, 8);
+  return k;
+}
+
+void lookahead_reset()
+{
+  if (g_pending.in_flight)
+  {
+    g_succ.resize((size_t)32 * (size_t)ga_expand_stride(ctx()));
+    ga_expand_collect(ctx(), g_pending.ticket, g_succ.data(), nullptr);  // drain; results are dropped
+    g_pending.in_flight = false;
+  }
+  g_lookahead.clear();
+}
+
+inline unsigned long long now_ns()
+{
+  return (unsigned long long)std::chrono::duration_cast<std::chrono::nanoseconds>(
+             std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+void lookahead_harvest()
+{
+  if (!g_pending.in_flight) return;
+  const unsigned long long t0 = now_ns();
+  const int stride = ga_expand_stride(ctx());
+  g_succ.resize((size_t)32 * (size_t)stride);
+  int n = 0;
+  check(ga_expand_collect(ctx(), g_pending.ticket, g_succ.data(), &n));
+  const unsigned long long t1 = now_ns();
+  g_stats.ns_collect += t1 - t0;
+  g_pending.in_flight = false;
+  if (g_lookahead.size() > (1u << 21)) g_lookahead.clear();
+  for (int j = 0; j < n && j < g_pending.n; ++j)
+  {
+    FanAnswers a;
+    a.motion_res = g_pending.motion_res[j];
+    for (int k = 0; k < 2 * NB_STEER; ++k)
+    {
+      const ga_succ& s = g_succ[(size_t)j * stride + k];
+      a.ans[k] = s.collision_ambiguous ? 2 : (s.collision_free ? 1 : 0);
+    }
+    g_lookahead[g_pending.key[j]] = a;
+  }
+  g_stats.ns_harvest += now_ns() - t1;
+  g_stats.lookahead_launches++;
+}
+
+// successors of the fan just answered -> device
+void lookahead_submit(const Fan& f, double arc_l)
+{
+  if (!g_lookahead_on) return;
+  ga_ctx* c = ctx();
+  if (!g_expand_params_set || g_expand_arc_l != arc_l)
+  {
+    const ga_expand_params ep{ Vehicle::max_steer_, Vehicle::w_b_, arc_l, g_yaw_res_deg, g_turn_on_point_angle, NB_STEER };
+    check(ga_set_expand_params(c, &ep));
+    g_expand_params_set = true;
+    g_expand_arc_l = arc_l;
+  }
+  ga_node nodes[2 * NB_STEER];
+  int n = 0;
+  const int ad = AStar::astar_dim_;
+  for (size_t k = 0; k < f.prims.size() && n < 2 * NB_STEER; ++k)
+  {
+    const MotionPrimitive& p = f.prims[k];
+    if (f.first_hit[k] >= 0 || p.x_list_.empty()) continue;
+    const double x = p.x_list_.back(), y = p.y_list_.back(), yaw = p.yaw_list_.back();
+    const int xi = static_cast<int>(x * grid_tf::con2star_), yi = static_cast<int>(y * grid_tf::con2star_);  // mapCont2Disc
+    if (!(-1 < xi && xi < ad && -1 < yi && yi < ad)) continue;
+    const PoseKey key = key_of(x, y, yaw);
+    if (g_lookahead.find(key) != g_lookahead.end()) continue;
+    const double mr = AStar::motion_res_map_(yi, xi);  // the resolution hAstarCore will roll this node out with (:1483)
+    nodes[n] = ga_node{ x, y, yaw, mr, 0, 0 };
+    g_pending.key[n] = key;
+    g_pending.motion_res[n] = mr;
+    ++n;
+  }
+  if (n == 0) return;
+  const unsigned long long t0 = now_ns();
+  check(ga_expand_submit(c, nodes, n, &g_pending.ticket));
+  g_stats.ns_submit += now_ns() - t0;
+  g_pending.n = n;
+  g_pending.in_flight = true;
+}
 }  // namespace
+void setLookahead(bool on)
+{
+  if (!on) lookahead_reset();
+  g_lookahead_on = on;
+}
 }  // namespace ga_dropin
 
 using namespace ga_dropin;
@@ -207,7 +343,45 @@ MotionPrimitive Vehicle::move_car_some_steps(const Pose<double>& pose, double ar
     f.valid = true;
     f.last = -1;
     g_ra_fan.valid = false;
-    check_fan(f);
+    // answers: from the look-ahead when this node's fan was checked while its parent was expanded, else now
+    lookahead_harvest();
+    const auto hit = g_lookahead_on ? g_lookahead.find(key_of(pose.x, pose.y, pose.yaw)) : g_lookahead.end();
+    if (hit != g_lookahead.end() && hit->second.motion_res == motion_res)
+    {
+      f.first_hit.assign(f.prims.size(), -1);
+      g_x.clear();
+      g_y.clear();
+      g_yaw.clear();
+      g_seg.assign(1, 0);
+      std::vector<int> again;
+      for (size_t k = 0; k < f.prims.size(); ++k)
+      {
+        const int8_t a = hit->second.ans[k];
+        if (a == 0)
+          f.first_hit[k] = 0;
+        else if (a == 2)
+        {
+          const MotionPrimitive& p = f.prims[k];
+          g_x.insert(g_x.end(), p.x_list_.begin(), p.x_list_.end());
+          g_y.insert(g_y.end(), p.y_list_.begin(), p.y_list_.end());
+          g_yaw.insert(g_yaw.end(), p.yaw_list_.begin(), p.yaw_list_.end());
+          g_seg.push_back((int)g_x.size());
+          again.push_back((int)k);
+        }
+      }
+      if (!again.empty())
+      {
+        std::vector<int> h(again.size(), -1);
+        check(ga_check_poses(ctx(), g_x.data(), g_y.data(), g_yaw.data(), (int)g_x.size(), g_seg.data(), (int)again.size(), 0,
+                             h.data()));
+        for (size_t i = 0; i < again.size(); ++i) f.first_hit[(size_t)again[i]] = h[i];
+        g_stats.lookahead_rechecks += again.size();
+      }
+      ++g_stats.lookahead_hits;
+    }
+    else
+      check_fan(f);
+    lookahead_submit(f, arc_l);
   }
   for (int k = 0; k < (int)f.prims.size(); ++k)
     if (f.dir[(size_t)k] == direction && f.key[(size_t)k] == steer)
@@ -300,6 +474,7 @@ void CollisionChecker::initialize(size_t patch_dim, const std::string& path2conf
   try
   {
     g_turn_on_point_angle = config["TURN_ON_POINT_ANGLE"].as<double>();
+    g_yaw_res_deg = config["YAW_RES"].as<double>();
   }
   catch (const std::exception&)
   {
@@ -358,8 +533,10 @@ void CollisionChecker::calculateDisks()
   }
   const ga_collision_params p{ (int)min_thresh_, (int)max_thresh_, disk_r_c_, (int)yaw_res_coll_, (int)nb_disks_,
                                (int)ceil(grid_tf::star2gm_) };
+  lookahead_reset();
   check(ga_set_collision_params(ctx(), &p, lut.data()));
   g_move_fan.valid = g_ra_fan.valid = false;
+  g_expand_params_set = false;
 }
 
 std::vector<Point<double>> CollisionChecker::returnDiskPositions(double yaw)  // :320-331
@@ -378,12 +555,14 @@ void CollisionChecker::resetPatch(size_t patch_dim)  // :37-42; sizes the astar-
   check(ga_patch_reset(ctx(), (int)patch_dim));  // every device grid back to its initial value
   host_patch_stale_ = host_safety_stale_ = true;
   g_move_fan.valid = g_ra_fan.valid = false;
+  lookahead_reset();
   g_maps_dirty = true;  // the host mirrors (lane costs, geofence, carried-over potential field) are authoritative
   flush_maps();
 }
 
 void CollisionChecker::processSafetyPatch()  // :193-224 (+ the 4x4 pooling of AStar::calcAstarGridCuda, fused)
 {
+  lookahead_reset();
   check(ga_build_safety(ctx()));
   host_safety_stale_ = true;
   g_move_fan.valid = g_ra_fan.valid = false;

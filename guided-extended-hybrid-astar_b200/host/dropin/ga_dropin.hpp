@@ -170,6 +170,8 @@ void check(int rc);  // throws std::runtime_error(ga_last_error) on failure
 // (the GPU fixed point: every reachable cell closed, optimal costs)
 void setHeuristicMode(unsigned ga_heur_flags);
 unsigned heuristicMode();
+// look-ahead fan checks (default on): see ga_dropin.cpp
+void setLookahead(bool on);
 // which arithmetic of cv::distanceTransform the potential field follows (GA_DT_IPPFLOAT: OpenCV built WITH_IPP, the
 // reference's Docker image; GA_DT_FIXEDPOINT: plain OpenCV)
 void setDistanceTransformVariant(int ga_dt_variant);
@@ -180,6 +182,11 @@ struct Stats
   unsigned long long path_checks_cached = 0;     // checkPathCollision calls answered from that launch
   unsigned long long path_checks_direct = 0;     // calls that needed their own launch (analytic expansions ...)
   unsigned long long poses_checked = 0;
+  unsigned long long lookahead_launches = 0;  // asynchronous fan checks of the successors just created
+  unsigned long long lookahead_hits = 0;      // expansions answered from them (no launch on the critical path)
+  unsigned long long lookahead_rechecks = 0;
+  unsigned long long ns_submit = 0, ns_collect = 0, ns_harvest = 0;  // host time in ga_expand_submit / waiting + copying in ga_expand_collect / filling the answer table
+   // primitives re-checked because a pose lay on a cell / yaw-bin edge
 };
 Stats& stats();
 }  // namespace ga_dropin

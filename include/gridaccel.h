@@ -203,7 +203,10 @@ typedef struct
   uint8_t valid;       /* 1 = neighbour would be created (on grid and collision-free) */
   uint8_t near_cell_edge; /* 1 = some pose lies within 1e-9 cells of a cell / yaw-bin boundary:
                              device libm and glibc may disagree there, re-check on the host */
-  uint8_t pad_[6];
+  uint8_t collision_free; /* 1 = every rolled-out pose passed checkPose (valid = collision_free && on the astar grid) */
+  uint8_t collision_ambiguous; /* 1 = some pose lies within 1e-9 of a gm-cell / yaw-bin edge AND the neighbouring cell or
+                             bin gives another answer: collision_free may differ for poses rolled out with glibc */
+  uint8_t pad_[4];
 } ga_succ;
 
 /* number of primitives ga_expand writes per node: 2*nb_steer, + rear-axis deltas when the node
@@ -212,6 +215,31 @@ typedef struct
 GA_API int ga_set_expand_params(ga_ctx* ctx, const ga_expand_params* p);
 GA_API int ga_expand_stride(const ga_ctx* ctx);
 GA_API int ga_expand(ga_ctx* ctx, const ga_node* nodes, int n_nodes, ga_succ* out);
+
+/* ga_expand with the successor epilogue: the grid reads the serial search makes for every
+ * successor are done in the same launch, so movement_cost_map_, motion_res_map_, h_prox_arr_ and the closed-set
+ * planes never have to be copied to the host.  Per (node, primitive), same layout as `out`:
+ *   heur_cost     closed_set (slot) cost_ at the successor's astar cell, GA_OUT_OF_HEURISTIC when the cell is not in
+ *                 the set (HybridAStar::calcCost, hybrid_a_star_lib.cpp:242-250)
+ *   heur_dist     cost_dist_ there (getDistance2goal, :781-798), GA_OUT_OF_HEURISTIC when absent
+ *   movement_cost AStar::movement_cost_map_(yi, xi) (getPathCosts, :324)
+ *   motion_res    AStar::motion_res_map_(yi, xi): the resolution the successor is rolled out with when it is
+ *                 expanded itself (:1483)
+ * and per node out_parent_prox = getProxOfCorners(parent pose * con2star_) (getPathCosts :335-336, the same for all
+ * primitives of the node; device sin / cos: 1e-15 relative, see ga_prox_of_corners).  Needs ga_set_prox_params. */
+#define GA_OUT_OF_HEURISTIC 999999999.0 /* HybridAStar::OUT_OF_HEURISTIC, hybrid_a_star_lib.hpp:103 */
+typedef struct
+{
+  double heur_cost, heur_dist, movement_cost, motion_res;
+} ga_succ_cost;
+/* Asynchronous ga_expand for the nodes a search will expand NEXT (the successors it has just created; <= 32 per
+ * submission, <= 4 submissions in flight): ga_expand_submit launches and returns, ga_expand_collect waits for that
+ * submission (usually it is long finished) and copies its n_nodes * ga_expand_stride results.  The device round trip
+ * then overlaps the caller's own work instead of sitting on its critical path. */
+GA_API int ga_expand_submit(ga_ctx* ctx, const ga_node* nodes, int n_nodes, int* ticket);
+GA_API int ga_expand_collect(ga_ctx* ctx, int ticket, ga_succ* out, int* n_nodes);
+GA_API int ga_expand_ex(ga_ctx* ctx, const ga_node* nodes, int n_nodes, int slot, ga_succ* out, ga_succ_cost* out_cost,
+                        double* out_parent_prox);
 
 /* ---- proximity scoring of sampled poses ----------------------------- */
 

@@ -96,8 +96,10 @@ class Planner:
         L.gap_get_closed.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.gap_get_heuristic.argtypes = [C.c_int] + [C.c_void_p] * 4
         L.gap_get_map.argtypes = [C.c_int, C.c_void_p]
-        if arm == "b200" and hasattr(L, "gap_b200_set_mode"):
+        if arm == "b200":
             L.gap_b200_set_mode.argtypes = [C.c_int]
+            L.gap_b200_set_lookahead.argtypes = [C.c_int]
+            L.gap_b200_stats.argtypes = [C.c_void_p, C.c_void_p]
         cfg = dict(CONFIG)
         cfg.update(config or {})
         cfg["IS_USHIFT"] = bool(is_ushift)
@@ -179,7 +181,12 @@ class Planner:
         nc = int(out[1])
         key5, cost2 = np.zeros((nc, 5), np.int64), np.zeros((nc, 2))
         self.L.gap_get_closed(_p(key5), _p(cost2), nc)
-        return dict(found=int(out[0]), n_closed=nc, n_open=int(out[2]), path_cost=out[4], idx_analytic=int(out[5]),
+        extra = {}
+        if self.arm == "b200":
+            st, ns = np.zeros(8, np.uint64), np.zeros(3, np.uint64)
+            self.L.gap_b200_stats(_p(st), _p(ns))
+            extra = dict(b200_stats=st, b200_ns=ns)  # ns: submit, wait + copy, answer table  # fans checked synchronously, cached / direct path checks, poses, look-ahead launches / hits / re-checks, kernel launches
+        return dict(extra, found=int(out[0]), n_closed=nc, n_open=int(out[2]), path_cost=out[4], idx_analytic=int(out[5]),
                     is_analytic=int(out[6]), search_ms=out[7], path_x=x, path_y=y, path_yaw=yaw, path_delta=delta,
                     path_dir=d, path_type=t, n_expanded=int(tr[0]), n_checks=int(tr[1]), n_check_poses=int(tr[2]),
                     check_hash=h[0], expanded=exp, closed_keys=key5, closed_cost=cost2)
@@ -305,10 +312,13 @@ def main():
     ap.add_argument("--timeout-ms", type=int, default=10**9)
     ap.add_argument("--no-trace", action="store_true")
     ap.add_argument("--heuristic", action="store_true", help="also store the heuristic planes")
+    ap.add_argument("--no-lookahead", action="store_true", help="arm b200: check every fan synchronously")
     ap.add_argument("--out", required=True)
     a = ap.parse_args()
     pl = Planner(a.arm, is_ushift=a.ushift, timeout_ms=a.timeout_ms)
     pl.set_heuristic_mode(a.mode)
+    if a.arm == "b200" and a.no_lookahead:
+        pl._ck(pl.L.gap_b200_set_lookahead(0))
     out = dict(init_s=np.array(pl.init_s))
     if a.scenario:
         r = run_scenario(pl, a.scenario, trace=not a.no_trace)

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <mutex>
 #include <new>
 
 #include "ga_oracle.h"
@@ -24,21 +25,21 @@ namespace
 struct pool_t
 {
   std::vector<std::pair<size_t, uchar*>> free_list;
-  ~pool_t()
-  {
-    for (auto& e : free_list) std::free(e.second);
-  }
 };
 pool_t& pool()
 {
-  static thread_local pool_t p;
-  return p;
+  // never destroyed: the reference keeps cv::Mat objects in static members (CollisionChecker::dil_kernel_), whose
+  // storage comes back here after every other destructor has run
+  static pool_t* p = new pool_t();
+  return *p;
 }
 }  // namespace
+static std::mutex g_pool_mutex;
 std::shared_ptr<uchar> shim_alloc(size_t bytes)
 {
   pool_t& p = pool();
   uchar* buf = nullptr;
+  std::unique_lock<std::mutex> lock(g_pool_mutex);
   for (size_t i = 0; i < p.free_list.size(); ++i)
     if (p.free_list[i].first == bytes)
     {
@@ -46,10 +47,12 @@ std::shared_ptr<uchar> shim_alloc(size_t bytes)
       p.free_list.erase(p.free_list.begin() + (long)i);
       break;
     }
+  lock.unlock();
   if (!buf) buf = static_cast<uchar*>(std::malloc(bytes ? bytes : 1));
   if (!buf) throw std::bad_alloc();
   return std::shared_ptr<uchar>(buf, [bytes](uchar* q) {
     pool_t& pp = pool();
+    std::lock_guard<std::mutex> g(g_pool_mutex);
     if (pp.free_list.size() < 24)
       pp.free_list.emplace_back(bytes, q);
     else

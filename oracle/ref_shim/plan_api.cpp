@@ -383,14 +383,25 @@ int gap_set_dt_variant(int v)
 {
   GAP_TRY({ ga_dropin::setDistanceTransformVariant(v); })
 }
-int gap_b200_stats(unsigned long long* out4)
+int gap_b200_stats(unsigned long long* out8, unsigned long long* ns3)
 {
   const ga_dropin::Stats& s = ga_dropin::stats();
-  out4[0] = s.expansions_prefetched;
-  out4[1] = s.path_checks_cached;
-  out4[2] = s.path_checks_direct;
-  out4[3] = s.poses_checked;
+  out8[0] = s.expansions_prefetched;
+  out8[1] = s.path_checks_cached;
+  out8[2] = s.path_checks_direct;
+  out8[3] = s.poses_checked;
+  out8[4] = s.lookahead_launches;
+  out8[5] = s.lookahead_hits;
+  out8[6] = s.lookahead_rechecks;
+  out8[7] = (unsigned long long)ga_launch_count(ga_dropin::ctx());
+  ns3[0] = s.ns_submit;
+  ns3[1] = s.ns_collect;
+  ns3[2] = s.ns_harvest;
   return 0;
+}
+int gap_b200_set_lookahead(int on)
+{
+  GAP_TRY({ ga_dropin::setLookahead(on != 0); })
 }
 long long gap_b200_launches() { return ga_launch_count(ga_dropin::ctx()); }
 #else

@@ -25,6 +25,9 @@ d = tempfile.mkdtemp()
 kw = dict(scenario=a.scenario, synthetic=a.synthetic, seed=a.seed, queries=a.queries, ushift=a.ushift)
 ra = gp.run_query_subprocess("ref", os.path.join(d, "a.npz"), extra=["--heuristic"] if a.scenario else [], **kw)
 rb = gp.run_query_subprocess("b200", os.path.join(d, "b.npz"), mode=a.mode, extra=["--heuristic"] if a.scenario else [], **kw)
+if "b200_stats" in rb:
+    print("b200 host ms in submit / collect (wait + copy) / answer table:", (rb["b200_ns"] / 1e6).tolist())
+    print("b200_stats (sync fans, cached checks, direct checks, poses, look-ahead launches, hits, re-checks, launches):", rb["b200_stats"].tolist())
 for k in sorted(ra):
     if k not in rb:
         print("missing in b200:", k)
