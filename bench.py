@@ -653,6 +653,7 @@ def main():
     ap.add_argument("--no-plan", action="store_true", help="skip the plan queries/s leg")
     ap.add_argument("--plan-procs", type=int, default=4, help="planner processes per GPU of the plan leg (fixed per GPU: weak scaling)")
     ap.add_argument("--plan-queries", type=int, default=6, help="queries per planner process of the plan leg")
+    ap.add_argument("--e2e-threads", type=int, default=8, help="planner contexts / host threads of the e2e leg")
     ap.add_argument("--no-mps", action="store_true", help="plan leg: do not start a CUDA MPS daemon for the planner processes")
     ap.add_argument("--plan-only", action="store_true", help="run only the plan leg (development)")
     ap.add_argument("--batch", type=int, default=128, help="queries of the batched-heuristic leg (0 = skip)")
@@ -681,11 +682,13 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    envs = [make_env(ga_b200, local_rank, 20240 + rank * N_ROT + i, torch) for i in range(N_ROT)]
+    n_thr = max(N_ROT, min(args.e2e_threads, len(os.sched_getaffinity(0))))
+    envs_e2e = [make_env(ga_b200, local_rank, 20240 + rank * 64 + i, torch) for i in range(n_thr)]
+    envs = envs_e2e[:N_ROT]
     hbm_peak, peak_src = load_peaks()
 
     def barrier():
-        for e in envs:
+        for e in envs_e2e:
             e["ctx"].sync()
         torch.cuda.synchronize()
         if world > 1:
@@ -693,11 +696,12 @@ def main():
             torch.cuda.synchronize()
 
     # cells closed per environment (fixed by the map)
-    closed = []
-    for e in envs:
+    closed_e2e = []
+    for e in envs_e2e:
         n = C.c_int()
         step_resident(e, C.byref(n))
-        closed.append(n.value)
+        closed_e2e.append(n.value)
+    closed = closed_e2e[:N_ROT]
 
     def timed(step_fn, steps, profile):
         for i in range(args.warmup):
@@ -735,28 +739,39 @@ def main():
                 e["ctx"].prof_enable(False)
         return dev_ms, wall * 1e3, launches, cells
 
-    def timed_e2e(steps, pipelined, lean):
-        """host-clocked: every step copies its window in and its results out inside the timed region.  pipelined: the
-        N_ROT planner contexts (one stream and pinned buffer set each) are in flight together, a context is synced
-        only before its buffers are reused, so one step's copies overlap the other contexts' kernels."""
+    def timed_e2e(steps, threaded, lean):
+        """host-clocked: every step copies its window in and its results out inside the timed region and waits for them.
+        threaded: one host thread per planner context (its own stream and pinned buffers), as a planner service with a
+        thread pool per GPU runs it: the Fortune sweeps of different contexts run on different host cores and one
+        context's copies overlap the other contexts' kernels."""
         sweep_s = [0.0]
-        for i in range(args.warmup):
-            step_e2e(envs[i % N_ROT], sweep_s, wait=True, lean=lean)
+        for e in envs_e2e:
+            step_e2e(e, sweep_s, wait=True, lean=lean)
         barrier()
-        sweep_s = [0.0]
+        nenv = len(envs_e2e) if threaded else N_ROT
+        per = [steps // nenv + (1 if i < steps % nenv else 0) for i in range(nenv)]
+        sweeps = [[0.0] for _ in range(nenv)]
+
+        def worker(i):
+            for _ in range(per[i]):
+                step_e2e(envs_e2e[i], sweeps[i], wait=True, lean=lean)
+
         sampler.active = True
         t0 = time.perf_counter()
-        for i in range(steps):
-            e = envs[i % N_ROT]
-            if pipelined and i >= N_ROT:
-                e["ctx"].sync()
-            step_e2e(e, sweep_s, wait=not pipelined, lean=lean)
-        for e in envs:
-            e["ctx"].sync()
+        if threaded:
+            ths = [threading.Thread(target=worker, args=(i,)) for i in range(nenv)]
+            for th in ths:
+                th.start()
+            for th in ths:
+                th.join()
+        else:
+            for i in range(steps):
+                step_e2e(envs_e2e[i % N_ROT], sweeps[i % N_ROT], wait=True, lean=lean)
         barrier()
         wall = time.perf_counter() - t0
         sampler.active = False
-        return wall * 1e3, sum(closed[i % N_ROT] for i in range(steps)), sweep_s[0] * 1e3
+        cells = sum(closed_e2e[i] * per[i] for i in range(nenv)) if threaded else sum(closed_e2e[i % N_ROT] for i in range(steps))
+        return wall * 1e3, cells, sum(x[0] for x in sweeps) * 1e3
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -775,14 +790,15 @@ def main():
             n += n_
         kt[name] = (ms, n)
     e2e_steps = max(20, args.steps // 2)
-    e2e_serial_ms, e2e_serial_cells, _ = timed_e2e(e2e_steps, False, False)
-    e2e_wall_ms, e2e_cells, sweep_ms = timed_e2e(e2e_steps, True, False)
+    e2e_steps = max(e2e_steps, 4 * n_thr)
+    e2e_serial_ms, e2e_serial_cells, sweep_ms = timed_e2e(e2e_steps, False, False)
+    e2e_wall_ms, e2e_cells, _ = timed_e2e(e2e_steps, True, False)
     lean_wall_ms, lean_cells, _ = timed_e2e(e2e_steps, True, True)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
     collision = run_collision_leg(envs[0], args, ga_b200) if (rank == 0 and not args.no_collision) else None
     replan = run_replan_leg(ga_b200, local_rank, args) if (rank == 0 and not args.no_replan) else None
     sampler.stop_flag = True
-    for e in envs[1:]:
+    for e in envs_e2e:
         e["ctx"].sync()
     plan = None
     if not args.no_plan:
@@ -831,7 +847,7 @@ def main():
                         "ms_per_step": e2e_wall_ms / e2e_steps, "steps": e2e_steps,
                         "what": "801^2 window in (ga_patch_insert), safety, sites out, Fortune sweep on the host, potential field, "
                                 "heuristic, h_prox / motion_res windows + four closed-set planes out",
-                        "pipeline": "%d planner contexts in flight (one stream and pinned buffer set each)" % N_ROT,
+                        "pipeline": "%d planner contexts, one host thread each (own stream and pinned buffers)" % n_thr,
                         "host_sweep_ms_per_step": sweep_ms / e2e_steps,
                         "serial_value": e2e_serial_cells / (e2e_serial_ms * 1e-3) / 1e6,
                         "serial_ms_per_step": e2e_serial_ms / e2e_steps,
@@ -874,7 +890,7 @@ def main():
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    for e in envs:
+    for e in envs_e2e:
         e["ctx"].close()
 
 

@@ -18,7 +18,10 @@
 
 #include "ga_internal.cuh"
 
-#define PB 2            // border cells around the staged window
+#define PB 2            // border rows above / below the staged window
+#define PX 6            // border columns on the left (DT_K + 2); the row pitch adds the right border
+#define DT_K 4          // cells per thread and step
+#define DT_PITCH(V) ((V) + 2 * PX + 1)  // V = 200: 213 words, so that consecutive threads' block starts (pitch - DT_K - 2 apart) hit distinct banks
 #define P_THREADS 256   // >= vor_dim
 
 template <bool IPP>
@@ -68,13 +71,15 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
   typedef typename TR::T T;
   extern __shared__ unsigned char dt_smem[];
   T* s = reinterpret_cast<T*>(dt_smem);
-  const int V = a.V, S = V + 2 * PB;
+  const int V = a.V, S = DT_PITCH(V), R = V + 2 * PB;
   const int which = blockIdx.x;  // 0: obstacle transform, 1: Voronoi transform
 
-  // OCC cells of the window (both CTAs count: the Voronoi one must know about the early return)
+  // OCC cells of the window (both CTAs count: the Voronoi one must know about the early return).  Eight loads in
+  // flight per thread: the prologue is latency bound (40 000 scattered bytes through 256 threads).
   int occ = 0;
+#pragma unroll 8
   for (int i = threadIdx.x; i < V * V; i += P_THREADS)
-    occ += a.grid[(size_t)(a.oy + i / V) * a.dim + a.ox + i % V] == GA_OCC;
+    occ += __ldg(a.grid + (size_t)(a.oy + i / V) * a.dim + a.ox + i % V) == GA_OCC;
   occ = __syncthreads_count(occ > 0) ? 1 : 0;
   if (which == 0 && threadIdx.x == 0) a.flag[0] = occ;
   if (which == 1)
@@ -88,65 +93,113 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
     }
     __syncthreads();
   }
-  for (int i = threadIdx.x; i < S * S; i += P_THREADS)
+  // borders first (no global access), then the window itself
+  for (int i = threadIdx.x; i < R * S; i += P_THREADS)
   {
-    const int x = i % S - PB, y = i / S - PB;
-    T v = TR::big();
-    if (x >= 0 && y >= 0 && x < V && y < V)
-    {
-      // source image 1 - (val == mat): zero exactly where the value is OCC (== 2)
-      const bool zero = which == 0 ? a.grid[(size_t)(a.oy + y) * a.dim + a.ox + x] == GA_OCC
-                                   : a.vdist[(size_t)y * V + x] == 2.0f;
-      v = zero ? (T)0 : TR::big();
-    }
-    s[i] = v;
+    const int x = i % S - PX, y = i / S - PB;
+    if (!(x >= 0 && y >= 0 && x < V && y < V)) s[i] = TR::big();
+  }
+#pragma unroll 8
+  for (int i = threadIdx.x; i < V * V; i += P_THREADS)
+  {
+    const int x = i % V, y = i / V;
+    // source image 1 - (val == mat): zero exactly where the value is OCC (== 2)
+    const bool zero = which == 0 ? __ldg(a.grid + (size_t)(a.oy + y) * a.dim + a.ox + x) == GA_OCC
+                                 : __ldcg(a.vdist + (size_t)y * V + x) == 2.0f;
+    s[(size_t)(y + PB) * S + x + PX] = zero ? (T)0 : TR::big();
   }
   __syncthreads();
 
+  // Both passes are shortest-path computations over a DAG (every cell depends on cells earlier in raster order only),
+  // so ANY schedule that respects the dependencies gives the raster result bit for bit.  Thread y owns row y and works
+  // on blocks of DT_K consecutive cells; row y's blocks are shifted two cells to the left of row y-1's, which makes
+  // everything block u of row y needs -- cells up to x + 2 of row y-1, x + 1 of row y-2 -- part of block u of those
+  // rows, finished one step earlier: one barrier per DT_K cells and per row of skew, V + 3V / DT_K steps per pass
+  // instead of 4V.  The upper rows' values are fetched into registers before the (sequentially dependent) cells of the
+  // block are computed.
   const int y = threadIdx.x;
-  const int steps = (V - 1) + 3 * (V - 1) + 1;
+  const int n_blocks = (V - 1 + 2 * (V - 1)) / DT_K + 1;  // block index of the last cell of the last row
+  const int steps = n_blocks + V - 1;
   // ---- forward pass
   {
-    T* row = s + (size_t)(y + PB) * S + PB;
+    T* row = s + (size_t)(y + PB) * S + PX;
     for (int t = 0; t < steps; ++t)
     {
-      const int x = t - 3 * y;
-      if (y < V && x >= 0 && x < V && row[x] != (T)0)
+      const int x0 = DT_K * (t - y) - 2 * y;
+      if (y < V && x0 + DT_K - 1 >= 0 && x0 < V)
       {
-        T t0 = row[x - 2 * S - 1] + TR::lg();
-        t0 = min(t0, row[x - 2 * S + 1] + TR::lg());
-        t0 = min(t0, row[x - S - 2] + TR::lg());
-        t0 = min(t0, row[x - S - 1] + TR::dg());
-        t0 = min(t0, row[x - S] + TR::hv());
-        t0 = min(t0, row[x - S + 1] + TR::dg());
-        t0 = min(t0, row[x - S + 2] + TR::lg());
-        t0 = min(t0, row[x - 1] + TR::hv());
-        row[x] = IPP ? min(t0, TR::big()) : t0;
+        T u1[DT_K + 4], u2[DT_K + 2];
+#pragma unroll
+        for (int j = 0; j < DT_K + 4; ++j) u1[j] = row[x0 - 2 + j - S];
+#pragma unroll
+        for (int j = 0; j < DT_K + 2; ++j) u2[j] = row[x0 - 1 + j - 2 * S];
+        T own[DT_K];
+#pragma unroll
+        for (int j = 0; j < DT_K; ++j) own[j] = row[x0 + j];
+        T left = row[x0 - 1];
+#pragma unroll
+        for (int j = 0; j < DT_K; ++j)
+        {
+          const int x = x0 + j;
+          T v = own[j];
+          if (x >= 0 && x < V && v != (T)0)
+          {
+            T t0 = u2[j] + TR::lg();                 // (y-2, x-1)
+            t0 = min(t0, u2[j + 2] + TR::lg());      // (y-2, x+1)
+            t0 = min(t0, u1[j] + TR::lg());          // (y-1, x-2)
+            t0 = min(t0, u1[j + 1] + TR::dg());      // (y-1, x-1)
+            t0 = min(t0, u1[j + 2] + TR::hv());      // (y-1, x)
+            t0 = min(t0, u1[j + 3] + TR::dg());      // (y-1, x+1)
+            t0 = min(t0, u1[j + 4] + TR::lg());      // (y-1, x+2)
+            t0 = min(t0, left + TR::hv());           // (y, x-1)
+            v = IPP ? min(t0, TR::big()) : t0;
+            row[x] = v;
+          }
+          left = v;
+        }
       }
       __syncthreads();
     }
   }
-  // ---- backward pass (mirrored skew)
+  // ---- backward pass (mirrored: row V-1-y, cells from the right)
   {
     const int yy = V - 1 - y;
-    T* row = s + (size_t)(yy + PB) * S + PB;
+    T* row = s + (size_t)(yy + PB) * S + PX;
     for (int t = 0; t < steps; ++t)
     {
-      const int x = V - 1 - (t - 3 * y);
-      if (y < V && x >= 0 && x < V)
+      const int m0 = DT_K * (t - y) - 2 * y;  // first mirrored column of the block; real column = V - 1 - m
+      if (y < V && m0 + DT_K - 1 >= 0 && m0 < V)
       {
-        T t0 = row[x];
-        if (IPP || t0 > TR::hv())
+        const int xr = V - 1 - m0;            // real column of the block's first cell (blocks run right to left)
+        T d1[DT_K + 4], d2[DT_K + 2];
+#pragma unroll
+        for (int j = 0; j < DT_K + 4; ++j) d1[j] = row[xr + 2 - j + S];
+#pragma unroll
+        for (int j = 0; j < DT_K + 2; ++j) d2[j] = row[xr + 1 - j + 2 * S];
+        T own[DT_K];
+#pragma unroll
+        for (int j = 0; j < DT_K; ++j) own[j] = row[xr - j];
+        T right = row[xr + 1];
+#pragma unroll
+        for (int j = 0; j < DT_K; ++j)
         {
-          t0 = min(t0, row[x + 2 * S + 1] + TR::lg());
-          t0 = min(t0, row[x + 2 * S - 1] + TR::lg());
-          t0 = min(t0, row[x + S + 2] + TR::lg());
-          t0 = min(t0, row[x + S + 1] + TR::dg());
-          t0 = min(t0, row[x + S] + TR::hv());
-          t0 = min(t0, row[x + S - 1] + TR::dg());
-          t0 = min(t0, row[x + S - 2] + TR::lg());
-          t0 = min(t0, row[x + 1] + TR::hv());
-          row[x] = t0;
+          const int x = xr - j;
+          T v = own[j];
+          if (x >= 0 && x < V && (IPP || v > TR::hv()))
+          {
+            T t0 = v;
+            t0 = min(t0, d2[j] + TR::lg());          // (y+2, x+1)
+            t0 = min(t0, d2[j + 2] + TR::lg());      // (y+2, x-1)
+            t0 = min(t0, d1[j] + TR::lg());          // (y+1, x+2)
+            t0 = min(t0, d1[j + 1] + TR::dg());      // (y+1, x+1)
+            t0 = min(t0, d1[j + 2] + TR::hv());      // (y+1, x)
+            t0 = min(t0, d1[j + 3] + TR::dg());      // (y+1, x-1)
+            t0 = min(t0, d1[j + 4] + TR::lg());      // (y+1, x-2)
+            t0 = min(t0, right + TR::hv());          // (y, x+1)
+            v = t0;
+            row[x] = v;
+          }
+          right = v;
         }
       }
       __syncthreads();
@@ -155,7 +208,7 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
   // dist_map *= grid_tf::star2con_ (a_star.cpp:432): float element times 0.625
   float* dst = which == 0 ? a.odist : a.vdist;
   for (int i = threadIdx.x; i < V * V; i += P_THREADS)
-    dst[i] = TR::out(s[(size_t)(i / V + PB) * S + i % V + PB]) * 0.625f;
+    dst[i] = TR::out(s[(size_t)(i / V + PB) * S + i % V + PX]) * 0.625f;
 }
 
 // K4: AStar::setCostmapValue (a_star.cpp:486-508)
@@ -304,7 +357,7 @@ extern "C" int ga_build_potential(ga_ctx* c, int ego_x, int ego_y, const int* vo
   a.mr_max = c->ap.motion_res_max;
   a.dv_min = c->ap.dist_val_min;
   a.dv_max = c->ap.dist_val_max;
-  const size_t smem = sizeof(float) * (size_t)(V + 2 * PB) * (V + 2 * PB);
+  const size_t smem = sizeof(float) * (size_t)(V + 2 * PB) * DT_PITCH(V) + 64;
   {
     ga_launch_scope ls(c, GA_K_DT);
     if (c->ap.dt_variant == GA_DT_IPPFLOAT)

@@ -94,6 +94,47 @@ class Vehicle:
     def from_config(cls, v):
         return cls(v.max_steer, v.wb, v.lf, v.lb, v.width, v.is_ushift)
 
+    # host rollouts with the C library's sin / cos / tan / fmod, the reference's operand order: what the device
+    # results are re-checked against when a pose lies on a cell / yaw-bin edge (ga_succ.near_cell_edge)
+    @staticmethod
+    def _mpi_pi(a):  # util::constrainAngleMinPIPlusPi (util1.cpp:17-24)
+        while a < 0:
+            a += 2 * math.pi
+        return math.fmod(a + math.pi, 2.0 * math.pi) - math.pi
+
+    def move_car_some_steps(self, pose, arc_l, motion_res, direction, steer):
+        """Vehicle::move_car_some_steps (vehicle.cpp:100-122) -> lists x, y, yaw"""
+        n = _cround(arc_l / motion_res)
+        x, y, yaw = pose
+        xs, ys, yaws = [], [], []
+        d = motion_res * direction
+        for _ in range(n):
+            x += d * math.cos(yaw)  # Vehicle::move (vehicle.cpp:34-43)
+            y += d * math.sin(yaw)
+            yaw += d * math.tan(steer) / self.w_b_
+            yaw = self._mpi_pi(yaw)
+            xs.append(x)
+            ys.append(y)
+            yaws.append(yaw)
+        return xs, ys, yaws
+
+    def turn_on_rear_axis(self, pose, delta_angle, yaw_res_coll_deg):
+        """Vehicle::turn_on_rear_axis (vehicle.cpp:45-98) -> lists x, y, yaw"""
+        x, y, yaw = pose
+        goal_yaw = self._mpi_pi(yaw + delta_angle)
+        res = yaw_res_coll_deg * TO_RAD
+        sg = (0.0 < delta_angle) - (delta_angle < 0.0)
+        yaws = []
+        while True:
+            yaw = self._mpi_pi(yaw + sg * res)
+            yaws.append(yaw)
+            diff = self._mpi_pi(self._mpi_pi(goal_yaw) - self._mpi_pi(yaw))  # util::getAngleDiff (util1.cpp:26-34)
+            if not abs(diff) >= res:
+                break
+        if yaws[-1] != goal_yaw:
+            yaws[-1] = goal_yaw
+        return [x] * len(yaws), [y] * len(yaws), yaws
+
 
 def _cround(v):
     """std::round: half away from zero."""
@@ -321,13 +362,62 @@ class CollisionChecker:
         p = _abi.ExpandParams(v.max_steer_, v.w_b_, arc_l, float(cfg.YAW_RES), float(cfg.TURN_ON_POINT_ANGLE), nb_steer)
         self.ctx.check(self.ctx.lib.ga_set_expand_params(self.ctx.h, C.byref(p)))
         self.expand_stride_ = self.ctx.lib.ga_expand_stride(self.ctx.h)
+        self.expand_params_ = dict(arc_l=arc_l, nb_steer=nb_steer, yaw_res=float(cfg.YAW_RES),
+                                   turn_on_point_angle=float(cfg.TURN_ON_POINT_ANGLE))
 
-    def expandNodes(self, nodes):
-        """nodes: structured array _abi.NODE_DTYPE -> successors [n_nodes, stride] _abi.SUCC_DTYPE"""
+    def expandNodes(self, nodes, exact=True):
+        """nodes: structured array _abi.NODE_DTYPE -> successors [n_nodes, stride] _abi.SUCC_DTYPE.
+        exact: primitives the device flags near_cell_edge (a pose within 1e-9 of a cell / yaw-bin boundary, where the
+        device's libm and glibc may round to different cells) are rolled out again on the host with the reference's
+        arithmetic and re-checked from those poses, so that valid / xi / yi / yawi equal the reference's for EVERY
+        primitive (Vehicle::move_car_some_steps / turn_on_rear_axis, vehicle.cpp:45-122)."""
         nodes = np.ascontiguousarray(nodes, _abi.NODE_DTYPE)
         out = np.zeros((len(nodes), self.expand_stride_), _abi.SUCC_DTYPE)
         self.ctx.check(self.ctx.lib.ga_expand(self.ctx.h, _abi.ptr(nodes), len(nodes), _abi.ptr(out)))
+        if exact:
+            self._recheck_flagged(nodes, out)
         return out
+
+    def _recheck_flagged(self, nodes, out):
+        flagged = np.argwhere((out["near_cell_edge"] != 0) & (out["n_poses"] > 0))
+        if len(flagged) == 0:
+            return
+        ep = self.expand_params_
+        n_steer = ep["nb_steer"]
+        delta_steer = (2 * self.vehicle.max_steer_) / float(n_steer - 1)
+        step = ep["turn_on_point_angle"] * TO_RAD
+        ra, d = [], -2 * math.pi + step
+        while d <= 2 * math.pi - step:  # the accumulating loop of setNeighbors (hybrid_a_star_lib.cpp:519-531)
+            if d != 0:
+                ra.append(d)
+            d += step
+        xs, ys, yaws, seg = [], [], [], [0]
+        for i, k in flagged:
+            nd = nodes[i]
+            pose = (float(nd["x"]), float(nd["y"]), float(nd["yaw"]))
+            if k < 2 * n_steer:
+                steer = (k // 2 - n_steer // 2) * delta_steer
+                lx, ly, lyaw = self.vehicle.move_car_some_steps(pose, ep["arc_l"], float(nd["motion_res"]), -1 if k & 1 else 1, steer)
+            else:
+                lx, ly, lyaw = self.vehicle.turn_on_rear_axis(pose, ra[k - 2 * n_steer], float(self.cfg.YAW_RES_COLL))
+            xs += lx
+            ys += ly
+            yaws += lyaw
+            seg.append(len(xs))
+        hits = self.checkSegments(np.array(xs), np.array(ys), np.array(yaws), np.array(seg, np.int32))
+        adim = self.ctx.lib.ga_astar_dim(self.ctx.h)
+        inv = 1.0 / (ep["yaw_res"] * TO_RAD)
+        for j, (i, k) in enumerate(flagged):
+            x, y, yaw = xs[seg[j + 1] - 1], ys[seg[j + 1] - 1], yaws[seg[j + 1] - 1]
+            s = out[i, k]
+            s["x"], s["y"], s["yaw"] = x, y, yaw
+            s["xi"], s["yi"], s["yawi"] = int(x * CON2STAR), int(y * CON2STAR), _cround(yaw * inv)  # mapCont2Disc
+            ok = hits[j] < 0
+            on_grid = (k >= 2 * n_steer) or (-1 < s["xi"] < adim and -1 < s["yi"] < adim)
+            s["valid"] = 1 if (ok and on_grid) else 0
+            s["collision_free"] = 1 if ok else 0
+            s["near_cell_edge"] = 0
+            out[i, k] = s
 
     def expandNodesWithCosts(self, nodes, for_path=True):
         """ga_expand_ex: successors plus the grid reads the search makes per successor (heuristic cost_ / cost_dist_

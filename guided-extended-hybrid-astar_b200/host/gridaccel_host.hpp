@@ -590,6 +590,8 @@ public:
     motion_res_max_ = cfg.num("MOTION_RES_MAX", 1.0);
     dist_val_min_ = cfg.num("MIN_DIST_VAL", 3);
     dist_val_max_ = cfg.num("MAX_DIST_VAL", 10);
+    heuristic_early_exit_ = cfg.flag("HEURISTIC_EARLY_EXIT", true);
+    max_extra_nodes_ = (unsigned)cfg.num("MAX_EXTRA_NODES_ASTAR", 10000);
     pushParams();
   }
   void pushParams()
@@ -611,13 +613,49 @@ public:
     ctx_.check(ga_set_astar_params(ctx_.handle(), &p));
     ctx_.astar_params_set = true;
   }
-  // a_star.cpp:70-99.  CollisionChecker::resetPatch (ga_patch_reset) sizes and resets the device
-  // grids; carrying h_prox_arr_ / motion_res_map_ over a patch move is a download / shift / upload.
+  // a_star.cpp:70-99.  Call BEFORE CollisionChecker::resetPatch, as HybridAStar::reinit does (hybrid_a_star_lib.cpp:
+  // 100-101): the potential field and the motion-resolution map are saved here and carried over the patch move by
+  // finishReinit() once ga_patch_reset has resized the device grids (util::saveTemp + copyPatch2Patch, util2.hpp:20-67).
   void reinit(const Point<double>& patch_origin_utm, int patch_dim)
   {
+    if (ga_patch_dim(ctx_.handle()) > 0)
+    {
+      const size_t d = (size_t)ga_astar_dim(ctx_.handle());
+      ctx_.download(GA_GRID_H_PROX, temp_h_prox_arr_, d);
+      ctx_.download(GA_GRID_MOTION_RES, temp_motion_res_map_, d);
+      have_temp_ = true;
+    }
+    prev_origin_astar_ = patch_origin_astar_;
     patch_origin_utm_ = patch_origin_utm;
+    patch_origin_astar_ = Point<int>((int)std::round(patch_origin_utm.x * CON2STAR), (int)std::round(patch_origin_utm.y * CON2STAR));
     patch_dim_ = patch_dim;
+    astar_dim_ = (int)std::floor((double)patch_dim * GM_RES / ASTAR_RES);
+  }
+  // after CollisionChecker::resetPatch: copy the overlap of the previous maps into the new ones (copyPatch2Patch,
+  // including its exclusive end point) and upload them
+  void finishReinit()
+  {
     astar_dim_ = ga_astar_dim(ctx_.handle());
+    if (!have_temp_) return;
+    const size_t nd = (size_t)astar_dim_;
+    h_prox_arr_.resize_and_reset(nd, nd, 0.0);
+    motion_res_map_.resize_and_reset(nd, nd, motion_res_max_);
+    const int prev_dim = (int)temp_h_prox_arr_.xDim(), next_dim = astar_dim_;
+    const Point<int> po = prev_origin_astar_, no = patch_origin_astar_;
+    const Point<int> start_prev(std::max(no.x - po.x, 0), std::max(no.y - po.y, 0));
+    const Point<int> start_next(std::max(po.x - no.x, 0), std::max(po.y - no.y, 0));
+    const Point<int> end_next(std::min(po.x + prev_dim - no.x, next_dim - 1), std::min(po.y + prev_dim - no.y, next_dim - 1));
+    for (int x = 0; x < end_next.x - start_next.x; ++x)
+      for (int y = 0; y < end_next.y - start_next.y; ++y)
+      {
+        h_prox_arr_((size_t)(start_next.y + y), (size_t)(start_next.x + x)) =
+            temp_h_prox_arr_((size_t)(start_prev.y + y), (size_t)(start_prev.x + x));
+        motion_res_map_((size_t)(start_next.y + y), (size_t)(start_next.x + x)) =
+            temp_motion_res_map_((size_t)(start_prev.y + y), (size_t)(start_prev.x + x));
+      }
+    ctx_.upload(GA_GRID_H_PROX, h_prox_arr_);
+    ctx_.upload(GA_GRID_MOTION_RES, motion_res_map_);
+    have_temp_ = false;
   }
 
   size_t calcIndex(size_t x, size_t y) const { return y * (size_t)astar_dim_ + x; }  // a_star.cpp:303-316
@@ -625,13 +663,29 @@ public:
   // a_star.cpp:536-542: Pooling::execute is fused into processSafetyPatch's kernel
   void calcAstarGridCuda() {}
 
-  // a_star.cpp:110-295, fixed-point mode: closes every cell reachable from the goal
-  void calcDistanceHeuristic(const Point<int>& goal_pos, const Point<int>& /*start_pos*/, bool for_path = true,
-                             bool /*get_only_near*/ = false)
+  // a_star.cpp:110-295.  reference_order = true (default): the reference's own closing order with its start cell,
+  // early exit (config HEURISTIC_EARLY_EXIT / MAX_EXTRA_NODES_ASTAR) and get_only_near -- planes and
+  // nodes_near_goal_ bit-identical to the reference's (GA_HEUR_REFORDER).  false: the GPU fixed point, every cell
+  // reachable from the goal closed with its optimal cost; the start cell only matters for get_only_near then.
+  bool reference_order_ = true;
+  bool heuristic_early_exit_ = true;
+  unsigned max_extra_nodes_ = 10000;
+  std::vector<std::pair<double, NodeDisc>> nodes_near_goal_;
+  void calcDistanceHeuristic(const Point<int>& goal_pos, const Point<int>& start_pos, bool for_path = true,
+                             bool get_only_near = false)
   {
     const int slot = for_path ? 1 : 0;
     int n = 0;
-    ctx_.check(ga_build_heuristic(ctx_.handle(), slot, goal_pos.x, goal_pos.y, &n));
+    ga_heur_query q{};
+    q.goal_x = goal_pos.x;
+    q.goal_y = goal_pos.y;
+    q.start_x = start_pos.x;
+    q.start_y = start_pos.y;
+    q.max_extra_nodes = max_extra_nodes_;
+    q.flags = reference_order_ ? (GA_HEUR_REFORDER | (heuristic_early_exit_ ? GA_HEUR_EARLY_EXIT : 0) |
+                                  (get_only_near ? GA_HEUR_ONLY_NEAR : 0))
+                               : GA_HEUR_FIXEDPOINT;
+    ctx_.check(ga_build_heuristic_ex(ctx_.handle(), slot, &q, &n));
     ClosedSet& cs = for_path ? closed_set_path_ : closed_set_guidance_;
     astar_dim_ = ga_astar_dim(ctx_.handle());
     const size_t d = (size_t)astar_dim_;
@@ -641,6 +695,14 @@ public:
     ctx_.download(GA_GRID_HEUR_PARENT + slot, cs.parent, d);
     ctx_.download(GA_GRID_HEUR_FLAGS + slot, cs.flags, d);
     cs.n_closed = (size_t)n;
+    nodes_near_goal_.clear();  // a_star.cpp:141
+    if (get_only_near)
+    {
+      int ids[400], cnt = 0;
+      double dist[400];
+      ctx_.check(ga_heur_near_nodes(ctx_.handle(), slot, start_pos.x, start_pos.y, ids, dist, 400, &cnt));
+      for (int i = 0; i < cnt && i < 400; ++i) nodes_near_goal_.emplace_back(dist[i], cs.at((size_t)ids[i]));
+    }
   }
 
   // a_star.cpp:351-378
@@ -714,6 +776,9 @@ public:
 private:
   Context& ctx_;
   Point<double> patch_origin_utm_;
+  Point<int> patch_origin_astar_, prev_origin_astar_;
+  Vec2DFlat<double> temp_h_prox_arr_, temp_motion_res_map_;
+  bool have_temp_ = false;
   int patch_dim_ = 0;
   double unknown_cost_w_ = 0, motion_res_min_ = 0.1, motion_res_max_ = 1.0, dist_val_min_ = 3, dist_val_max_ = 10;
 };

@@ -104,6 +104,7 @@ int main()
   // heuristic: goal cost 0, every free cell closed, parent walk reaches the goal with cost
   // decreasing, Bellman consistency of the cost plane along the path
   const Point<int> goal(20, 20), start(230, 225);
+  astar.reference_order_ = false;  // the GPU fixed point: every reachable cell closed
   astar.calcDistanceHeuristic(goal, start, false);
   const ClosedSet& cs = astar.closed_set_guidance_;
   EXPECT(cs.contains(astar.calcIndex(goal.x, goal.y)) && cs.at(astar.calcIndex(goal.x, goal.y)).cost_ == 0.0);

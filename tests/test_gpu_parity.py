@@ -178,12 +178,32 @@ def test_expand_matches_oracle(planner, oracle, ushift):
         assert np.all(g["n_poses"][k:] == 0)
         # continuous end poses: device libm vs glibc, a few ulp
         assert np.allclose(np.stack([g["x"][:k], g["y"][:k], g["yaw"][:k]], 1), end, rtol=0, atol=1e-12)
-        safe = g["near_cell_edge"][:k] == 0
-        n_flagged += int((~safe).sum())
-        assert np.array_equal(g["valid"][:k][safe], v[safe])
+        # every primitive, bit for bit: the ones the device flags near_cell_edge were rolled out again on the host
+        # with the reference's arithmetic (CollisionChecker.expandNodes(exact=True))
+        assert np.all(g["near_cell_edge"][:k] == 0)
+        assert np.array_equal(g["valid"][:k], v)
         gd = np.stack([g["xi"][:k], g["yi"][:k], g["yawi"][:k]], 1)
-        assert np.array_equal(gd[safe], disc[safe])
+        assert np.array_equal(gd, disc)
+    raw = cc.expandNodes(nodes, exact=False)
+    n_flagged = int((raw["near_cell_edge"] != 0).sum())
     assert n_flagged < 0.001 * n * stride
+    # nodes ON cell edges (coordinates that are multiples of the cell size, axis-aligned yaws): many flagged primitives
+    m = 256
+    edge = np.zeros(m, _abi.NODE_DTYPE)
+    edge["x"] = rng.integers(40, int(ext / 0.625) - 40, m) * 0.625
+    edge["y"] = rng.integers(40, int(ext / 0.625) - 40, m) * 0.625
+    edge["yaw"] = rng.choice([0.0, math.pi / 2, -math.pi / 2, math.pi / 6], m)
+    edge["motion_res"] = rng.choice([0.1, 0.3125, 0.625], m)
+    edge["with_rear_axis"] = 1 if ushift else 0
+    got = cc.expandNodes(edge)
+    assert int((cc.expandNodes(edge, exact=False)["near_cell_edge"] != 0).sum()) > 0
+    for i in range(m):
+        v, disc, end, npos = oracle.expand_node(safety, cc.disk_centers_, 3, ep, float(edge["x"][i]), float(edge["y"][i]),
+                                                float(edge["yaw"][i]), float(edge["motion_res"][i]))
+        k = len(v)
+        g = got[i]
+        assert np.array_equal(g["valid"][:k], v)
+        assert np.array_equal(np.stack([g["xi"][:k], g["yi"][:k], g["yawi"][:k]], 1), disc)
 
 
 # ---- K5: heuristic grid ---------------------------------------------------------------------------
