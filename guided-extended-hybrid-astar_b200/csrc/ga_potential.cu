@@ -19,9 +19,9 @@
 #include "ga_internal.cuh"
 
 #define PB 2            // border rows above / below the staged window
-#define PX 6            // border columns on the left (DT_K + 2); the row pitch adds the right border
-#define DT_K 4          // cells per thread and step
-#define DT_PITCH(V) ((V) + 2 * PX + 1)  // V = 200: 213 words, so that consecutive threads' block starts (pitch - DT_K - 2 apart) hit distinct banks
+#define PX 7            // border columns (DT_K + 2) on either side
+#define DT_K 5          // cells per lane and step
+#define DT_PITCH(V) ((((V) + 2 * PX) & 1) ? (V) + 2 * PX + 1 : (V) + 2 * PX)  // even pitch: consecutive lanes' block starts are pitch - DT_K - 2 words apart, odd = distinct banks
 #define P_THREADS 256   // >= vor_dim
 
 template <bool IPP>
@@ -111,100 +111,107 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
   __syncthreads();
 
   // Both passes are shortest-path computations over a DAG (every cell depends on cells earlier in raster order only),
-  // so ANY schedule that respects the dependencies gives the raster result bit for bit.  Thread y owns row y and works
-  // on blocks of DT_K consecutive cells; row y's blocks are shifted two cells to the left of row y-1's, which makes
-  // everything block u of row y needs -- cells up to x + 2 of row y-1, x + 1 of row y-2 -- part of block u of those
-  // rows, finished one step earlier: one barrier per DT_K cells and per row of skew, V + 3V / DT_K steps per pass
-  // instead of 4V.  The upper rows' values are fetched into registers before the (sequentially dependent) cells of the
-  // block are computed.
-  const int y = threadIdx.x;
-  const int n_blocks = (V - 1 + 2 * (V - 1)) / DT_K + 1;  // block index of the last cell of the last row
-  const int steps = n_blocks + V - 1;
-  // ---- forward pass
+  // so ANY schedule that respects the dependencies gives the raster result bit for bit.  Rows work on blocks of DT_K
+  // consecutive cells; row y's blocks are shifted two cells to the left of row y-1's, which makes everything block u of
+  // row y needs -- cells up to x + 2 of row y-1, x + 1 of row y-2 -- part of block u of those rows, finished one step
+  // earlier.  Row y is therefore busy during steps [y (1 + 2 / DT_K), + V / DT_K): at any step only ~32 rows have work,
+  // and with DT_K = 5 the windows of rows y and y + 32 do not overlap.  So ONE WARP runs the whole pass: lane l takes
+  // rows l, l + 32, l + 64 ... one after the other, the lanes meet at a __syncwarp per step -- no CTA barrier on the
+  // chain (it cost more than the arithmetic: 54 % of the stall samples of the 256-thread version).
+  const int lane = threadIdx.x & 31;
+  const int steps = (V - 1) + (V - 1 + 2 * (V - 1)) / DT_K + 1;
+  if (threadIdx.x < 32)
   {
-    T* row = s + (size_t)(y + PB) * S + PX;
+    // ---- forward pass
+    int y = lane;
     for (int t = 0; t < steps; ++t)
     {
-      const int x0 = DT_K * (t - y) - 2 * y;
+      int x0 = DT_K * (t - y) - 2 * y;
+      if (y < V && x0 >= V)  // this row is finished: on to the lane's next one
+      {
+        y += 32;
+        x0 = DT_K * (t - y) - 2 * y;
+      }
       if (y < V && x0 + DT_K - 1 >= 0 && x0 < V)
       {
-        T u1[DT_K + 4], u2[DT_K + 2];
+        T* row = s + (size_t)(y + PB) * S + PX;
+        T u1[DT_K + 4], u2[DT_K + 2], own[DT_K];
 #pragma unroll
         for (int j = 0; j < DT_K + 4; ++j) u1[j] = row[x0 - 2 + j - S];
 #pragma unroll
         for (int j = 0; j < DT_K + 2; ++j) u2[j] = row[x0 - 1 + j - 2 * S];
-        T own[DT_K];
 #pragma unroll
         for (int j = 0; j < DT_K; ++j) own[j] = row[x0 + j];
         T left = row[x0 - 1];
+        // the seven candidates from the rows above do not depend on this block's own results: all DT_K minima are
+        // formed first (independent instructions), only min(., left + 1) runs as a chain; selects instead of branches
+        T up[DT_K];
+#pragma unroll
+        for (int j = 0; j < DT_K; ++j)
+        {
+          const T a0 = min(u2[j] + TR::lg(), u2[j + 2] + TR::lg());        // (y-2, x-1), (y-2, x+1)
+          const T a1 = min(u1[j] + TR::lg(), u1[j + 1] + TR::dg());        // (y-1, x-2), (y-1, x-1)
+          const T a2 = min(u1[j + 2] + TR::hv(), u1[j + 3] + TR::dg());    // (y-1, x), (y-1, x+1)
+          up[j] = min(min(a0, a1), min(a2, u1[j + 4] + TR::lg()));         // (y-1, x+2)
+        }
 #pragma unroll
         for (int j = 0; j < DT_K; ++j)
         {
           const int x = x0 + j;
-          T v = own[j];
-          if (x >= 0 && x < V && v != (T)0)
-          {
-            T t0 = u2[j] + TR::lg();                 // (y-2, x-1)
-            t0 = min(t0, u2[j + 2] + TR::lg());      // (y-2, x+1)
-            t0 = min(t0, u1[j] + TR::lg());          // (y-1, x-2)
-            t0 = min(t0, u1[j + 1] + TR::dg());      // (y-1, x-1)
-            t0 = min(t0, u1[j + 2] + TR::hv());      // (y-1, x)
-            t0 = min(t0, u1[j + 3] + TR::dg());      // (y-1, x+1)
-            t0 = min(t0, u1[j + 4] + TR::lg());      // (y-1, x+2)
-            t0 = min(t0, left + TR::hv());           // (y, x-1)
-            v = IPP ? min(t0, TR::big()) : t0;
-            row[x] = v;
-          }
+          T t0 = min(up[j], left + TR::hv());                              // (y, x-1)
+          if (IPP) t0 = min(t0, TR::big());
+          const T v = own[j] != (T)0 ? t0 : own[j];
+          if (x >= 0 && x < V) row[x] = v;
           left = v;
         }
       }
-      __syncthreads();
+      __syncwarp();
     }
-  }
-  // ---- backward pass (mirrored: row V-1-y, cells from the right)
-  {
-    const int yy = V - 1 - y;
-    T* row = s + (size_t)(yy + PB) * S + PX;
+    // ---- backward pass (mirrored: lane's row V-1-y, cells from the right)
+    y = lane;
     for (int t = 0; t < steps; ++t)
     {
-      const int m0 = DT_K * (t - y) - 2 * y;  // first mirrored column of the block; real column = V - 1 - m
+      int m0 = DT_K * (t - y) - 2 * y;  // first mirrored column of the block; real column = V - 1 - m
+      if (y < V && m0 >= V)
+      {
+        y += 32;
+        m0 = DT_K * (t - y) - 2 * y;
+      }
       if (y < V && m0 + DT_K - 1 >= 0 && m0 < V)
       {
+        T* row = s + (size_t)(V - 1 - y + PB) * S + PX;
         const int xr = V - 1 - m0;            // real column of the block's first cell (blocks run right to left)
-        T d1[DT_K + 4], d2[DT_K + 2];
+        T d1[DT_K + 4], d2[DT_K + 2], own[DT_K];
 #pragma unroll
         for (int j = 0; j < DT_K + 4; ++j) d1[j] = row[xr + 2 - j + S];
 #pragma unroll
         for (int j = 0; j < DT_K + 2; ++j) d2[j] = row[xr + 1 - j + 2 * S];
-        T own[DT_K];
 #pragma unroll
         for (int j = 0; j < DT_K; ++j) own[j] = row[xr - j];
         T right = row[xr + 1];
+        T dn[DT_K];
+#pragma unroll
+        for (int j = 0; j < DT_K; ++j)
+        {
+          const T a0 = min(d2[j] + TR::lg(), d2[j + 2] + TR::lg());        // (y+2, x+1), (y+2, x-1)
+          const T a1 = min(d1[j] + TR::lg(), d1[j + 1] + TR::dg());        // (y+1, x+2), (y+1, x+1)
+          const T a2 = min(d1[j + 2] + TR::hv(), d1[j + 3] + TR::dg());    // (y+1, x), (y+1, x-1)
+          dn[j] = min(min(a0, a1), min(a2, d1[j + 4] + TR::lg()));         // (y+1, x-2)
+        }
 #pragma unroll
         for (int j = 0; j < DT_K; ++j)
         {
           const int x = xr - j;
-          T v = own[j];
-          if (x >= 0 && x < V && (IPP || v > TR::hv()))
-          {
-            T t0 = v;
-            t0 = min(t0, d2[j] + TR::lg());          // (y+2, x+1)
-            t0 = min(t0, d2[j + 2] + TR::lg());      // (y+2, x-1)
-            t0 = min(t0, d1[j] + TR::lg());          // (y+1, x+2)
-            t0 = min(t0, d1[j + 1] + TR::dg());      // (y+1, x+1)
-            t0 = min(t0, d1[j + 2] + TR::hv());      // (y+1, x)
-            t0 = min(t0, d1[j + 3] + TR::dg());      // (y+1, x-1)
-            t0 = min(t0, d1[j + 4] + TR::lg());      // (y+1, x-2)
-            t0 = min(t0, right + TR::hv());          // (y, x+1)
-            v = t0;
-            row[x] = v;
-          }
+          const T t0 = min(min(own[j], dn[j]), right + TR::hv());          // (y, x+1)
+          const T v = (IPP || own[j] > TR::hv()) ? t0 : own[j];
+          if (x >= 0 && x < V) row[x] = v;
           right = v;
         }
       }
-      __syncthreads();
+      __syncwarp();
     }
   }
+  __syncthreads();
   // dist_map *= grid_tf::star2con_ (a_star.cpp:432): float element times 0.625
   float* dst = which == 0 ? a.odist : a.vdist;
   for (int i = threadIdx.x; i < V * V; i += P_THREADS)
