@@ -360,7 +360,7 @@ def run_plan_leg(args, local_rank, rank):
 
     # Several planner PROCESSES on one GPU only run concurrently under CUDA MPS (otherwise the driver time-slices whole
     # contexts and every launch waits for a slice).  One MPS control daemon per rank, restricted to the rank's GPU.
-    mps_env = None
+    mps_env, mps_note = None, ""
     if not args.no_mps and procs > 1:
         vis = os.environ.get("CUDA_VISIBLE_DEVICES")
         phys = vis.split(",")[local_rank] if vis else str(local_rank)
@@ -372,13 +372,16 @@ def run_plan_leg(args, local_rank, rank):
             r = subprocess.run(["nvidia-cuda-mps-control", "-d"], env=cand, capture_output=True, timeout=20)
             if r.returncode == 0:
                 mps_env = cand
+            else:
+                mps_note = r.stderr.decode()[-200:]
         except (OSError, subprocess.TimeoutExpired):
             mps_env = None
 
     def run_arm(arm, tag):
         ps = []
         if arm == "b200" and mps_env is not None:
-            env = dict(mps_env, GA_DEVICE="0")
+            # an MPS client names devices relative to the set its control daemon was started with (one GPU here)
+            env = dict(mps_env, CUDA_VISIBLE_DEVICES="0", GA_DEVICE="0")
         else:
             env = dict(os.environ, GA_DEVICE=str(local_rank))
         for w in range(procs):
@@ -406,6 +409,8 @@ def run_plan_leg(args, local_rank, rank):
     out = {"workload": "%d planner processes x %d queries on synthetic 2048^2 maps (one map per process), shipped config" % (procs, nq),
            "b200": run_arm("b200", "b")}
     out["b200"]["mps"] = mps_env is not None
+    if mps_note:
+        out["b200"]["mps_note"] = mps_note
     if mps_env is not None:
         try:
             subprocess.run(["nvidia-cuda-mps-control"], input=b"quit\n", env=mps_env, capture_output=True, timeout=20)
@@ -667,9 +672,6 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
-    if args.plan_only:
-        print(json.dumps(run_plan_leg(args, local_rank, rank)), flush=True)
-        return
 
     import torch
     import torch.distributed as dist
@@ -683,6 +685,16 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     n_thr = max(N_ROT, min(args.e2e_threads, len(os.sched_getaffinity(0))))
+    if args.plan_only:
+        plan = run_plan_leg(args, local_rank, rank)
+        if world > 1:
+            allp = [None] * world
+            dist.all_gather_object(allp, plan)
+            plan = {"per_rank": allp}
+            dist.destroy_process_group()
+        if rank == 0:
+            print(json.dumps(plan), flush=True)
+        return
     envs_e2e = [make_env(ga_b200, local_rank, 20240 + rank * 64 + i, torch) for i in range(n_thr)]
     envs = envs_e2e[:N_ROT]
     hbm_peak, peak_src = load_peaks()
@@ -805,6 +817,11 @@ def main():
         if world > 1:
             dist.barrier()
         plan = run_plan_leg(args, local_rank, rank)
+        if world > 1:
+            allp = [None] * world
+            dist.all_gather_object(allp, plan)
+            if rank == 0:
+                plan["per_rank_b200"] = [p.get("b200") for p in allp]
 
     # max over ranks of the times, sum over ranks of the work
     plan_qps = plan["b200"].get("queries_per_s", 0.0) if plan and "b200" in plan else 0.0
