@@ -163,6 +163,26 @@ static void build_se(int r, ga_se* se)
     }
     se->row_var[i] = v;
   }
+  // column view: hmax(w) = largest |dy| whose half width is >= w
+  int hw_of[GA_MAX_DISK_R + 1];
+  for (int d = 0; d <= r; ++d) hw_of[d] = se->var_w[se->row_var[r + d]];
+  int hmax[GA_MAX_DISK_R + 1];
+  for (int w = 0; w <= r; ++w)
+  {
+    hmax[w] = 0;
+    for (int d = 0; d <= r; ++d)
+      if (hw_of[d] >= w) hmax[w] = d;  // half widths are non-increasing in |dy| for an ellipse: the last hit is the largest
+  }
+  se->n_lvl = 0;
+  for (int h = 0; h <= r; ++h)
+  {
+    bool used = false;
+    for (int w = 0; w <= r; ++w) used |= hmax[w] == h;
+    if (used) se->lvl_h[se->n_lvl++] = h;
+  }
+  for (int w = 0; w <= r; ++w)
+    for (int l = 0; l < se->n_lvl; ++l)
+      if (se->lvl_h[l] == hmax[w]) se->lvl_of_w[w] = l;
 }
 
 extern "C" int ga_set_collision_params(ga_ctx* c, const ga_collision_params* p, const int* centers)

@@ -23,6 +23,11 @@ struct ga_se  // structuring element, passed to kernels by value
   int n_var;             // distinct half widths
   int var_w[GA_MAX_DISK_R + 1];        // half width of variant v
   int row_var[2 * GA_MAX_DISK_R + 1];  // variant index of SE row dy + r
+  // the same element seen by columns: a cell at horizontal distance w is covered by the rows |dy| <= hmax(w)
+  // (half widths shrink monotonically with |dy|); levels = the distinct hmax values, ascending
+  int n_lvl;
+  int lvl_h[GA_MAX_DISK_R + 1];     // hmax of level l
+  int lvl_of_w[GA_MAX_DISK_R + 1];  // level whose hmax belongs to distance w (w = 0 .. r)
 };
 
 struct ga_prof_rec

@@ -36,19 +36,28 @@ __device__ __forceinline__ uint32_t bytes_gt(uint32_t x, uint32_t k7, bool c_hig
 // bits 7, 15, 23, 31 -> bits 0..3
 __device__ __forceinline__ uint32_t nibble_of_high_bits(uint32_t m) { return ((m >> 7) * 0x01020408u) >> 24; }
 
+// The shipped footprint (default vehicle, SAFETY_DISTANCE_M 0.1) gives the 21 x 21 disk: radius 10, half widths
+// 10,10,10,10,9,9,8,7,6,4,0 for |dy| = 0..10.  Its column view as compile-time tables lets phases V and B unroll
+// completely (SPEC10); any other element runs the same kernel with the tables read from `se`.
+__device__ constexpr int K10_R = 10, K10_NLVL = 7;
+__device__ constexpr int K10_LVL_H[K10_NLVL] = { 3, 5, 6, 7, 8, 9, 10 };
+__device__ constexpr int K10_LVL_OF_W[K10_R + 1] = { 6, 5, 5, 5, 5, 4, 4, 3, 2, 1, 0 };
+
+template <bool SPEC10>
 __global__ void __launch_bounds__(DT_THREADS)
 safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ safety, uint8_t* __restrict__ astar,
               int astar_dim, const ga_se se, uint32_t lo4, uint32_t hi4)
 {
   extern __shared__ __align__(16) uint32_t smem[];
   __shared__ uint32_t s_lut[256];   // (P1 nibble | P2 nibble << 4) -> 4 cell bytes
-  __shared__ int s_var_of_w[GA_MAX_DISK_R + 1];
-  const int r = se.r, nv = se.n_var;
+  const int r = SPEC10 ? K10_R : se.r;
+  const int n_lvl = SPEC10 ? K10_NLVL : se.n_lvl;
   const int rows_in = DT_TH + 2 * r;
   uint32_t* sP = smem;                                   // [plane][rows_in][DT_SW]   thresholded bit planes
-  uint32_t* sH = sP + 2 * rows_in * DT_SW;               // [plane][variant][rows_in][DT_TW]  span dilations
-  uint32_t* sOut = sH + 2 * nv * rows_in * DT_TW;        // [plane][DT_TH][DT_TW]   dilated planes
-  const int plane_stride = nv * rows_in * DT_TW;
+  uint32_t* sV = sP + 2 * rows_in * DT_SW;               // [plane][level][DT_TH][DT_SW]  vertical ORs over |dy| <= hmax(level)
+  uint32_t* sOut = sV + 2 * n_lvl * DT_TH * DT_SW;       // [plane][DT_TH][DT_TW]   dilated planes
+  constexpr int lvl_stride = DT_TH * DT_SW;
+  const int plane_stride = n_lvl * lvl_stride;
   const int w0 = blockIdx.x * DT_TW, y0 = blockIdx.y * DT_TH;
   const int tid = threadIdx.x;
   const bool vec = (dim & 15) == 0;
@@ -60,13 +69,6 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
     // table: byte k = ((idx >> k) & 1) + ((idx >> (4 + k)) & 1)
     const uint32_t a = tid & 15, b = tid >> 4;
     s_lut[tid] = (((a & 0xFu) * 0x00204081u) & 0x01010101u) + (((b & 0xFu) * 0x00204081u) & 0x01010101u);
-    if (tid <= GA_MAX_DISK_R)
-    {
-      int v = -1;
-      for (int k = 0; k < nv; ++k)
-        if (se.var_w[k] == tid) v = k;
-      s_var_of_w[tid] = v;
-    }
   }
 
   // ---- phase 0: threshold + pack.  One item = 16 cells (half a plane word); two neighbouring
@@ -96,13 +98,15 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
       const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32 + half * 16;
       const bool inside = it < n_items && y >= 0 && y < dim && x >= 0 && x < dim;
       const uint32_t w[4] = { v[j].x, v[j].y, v[j].z, v[j].w };
-      uint32_t b_occ = 0, b_nf = (lo == 0 && inside) ? 0xFFFFu : 0u;  // nothing is below 0
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-      {
-        b_occ |= nibble_of_high_bits(bytes_gt(w[k], hi_k7, hi_high)) << (4 * k);  // v > MAX_THRESH -> OCC  (collision_checking.cpp:214,220)
-        b_nf |= nibble_of_high_bits(bytes_gt(w[k], lo_k7, lo_high)) << (4 * k);    // !(v < MIN_THRESH), i.e. v > MIN_THRESH - 1  (:213,219)
-      }
+      // 16 byte compares -> 16 bits: the compare leaves 0x80 in every byte that passes; a byte-wise dot product with the
+      // weights 1, 2, 4, 8 (16 .. 128 for the next word) adds up 128 x the bit pattern -- one DP4A per word instead of
+      // shift / multiply / shift per word and the shift-ors that assemble the nibbles
+      const uint32_t o_lo = __dp4a(bytes_gt(w[1], hi_k7, hi_high), 0x80402010u, __dp4a(bytes_gt(w[0], hi_k7, hi_high), 0x08040201u, 0u));
+      const uint32_t o_hi = __dp4a(bytes_gt(w[3], hi_k7, hi_high), 0x80402010u, __dp4a(bytes_gt(w[2], hi_k7, hi_high), 0x08040201u, 0u));
+      const uint32_t n_lo = __dp4a(bytes_gt(w[1], lo_k7, lo_high), 0x80402010u, __dp4a(bytes_gt(w[0], lo_k7, lo_high), 0x08040201u, 0u));
+      const uint32_t n_hi = __dp4a(bytes_gt(w[3], lo_k7, lo_high), 0x80402010u, __dp4a(bytes_gt(w[2], lo_k7, lo_high), 0x08040201u, 0u));
+      uint32_t b_occ = (o_lo >> 7) | ((o_hi >> 7) << 8);                                  // v > MAX_THRESH -> OCC  (collision_checking.cpp:214,220)
+      uint32_t b_nf = (lo == 0) ? 0xFFFFu : ((n_lo >> 7) | ((n_hi >> 7) << 8));           // !(v < MIN_THRESH), i.e. v > MIN_THRESH - 1  (:213,219); nothing is below 0
       if (!inside) b_occ = b_nf = 0;
       b_nf |= b_occ;  // setTo(OCC) runs after setTo(FREE): OCC wins
       // lanes 2k, 2k+1 hold the halves of one word
@@ -138,57 +142,98 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
   }
   __syncthreads();
 
-  // ---- phase A: horizontal span dilations of every staged row
+  // ---- phase V: vertical ORs.  A cell at horizontal distance w of the centre column is covered by the SE rows
+  //      |dy| <= hmax(w), so  dilated(y) = OR_w shift(+-w) of V_hmax(w)(y),  V_h(y) = OR of the plane rows y-h .. y+h.
+  //      One item = one staged word of one output row: the cumulative OR over h = 0 .. r, stored at the distinct hmax
+  //      values (7 for the 21 x 21 disk).  The horizontal work then runs on the 64 output rows only and needs no
+  //      per-input-row span chains: 40 + 55 instructions per output word against 260 for spans-then-OR.
+  for (int it = tid; it < 2 * DT_TH * DT_SW; it += DT_THREADS)
   {
-    const int wl = tid & (DT_TW - 1);
-    uint32_t keep = 0;  // bit w: half width w is one of the SE's
-    for (int w = 0; w <= r; ++w) keep |= (s_var_of_w[w] >= 0 ? 1u : 0u) << w;
-    for (int pr = tid >> 3; pr < 2 * rows_in; pr += DT_THREADS / DT_TW)
+    const int pl = it >= DT_TH * DT_SW, rem = it - pl * (DT_TH * DT_SW);  // rem = rl * DT_SW + wi: rows are contiguous
+    const uint32_t* src = sP + pl * rows_in * DT_SW + r * DT_SW + rem;
+    uint32_t* dst = sV + pl * plane_stride + rem;
+    uint32_t acc = src[0];
+    if (SPEC10)
     {
-      const int pl = pr >= rows_in, rl = pr - pl * rows_in;
-      const uint32_t* src = sP + pr * DT_SW + wl;
-      const uint32_t a = src[0], b = src[1], c = src[2];
-      uint32_t* dst = sH + pl * plane_stride + rl * DT_TW + wl;
-      uint32_t D = b;
-      const int v0 = s_var_of_w[0];
-      if (v0 >= 0) dst[v0 * rows_in * DT_TW] = D;
-      if ((a | b | c) == 0)
-      {
-        for (int v = 0; v < nv; ++v) dst[v * rows_in * DT_TW] = 0;
-        continue;
-      }
-      // build_se lists the half widths in increasing order, so the variant index just counts up
-      uint32_t* o = dst + (v0 >= 0 ? rows_in * DT_TW : 0);
+      int lv = 0;
 #pragma unroll
-      for (int w = 1; w <= GA_MAX_DISK_R; ++w)
+      for (int h = 1; h <= K10_R; ++h)
       {
-        if (w > r) break;
-        D |= __funnelshift_l(a, b, w) | __funnelshift_r(b, c, w);  // cells at distance exactly w, left and right
-        if ((keep >> w) & 1u)
+        acc |= src[h * DT_SW] | src[-h * DT_SW];
+        if (lv < K10_NLVL && K10_LVL_H[lv] == h)  // compile-time after unrolling
         {
-          *o = D;
-          o += rows_in * DT_TW;
+          dst[lv * lvl_stride] = acc;
+          ++lv;
+        }
+      }
+    }
+    else
+    {
+      int lv = 0;
+      if (se.lvl_h[0] == 0)
+      {
+        dst[0] = acc;
+        lv = 1;
+      }
+      for (int h = 1; h <= r; ++h)
+      {
+        acc |= src[h * DT_SW] | src[-h * DT_SW];
+        if (lv < n_lvl && se.lvl_h[lv] == h)
+        {
+          dst[lv * lvl_stride] = acc;
+          ++lv;
         }
       }
     }
   }
   __syncthreads();
 
-  // ---- phase B: vertical OR over the SE rows; one thread = 4 words of one row of one plane
-  for (int it = tid; it < 2 * DT_TH * (DT_TW / 4); it += DT_THREADS)
+  // ---- phase B: horizontal shifts of the vertical ORs, one item = one output word
+  for (int it = tid; it < 2 * DT_TH * DT_TW; it += DT_THREADS)
   {
-    const int q = it & 1, rl = (it >> 1) % DT_TH, pl = (it >> 1) / DT_TH;
-    const uint32_t* base = sH + pl * plane_stride + rl * DT_TW + q * 4;
-    uint4 acc = make_uint4(0, 0, 0, 0);
-    for (int i = 0; i <= 2 * r; ++i)
+    const int wl = it & (DT_TW - 1), rl = (it >> 3) & (DT_TH - 1), pl = it >> 9;
+    static_assert(DT_TW == 8 && DT_TH == 64, "item decoding of phase B");
+    const uint32_t* base = sV + pl * plane_stride + rl * DT_SW + wl;
+    uint32_t out;
+    if (SPEC10)
     {
-      const uint4 h = *reinterpret_cast<const uint4*>(base + (se.row_var[i] * rows_in + i) * DT_TW);
-      acc.x |= h.x;
-      acc.y |= h.y;
-      acc.z |= h.z;
-      acc.w |= h.w;
+      uint32_t a[K10_NLVL], b[K10_NLVL], c[K10_NLVL];
+#pragma unroll
+      for (int l = 0; l < K10_NLVL; ++l)
+      {
+        a[l] = base[l * lvl_stride];
+        b[l] = base[l * lvl_stride + 1];
+        c[l] = base[l * lvl_stride + 2];
+      }
+      out = b[K10_LVL_OF_W[0]];
+#pragma unroll
+      for (int w = 1; w <= K10_R; ++w)
+      {
+        constexpr int dummy = 0;
+        (void)dummy;
+        const int l = K10_LVL_OF_W[w];
+        out |= __funnelshift_l(a[l], b[l], w) | __funnelshift_r(b[l], c[l], w);  // cells at distance exactly w
+      }
     }
-    *reinterpret_cast<uint4*>(sOut + (pl * DT_TH + rl) * DT_TW + q * 4) = acc;
+    else
+    {
+      int cur = se.lvl_of_w[0];
+      uint32_t a = base[cur * lvl_stride], b = base[cur * lvl_stride + 1], c = base[cur * lvl_stride + 2];
+      out = b;
+      for (int w = 1; w <= r; ++w)
+      {
+        const int lv = se.lvl_of_w[w];
+        if (lv != cur)
+        {
+          cur = lv;
+          a = base[cur * lvl_stride];
+          b = base[cur * lvl_stride + 1];
+          c = base[cur * lvl_stride + 2];
+        }
+        out |= __funnelshift_l(a, b, w) | __funnelshift_r(b, c, w);
+      }
+    }
+    sOut[(pl * DT_TH + rl) * DT_TW + wl] = out;
   }
   __syncthreads();
 
@@ -281,11 +326,23 @@ extern "C" int ga_build_safety(ga_ctx* c)
   {
     ga_launch_scope ls(c, GA_K_DILATE);
     const int rows_in = DT_TH + 2 * c->se.r;
-    const size_t smem = sizeof(uint32_t) * ((size_t)2 * rows_in * DT_SW + (size_t)2 * c->se.n_var * rows_in * DT_TW + 2 * DT_TH * DT_TW);
+    const size_t smem = sizeof(uint32_t) * ((size_t)2 * rows_in * DT_SW + (size_t)2 * c->se.n_lvl * DT_TH * DT_SW + 2 * DT_TH * DT_TW);
     const int words = (dim + 31) / 32;
     dim3 grid((words + DT_TW - 1) / DT_TW, (dim + DT_TH - 1) / DT_TH);
-    GA_CUDA(c, cudaFuncSetAttribute(safety_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    safety_kernel<<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo4, hi4);
+    // the shipped 21 x 21 disk has compile-time tables
+    bool spec10 = c->se.r == K10_R && c->se.n_lvl == K10_NLVL;
+    for (int l = 0; spec10 && l < K10_NLVL; ++l) spec10 = c->se.lvl_h[l] == K10_LVL_H[l];
+    for (int w = 0; spec10 && w <= K10_R; ++w) spec10 = c->se.lvl_of_w[w] == K10_LVL_OF_W[w];
+    if (spec10)
+    {
+      GA_CUDA(c, cudaFuncSetAttribute(safety_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      safety_kernel<true><<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo4, hi4);
+    }
+    else
+    {
+      GA_CUDA(c, cudaFuncSetAttribute(safety_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      safety_kernel<false><<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo4, hi4);
+    }
   }
   GA_CUDA(c, cudaGetLastError());
   return GA_OK;
