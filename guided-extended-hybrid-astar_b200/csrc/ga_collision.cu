@@ -521,12 +521,19 @@ struct expand_nodes_param
 };
 __global__ void __launch_bounds__(128)
 expand_param_kernel(coll_view v, expand_view e, const __grid_constant__ expand_nodes_param nodes, int n_nodes,
-                    ga_succ* __restrict__ out, expand_done done)
+                    ga_succ* __restrict__ out, uint8_t* __restrict__ flags, expand_done done)
 {
   const int stride = 2 * e.nb_steer + e.n_ra;
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   expand_epilogue ep{};
-  if (t < (long long)n_nodes * stride) expand_one(v, e, ep, nodes.n, out, t);
+  if (t < (long long)n_nodes * stride)
+  {
+    expand_one(v, e, ep, nodes.n, out, t);
+    // one byte per primitive for callers that only need the collision answer (ga_expand_collect_flags)
+    const ga_succ& s = out[t];
+    flags[t] = (uint8_t)((s.n_poses > 0 ? GA_SUCC_ROLLED : 0) | (s.collision_free ? GA_SUCC_FREE : 0) |
+                         (s.collision_ambiguous ? GA_SUCC_AMBIGUOUS : 0) | (s.valid ? GA_SUCC_VALID : 0));
+  }
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0)
@@ -775,6 +782,8 @@ struct expand_async_state
 {
   ga_succ* h_out[GA_ASYNC_RING];  // mapped pinned, GA_EXPAND_ASYNC_MAX * stride entries each
   ga_succ* d_out[GA_ASYNC_RING];
+  uint8_t* h_flags[GA_ASYNC_RING];  // mapped pinned, one byte per primitive
+  uint8_t* d_flags[GA_ASYNC_RING];
   volatile unsigned* h_flag;      // GA_ASYNC_RING ticket words (mapped)
   unsigned* d_flag;
   unsigned* d_counter;            // GA_ASYNC_RING CTA counters (device)
@@ -790,7 +799,10 @@ void ga_expand_async_free(ga_ctx* c)
   expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
   if (!a) return;
   for (int i = 0; i < GA_ASYNC_RING; ++i)
+  {
     if (a->h_out[i]) cudaFreeHost(a->h_out[i]);
+    if (a->h_flags[i]) cudaFreeHost(a->h_flags[i]);
+  }
   if (a->h_flag) cudaFreeHost((void*)a->h_flag);
   if (a->d_counter) cudaFree(a->d_counter);
   delete a;
@@ -821,6 +833,8 @@ extern "C" int ga_expand_submit(ga_ctx* c, const ga_node* nodes, int n_nodes, in
     {
       GA_CUDA(c, cudaHostAlloc((void**)&a->h_out[i], sizeof(ga_succ) * GA_EXPAND_ASYNC_MAX * (size_t)stride, cudaHostAllocMapped));
       GA_CUDA(c, cudaHostGetDevicePointer((void**)&a->d_out[i], a->h_out[i], 0));
+      GA_CUDA(c, cudaHostAlloc((void**)&a->h_flags[i], GA_EXPAND_ASYNC_MAX * (size_t)stride, cudaHostAllocMapped));
+      GA_CUDA(c, cudaHostGetDevicePointer((void**)&a->d_flags[i], a->h_flags[i], 0));
     }
     GA_CUDA(c, cudaHostAlloc((void**)&a->h_flag, sizeof(unsigned) * GA_ASYNC_RING, cudaHostAllocMapped));
     GA_CUDA(c, cudaHostGetDevicePointer((void**)&a->d_flag, (void*)a->h_flag, 0));
@@ -842,18 +856,18 @@ extern "C" int ga_expand_submit(ga_ctx* c, const ga_node* nodes, int n_nodes, in
   {
     ga_launch_scope ls(c, GA_K_EXPAND);
     const int threads = n_nodes * stride;
-    expand_param_kernel<<<(threads + 127) / 128, 128, 0, c->stream>>>(make_view(c), make_expand_view(c), p, n_nodes, a->d_out[slot], done);
+    expand_param_kernel<<<(threads + 127) / 128, 128, 0, c->stream>>>(make_view(c), make_expand_view(c), p, n_nodes, a->d_out[slot],
+                                                                        a->d_flags[slot], done);
   }
   GA_CUDA(c, cudaGetLastError());
   *ticket = (int)((tk << 2) | (unsigned)slot);
   return GA_OK;
 }
 
-extern "C" int ga_expand_collect(ga_ctx* c, int ticket, ga_succ* out, int* n_nodes)
+static int expand_wait(ga_ctx* c, int ticket, int* slot_out)
 {
-  if (!c) return GA_ERR_ARG;
   expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
-  GA_REQUIRE(c, a != nullptr && out != nullptr, GA_ERR_STATE, "nothing was submitted");
+  GA_REQUIRE(c, a != nullptr, GA_ERR_STATE, "nothing was submitted");
   const int slot = ticket & 3;
   const unsigned tk = (unsigned)ticket >> 2;
   GA_REQUIRE(c, (a->ticket[slot] & 0x3FFFFFFFu) == tk, GA_ERR_ARG, "stale ticket: the ring slot was reused (at most 4 submissions in flight)");
@@ -873,7 +887,30 @@ extern "C" int ga_expand_collect(ga_ctx* c, int ticket, ga_succ* out, int* n_nod
     __builtin_ia32_pause();
 #endif
   }
+  *slot_out = slot;
+  return GA_OK;
+}
+
+extern "C" int ga_expand_collect(ga_ctx* c, int ticket, ga_succ* out, int* n_nodes)
+{
+  if (!c || !out) return GA_ERR_ARG;
+  int slot;
+  const int rc = expand_wait(c, ticket, &slot);
+  if (rc != GA_OK) return rc;
+  expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
   memcpy(out, a->h_out[slot], sizeof(ga_succ) * (size_t)a->n_nodes[slot] * a->stride);
+  if (n_nodes) *n_nodes = a->n_nodes[slot];
+  return GA_OK;
+}
+
+extern "C" int ga_expand_collect_flags(ga_ctx* c, int ticket, uint8_t* flags, int* n_nodes)
+{
+  if (!c || !flags) return GA_ERR_ARG;
+  int slot;
+  const int rc = expand_wait(c, ticket, &slot);
+  if (rc != GA_OK) return rc;
+  expand_async_state* a = static_cast<expand_async_state*>(c->expand_async);
+  memcpy(flags, a->h_flags[slot], (size_t)a->n_nodes[slot] * a->stride);
   if (n_nodes) *n_nodes = a->n_nodes[slot];
   return GA_OK;
 }

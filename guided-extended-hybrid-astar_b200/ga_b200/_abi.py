@@ -94,6 +94,7 @@ SYMBOLS = {
     "ga_expand": (C.c_int, [_P, _P, C.c_int, _P]),
     "ga_expand_submit": (C.c_int, [_P, _P, C.c_int, C.POINTER(C.c_int)]),
     "ga_expand_collect": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int)]),
+    "ga_expand_collect_flags": (C.c_int, [_P, C.c_int, _P, C.POINTER(C.c_int)]),
     "ga_expand_ex": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P, _P]),
     "ga_set_astar_params": (C.c_int, [_P, C.POINTER(AstarParams)]),
     "ga_cart_reset": (C.c_int, [_P, C.c_int]),

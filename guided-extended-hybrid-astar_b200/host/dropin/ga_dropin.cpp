@@ -43,16 +43,37 @@ namespace
 constexpr int NB_STEER = 13;  // HybridAStar::NB_STEER (hybrid_a_star_lib.hpp:48)
 double g_turn_on_point_angle = 90.0;  // config.yml TURN_ON_POINT_ANGLE (read in CollisionChecker::initialize)
 
-// All primitives of one expanded node, rolled out on the host and checked on the device in one launch.
+// All primitives of one expanded node, rolled out on the host and checked on the device in one launch.  The poses live
+// in flat arrays that are reused from expansion to expansion (no allocation per primitive); a MotionPrimitive is only
+// built for the one the caller asks for.
 struct Fan
 {
   bool valid = false;
   double parent[3] = { 0, 0, 0 }, arc_l = 0, motion_res = 0;
-  std::vector<MotionPrimitive> prims;
-  std::vector<double> key;  // steer (move fan) or delta_angle (rear-axis fan)
+  std::vector<double> x, y, yaw;  // poses of all primitives, primitive k = [off[k], off[k + 1])
+  std::vector<int> off;
+  std::vector<double> key;        // steer (move fan) or delta_angle (rear-axis fan)
   std::vector<int> dir;
   std::vector<int> first_hit;
   int last = -1;  // primitive handed out last (checkPathCollision is asked about it next)
+  int size() const { return (int)key.size(); }
+  int count(int k) const { return off[(size_t)k + 1] - off[(size_t)k]; }
+  void clear()
+  {
+    x.clear();
+    y.clear();
+    yaw.clear();
+    off.assign(1, 0);
+    key.clear();
+    dir.clear();
+    last = -1;
+  }
+  void close_prim(double k, int d)
+  {
+    off.push_back((int)x.size());
+    key.push_back(k);
+    dir.push_back(d);
+  }
 };
 Fan g_move_fan, g_ra_fan;
 std::vector<double> g_x, g_y, g_yaw;
@@ -60,39 +81,26 @@ std::vector<int> g_seg;
 
 void check_fan(Fan& f)
 {
-  g_x.clear();
-  g_y.clear();
-  g_yaw.clear();
-  g_seg.assign(1, 0);
-  for (const MotionPrimitive& p : f.prims)
-  {
-    g_x.insert(g_x.end(), p.x_list_.begin(), p.x_list_.end());
-    g_y.insert(g_y.end(), p.y_list_.begin(), p.y_list_.end());
-    g_yaw.insert(g_yaw.end(), p.yaw_list_.begin(), p.yaw_list_.end());
-    g_seg.push_back((int)g_x.size());
-  }
-  f.first_hit.assign(f.prims.size(), -1);
-  if (!g_x.empty())
-    check(ga_check_poses(ctx(), g_x.data(), g_y.data(), g_yaw.data(), (int)g_x.size(), g_seg.data(), (int)f.prims.size(), 0,
+  f.first_hit.assign((size_t)f.size(), -1);
+  if (!f.x.empty())
+    check(ga_check_poses(ctx(), f.x.data(), f.y.data(), f.yaw.data(), (int)f.x.size(), f.off.data(), f.size(), 0,
                          f.first_hit.data()));
-  g_stats.poses_checked += g_x.size();
+  g_stats.poses_checked += f.x.size();
   ++g_stats.expansions_prefetched;
 }
 
-inline bool same_list(const std::vector<double>& a, const std::vector<double>& b)
-{
-  return a.size() == b.size() && (a.empty() || std::memcmp(a.data(), b.data(), a.size() * sizeof(double)) == 0);
-}
 // index of the fan primitive whose pose lists are exactly (x, y, yaw), or -1
 int match_fan(const Fan& f, const std::vector<double>& x, const std::vector<double>& y, const std::vector<double>& yaw)
 {
   if (!f.valid) return -1;
   auto is = [&](int k) {
-    const MotionPrimitive& p = f.prims[(size_t)k];
-    return same_list(p.x_list_, x) && same_list(p.y_list_, y) && same_list(p.yaw_list_, yaw);
+    const size_t n = (size_t)f.count(k), o = (size_t)f.off[(size_t)k];
+    return x.size() == n && y.size() == n && yaw.size() == n &&
+           (n == 0 || (std::memcmp(f.x.data() + o, x.data(), n * 8) == 0 && std::memcmp(f.y.data() + o, y.data(), n * 8) == 0 &&
+                       std::memcmp(f.yaw.data() + o, yaw.data(), n * 8) == 0));
   };
   if (f.last >= 0 && is(f.last)) return f.last;
-  for (int k = 0; k < (int)f.prims.size(); ++k)
+  for (int k = 0; k < f.size(); ++k)
     if (is(k)) return k;
   return -1;
 }
@@ -118,23 +126,69 @@ struct PoseKeyHash
     return (size_t)h;
   }
 };
-struct FanAnswers
+// answers of one fan, filed under the pose bits of the node it belongs to: open addressing in one preallocated array
+// (no allocation per entry), validity by epoch (forgetting everything = one increment)
+struct FanSlot
 {
+  PoseKey key;
   double motion_res;
+  uint32_t epoch;
   int8_t ans[2 * NB_STEER];  // 0 collides, 1 free, 2 ask again (near a cell / yaw-bin edge)
 };
-std::unordered_map<PoseKey, FanAnswers, PoseKeyHash> g_lookahead;
+class FanTable
+{
+public:
+  FanTable() : slots_(size_t(1) << 19), mask_((size_t(1) << 19) - 1) {}
+  void reset()
+  {
+    ++epoch_;
+    count_ = 0;
+  }
+  FanSlot* find(const PoseKey& k)
+  {
+    for (size_t i = PoseKeyHash()(k) & mask_;; i = (i + 1) & mask_)
+    {
+      FanSlot& s = slots_[i];
+      if (s.epoch != epoch_) return nullptr;
+      if (s.key == k) return &s;
+    }
+  }
+  FanSlot* insert(const PoseKey& k)
+  {
+    if (count_ * 2 > slots_.size()) reset();  // cannot happen within one search of the reference's size; stay bounded
+    for (size_t i = PoseKeyHash()(k) & mask_;; i = (i + 1) & mask_)
+    {
+      FanSlot& s = slots_[i];
+      if (s.epoch != epoch_)
+      {
+        s.epoch = epoch_;
+        s.key = k;
+        ++count_;
+        return &s;
+      }
+      if (s.key == k) return &s;
+    }
+  }
+
+private:
+  std::vector<FanSlot> slots_;
+  size_t mask_, count_ = 0;
+  uint32_t epoch_ = 1;
+};
+FanTable g_lookahead;
 struct Pending
 {
-  bool in_flight = false;
   int ticket = 0, n = 0;
   PoseKey key[2 * NB_STEER];
   double motion_res[2 * NB_STEER];
-} g_pending;
+};
+constexpr int MAX_PENDING = 3;  // ga_expand_submit keeps four submissions alive
+Pending g_pend[MAX_PENDING];
+int g_pend_head = 0, g_pend_count = 0;  // oldest submission, number in flight
 bool g_lookahead_on = true;
 bool g_expand_params_set = false;
 double g_expand_arc_l = 0, g_yaw_res_deg = 10.0;
-std::vector<ga_succ> g_succ;
+std::vector<uint8_t> g_flags;
 
 inline PoseKey key_of(double x, double y, double yaw)
 {
@@ -147,13 +201,14 @@ inline PoseKey key_of(double x, double y, double yaw)
 
 void lookahead_reset()
 {
-  if (g_pending.in_flight)
+  while (g_pend_count > 0)
   {
-    g_succ.resize((size_t)32 * (size_t)ga_expand_stride(ctx()));
-    ga_expand_collect(ctx(), g_pending.ticket, g_succ.data(), nullptr);  // drain; results are dropped
-    g_pending.in_flight = false;
+    g_flags.resize((size_t)32 * (size_t)ga_expand_stride(ctx()));
+    ga_expand_collect_flags(ctx(), g_pend[g_pend_head].ticket, g_flags.data(), nullptr);  // drain; results are dropped
+    g_pend_head = (g_pend_head + 1) % MAX_PENDING;
+    --g_pend_count;
   }
-  g_lookahead.clear();
+  g_lookahead.reset();
 }
 
 inline unsigned long long now_ns()
@@ -162,28 +217,26 @@ inline unsigned long long now_ns()
              std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// files the answers of the OLDEST submission still in flight (waits for it if it has not finished)
 void lookahead_harvest()
 {
-  if (!g_pending.in_flight) return;
+  if (g_pend_count == 0) return;
+  Pending& g_pending = g_pend[g_pend_head];
+  g_pend_head = (g_pend_head + 1) % MAX_PENDING;
+  --g_pend_count;
   const unsigned long long t0 = now_ns();
   const int stride = ga_expand_stride(ctx());
-  g_succ.resize((size_t)32 * (size_t)stride);
+  g_flags.resize((size_t)32 * (size_t)stride);
   int n = 0;
-  check(ga_expand_collect(ctx(), g_pending.ticket, g_succ.data(), &n));
+  check(ga_expand_collect_flags(ctx(), g_pending.ticket, g_flags.data(), &n));
   const unsigned long long t1 = now_ns();
   g_stats.ns_collect += t1 - t0;
-  g_pending.in_flight = false;
-  if (g_lookahead.size() > (1u << 21)) g_lookahead.clear();
   for (int j = 0; j < n && j < g_pending.n; ++j)
   {
-    FanAnswers a;
-    a.motion_res = g_pending.motion_res[j];
-    for (int k = 0; k < 2 * NB_STEER; ++k)
-    {
-      const ga_succ& s = g_succ[(size_t)j * stride + k];
-      a.ans[k] = s.collision_ambiguous ? 2 : (s.collision_free ? 1 : 0);
-    }
-    g_lookahead[g_pending.key[j]] = a;
+    FanSlot* a = g_lookahead.insert(g_pending.key[j]);
+    a->motion_res = g_pending.motion_res[j];
+    const uint8_t* f = g_flags.data() + (size_t)j * stride;
+    for (int k = 0; k < 2 * NB_STEER; ++k) a->ans[k] = (f[k] & GA_SUCC_AMBIGUOUS) ? 2 : ((f[k] & GA_SUCC_FREE) ? 1 : 0);
   }
   g_stats.ns_harvest += now_ns() - t1;
   g_stats.lookahead_launches++;
@@ -201,18 +254,20 @@ void lookahead_submit(const Fan& f, double arc_l)
     g_expand_params_set = true;
     g_expand_arc_l = arc_l;
   }
+  if (g_pend_count == MAX_PENDING) lookahead_harvest();
+  Pending& g_pending = g_pend[(g_pend_head + g_pend_count) % MAX_PENDING];
   ga_node nodes[2 * NB_STEER];
   int n = 0;
   const int ad = AStar::astar_dim_;
-  for (size_t k = 0; k < f.prims.size() && n < 2 * NB_STEER; ++k)
+  for (int k = 0; k < f.size() && n < 2 * NB_STEER; ++k)
   {
-    const MotionPrimitive& p = f.prims[k];
-    if (f.first_hit[k] >= 0 || p.x_list_.empty()) continue;
-    const double x = p.x_list_.back(), y = p.y_list_.back(), yaw = p.yaw_list_.back();
+    if (f.first_hit[(size_t)k] >= 0 || f.count(k) == 0) continue;
+    const size_t e = (size_t)f.off[(size_t)k + 1] - 1;
+    const double x = f.x[e], y = f.y[e], yaw = f.yaw[e];
     const int xi = static_cast<int>(x * grid_tf::con2star_), yi = static_cast<int>(y * grid_tf::con2star_);  // mapCont2Disc
     if (!(-1 < xi && xi < ad && -1 < yi && yi < ad)) continue;
     const PoseKey key = key_of(x, y, yaw);
-    if (g_lookahead.find(key) != g_lookahead.end()) continue;
+    if (g_lookahead.find(key) != nullptr) continue;
     const double mr = AStar::motion_res_map_(yi, xi);  // the resolution hAstarCore will roll this node out with (:1483)
     nodes[n] = ga_node{ x, y, yaw, mr, 0, 0 };
     g_pending.key[n] = key;
@@ -224,7 +279,7 @@ void lookahead_submit(const Fan& f, double arc_l)
   check(ga_expand_submit(c, nodes, n, &g_pending.ticket));
   g_stats.ns_submit += now_ns() - t0;
   g_pending.n = n;
-  g_pending.in_flight = true;
+  ++g_pend_count;
 }
 }  // namespace
 void setLookahead(bool on)
@@ -271,43 +326,59 @@ void Vehicle::move(Pose<double>& pose, double distance, double steer)  // :34-43
 
 namespace
 {
-MotionPrimitive roll_out(const Pose<double>& pose, double arc_l, double motion_res, int direction, double steer)  // :100-122
+// Vehicle::move_car_some_steps (:100-122) into the fan's flat arrays
+void roll_out(Fan& f, const Pose<double>& pose, double arc_l, double motion_res, int direction, double steer)
 {
   const auto n = static_cast<size_t>(round(arc_l / motion_res));
-  MotionPrimitive mp = MotionPrimitive(n);
   Pose<double> p = pose;
   for (size_t i = 0; i < n; ++i)
   {
     Vehicle::move(p, motion_res * direction, steer);
-    mp.x_list_.push_back(p.x);
-    mp.y_list_.push_back(p.y);
-    mp.yaw_list_.push_back(p.yaw);
-    mp.dir_list_.push_back(direction);
-    mp.delta_list_.push_back(steer);
+    f.x.push_back(p.x);
+    f.y.push_back(p.y);
+    f.yaw.push_back(p.yaw);
   }
-  return mp;
+  f.close_prim(steer, direction);
 }
 
-MotionPrimitive rotate_on_axis(const Pose<double>& pose, double delta_angle, double yaw_res_coll)  // :45-98
+// Vehicle::turn_on_rear_axis (:45-98) into the fan's flat arrays
+void rotate_on_axis(Fan& f, const Pose<double>& pose, double delta_angle, double yaw_res_coll)
 {
-  MotionPrimitive mp;
   double yaw = pose.yaw;
   const double goal_yaw = util::constrainAngleMinPIPlusPi(yaw + delta_angle);
   const double step = yaw_res_coll * util::TO_RAD;
-  mp.yaw_list_.reserve((size_t)ceil(std::abs(delta_angle) / step));
   double margin;
   do
   {
     yaw = util::constrainAngleMinPIPlusPi(yaw + util::sgn(delta_angle) * step);
-    mp.yaw_list_.push_back(yaw);
+    f.x.push_back(pose.x);
+    f.y.push_back(pose.y);
+    f.yaw.push_back(yaw);
     margin = std::abs(util::getAngleDiff(yaw, goal_yaw));
   } while (margin >= step);
-  if (mp.yaw_list_.back() != goal_yaw) mp.yaw_list_.back() = goal_yaw;
-  mp.nb_elements_ = mp.yaw_list_.size();
-  mp.x_list_.resize(mp.nb_elements_, pose.x);
-  mp.y_list_.resize(mp.nb_elements_, pose.y);
-  mp.dir_list_.resize(mp.nb_elements_, 1);
-  mp.delta_list_.resize(mp.nb_elements_, delta_angle > 0 ? util::PI / 2.0 : -util::PI / 2.0);
+  if (f.yaw.back() != goal_yaw) f.yaw.back() = goal_yaw;
+  f.close_prim(delta_angle, 1);
+}
+
+// the MotionPrimitive the reference's function returns, from primitive k of a fan
+MotionPrimitive make_primitive(const Fan& f, int k, bool rear_axis)
+{
+  const size_t n = (size_t)f.count(k), o = (size_t)f.off[(size_t)k];
+  MotionPrimitive mp;
+  mp.x_list_.assign(f.x.begin() + (long)o, f.x.begin() + (long)(o + n));
+  mp.y_list_.assign(f.y.begin() + (long)o, f.y.begin() + (long)(o + n));
+  mp.yaw_list_.assign(f.yaw.begin() + (long)o, f.yaw.begin() + (long)(o + n));
+  mp.nb_elements_ = n;
+  if (rear_axis)
+  {
+    mp.dir_list_.assign(n, 1);
+    mp.delta_list_.assign(n, f.key[(size_t)k] > 0 ? util::PI / 2.0 : -util::PI / 2.0);
+  }
+  else
+  {
+    mp.dir_list_.assign(n, f.dir[(size_t)k]);
+    mp.delta_list_.assign(n, f.key[(size_t)k]);
+  }
   return mp;
 }
 }  // namespace
@@ -322,51 +393,48 @@ MotionPrimitive Vehicle::move_car_some_steps(const Pose<double>& pose, double ar
   {
     // the fan HybridAStar::setNeighbors is about to ask for (hybrid_a_star_lib.cpp:492-510): calcSteeringInputs'
     // 13 steers (:115-129) x directions {+1, -1}
-    f.prims.clear();
-    f.key.clear();
-    f.dir.clear();
+    f.clear();
     const double delta_steer = (2 * max_steer_) / static_cast<double>(NB_STEER - 1);
     const int side = NB_STEER / 2;
     for (int i = -side; i <= side; ++i)
-      for (const int d : { 1, -1 })
-      {
-        const double st = i * delta_steer;
-        f.prims.push_back(roll_out(pose, arc_l, motion_res, d, st));
-        f.key.push_back(st);
-        f.dir.push_back(d);
-      }
+      for (const int d : { 1, -1 }) roll_out(f, pose, arc_l, motion_res, d, i * delta_steer);
     f.parent[0] = pose.x;
     f.parent[1] = pose.y;
     f.parent[2] = pose.yaw;
     f.arc_l = arc_l;
     f.motion_res = motion_res;
     f.valid = true;
-    f.last = -1;
     g_ra_fan.valid = false;
     // answers: from the look-ahead when this node's fan was checked while its parent was expanded, else now
-    lookahead_harvest();
-    const auto hit = g_lookahead_on ? g_lookahead.find(key_of(pose.x, pose.y, pose.yaw)) : g_lookahead.end();
-    if (hit != g_lookahead.end() && hit->second.motion_res == motion_res)
+    // (submissions still in flight are only waited for when this node's answers are not on file yet)
+    const PoseKey me = key_of(pose.x, pose.y, pose.yaw);
+    const FanSlot* hit = g_lookahead_on ? g_lookahead.find(me) : nullptr;
+    while (hit == nullptr && g_pend_count > 0)
     {
-      f.first_hit.assign(f.prims.size(), -1);
+      lookahead_harvest();
+      hit = g_lookahead.find(me);
+    }
+    if (hit != nullptr && hit->motion_res == motion_res)
+    {
+      f.first_hit.assign((size_t)f.size(), -1);
       g_x.clear();
       g_y.clear();
       g_yaw.clear();
       g_seg.assign(1, 0);
       std::vector<int> again;
-      for (size_t k = 0; k < f.prims.size(); ++k)
+      for (int k = 0; k < f.size(); ++k)
       {
-        const int8_t a = hit->second.ans[k];
+        const int8_t a = hit->ans[k];
         if (a == 0)
-          f.first_hit[k] = 0;
+          f.first_hit[(size_t)k] = 0;
         else if (a == 2)
         {
-          const MotionPrimitive& p = f.prims[k];
-          g_x.insert(g_x.end(), p.x_list_.begin(), p.x_list_.end());
-          g_y.insert(g_y.end(), p.y_list_.begin(), p.y_list_.end());
-          g_yaw.insert(g_yaw.end(), p.yaw_list_.begin(), p.yaw_list_.end());
+          const long o = f.off[(size_t)k], e = f.off[(size_t)k + 1];
+          g_x.insert(g_x.end(), f.x.begin() + o, f.x.begin() + e);
+          g_y.insert(g_y.end(), f.y.begin() + o, f.y.begin() + e);
+          g_yaw.insert(g_yaw.end(), f.yaw.begin() + o, f.yaw.begin() + e);
           g_seg.push_back((int)g_x.size());
-          again.push_back((int)k);
+          again.push_back(k);
         }
       }
       if (!again.empty())
@@ -383,14 +451,17 @@ MotionPrimitive Vehicle::move_car_some_steps(const Pose<double>& pose, double ar
       check_fan(f);
     lookahead_submit(f, arc_l);
   }
-  for (int k = 0; k < (int)f.prims.size(); ++k)
+  for (int k = 0; k < f.size(); ++k)
     if (f.dir[(size_t)k] == direction && f.key[(size_t)k] == steer)
     {
       f.last = k;
-      return f.prims[(size_t)k];
+      return make_primitive(f, k, false);
     }
   f.last = -1;  // a primitive outside the fan: rolled out alone, checked by its own launch
-  return roll_out(pose, arc_l, motion_res, direction, steer);
+  Fan one;
+  one.clear();
+  roll_out(one, pose, arc_l, motion_res, direction, steer);
+  return make_primitive(one, 0, false);
 }
 
 MotionPrimitive Vehicle::turn_on_rear_axis(const Pose<double>& pose, double delta_angle, double yaw_res_coll)
@@ -401,34 +472,32 @@ MotionPrimitive Vehicle::turn_on_rear_axis(const Pose<double>& pose, double delt
   if (!same)
   {
     // the rotations setNeighbors tries (hybrid_a_star_lib.cpp:512-533), same loop arithmetic
-    f.prims.clear();
-    f.key.clear();
-    f.dir.clear();
+    f.clear();
     const double a = g_turn_on_point_angle * util::TO_RAD;
     if (a > 1e-6)
       for (double d = -2 * util::PI + a; d <= 2 * util::PI - a; d += a)
       {
         if (d == 0) continue;
-        f.prims.push_back(rotate_on_axis(pose, d, yaw_res_coll));
-        f.key.push_back(d);
-        f.dir.push_back(1);
+        rotate_on_axis(f, pose, d, yaw_res_coll);
       }
     f.parent[0] = pose.x;
     f.parent[1] = pose.y;
     f.parent[2] = pose.yaw;
     f.motion_res = yaw_res_coll;
     f.valid = true;
-    f.last = -1;
     check_fan(f);
   }
-  for (int k = 0; k < (int)f.prims.size(); ++k)
+  for (int k = 0; k < f.size(); ++k)
     if (f.key[(size_t)k] == delta_angle)
     {
       f.last = k;
-      return f.prims[(size_t)k];
+      return make_primitive(f, k, true);
     }
   f.last = -1;
-  return rotate_on_axis(pose, delta_angle, yaw_res_coll);
+  Fan one;
+  one.clear();
+  rotate_on_axis(one, pose, delta_angle, yaw_res_coll);
+  return make_primitive(one, 0, true);
 }
 
 // ---- host mirrors of the astar-side maps that still have to reach the device ------------------------------

@@ -238,6 +238,10 @@ typedef struct
  * then overlaps the caller's own work instead of sitting on its critical path. */
 GA_API int ga_expand_submit(ga_ctx* ctx, const ga_node* nodes, int n_nodes, int* ticket);
 GA_API int ga_expand_collect(ga_ctx* ctx, int ticket, ga_succ* out, int* n_nodes);
+/* the same wait, but only one byte per primitive comes back (n_nodes * ga_expand_stride bytes) -- all a caller needs
+ * that rolls the poses out itself and wants the collision answers (the drop-in's look-ahead) */
+enum { GA_SUCC_ROLLED = 1, GA_SUCC_FREE = 2, GA_SUCC_AMBIGUOUS = 4, GA_SUCC_VALID = 8 };
+GA_API int ga_expand_collect_flags(ga_ctx* ctx, int ticket, uint8_t* flags, int* n_nodes);
 GA_API int ga_expand_ex(ga_ctx* ctx, const ga_node* nodes, int n_nodes, int slot, ga_succ* out, ga_succ_cost* out_cost,
                         double* out_parent_prox);
 
