@@ -355,7 +355,14 @@ def run_plan_leg(args, local_rank, rank):
     import ga_plan_py as gp
     if not (os.path.exists(gp.LIBS["b200"]) and os.path.exists(gp.LIBS["ref"])):
         return {"unavailable": "oracle/_ref plan libraries not built (need /root/reference at build time)"}
+    from ga_b200.sharding import shard_queries
     procs, nq = args.plan_procs, args.plan_queries
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    # the job: --plan-total queries (default: a bounded sample of procs x nq per GPU; 4096 = BASELINE config 5), whole
+    # maps per rank (ga_b200/sharding.py), each rank's block split over its planner processes
+    total = args.plan_total if args.plan_total > 0 else world * procs * nq
+    ids = shard_queries(total, world, rank) if args.plan_total > 0 else np.arange(rank * procs * nq, (rank + 1) * procs * nq)
+    blocks = [b for b in np.array_split(ids, procs) if len(b)]
     tmp = tempfile.mkdtemp(prefix="ga_plan_")
 
     # Several planner PROCESSES on one GPU only run concurrently under CUDA MPS (otherwise the driver time-slices whole
@@ -384,10 +391,10 @@ def run_plan_leg(args, local_rank, rank):
             env = dict(mps_env, CUDA_VISIBLE_DEVICES="0", GA_DEVICE="0")
         else:
             env = dict(os.environ, GA_DEVICE=str(local_rank))
-        for w in range(procs):
+        for w, blk in enumerate(blocks):
             out = os.path.join(tmp, "%s_%d_%d.npz" % (tag, rank, w))
             cmd = [sys.executable, os.path.join(ROOT, "oracle", "ga_plan_py.py"), "--arm", arm, "--synthetic", "2048",
-                   "--seed", str(50000 + rank * 64 + w), "--queries", str(nq), "--no-trace", "--timeout-ms", "2000", "--out", out]
+                   "--query-ids", str(int(blk[0])), str(int(blk[-1]) + 1), "--no-trace", "--timeout-ms", "2000", "--out", out]
             ps.append((subprocess.Popen(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE), out))
         tot, found, exp, env_ms, search_ms, n = [], 0, 0, 0.0, 0.0, 0
         for p, out in ps:
@@ -406,7 +413,8 @@ def run_plan_leg(args, local_rank, rank):
         return {"queries_per_s": n / (max(tot) * 1e-3), "queries": n, "processes": procs, "found": found,
                 "expanded_nodes": exp, "env_ms_per_query": env_ms / n, "search_ms_per_query": search_ms / n}
 
-    out = {"workload": "%d planner processes x %d queries on synthetic 2048^2 maps (one map per process), shipped config" % (procs, nq),
+    out = {"workload": "queries %d..%d of a %d-query job on synthetic 2048^2 maps (64 queries per map, shipped config), %d planner "
+                       "processes on this rank" % (int(ids[0]) if len(ids) else 0, int(ids[-1]) if len(ids) else 0, total, len(blocks)),
            "b200": run_arm("b200", "b")}
     out["b200"]["mps"] = mps_env is not None
     if mps_note:
@@ -575,19 +583,45 @@ def run_collision_leg(env, args, ga):
     dt = (time.perf_counter() - t0) / reps
     out = {"pose_checks_per_s": n / dt, "poses_per_launch": n, "segments": len(seg) - 1, "disks": 3,
            "free_segments": float((hits < 0).mean())}
+    # kernel-level figure of the same batch: device time of check_poses_kernel alone (CUDA events around the launch)
+    # against the bytes it must move -- 24 B pose in, one 32 B sector per disk lookup (random gathers), 4 B per segment out
+    ctx.prof_reset()
+    ctx.prof_enable(True)
+    for _ in range(reps):
+        cc.checkSegments(x, y, yaw, seg)
+    ctx.sync()
+    ctx.prof_enable(False)
+    k_ms = ctx.prof_get(_abi.K_COLLISION)[0] / reps
+    sector_bytes = n * (24 + 3 * 32) + 4 * (len(seg) - 1)
+    hbm_peak = load_peaks()[0]
+    out["check_poses_kernel"] = {"ms": k_ms, "pose_checks_per_s_device": n / (k_ms * 1e-3),
+                                 "algorithmic_bytes_per_pose": 24 + 3 + 4 / seg_len, "sector_bytes_per_pose": 24 + 3 * 32 + 4 / seg_len,
+                                 "achieved_gbs_sectors": sector_bytes / (k_ms * 1e-3) / 1e9,
+                                 "frac_of_hbm_peak": sector_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
+                                 "note": "L2 / DRAM random-access bound: 3 scattered byte gathers per pose, each a 32 B sector; the host "
+                                         "API figure above is PCIe bound (24 B per pose over the link)"}
     # expansion batches
     cc.setExpandParams()
     nodes = np.zeros(4096, _abi.NODE_DTYPE)
     nodes["x"], nodes["y"] = rng.uniform(20, ext - 20, 4096), rng.uniform(20, ext - 20, 4096)
     nodes["yaw"], nodes["motion_res"], nodes["with_rear_axis"] = rng.uniform(-3.14, 3.14, 4096), 0.3125, 1
-    succ = cc.expandNodes(nodes)
+    succ = cc.expandNodes(nodes, exact=False)
     ctx.sync()
     t0 = time.perf_counter()
     for _ in range(reps):
-        succ = cc.expandNodes(nodes)
+        succ = cc.expandNodes(nodes, exact=False)
     ctx.sync()
     dt = (time.perf_counter() - t0) / reps
     poses = int(succ["n_poses"].sum())
+    ctx.prof_reset()
+    ctx.prof_enable(True)
+    for _ in range(reps):
+        cc.expandNodes(nodes, exact=False)
+    ctx.sync()
+    ctx.prof_enable(False)
+    e_ms = ctx.prof_get(_abi.K_EXPAND)[0] / reps
+    out["expand_kernel"] = {"ms": e_ms, "nodes_per_s_device": len(nodes) / (e_ms * 1e-3), "pose_checks_per_s_device": poses / (e_ms * 1e-3),
+                            "note": "fp64 rollout (sin / cos / tan per step) + 3 gathers per pose; compute bound on the fp64 pipe"}
     out.update({"expand_nodes_per_s": len(nodes) / dt, "expand_primitives_per_s": int((succ["n_poses"] > 0).sum()) / dt,
                 "expand_pose_checks_per_s": poses / dt, "expand_batch_nodes": len(nodes), "ushift": True})
     # (c) proximity scoring of sampled analytic-expansion paths: host pose lists
@@ -658,6 +692,7 @@ def main():
     ap.add_argument("--no-plan", action="store_true", help="skip the plan queries/s leg")
     ap.add_argument("--plan-procs", type=int, default=4, help="planner processes per GPU of the plan leg (fixed per GPU: weak scaling)")
     ap.add_argument("--plan-queries", type=int, default=6, help="queries per planner process of the plan leg")
+    ap.add_argument("--plan-total", type=int, default=0, help="plan leg: total queries of the job over all ranks (4096 = BASELINE config 5); 0 = procs x queries per GPU")
     ap.add_argument("--e2e-threads", type=int, default=8, help="planner contexts / host threads of the e2e leg")
     ap.add_argument("--no-mps", action="store_true", help="plan leg: do not start a CUDA MPS daemon for the planner processes")
     ap.add_argument("--plan-only", action="store_true", help="run only the plan leg (development)")

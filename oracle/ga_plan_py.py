@@ -278,6 +278,33 @@ def run_synthetic(pl, dim, seed, n_queries, trace=True):
     return results
 
 
+def run_query_range(pl, dim, first_id, last_id, trace=False):
+    """BASELINE config 5 proper: the queries [first_id, last_id) of the 4096-query job.  Query q lives on the synthetic
+    map of seed 50000 + q // 64 (64 start / goal pairs per map, SURVEY.md 8(d)) and is the (q % 64)-th pair sampled on it;
+    a planner process walks its block of ids map by map (ga_b200/sharding.py decides who gets which block)."""
+    sys.path.insert(0, os.path.join(ROOT, "guided-extended-hybrid-astar_b200"))
+    from ga_b200.synth import gen_map
+    from ga_b200.sharding import QUERIES_PER_MAP, map_seed
+    results, cur_seed, pairs = [], None, None
+    for q in range(first_id, last_id):
+        seed = map_seed(q)
+        t0 = time.perf_counter()
+        if seed != cur_seed:
+            pl.reinit((0.0, 0.0), dim)
+            pl.pass_local_map(gen_map(dim, seed), 0, 0)
+            pl.process_safety()
+            pairs = sample_queries(pl, dim, seed, QUERIES_PER_MAP)
+            cur_seed = seed
+            t0 = time.perf_counter()  # map generation and the sampling of the pairs are the job's input, not planner work
+        ego, goal = pairs[q % QUERIES_PER_MAP]
+        n_guid, env_ms = pl.recalc_env(ego, goal)
+        r = pl.plan(ego, ego, goal, True, trace)
+        r.update(env_ms=env_ms, n_guidance_path=n_guid, query_ms=(time.perf_counter() - t0) * 1e3, ego=ego, goal=goal,
+                 query_id=q)
+        results.append(r)
+    return results
+
+
 def _flatten(prefix, r, out):
     for k, v in r.items():
         out[prefix + k] = np.asarray(v)
@@ -307,6 +334,7 @@ def main():
     ap.add_argument("--synthetic", type=int)
     ap.add_argument("--seed", type=int, default=50000)
     ap.add_argument("--queries", type=int, default=1)
+    ap.add_argument("--query-ids", type=int, nargs=2, help="config 5: run the queries [a, b) of the sharded job on --synthetic maps")
     ap.add_argument("--ushift", action="store_true")
     ap.add_argument("--mode", type=int, default=0, help="arm b200: 0 reference-order heuristic, 1 GPU fixed point")
     ap.add_argument("--timeout-ms", type=int, default=10**9)
@@ -330,7 +358,10 @@ def main():
             out["motion_res"] = pl.get_map(2)
             out["astar_grid"] = pl.get_map(0)
     else:
-        rs = run_synthetic(pl, a.synthetic, a.seed, a.queries, trace=not a.no_trace)
+        if a.query_ids:
+            rs = run_query_range(pl, a.synthetic, a.query_ids[0], a.query_ids[1], trace=not a.no_trace)
+        else:
+            rs = run_synthetic(pl, a.synthetic, a.seed, a.queries, trace=not a.no_trace)
         out["n_queries"] = np.array(len(rs))
         for i, r in enumerate(rs):
             _flatten("q%d_" % i, r, out)
