@@ -240,6 +240,33 @@ def run_scenario(pl, name, trace=True, do_plan=True):
     return res
 
 
+def run_patch_move(pl, name):
+    """config 3's patch move: a first cycle on the scenario (environment built), then the ego has moved and a new patch is
+    created around it (planning.py:668-715 -> create_patch -> HybridAStar::reinit -> AStar::reinit, a_star.cpp:70-99):
+    h_prox_arr_ / motion_res_map_ are carried over the move (util::saveTemp + copyPatch2Patch), the next environment
+    build and heuristic run on the carried field."""
+    gmap, start, goal = load_scenario(name)
+    first = run_scenario(pl, name, trace=False, do_plan=False)
+    ego2 = np.array([start[0] - 9.0, start[1] + 13.0, start[2]])
+    pl.create_patch(ego2, goal)
+    ego, g = pl.to_patch(ego2), pl.to_patch(goal)
+    out = dict(first_patch_dim=first["patch_dim"], patch_dim=pl.patch_dim, origin=pl.origin,
+               carried_h_prox=pl.get_map(1), carried_motion_res=pl.get_map(2))
+    if pl.arm == "b200":
+        d = pl.L.gap_astar_dim()
+        for which, key in ((1, "device_h_prox"), (2, "device_motion_res")):
+            a = np.zeros((d, d))
+            pl._ck(pl.L.gap_b200_device_map(which, _p(a)))
+            out[key] = a
+    pl.insert_window_sim(local_window(gmap, ego2), ego)
+    pl.process_safety()
+    n_guid, env_ms = pl.recalc_env(ego, g)
+    h = pl.heuristic(0)
+    out.update(n_guidance_path=n_guid, h_prox=pl.get_map(1), motion_res=pl.get_map(2), hg_cost=h["cost"], hg_parent=h["parent"],
+               hg_flags=h["flags"], hg_dist=h["dist"])
+    return out
+
+
 def sample_queries(pl, dim, seed, n, margin_cells=101):
     """start / goal poses on a synthetic map: uniform in metres, yaw U[-pi, pi), until checkPose passes
     (SURVEY.md 8(d)); the ego keeps 101 astar cells from the far border (Voronoi window)."""
@@ -341,6 +368,7 @@ def main():
     ap.add_argument("--no-trace", action="store_true")
     ap.add_argument("--heuristic", action="store_true", help="also store the heuristic planes")
     ap.add_argument("--no-lookahead", action="store_true", help="arm b200: check every fan synchronously")
+    ap.add_argument("--patch-move", action="store_true", help="with --scenario: first cycle, then a patch move and a second environment build")
     ap.add_argument("--out", required=True)
     a = ap.parse_args()
     pl = Planner(a.arm, is_ushift=a.ushift, timeout_ms=a.timeout_ms)
@@ -348,7 +376,11 @@ def main():
     if a.arm == "b200" and a.no_lookahead:
         pl._ck(pl.L.gap_b200_set_lookahead(0))
     out = dict(init_s=np.array(pl.init_s))
-    if a.scenario:
+    if a.scenario and a.patch_move:
+        if a.arm == "b200":
+            pl.L.gap_b200_device_map.argtypes = [C.c_int, C.c_void_p]
+        _flatten("", run_patch_move(pl, a.scenario), out)
+    elif a.scenario:
         r = run_scenario(pl, a.scenario, trace=not a.no_trace)
         _flatten("", r, out)
         if a.heuristic:

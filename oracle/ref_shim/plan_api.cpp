@@ -404,6 +404,15 @@ int gap_b200_set_lookahead(int on)
   GAP_TRY({ ga_dropin::setLookahead(on != 0); })
 }
 long long gap_b200_launches() { return ga_launch_count(ga_dropin::ctx()); }
+// the DEVICE copy of a map (1 h_prox_arr_, 2 motion_res_map_, 3 movement_cost_map_): what the kernels read
+int gap_b200_device_map(int which, double* dst)
+{
+  GAP_TRY({
+    const size_t n = (size_t)AStar::astar_dim_ * AStar::astar_dim_;
+    const int id = which == 1 ? GA_GRID_H_PROX : which == 2 ? GA_GRID_MOTION_RES : GA_GRID_MOVEMENT_COST;
+    ga_dropin::check(ga_download(ga_dropin::ctx(), id, dst, n * sizeof(double)));
+  })
+}
 #else
 int gap_set_dt_variant(int v)
 {

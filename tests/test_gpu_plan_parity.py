@@ -80,3 +80,19 @@ def test_config5_synthetic_queries_sequences(tmp_path):
     assert int(a["n_queries"]) == int(b["n_queries"]) == 3
     for i in range(3):
         _same_plan(a, b, "q%d_" % i)
+
+
+def test_patch_move_carries_the_potential_field(tmp_path):
+    """AStar::reinit (a_star.cpp:70-99): h_prox_arr_ and motion_res_map_ survive a patch move (util::saveTemp +
+    copyPatch2Patch).  Both arms build the environment, move the patch with the ego, and build again: the carried
+    maps -- on the host AND in the device copy the kernels read -- and the guidance heuristic computed on them are equal."""
+    a = gp.run_query_subprocess("ref", str(tmp_path / "a.npz"), scenario="Valet_parking_015", extra=["--patch-move"])
+    b = gp.run_query_subprocess("b200", str(tmp_path / "b.npz"), scenario="Valet_parking_015", mode=0, extra=["--patch-move"])
+    assert int(a["patch_dim"]) == int(b["patch_dim"]) and np.array_equal(a["origin"], b["origin"])
+    assert np.count_nonzero(a["carried_h_prox"]) > 1000            # the field really is carried, not zeroed
+    for k in ("carried_h_prox", "carried_motion_res"):
+        assert np.array_equal(a[k], b[k], equal_nan=True), k
+    assert np.array_equal(a["carried_h_prox"], b["device_h_prox"], equal_nan=True)
+    assert np.array_equal(a["carried_motion_res"], b["device_motion_res"])
+    for k in ("h_prox", "motion_res", "hg_cost", "hg_dist", "hg_parent", "hg_flags"):
+        assert np.array_equal(a[k], b[k], equal_nan=True), k
