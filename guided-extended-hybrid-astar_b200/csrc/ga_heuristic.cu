@@ -930,7 +930,6 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
   __shared__ double sg[FS * FS];
   __shared__ double sb[FS * FS];
   __shared__ uint8_t su[FS * FS];
-  __shared__ short lp[FB * FB];  // -1: terminal (parent outside the block, root, or not closed); else parent's local index | step type << 10
   __shared__ int s_cnt[2][FB];   // per warp: closed cells, terminal cells
   const heur_args& a = many ? many[blockIdx.y] : single;
   const int dim = a.dim, nbx = (dim + FB - 1) / FB;
@@ -1001,7 +1000,6 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
       }
     }
   }
-  lp[threadIdx.x] = (short)lpar;
   if (in)
   {
     a.parent[n] = par;
@@ -1040,16 +1038,30 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
     a.tlist[blockIdx.x * FIN_SLOTS + s_cnt[1][warp] + __popc(m_term & ((1u << lane) - 1u))] = n;
     a.tot[n] = make_int2(-1, -1);  // "not known yet" for finish B's shortcut
   }
-  // chain walk inside the block (shared memory, one load per hop)
-  // (hop cap: parent pointers cannot form a cycle while every edge weight is positive -- ga_set_astar_params and
-  // ga_upload enforce that -- the cap keeps a corrupted plane from hanging the kernel)
-  int cur = threadIdx.x, cs = 0, cd = 0, hops = 0;
-  for (int v = lpar; v >= 0 && hops < FB * FB; v = lp[cur], ++hops)
+  // chain to the block's terminal cell by pointer jumping in shared memory: every cell holds (pointer, straight steps,
+  // diagonal steps) and replaces it by the composition with its pointer's entry until every pointer is a terminal --
+  // log2(chain length) rounds instead of one hop per step (a warp used to wait for its longest chain: ~360 of the
+  // ~560 warp instructions per cell).  Parent pointers cannot form a cycle while every edge weight is positive
+  // (ga_set_astar_params and ga_upload enforce that); the round cap keeps a corrupted plane from hanging the kernel.
+  unsigned* sj = reinterpret_cast<unsigned*>(sb);  // the prox plane is not needed any more
+  __syncthreads();
   {
-    cd += v >> 10;
-    cs += 1 - (v >> 10);
-    cur = v & 1023;
+    const unsigned diag = lpar >= 0 ? (unsigned)(lpar >> 10) : 0u;
+    sj[threadIdx.x] = lpar >= 0 ? ((unsigned)(lpar & 1023) | ((1u - diag) << 10) | (diag << 21)) : (unsigned)threadIdx.x;
   }
+  __syncthreads();
+  for (int round = 0; round < 11; ++round)
+  {
+    const unsigned w = sj[threadIdx.x];
+    const unsigned wp = sj[w & 1023u];
+    const bool changed = (wp & 1023u) != (w & 1023u);
+    const unsigned nw = (wp & 1023u) | ((w & ~1023u) + (wp & ~1023u));  // steps add field by field (each < 1024: no carry across)
+    __syncthreads();
+    sj[threadIdx.x] = nw;
+    if (!__syncthreads_or(changed)) break;
+  }
+  const unsigned fin = sj[threadIdx.x];
+  const int cur = (int)(fin & 1023u), cs = (int)((fin >> 10) & 2047u), cd = (int)(fin >> 21);
   if (in) a.scratch[n] = fin_pack(cur % FB - lx, cur / FB - ly, cs, cd);
 }
 

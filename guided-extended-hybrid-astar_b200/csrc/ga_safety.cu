@@ -8,33 +8,47 @@
 // Design: thresholded cells take the values {FREE 0, UNKNOWN 1, OCC 2} and cv::dilate is a max
 // filter, so the whole pipeline is exact on two 1-bit planes: P2 = (cell == OCC) and
 // P1 = (cell != FREE), 32 cells per word; max over the disk = P1' + P2' where ' is binary
-// dilation.  The elliptical structuring element is a stack of horizontal spans (one half width per
-// row dy).  A CTA owns a tile of 256 x 64 cells:
-//   0  reads the raw bytes of the tile + halo (16-byte loads), thresholds and packs them into the
-//      two bit planes in shared memory -- the planes never exist in global memory;
-//   A  per plane word, the span dilations D_w = D_(w-1) | cells << w | cells >> w for w = 1..r by
-//      32-bit funnel shifts; the distinct half widths the SE uses are kept;
-//   B  vertical OR over the 2r+1 SE rows, four words per thread (128-bit shared loads);
+// dilation.  The elliptical structuring element is read by columns: a cell at horizontal distance w
+// of the centre is covered by the rows |dy| <= hmax(w).  A CTA owns a tile of 256 x 64 cells:
+//   0  reads the raw bytes of the tile + halo (16-byte loads, all in flight before the first is used),
+//      thresholds them (SWAR compare + DP4A bit gather) and writes 16-bit halves of the two bit planes
+//      to shared memory -- the planes never exist in global memory; of the halo words left and right
+//      only the inner 16 cells are read (r <= 16);
+//   V  cumulative vertical ORs V_h(y) = OR of the plane rows y-h .. y+h, two words per thread (64-bit
+//      shared accesses), stored at the distinct hmax values (7 for the 21 x 21 disk);
+//   B  dilated(y) = OR_w shift(+-w) of V_hmax(w)(y) by funnel shifts, two output words per thread;
+//      the rows of a warp are 4 apart so that its shared accesses (row pitch 10 words) are conflict free;
 //   C  bits -> bytes through a 256-entry table (4 cells per lookup), 16-byte coalesced stores;
 //   P  4x4 max-pool of the tile from the same shared words (8 pooled cells per thread).
 // HBM traffic is the compulsory 1 B/cell read + 1 B/cell write + 1/16 B/cell pooled write; the halo
-// re-reads (1.6x) hit L2.
+// re-reads (1.5x) hit L2.
 #include "ga_internal.cuh"
 
-#define DT_TW 8          // tile width in words (256 cells)
-#define DT_TH 64         // tile height in rows
-#define DT_SW (DT_TW + 2)  // staged plane words per row (one halo word each side)
+#define DT_TW 8            // tile width in words (256 cells)
+#define DT_TH 64           // tile height in rows
+#define DT_SW (DT_TW + 2)  // staged plane words per row (one halo word each side); also the pitch of the output planes
+#define DT_SH (2 * DT_SW)  // the same in 16-cell halves
+#define DT_NH (DT_SH - 2)  // halves that are read: the outer half of each halo word is never needed (r <= 16)
 #define DT_THREADS 256
+static_assert(GA_MAX_DISK_R <= 16, "phase 0 reads only the inner half of the halo words");
 
 // SWAR byte compare: bit 7 of byte k of the result = (byte k of x > c), any c in 0..255.
-// k7 = 0x01010101 * (127 - (c & 127)): adding it to the low 7 bits carries into bit 7 iff they exceed c & 127.
-__device__ __forceinline__ uint32_t bytes_gt(uint32_t x, uint32_t k7, bool c_high)
+// k7 = 0x01010101 * (127 - (c & 127)): adding it to the low 7 bits carries into bit 7 iff they exceed c & 127;
+// sel = all ones when c >= 128 (then bit 7 of x must be set as well), 0 otherwise (then bit 7 of x suffices).
+// Three logic operations and one add, no branch on the threshold.
+__device__ __forceinline__ uint32_t bytes_gt(uint32_t x, uint32_t k7, uint32_t sel)
 {
   const uint32_t m = (x & 0x7F7F7F7Fu) + k7;
-  return (c_high ? (m & x) : (m | x)) & 0x80808080u;
+  return ((m & x) | (~sel & (m | x))) & 0x80808080u;
 }
-// bits 7, 15, 23, 31 -> bits 0..3
-__device__ __forceinline__ uint32_t nibble_of_high_bits(uint32_t m) { return ((m >> 7) * 0x01020408u) >> 24; }
+// 16 compared bytes (0x80 where the compare passed) -> 16 bits.  A byte-wise dot product with the weights 1, 2, 4, 8
+// (16 .. 128 for the next word) adds up 128 x the bit pattern: one DP4A per word.
+__device__ __forceinline__ uint32_t gather16(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3)
+{
+  const uint32_t lo = __dp4a(c1, 0x80402010u, __dp4a(c0, 0x08040201u, 0u));  // 128 * bits 0..7
+  const uint32_t hi = __dp4a(c3, 0x80402010u, __dp4a(c2, 0x08040201u, 0u));  // 128 * bits 8..15
+  return (lo >> 7) + (hi << 1);
+}
 
 // The shipped footprint (default vehicle, SAFETY_DISTANCE_M 0.1) gives the 21 x 21 disk: radius 10, half widths
 // 10,10,10,10,9,9,8,7,6,4,0 for |dy| = 0..10.  Its column view as compile-time tables lets phases V and B unroll
@@ -43,219 +57,269 @@ __device__ constexpr int K10_R = 10, K10_NLVL = 7;
 __device__ constexpr int K10_LVL_H[K10_NLVL] = { 3, 5, 6, 7, 8, 9, 10 };
 __device__ constexpr int K10_LVL_OF_W[K10_R + 1] = { 6, 5, 5, 5, 5, 4, 4, 3, 2, 1, 0 };
 
-template <bool SPEC10>
-__global__ void __launch_bounds__(DT_THREADS)
+// LOADW: widest aligned access the row pitch allows -- 16 (dim % 16 == 0), 4 (dim % 4 == 0) or 1.
+template <bool SPEC10, int LOADW>
+__global__ void __launch_bounds__(DT_THREADS, SPEC10 ? 7 : 1)
 safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ safety, uint8_t* __restrict__ astar,
-              int astar_dim, const ga_se se, uint32_t lo4, uint32_t hi4)
+              int astar_dim, const ga_se se, const uint32_t lo, const uint4 thr)
 {
   extern __shared__ __align__(16) uint32_t smem[];
   __shared__ uint32_t s_lut[256];   // (P1 nibble | P2 nibble << 4) -> 4 cell bytes
   const int r = SPEC10 ? K10_R : se.r;
   const int n_lvl = SPEC10 ? K10_NLVL : se.n_lvl;
   const int rows_in = DT_TH + 2 * r;
-  uint32_t* sP = smem;                                   // [plane][rows_in][DT_SW]   thresholded bit planes
-  uint32_t* sV = sP + 2 * rows_in * DT_SW;               // [plane][level][DT_TH][DT_SW]  vertical ORs over |dy| <= hmax(level)
-  uint32_t* sOut = sV + 2 * n_lvl * DT_TH * DT_SW;       // [plane][DT_TH][DT_TW]   dilated planes
+  uint32_t* sP = smem;                          // [plane][rows_in][DT_SW]   thresholded bit planes
+  uint32_t* sV = sP + 2 * rows_in * DT_SW;      // [level][DT_TH][DT_SW]  vertical ORs over |dy| <= hmax(level) of ONE plane at a time
+  uint32_t* sOut = sV + n_lvl * DT_TH * DT_SW;  // [plane][DT_TH][DT_SW]  dilated planes
   constexpr int lvl_stride = DT_TH * DT_SW;
-  const int plane_stride = n_lvl * lvl_stride;
   const int w0 = blockIdx.x * DT_TW, y0 = blockIdx.y * DT_TH;
   const int tid = threadIdx.x;
-  const bool vec = (dim & 15) == 0;
-  const uint32_t lo = lo4 & 0xFFu, hi = hi4 & 0xFFu;
-  const uint32_t hi_k7 = 0x01010101u * (127u - (hi & 127u)), lo_k7 = 0x01010101u * (127u - ((lo - 1u) & 127u));
-  const bool hi_high = hi >= 128u, lo_high = (lo - 1u) >= 128u && lo != 0u;
 
   {
     // table: byte k = ((idx >> k) & 1) + ((idx >> (4 + k)) & 1)
     const uint32_t a = tid & 15, b = tid >> 4;
     s_lut[tid] = (((a & 0xFu) * 0x00204081u) & 0x01010101u) + (((b & 0xFu) * 0x00204081u) & 0x01010101u);
   }
-
-  // ---- phase 0: threshold + pack.  One item = 16 cells (half a plane word); two neighbouring
-  //      lanes make a word.  Cells outside the image are 0 in both planes (OpenCV ignores them).
-  const int n_items = rows_in * DT_SW * 2;
-  constexpr int P0_MAX = ((DT_TH + 2 * GA_MAX_DISK_R) * DT_SW * 2 + DT_THREADS - 1) / DT_THREADS;  // items per thread, largest SE
-  if (vec)
+  // ---- phase 0: threshold + pack.  One item = 16 cells (half a plane word), stored as 16 bits.  Cells outside the
+  //      image are 0 in both planes (OpenCV ignores them).  Items are numbered row by row over the DT_NH halves a row
+  //      needs; a thread's next item is DT_THREADS further: (row, half) advance by constants, no division in the loop.
+  uint16_t* sP16 = reinterpret_cast<uint16_t*>(sP);
+  constexpr int P0_N = ((DT_TH + 2 * (SPEC10 ? K10_R : GA_MAX_DISK_R)) * DT_NH + DT_THREADS - 1) / DT_THREADS;  // items per thread
+  constexpr int STEP_R = DT_THREADS / DT_NH, STEP_C = DT_THREADS % DT_NH;
+  // compare constants of bytes_gt for MAX_THRESH and MIN_THRESH - 1, made on the host: as opaque kernel arguments they
+  // stay operands of one three-input logic operation (computed here, the compiler turns `sel` back into a predicate
+  // and a second, predicated operation per compare)
+  const uint32_t hi_k7 = thr.x, hi_sel = thr.y, lo_k7 = thr.z, lo_sel = thr.w;
+  const int xh0 = (w0 - 1) * 32 + 16;  // first cell of the first half that is read (inner half of the left halo word)
+  // the outer halves of the halo words: never shifted into the tile, zeroed so that phase V works on defined words
+  for (int i = tid; i < 4 * rows_in; i += DT_THREADS) sP16[(i >> 1) * DT_SH + (i & 1) * (DT_SH - 1)] = 0;
   {
-    // dim % 16 == 0: an item is 16 aligned bytes, fully inside or fully outside the image.  All loads
-    // of a thread are issued before the first one is used (one memory round trip per tile).
-    uint4 v[P0_MAX];
+    // the raw bytes are staged in the (still unused) area of the vertical ORs by asynchronous copies: every item of the
+    // tile is in flight at once (one memory round trip per tile, no registers held), rows / columns outside the image
+    // are zero-filled (src-size 0).  A thread thresholds the items it copied itself: no barrier in between.
+    uint8_t* sRaw = reinterpret_cast<uint8_t*>(sV);
+    const uint32_t raw0 = (uint32_t)__cvta_generic_to_shared(sRaw) + tid * 16;
+    int rl = tid / DT_NH, c = tid - rl * DT_NH;
 #pragma unroll
-    for (int j = 0; j < P0_MAX; ++j)
+    for (int j = 0; j < P0_N; ++j)
     {
-      const int it = tid + j * DT_THREADS;
-      const int half = it & 1, wi = (it >> 1) % DT_SW, rl = (it >> 1) / DT_SW;
-      const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32 + half * 16;
-      v[j] = make_uint4(0, 0, 0, 0);  // below any MIN_THRESH > 0: FREE, the neutral element of the max filter
-      if (it < n_items && y >= 0 && y < dim && x >= 0 && x < dim) v[j] = __ldg(reinterpret_cast<const uint4*>(patch + (size_t)y * dim + x));
-    }
-#pragma unroll
-    for (int j = 0; j < P0_MAX; ++j)
-    {
-      const int it = tid + j * DT_THREADS;
-      if (it - (tid & 31) >= n_items) break;  // whole warps leave together: the shuffle below needs all lanes
-      const int half = it & 1, wi = (it >> 1) % DT_SW, rl = (it >> 1) / DT_SW;
-      const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32 + half * 16;
-      const bool inside = it < n_items && y >= 0 && y < dim && x >= 0 && x < dim;
-      const uint32_t w[4] = { v[j].x, v[j].y, v[j].z, v[j].w };
-      // 16 byte compares -> 16 bits: the compare leaves 0x80 in every byte that passes; a byte-wise dot product with the
-      // weights 1, 2, 4, 8 (16 .. 128 for the next word) adds up 128 x the bit pattern -- one DP4A per word instead of
-      // shift / multiply / shift per word and the shift-ors that assemble the nibbles
-      const uint32_t o_lo = __dp4a(bytes_gt(w[1], hi_k7, hi_high), 0x80402010u, __dp4a(bytes_gt(w[0], hi_k7, hi_high), 0x08040201u, 0u));
-      const uint32_t o_hi = __dp4a(bytes_gt(w[3], hi_k7, hi_high), 0x80402010u, __dp4a(bytes_gt(w[2], hi_k7, hi_high), 0x08040201u, 0u));
-      const uint32_t n_lo = __dp4a(bytes_gt(w[1], lo_k7, lo_high), 0x80402010u, __dp4a(bytes_gt(w[0], lo_k7, lo_high), 0x08040201u, 0u));
-      const uint32_t n_hi = __dp4a(bytes_gt(w[3], lo_k7, lo_high), 0x80402010u, __dp4a(bytes_gt(w[2], lo_k7, lo_high), 0x08040201u, 0u));
-      uint32_t b_occ = (o_lo >> 7) | ((o_hi >> 7) << 8);                                  // v > MAX_THRESH -> OCC  (collision_checking.cpp:214,220)
-      uint32_t b_nf = (lo == 0) ? 0xFFFFu : ((n_lo >> 7) | ((n_hi >> 7) << 8));           // !(v < MIN_THRESH), i.e. v > MIN_THRESH - 1  (:213,219); nothing is below 0
-      if (!inside) b_occ = b_nf = 0;
-      b_nf |= b_occ;  // setTo(OCC) runs after setTo(FREE): OCC wins
-      // lanes 2k, 2k+1 hold the halves of one word
-      const uint32_t o_occ = __shfl_xor_sync(0xFFFFFFFFu, b_occ, 1), o_nf = __shfl_xor_sync(0xFFFFFFFFu, b_nf, 1);
-      if (!half && it < n_items)
+      if (rl < rows_in)
       {
-        sP[rl * DT_SW + wi] = b_occ | (o_occ << 16);
-        sP[(rows_in + rl) * DT_SW + wi] = b_nf | (o_nf << 16);
-      }
-    }
-  }
-  else
-  {
-    for (int it = tid; it < n_items / 2; it += DT_THREADS)  // one item = one plane word, byte loads
-    {
-      const int wi = it % DT_SW, rl = it / DT_SW;
-      const int y = y0 - r + rl, x = (w0 - 1 + wi) * 32;
-      uint32_t b_occ = 0, b_nf = 0;
-      if (y >= 0 && y < dim && x >= 0 && x < dim)
-      {
-        const uint8_t* p = patch + (size_t)y * dim + x;
-        const int n = min(32, dim - x);
-        for (int k = 0; k < n; ++k)
+        const int y = y0 - r + rl, x = xh0 + c * 16;
+        const bool ok = (unsigned)y < (unsigned)dim && x >= 0 && x < dim;
+        const uint8_t* p = patch + (ok ? (uint32_t)(y * dim + x) : 0u);  // patch_dim <= 32768: the offset fits 32 bits
+        const uint32_t dst = raw0 + j * (DT_THREADS * 16);
+        if (LOADW == 16)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(p), "r"(ok ? 16 : 0) : "memory");
+        else if (LOADW == 4)
         {
-          const uint32_t c = __ldg(p + k);
-          b_occ |= (c > hi ? 1u : 0u) << k;
-          b_nf |= (c >= lo ? 1u : 0u) << k;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+          {
+            const bool okk = ok && x + 4 * k < dim;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst + 4 * k), "l"(okk ? p + 4 * k : patch), "r"(okk ? 4 : 0) : "memory");
+          }
+        }
+        else
+        {
+          uint32_t w[4] = { 0, 0, 0, 0 };
+          if (ok)
+          {
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+              if (x + k < dim) w[k >> 2] |= (uint32_t)__ldg(p + k) << (8 * (k & 3));
+          }
+          *reinterpret_cast<uint4*>(sRaw + (tid + j * DT_THREADS) * 16) = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }
-      sP[rl * DT_SW + wi] = b_occ;
-      sP[(rows_in + rl) * DT_SW + wi] = b_nf | b_occ;
+      rl += STEP_R; c += STEP_C;
+      if (c >= DT_NH) { c -= DT_NH; ++rl; }
+    }
+    if (LOADW >= 4) asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    rl = tid / DT_NH; c = tid - rl * DT_NH;
+#pragma unroll
+    for (int j = 0; j < P0_N; ++j)
+    {
+      if (rl < rows_in)
+      {
+        const uint4 q = *reinterpret_cast<const uint4*>(sRaw + (tid + j * DT_THREADS) * 16);
+        const uint32_t v[4] = { q.x, q.y, q.z, q.w };
+        // v > MAX_THRESH -> OCC  (collision_checking.cpp:214,220).  Cells outside the image were zero-filled: never OCC
+        const uint32_t b_occ = gather16(bytes_gt(v[0], hi_k7, hi_sel), bytes_gt(v[1], hi_k7, hi_sel),
+                                        bytes_gt(v[2], hi_k7, hi_sel), bytes_gt(v[3], hi_k7, hi_sel));
+        // !(v < MIN_THRESH) -> not FREE  (:213,219)
+        uint32_t b_nf = gather16(bytes_gt(v[0], lo_k7, lo_sel), bytes_gt(v[1], lo_k7, lo_sel),
+                                 bytes_gt(v[2], lo_k7, lo_sel), bytes_gt(v[3], lo_k7, lo_sel));
+        if (lo == 0u)
+        {
+          // nothing is below MIN_THRESH = 0: every cell inside the image is at least UNKNOWN (the zero fill does not tell)
+          const int y = y0 - r + rl, x = xh0 + c * 16;
+          b_nf = ((unsigned)y < (unsigned)dim && x >= 0 && x < dim) ? 0xFFFFu : 0u;
+          if (LOADW != 16 && x + 16 > dim && x < dim) b_nf &= (1u << (dim - x)) - 1u;
+        }
+        b_nf |= b_occ;  // setTo(OCC) runs after setTo(FREE): OCC wins
+        sP16[rl * DT_SH + c + 1] = (uint16_t)b_occ;
+        sP16[(rows_in + rl) * DT_SH + c + 1] = (uint16_t)b_nf;
+      }
+      rl += STEP_R; c += STEP_C;
+      if (c >= DT_NH) { c -= DT_NH; ++rl; }
     }
   }
   __syncthreads();
 
   // ---- phase V: vertical ORs.  A cell at horizontal distance w of the centre column is covered by the SE rows
-  //      |dy| <= hmax(w), so  dilated(y) = OR_w shift(+-w) of V_hmax(w)(y),  V_h(y) = OR of the plane rows y-h .. y+h.
-  //      One item = one staged word of one output row: the cumulative OR over h = 0 .. r, stored at the distinct hmax
-  //      values (7 for the 21 x 21 disk).  The horizontal work then runs on the 64 output rows only and needs no
-  //      per-input-row span chains: 40 + 55 instructions per output word against 260 for spans-then-OR.
-  for (int it = tid; it < 2 * DT_TH * DT_SW; it += DT_THREADS)
+  //      |dy| <= hmax(w), so  dilated(y) = OR_w shift(+-w) of V_hmax(w)(y),  V_h(y) = OR of the plane rows y-h .. y+h,
+  //      stored at the distinct hmax values (7 for the 21 x 21 disk).  The horizontal work then runs on the 64 output
+  //      rows only.  One item = two staged words (64-bit accesses) of TWO neighbouring output rows y, y+1: they share
+  //      the core C_h = OR of the rows y-h+1 .. y+h,  V_h(y) = C_h | row(y-h),  V_h(y+1) = C_h | row(y+1+h), and the
+  //      two rows just used extend the core to C_(h+1): 11 shared-memory loads per output row instead of 21.
+  //      Lanes run along the rows first (8 row pairs x pitch 20 words visit every fourth bank pair): conflict free.
+  //      The two planes go through V and B one after the other: half the shared memory, 7 CTAs per SM -- the 1024
+  //      tiles of a 4096^2 patch are resident at once (148 x 7 = 1036) instead of running as 1.4 waves.
+  constexpr int RP = DT_SW / 2;  // 64-bit pairs per row
+  static_assert(DT_TW == 8 && DT_TH == 64 && DT_THREADS == 256, "item decoding of phases V and B");
+  for (int pl = 0; pl < 2; ++pl)
   {
-    const int pl = it >= DT_TH * DT_SW, rem = it - pl * (DT_TH * DT_SW);  // rem = rl * DT_SW + wi: rows are contiguous
-    const uint32_t* src = sP + pl * rows_in * DT_SW + r * DT_SW + rem;
-    uint32_t* dst = sV + pl * plane_stride + rem;
-    uint32_t acc = src[0];
-    if (SPEC10)
+    if (tid < (DT_TH / 2) * RP)
     {
+      const int t = tid >> 3, cp = t % RP, y = 2 * ((t / RP) * 8 + (tid & 7));
+      const uint2* src = reinterpret_cast<const uint2*>(sP) + (pl * rows_in + r + y) * RP + cp;
+      uint2* dst = reinterpret_cast<uint2*>(sV) + y * RP + cp;
+      const uint2 r0 = src[0], r1 = src[RP];
+      uint2 core = make_uint2(r0.x | r1.x, r0.y | r1.y);  // C_1
       int lv = 0;
-#pragma unroll
-      for (int h = 1; h <= K10_R; ++h)
+      if (!SPEC10 && se.lvl_h[0] == 0)
       {
-        acc |= src[h * DT_SW] | src[-h * DT_SW];
-        if (lv < K10_NLVL && K10_LVL_H[lv] == h)  // compile-time after unrolling
-        {
-          dst[lv * lvl_stride] = acc;
-          ++lv;
-        }
-      }
-    }
-    else
-    {
-      int lv = 0;
-      if (se.lvl_h[0] == 0)
-      {
-        dst[0] = acc;
+        dst[0] = r0;
+        dst[RP] = r1;
         lv = 1;
       }
-      for (int h = 1; h <= r; ++h)
+      if (SPEC10)
       {
-        acc |= src[h * DT_SW] | src[-h * DT_SW];
-        if (lv < n_lvl && se.lvl_h[lv] == h)
+#pragma unroll
+        for (int h = 1; h <= K10_R; ++h)
         {
-          dst[lv * lvl_stride] = acc;
-          ++lv;
+          const uint2 u = src[-h * RP], d = src[(h + 1) * RP];
+          if (lv < K10_NLVL && K10_LVL_H[lv] == h)  // compile-time after unrolling
+          {
+            dst[lv * (lvl_stride / 2)] = make_uint2(core.x | u.x, core.y | u.y);
+            dst[lv * (lvl_stride / 2) + RP] = make_uint2(core.x | d.x, core.y | d.y);
+            ++lv;
+          }
+          core.x |= u.x | d.x;
+          core.y |= u.y | d.y;
+        }
+      }
+      else
+      {
+        for (int h = 1; h <= r; ++h)
+        {
+          const uint2 u = src[-h * RP], d = src[(h + 1) * RP];
+          if (lv < n_lvl && se.lvl_h[lv] == h)
+          {
+            dst[lv * (lvl_stride / 2)] = make_uint2(core.x | u.x, core.y | u.y);
+            dst[lv * (lvl_stride / 2) + RP] = make_uint2(core.x | d.x, core.y | d.y);
+            ++lv;
+          }
+          core.x |= u.x | d.x;
+          core.y |= u.y | d.y;
         }
       }
     }
-  }
-  __syncthreads();
+    __syncthreads();
 
-  // ---- phase B: horizontal shifts of the vertical ORs, one item = one output word
-  for (int it = tid; it < 2 * DT_TH * DT_TW; it += DT_THREADS)
+  // ---- phase B: horizontal shifts of the vertical ORs.  One item = two neighbouring output words (staged words
+  //      2p+1, 2p+2) from the aligned pairs p and p+1 of every level.  The 8 rows a warp works on are 4 apart:
+  //      4 rows x pitch 10 words tile the 32 banks exactly (10 * 4 = 40 = 8 mod 32), loads and stores are conflict free.
   {
-    const int wl = it & (DT_TW - 1), rl = (it >> 3) & (DT_TH - 1), pl = it >> 9;
-    static_assert(DT_TW == 8 && DT_TH == 64, "item decoding of phase B");
-    const uint32_t* base = sV + pl * plane_stride + rl * DT_SW + wl;
-    uint32_t out;
-    if (SPEC10)
+    const uint2* sV64 = reinterpret_cast<const uint2*>(sV);
+    uint2* sOut64 = reinterpret_cast<uint2*>(sOut);
+    const int warp = tid >> 5, lane = tid & 31;
+    const int rl = (warp >> 2) * 32 + (warp & 3) + 4 * (lane >> 2), p = lane & 3;
     {
-      uint32_t a[K10_NLVL], b[K10_NLVL], c[K10_NLVL];
+      const uint2* base = sV64 + rl * RP + p;
+      uint32_t out0, out1;
+      if (SPEC10)
+      {
+        uint2 A[K10_NLVL], B[K10_NLVL];
 #pragma unroll
-      for (int l = 0; l < K10_NLVL; ++l)
-      {
-        a[l] = base[l * lvl_stride];
-        b[l] = base[l * lvl_stride + 1];
-        c[l] = base[l * lvl_stride + 2];
-      }
-      out = b[K10_LVL_OF_W[0]];
-#pragma unroll
-      for (int w = 1; w <= K10_R; ++w)
-      {
-        constexpr int dummy = 0;
-        (void)dummy;
-        const int l = K10_LVL_OF_W[w];
-        out |= __funnelshift_l(a[l], b[l], w) | __funnelshift_r(b[l], c[l], w);  // cells at distance exactly w
-      }
-    }
-    else
-    {
-      int cur = se.lvl_of_w[0];
-      uint32_t a = base[cur * lvl_stride], b = base[cur * lvl_stride + 1], c = base[cur * lvl_stride + 2];
-      out = b;
-      for (int w = 1; w <= r; ++w)
-      {
-        const int lv = se.lvl_of_w[w];
-        if (lv != cur)
+        for (int l = 0; l < K10_NLVL; ++l)
         {
-          cur = lv;
-          a = base[cur * lvl_stride];
-          b = base[cur * lvl_stride + 1];
-          c = base[cur * lvl_stride + 2];
+          A[l] = base[l * (lvl_stride / 2)];
+          B[l] = base[l * (lvl_stride / 2) + 1];
         }
-        out |= __funnelshift_l(a, b, w) | __funnelshift_r(b, c, w);
+        out0 = A[K10_LVL_OF_W[0]].y;
+        out1 = B[K10_LVL_OF_W[0]].x;
+#pragma unroll
+        for (int w = 1; w <= K10_R; ++w)
+        {
+          const int l = K10_LVL_OF_W[w];  // cells at distance exactly w
+          out0 |= __funnelshift_l(A[l].x, A[l].y, w) | __funnelshift_r(A[l].y, B[l].x, w);
+          out1 |= __funnelshift_l(A[l].y, B[l].x, w) | __funnelshift_r(B[l].x, B[l].y, w);
+        }
       }
+      else
+      {
+        int cur = se.lvl_of_w[0];
+        uint2 A = base[cur * (lvl_stride / 2)], B = base[cur * (lvl_stride / 2) + 1];
+        out0 = A.y;
+        out1 = B.x;
+        for (int w = 1; w <= r; ++w)
+        {
+          const int lv = se.lvl_of_w[w];
+          if (lv != cur)
+          {
+            cur = lv;
+            A = base[cur * (lvl_stride / 2)];
+            B = base[cur * (lvl_stride / 2) + 1];
+          }
+          out0 |= __funnelshift_l(A.x, A.y, w) | __funnelshift_r(A.y, B.x, w);
+          out1 |= __funnelshift_l(A.y, B.x, w) | __funnelshift_r(B.x, B.y, w);
+        }
+      }
+      sOut64[(pl * DT_TH + rl) * RP + p] = make_uint2(out0, out1);
     }
-    sOut[(pl * DT_TH + rl) * DT_TW + wl] = out;
   }
   __syncthreads();
+  }
 
-  // ---- phase C: bits -> bytes, coalesced 16-byte stores (a warp writes 512 consecutive cells)
-  for (int it = tid; it < DT_TH * DT_TW * 2; it += DT_THREADS)
+  // ---- phase C: bits -> bytes, coalesced 16-byte stores (a warp writes 2 x 256 consecutive cells).  The four rows of
+  //      a thread are independent and branch free up to the store: their shared-memory loads overlap.
   {
-    const int sub = it & 1, wl = (it >> 1) & (DT_TW - 1), rl = it >> 4;
-    const int y = y0 + rl;
+    constexpr int NJ = DT_TH * DT_TW * 2 / DT_THREADS, RSTEP = DT_THREADS / 16;
+    const int sub = tid & 1, wl = (tid >> 1) & (DT_TW - 1), rl0 = tid >> 4;
     const int x = (w0 + wl) * 32 + sub * 16;
-    if (y >= dim || x >= dim) continue;
-    const uint32_t p2 = sOut[rl * DT_TW + wl] >> (sub * 16);
-    const uint32_t p1 = sOut[(DT_TH + rl) * DT_TW + wl] >> (sub * 16);
-    uint8_t* dst = safety + (size_t)y * dim + x;
-    uint32_t o[4];
+    uint8_t* dst0 = safety + (uint32_t)((y0 + rl0) * dim + x);
+    uint32_t p1[NJ], p2[NJ];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) o[k] = s_lut[((p1 >> (4 * k)) & 0xFu) | (((p2 >> (4 * k)) & 0xFu) << 4)];
-    if (vec)
-      *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
-    else
+    for (int j = 0; j < NJ; ++j)
     {
-      const int n = min(16, dim - x);
-      for (int k = 0; k < n; ++k) dst[k] = (uint8_t)(o[k >> 2] >> (8 * (k & 3)));
+      p2[j] = sOut[(rl0 + j * RSTEP) * DT_SW + wl] >> (sub * 16);
+      p1[j] = sOut[(DT_TH + rl0 + j * RSTEP) * DT_SW + wl] >> (sub * 16);
+    }
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+    {
+      uint32_t o[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = s_lut[((p1[j] >> (4 * k)) & 0xFu) | (((p2[j] >> (4 * k)) & 0xFu) << 4)];
+      uint8_t* dst = dst0 + (uint32_t)(j * RSTEP * dim);
+      if (y0 + rl0 + j * RSTEP < dim && x < dim)
+      {
+        if (LOADW == 16)
+          *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+        else if (LOADW == 4)
+        {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (x + 4 * k < dim) reinterpret_cast<uint32_t*>(dst)[k] = o[k];
+        }
+        else
+        {
+          const int n = min(16, dim - x);
+          for (int k = 0; k < n; ++k) dst[k] = (uint8_t)(o[k >> 2] >> (8 * (k & 3)));
+        }
+      }
     }
   }
 
@@ -270,23 +334,23 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
 #pragma unroll
     for (int j = 0; j < 4; ++j)
     {
-      o2 |= sOut[(yl * 4 + j) * DT_TW + wl];
-      o1 |= sOut[(DT_TH + yl * 4 + j) * DT_TW + wl];
+      o2 |= sOut[(yl * 4 + j) * DT_SW + wl];
+      o1 |= sOut[(DT_TH + yl * 4 + j) * DT_SW + wl];
     }
     // nibble k of n = any bit of nibble k set, per plane; cell = n1 + n2
     o1 |= o1 >> 1; o1 |= o1 >> 2; o1 &= 0x11111111u;
     o2 |= o2 >> 1; o2 |= o2 >> 2; o2 &= 0x11111111u;
     const uint32_t s = o1 + o2;  // 8 nibbles, each 0..2
-    uint32_t lo = s & 0xFFFFu, hi = s >> 16;
-    lo = (lo | (lo << 8)) & 0x00FF00FFu; lo = (lo | (lo << 4)) & 0x0F0F0F0Fu;
-    hi = (hi | (hi << 8)) & 0x00FF00FFu; hi = (hi | (hi << 4)) & 0x0F0F0F0Fu;
+    uint32_t lo8 = s & 0xFFFFu, hi8 = s >> 16;
+    lo8 = (lo8 | (lo8 << 8)) & 0x00FF00FFu; lo8 = (lo8 | (lo8 << 4)) & 0x0F0F0F0Fu;
+    hi8 = (hi8 | (hi8 << 8)) & 0x00FF00FFu; hi8 = (hi8 | (hi8 << 4)) & 0x0F0F0F0Fu;
     uint8_t* dst = astar + (size_t)Y * astar_dim + X;
     if ((astar_dim & 7) == 0)
-      *reinterpret_cast<uint2*>(dst) = make_uint2(lo, hi);
+      *reinterpret_cast<uint2*>(dst) = make_uint2(lo8, hi8);
     else
     {
       const int n = min(8, astar_dim - X);
-      for (int k = 0; k < n; ++k) dst[k] = (uint8_t)((k < 4 ? lo : hi) >> (8 * (k & 3)));
+      for (int k = 0; k < n; ++k) dst[k] = (uint8_t)((k < 4 ? lo8 : hi8) >> (8 * (k & 3)));
     }
   }
 }
@@ -322,27 +386,29 @@ extern "C" int ga_build_safety(ga_ctx* c)
   const int dim = c->patch_dim;
   // min_thresh_ / max_thresh_ are uint8_t (collision_checking.hpp:51-52)
   const uint32_t lo = (uint8_t)c->cp.min_thresh, hi = (uint8_t)c->cp.max_thresh;
-  const uint32_t lo4 = lo * 0x01010101u, hi4 = hi * 0x01010101u;
   {
     ga_launch_scope ls(c, GA_K_DILATE);
     const int rows_in = DT_TH + 2 * c->se.r;
-    const size_t smem = sizeof(uint32_t) * ((size_t)2 * rows_in * DT_SW + (size_t)2 * c->se.n_lvl * DT_TH * DT_SW + 2 * DT_TH * DT_TW);
+    // thresholded planes + the vertical ORs of every level (one plane at a time) + the dilated planes
+    const size_t stage = (size_t)rows_in * DT_NH * 16;  // raw bytes of the tile + halo, staged where the vertical ORs and the dilated planes go later
+    const size_t smem = sizeof(uint32_t) * (size_t)2 * rows_in * DT_SW + std::max(stage, sizeof(uint32_t) * (size_t)(c->se.n_lvl + 2) * DT_TH * DT_SW);
     const int words = (dim + 31) / 32;
     dim3 grid((words + DT_TW - 1) / DT_TW, (dim + DT_TH - 1) / DT_TH);
     // the shipped 21 x 21 disk has compile-time tables
     bool spec10 = c->se.r == K10_R && c->se.n_lvl == K10_NLVL;
     for (int l = 0; spec10 && l < K10_NLVL; ++l) spec10 = c->se.lvl_h[l] == K10_LVL_H[l];
     for (int w = 0; spec10 && w <= K10_R; ++w) spec10 = c->se.lvl_of_w[w] == K10_LVL_OF_W[w];
-    if (spec10)
-    {
-      GA_CUDA(c, cudaFuncSetAttribute(safety_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      safety_kernel<true><<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo4, hi4);
-    }
-    else
-    {
-      GA_CUDA(c, cudaFuncSetAttribute(safety_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      safety_kernel<false><<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo4, hi4);
-    }
+    const int loadw = (dim & 15) == 0 ? 16 : (dim & 3) == 0 ? 4 : 1;
+    // v > MAX_THRESH;  !(v < MIN_THRESH) <=> v > MIN_THRESH - 1 (MIN_THRESH = 0: nothing is below, handled in the kernel)
+    const uint32_t lm = (lo - 1u) & 0xFFu;
+    const uint4 thr = make_uint4(0x01010101u * (127u - (hi & 127u)), hi >= 128u ? 0xFFFFFFFFu : 0u,
+                                 0x01010101u * (127u - (lm & 127u)), lm >= 128u ? 0xFFFFFFFFu : 0u);
+    void (*kern)(const uint8_t*, int, uint8_t*, uint8_t*, int, const ga_se, const uint32_t, const uint4) =
+        spec10 ? (loadw == 16 ? safety_kernel<true, 16> : loadw == 4 ? safety_kernel<true, 4> : safety_kernel<true, 1>)
+               : (loadw == 16 ? safety_kernel<false, 16> : loadw == 4 ? safety_kernel<false, 4> : safety_kernel<false, 1>);
+    GA_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GA_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    kern<<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo, thr);
   }
   GA_CUDA(c, cudaGetLastError());
   return GA_OK;
