@@ -329,6 +329,7 @@ extern "C" int ga_patch_reset(ga_ctx* c, int patch_dim)
   GA_CUDA(c, cudaMemsetAsync(c->d_astar, GA_UNKNOWN, na, c->stream));
   GA_CUDA(c, cudaMemsetAsync(c->d_fence, 0, na, c->stream));
   GA_CUDA(c, cudaMemsetAsync(c->d_prox, 0, na * 8, c->stream));
+  c->prox_zero = true;
   GA_CUDA(c, cudaMemsetAsync(c->d_odist, 0, nv * 4, c->stream));
   GA_CUDA(c, cudaMemsetAsync(c->d_vdist, 0, nv * 4, c->stream));
   fill_f64_kernel<<<c->sm_count * 2, 256, 0, c->stream>>>(c->d_mc, na, c->ap.astar_movement_cost);
@@ -418,6 +419,7 @@ extern "C" int ga_device_ptr(ga_ctx* c, int grid_id, void** dptr)
   GA_REQUIRE(c, c->patch_dim > 0 || grid_id == GA_GRID_CART || grid_id == GA_GRID_PMAP, GA_ERR_STATE, "no patch (call ga_patch_reset)");
   size_t b;
   GA_REQUIRE(c, grid_lookup(c, grid_id, dptr, &b) == 0, GA_ERR_ARG, "unknown grid id");
+  if (grid_id == GA_GRID_H_PROX) c->prox_zero = false;  // the caller may write it
   return GA_OK;
 }
 
@@ -445,6 +447,7 @@ extern "C" int ga_upload(ga_ctx* c, int grid_id, const void* src, size_t bytes)
                grid_id == GA_GRID_MOVEMENT_COST ? "movement costs must be positive and finite" : "proximity costs must not be negative");
   }
   GA_CUDA(c, cudaSetDevice(c->device));
+  if (grid_id == GA_GRID_H_PROX) c->prox_zero = false;
   GA_CUDA(c, cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, c->stream));
   // pageable sources are staged by the driver before the call returns; pinned ones are the
   // caller's to keep alive until ga_sync

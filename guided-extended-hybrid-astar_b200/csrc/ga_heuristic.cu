@@ -219,14 +219,16 @@ __global__ void heur_init_kernel(heur_grid single, const heur_grid* many, heur_q
 #define SW_O 30                    // owned cells per tile edge
 #define SW_P 33                    // shared-memory pitch (doubles)
 #define SW_WARPS 8                 // workers per CTA (one CTA per SM: 8 x 25 KB of shared memory)
+#define SW_WARPS_LEAN 12           // the same without the proximity plane (12 x 17 KB)
 #define SW_FULL 0xFFFFFFFFu
 #define SW_EARLY_ALL 255           // heur_queue::early: publish after every changing sweep
 
-struct sweep_tile
+template <bool HAS_PB>  // false: a launch whose grids carry no proximity cost at all -- no pb plane, 12 workers per SM instead of 8
+struct sweep_tile_t
 {
   double g[32 * SW_P];   // cost plane, relaxed in place
   double mc[32 * SW_P];  // movement_cost_map_ of the cell (edge length factor of the DESTINATION); +inf = blocked
-  double pb[32 * SW_P];  // h_prox_arr_ of the cell (x astar_prox_cost_ = prox_cost, term of the PREDECESSOR)
+  double pb[HAS_PB ? 32 * SW_P : 1];  // h_prox_arr_ of the cell (x astar_prox_cost_ = prox_cost, term of the PREDECESSOR)
   unsigned urow[32], ucol[32];  // UNKNOWN masks: urow[y] bit x / ucol[x] bit y
   unsigned dirty[32];           // dirty[y] bit x: cell improved since it was last written to global memory
 };
@@ -249,8 +251,8 @@ __device__ __forceinline__ double umin_f64(double a, double b)
 // rows; ORIENT 1: lane = y, lines are columns.  Blocked cells (OCC, geofence, root, off-grid, halo)
 // carry mc = +inf, so their candidates are +inf / NaN and they keep their value; lanes 0 / 31 are
 // halo cells, so what their missing neighbour "sends" does not matter.
-template <int ORIENT, bool PROX, bool UNK>
-__device__ __forceinline__ double sweep_step(const sweep_tile& S, const int lane, const int sp, const int s, const double a,
+template <int ORIENT, bool PROX, bool UNK, class TILE>
+__device__ __forceinline__ double sweep_step(const TILE& S, const int lane, const int sp, const int s, const double a,
                                              const double w_prox, const double unk_w, const double L1, const double L2, double* old_out)
 {
   constexpr int dl = ORIENT == 0 ? 1 : SW_P;  // index stride of the lane
@@ -294,8 +296,8 @@ __device__ __forceinline__ double sweep_step(const sweep_tile& S, const int lane
 }
 
 // one sweep over the 30 owned lines; dir = +1 / -1: line order.  Returns 1 if this lane improved a cell.
-template <int ORIENT, bool PROX, bool UNK>
-__device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const int dir, const double w_prox, const double unk_w,
+template <int ORIENT, bool PROX, bool UNK, class TILE>
+__device__ __forceinline__ int sweep_lines(TILE& S, const int lane, const int dir, const double w_prox, const double unk_w,
                                            const double L1, const double L2)
 {
   constexpr int dl = ORIENT == 0 ? 1 : SW_P, ds = ORIENT == 0 ? SW_P : 1;
@@ -326,8 +328,8 @@ __device__ __forceinline__ int sweep_lines(sweep_tile& S, const int lane, const 
 }
 
 // can the halo improve a border cell?  (first line step of each of the four sweeps, nothing stored)
-template <bool PROX, bool UNK>
-__device__ __forceinline__ int halo_improves(const sweep_tile& S, const int lane, const double w_prox, const double unk_w, const double L1,
+template <bool PROX, bool UNK, class TILE>
+__device__ __forceinline__ int halo_improves(const TILE& S, const int lane, const double w_prox, const double unk_w, const double L1,
                                              const double L2)
 {
   double old;
@@ -339,8 +341,8 @@ __device__ __forceinline__ int halo_improves(const sweep_tile& S, const int lane
   return __any_sync(SW_FULL, imp);
 }
 
-template <bool PROX, bool UNK>
-__device__ __forceinline__ int sweep_once(sweep_tile& S, const int lane, const int d, const double w_prox, const double unk_w, const double L1,
+template <bool PROX, bool UNK, class TILE>
+__device__ __forceinline__ int sweep_once(TILE& S, const int lane, const int d, const double w_prox, const double unk_w, const double L1,
                                           const double L2)
 {
   int ch;
@@ -360,8 +362,8 @@ __device__ __forceinline__ int sweep_once(sweep_tile& S, const int lane, const i
 // only fall, and the loop ends on a round that stores nothing, i.e. on the fixed point.  Where two
 // chains meet in one cell in the same step (row s x column s) the later store may put the larger of
 // two improvements back; the next round repairs it (and reports a change now).
-template <bool PROX, bool UNK>
-__device__ __forceinline__ int sweep_round(sweep_tile& S, const int lane, const double w_prox, const double unk_w, const double L1,
+template <bool PROX, bool UNK, class TILE>
+__device__ __forceinline__ int sweep_round(TILE& S, const int lane, const double w_prox, const double unk_w, const double L1,
                                            const double L2)
 {
   double a0 = S.g[lane], a1 = S.g[lane * SW_P], a2 = S.g[31 * SW_P + lane], a3 = S.g[lane * SW_P + 31];
@@ -452,8 +454,8 @@ __device__ __forceinline__ unsigned sweep_dir_keys(const int lane, const unsigne
 
 // write back the owned cells that improved since the last publication, activate the neighbour tiles
 // whose halo they are
-template <bool FINAL>
-__device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
+template <bool FINAL, class TILE>
+__device__ __forceinline__ int sweep_publish(TILE& S, const sweep_visit& V, const heur_queue& q, const int lane,
                                              int* n_act, int* n_unused)
 {
   unsigned col_key = 0xFFFFFFFFu, kn = 0xFFFFFFFFu, ks = 0xFFFFFFFFu;
@@ -482,7 +484,8 @@ __device__ __forceinline__ int sweep_publish(sweep_tile& S, const sweep_visit& V
 
 // the border cells only (rows 1 / 30 with lane = x, columns 1 / 30 with lane = y): all a neighbour
 // needs, a third of the latency.  The interior goes out with the visit's final publication.
-__device__ __forceinline__ void sweep_publish_border(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
+template <class TILE>
+__device__ __forceinline__ void sweep_publish_border(TILE& S, const sweep_visit& V, const heur_queue& q, const int lane,
                                                      int* n_act, int* n_unused)
 {
   const unsigned none = 0xFFFFFFFFu;
@@ -510,7 +513,8 @@ __device__ __forceinline__ void sweep_publish_border(sweep_tile& S, const sweep_
 // mark back and re-read the halo ring only -- the owned cells are written by nobody else and the
 // static planes have not changed.  Replaces release + ring + pop + a full re-stage on the chain a
 // corrected value travels along.
-__device__ __forceinline__ int sweep_refresh_halo(sweep_tile& S, const sweep_visit& V, const int lane)
+template <class TILE>
+__device__ __forceinline__ int sweep_refresh_halo(TILE& S, const sweep_visit& V, const int lane)
 {
   if (lane == 0)
   {
@@ -582,8 +586,8 @@ __device__ __forceinline__ void sweep_prefetch(const sweep_visit& V, const heur_
 // `refresh` a neighbour's publication is picked up between sweeps; with `linger` (SM cycles; needs
 // SW_EARLY_ALL, everything is published then) the converged tile stays staged that long waiting for
 // the next one.
-template <bool PROX, bool UNK>
-__device__ __forceinline__ int sweep_tile_loop(sweep_tile& S, const sweep_visit& V, const heur_queue& q, const int lane,
+template <bool PROX, bool UNK, class TILE>
+__device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, const heur_queue& q, const int lane,
                                                int d, const bool must_run, const bool fresh, const double w_prox, const double unk_w,
                                                const double L1, const double L2, int* n_sweeps, int* n_act, int* n_unused, int* n_reserved)
 {
@@ -685,11 +689,12 @@ __device__ __forceinline__ void cp_async8(const unsigned dst_smem, const void* s
 
 #define SW_RESERVE 24  // pending counts reserved per visit: (two publications + the prefetch) x 8 neighbours
 
-__global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid single, const heur_grid* many, heur_queue q)
+template <bool HAS_PB, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid single, const heur_grid* many, heur_queue q)
 {
   extern __shared__ __align__(16) unsigned char sw_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  sweep_tile& S = reinterpret_cast<sweep_tile*>(sw_smem)[warp];
+  sweep_tile_t<HAS_PB>& S = reinterpret_cast<sweep_tile_t<HAS_PB>*>(sw_smem)[warp];
   const double L1 = 0.625, L2 = 0.625 * 1.4142135623730951;  // movement_distances_ (a_star.hpp:54-57)
   int cont = 0;
 
@@ -712,7 +717,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
     int* state = HG(state);
     const int dim = HG(dim), tiles_x = HG(tiles_x), goal = HG(goal);
     const double w_prox = HG(w_prox), unk_w = HG(unk_w);
-    const int has_prox = __ldg(HG(tprox) + tile) == HG(epoch);
+    const int has_prox = HAS_PB && __ldg(HG(tprox) + tile) == HG(epoch);
 #undef HG
     const int tx = tile % tiles_x, ty = tile / tiles_x;
     const int ox = tx * SW_O - 1, oy = ty * SW_O - 1;
@@ -733,7 +738,7 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
         const int cy = min(max(oy + r, 0), dim - 1);
         const size_t id = (size_t)cy * dim + cx;
         cp_async8(s_mc + r * SW_P * 8, p_mc + id);
-        if (has_prox) cp_async8(s_pb + r * SW_P * 8, p_prox + id);
+        if (HAS_PB && has_prox) cp_async8(s_pb + r * SW_P * 8, p_prox + id);
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     }
@@ -834,7 +839,12 @@ __global__ void __launch_bounds__(SW_WARPS * 32, 1) heur_sweep_kernel(heur_grid 
 
     const bool fresh = !__any_sync(SW_FULL, reached && lane >= 1 && lane <= SW_O);
     int any, n_sweeps = 0, n_act = 0, n_unused = 0, n_reserved = SW_RESERVE;
-    if (has_prox)
+    if constexpr (!HAS_PB)
+    {
+      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+    }
+    else if (has_prox)
     {
       if (unk_w != 0) any = sweep_tile_loop<true, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
       else any = sweep_tile_loop<true, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
@@ -1165,8 +1175,10 @@ int ga_heur_alloc(ga_ctx* c)
   GA_CUDA(c, cudaMalloc(&c->d_hcls, na));
   GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * (na + (size_t)((c->astar_dim + 31) / 32) * ((c->astar_dim + 31) / 32) * 129)));  // scratch words + per-block terminal slots and counts
   GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)(SW_WARPS * sizeof(sweep_tile))));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS * sizeof(sweep_tile_t<true>))));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS_LEAN * sizeof(sweep_tile_t<false>))));
   return GA_OK;
 }
 
@@ -1225,8 +1237,12 @@ static void queue_knobs(const ga_ctx* c, int n_grids, heur_queue* q)
   q->prefetch = c->sw_prefetch >= 0 ? (unsigned)c->sw_prefetch : (lat ? 1u : 0u);
 }
 
+// no cell of the context's h_prox plane can hold a cost: the plane is all zero since ga_patch_reset (nothing was
+// uploaded into it, no potential field built, its device pointer not handed out), or the weight is zero
+static bool prox_free(const ga_ctx* c) { return c->prox_zero || c->ap.astar_prox_cost == 0.0; }
+
 static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& a0, const heur_grid* dG, const heur_args* dA,
-                        const heur_queue& q, int max_dim, size_t total_tiles)
+                        const heur_queue& q, int max_dim, size_t total_tiles, bool lean)
 {
   GA_CUDA(c, cudaMemsetAsync(q.ctl, 0, sizeof(int) * HC_WORDS, c->stream));  // ring cursors, pending count, statistics
   {
@@ -1238,10 +1254,12 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
   GA_CUDA(c, cudaGetLastError());
   {
     ga_launch_scope ls(c, GA_K_HEUR_RELAX);
-    const int nw = c->sw_warps;
+    // no grid of the launch carries a proximity cost: the tiles need no prox plane and 12 workers fit an SM
+    const int nw = lean ? (c->sw_warps == SW_WARPS ? SW_WARPS_LEAN : c->sw_warps) : c->sw_warps;
     const size_t want = (total_tiles + nw - 1) / nw;
     const int g = (size_t)c->sm_count < want ? c->sm_count : (int)want;
-    heur_sweep_kernel<<<g, nw * 32, nw * sizeof(sweep_tile), c->stream>>>(G0, dG, q);
+    if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN><<<g, nw * 32, nw * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, q);
+    else heur_sweep_kernel<true, SW_WARPS><<<g, nw * 32, nw * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, q);
   }
   GA_CUDA(c, cudaGetLastError());
   {
@@ -1273,7 +1291,7 @@ extern "C" int ga_build_heuristic(ga_ctx* c, int slot, int goal_x, int goal_y, i
   q.ctl = c->d_hctl;
   q.poll_ns = (unsigned)c->sw_poll_ns;
   queue_knobs(c, 1, &q);
-  const int rc = launch_build(c, 1, G, a, nullptr, nullptr, q, dim, (size_t)c->n_tiles);
+  const int rc = launch_build(c, 1, G, a, nullptr, nullptr, q, dim, (size_t)c->n_tiles, prox_free(c));
   if (rc != GA_OK) return rc;
   if (n_closed)
   {
@@ -1402,6 +1420,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
   GA_REQUIRE(c, n <= 2047, GA_ERR_ARG, "at most 2047 grids per batch (ring entry encoding)");
   size_t total_tiles = 0;
   int max_dim = 0;
+  bool lean = true;
   for (int i = 0; i < n; ++i)
   {
     ga_ctx* k = ctxs[i];
@@ -1413,6 +1432,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
     GA_REQUIRE(c, gx >= 0 && gy >= 0 && gx < k->astar_dim && gy < k->astar_dim, GA_ERR_ARG, "goal outside the astar grid");
     total_tiles += (size_t)k->n_tiles;
     max_dim = k->astar_dim > max_dim ? k->astar_dim : max_dim;
+    lean = lean && prox_free(k);
   }
   GA_CUDA(c, cudaSetDevice(c->device));
   // batch scratch on the leading context: ring for all tiles, descriptors, closed counters
@@ -1456,7 +1476,7 @@ extern "C" int ga_build_heuristic_batch(ga_ctx* const* ctxs, int n, int slot, co
   q.ctl = c->d_hctl;
   q.poll_ns = (unsigned)c->sw_poll_ns;
   queue_knobs(c, n, &q);
-  const int rc = launch_build(c, n, hG[0], hA[0], dG, dA, q, max_dim, total_tiles);
+  const int rc = launch_build(c, n, hG[0], hA[0], dG, dA, q, max_dim, total_tiles, lean);
   if (rc != GA_OK) return rc;
   // the other contexts' streams continue after the batch
   if (!c->ev_batch) GA_CUDA(c, cudaEventCreateWithFlags(&c->ev_batch, cudaEventDisableTiming));

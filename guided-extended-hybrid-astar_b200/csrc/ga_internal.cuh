@@ -65,6 +65,7 @@ struct ga_ctx
   uint8_t* d_fence = nullptr;
   double* d_mc = nullptr;
   double* d_prox = nullptr;
+  bool prox_zero = false;  // d_prox is all zero (set by ga_patch_reset, cleared by whatever may write the plane)
   double* d_mres = nullptr;
   float* d_odist = nullptr;
   float* d_vdist = nullptr;

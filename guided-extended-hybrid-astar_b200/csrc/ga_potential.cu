@@ -349,6 +349,7 @@ extern "C" int ga_build_potential(ga_ctx* c, int ego_x, int ego_y, const int* vo
   a.grid = c->d_astar;
   a.odist = c->d_odist;
   a.vdist = c->d_vdist;
+  c->prox_zero = false;
   a.prox = c->d_prox;
   a.mres = c->d_mres;
   a.vor_xy = d_xy;
