@@ -693,7 +693,7 @@ def main():
     ap.add_argument("--plan-procs", type=int, default=4, help="planner processes per GPU of the plan leg (fixed per GPU: weak scaling)")
     ap.add_argument("--plan-queries", type=int, default=6, help="queries per planner process of the plan leg")
     ap.add_argument("--plan-total", type=int, default=0, help="plan leg: total queries of the job over all ranks (4096 = BASELINE config 5); 0 = procs x queries per GPU")
-    ap.add_argument("--e2e-threads", type=int, default=8, help="planner contexts / host threads of the e2e leg")
+    ap.add_argument("--e2e-threads", type=int, default=16, help="planner contexts / host threads of the e2e leg (capped by the host cores per rank)")
     ap.add_argument("--no-mps", action="store_true", help="plan leg: do not start a CUDA MPS daemon for the planner processes")
     ap.add_argument("--plan-only", action="store_true", help="run only the plan leg (development)")
     ap.add_argument("--batch", type=int, default=128, help="queries of the batched-heuristic leg (0 = skip)")
@@ -719,7 +719,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    n_thr = max(N_ROT, min(args.e2e_threads, len(os.sched_getaffinity(0))))
+    # one host thread per planner context; the Fortune sweep (7 ms of host work per step) scales with the cores a rank has
+    n_thr = max(N_ROT, min(args.e2e_threads, len(os.sched_getaffinity(0)) // max(world, 1)))
     if args.plan_only:
         plan = run_plan_leg(args, local_rank, rank)
         if world > 1:

@@ -74,12 +74,37 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
   const int V = a.V, S = DT_PITCH(V), R = V + 2 * PB;
   const int which = blockIdx.x;  // 0: obstacle transform, 1: Voronoi transform
 
-  // OCC cells of the window (both CTAs count: the Voronoi one must know about the early return).  Eight loads in
-  // flight per thread: the prologue is latency bound (40 000 scattered bytes through 256 threads).
+  // Prologue: a warp per window row, lanes along x, the loads of DT_RU rows in flight together (row-wise coalesced
+  // accesses and no division per cell: the scattered one-cell-per-thread version took a quarter of the kernel).
+  const int warp = threadIdx.x >> 5, ln = threadIdx.x & 31;
+  constexpr int NWARP = P_THREADS / 32, DT_RU = 4, DT_XN = (P_THREADS + 31) / 32;  // V <= P_THREADS
+  // everything "far": the borders stay that way, the zero cells of the source image are written below
+  for (int i = threadIdx.x; i < R * S; i += P_THREADS) s[i] = TR::big();
+  __syncthreads();
+  // OCC cells of the window (both CTAs look: the Voronoi one must know about the early return); the obstacle transform's
+  // source image 1 - (astar_grid == OCC) is zero exactly there
   int occ = 0;
-#pragma unroll 8
-  for (int i = threadIdx.x; i < V * V; i += P_THREADS)
-    occ += __ldg(a.grid + (size_t)(a.oy + i / V) * a.dim + a.ox + i % V) == GA_OCC;
+  for (int yb = warp * DT_RU; yb < V; yb += NWARP * DT_RU)
+  {
+    uint8_t b[DT_RU][DT_XN];
+#pragma unroll
+    for (int r = 0; r < DT_RU; ++r)
+#pragma unroll
+      for (int k = 0; k < DT_XN; ++k)
+      {
+        const int y = yb + r, x = ln + 32 * k;
+        b[r][k] = (y < V && x < V) ? __ldg(a.grid + (size_t)(a.oy + y) * a.dim + a.ox + x) : (uint8_t)0;
+      }
+#pragma unroll
+    for (int r = 0; r < DT_RU; ++r)
+#pragma unroll
+      for (int k = 0; k < DT_XN; ++k)
+        if (b[r][k] == GA_OCC)
+        {
+          occ = 1;
+          if (which == 0) s[(size_t)(yb + r + PB) * S + ln + 32 * k + PX] = (T)0;
+        }
+  }
   occ = __syncthreads_count(occ > 0) ? 1 : 0;
   if (which == 0 && threadIdx.x == 0) a.flag[0] = occ;
   if (which == 1)
@@ -92,21 +117,24 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
       if (x >= 0 && y >= 0 && x < V && y < V) a.vdist[(size_t)y * V + x] = 2.0f;
     }
     __syncthreads();
-  }
-  // borders first (no global access), then the window itself
-  for (int i = threadIdx.x; i < R * S; i += P_THREADS)
-  {
-    const int x = i % S - PX, y = i / S - PB;
-    if (!(x >= 0 && y >= 0 && x < V && y < V)) s[i] = TR::big();
-  }
-#pragma unroll 8
-  for (int i = threadIdx.x; i < V * V; i += P_THREADS)
-  {
-    const int x = i % V, y = i / V;
-    // source image 1 - (val == mat): zero exactly where the value is OCC (== 2)
-    const bool zero = which == 0 ? __ldg(a.grid + (size_t)(a.oy + y) * a.dim + a.ox + x) == GA_OCC
-                                 : __ldcg(a.vdist + (size_t)y * V + x) == 2.0f;
-    s[(size_t)(y + PB) * S + x + PX] = zero ? (T)0 : TR::big();
+    // source image 1 - (voronoi_dist_ == 2): zero at the marked cells (and at whatever held exactly 2.0 before)
+    for (int yb = warp * DT_RU; yb < V; yb += NWARP * DT_RU)
+    {
+      float f[DT_RU][DT_XN];
+#pragma unroll
+      for (int r = 0; r < DT_RU; ++r)
+#pragma unroll
+        for (int k = 0; k < DT_XN; ++k)
+        {
+          const int y = yb + r, x = ln + 32 * k;
+          f[r][k] = (y < V && x < V) ? __ldcg(a.vdist + (size_t)y * V + x) : 0.0f;
+        }
+#pragma unroll
+      for (int r = 0; r < DT_RU; ++r)
+#pragma unroll
+        for (int k = 0; k < DT_XN; ++k)
+          if (f[r][k] == 2.0f) s[(size_t)(yb + r + PB) * S + ln + 32 * k + PX] = (T)0;
+    }
   }
   __syncthreads();
 
@@ -214,8 +242,8 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
   __syncthreads();
   // dist_map *= grid_tf::star2con_ (a_star.cpp:432): float element times 0.625
   float* dst = which == 0 ? a.odist : a.vdist;
-  for (int i = threadIdx.x; i < V * V; i += P_THREADS)
-    dst[i] = TR::out(s[(size_t)(i / V + PB) * S + i % V + PX]) * 0.625f;
+  for (int y = warp; y < V; y += NWARP)
+    for (int x = ln; x < V; x += 32) dst[(size_t)y * V + x] = TR::out(s[(size_t)(y + PB) * S + x + PX]) * 0.625f;
 }
 
 // K4: AStar::setCostmapValue (a_star.cpp:486-508)
