@@ -25,6 +25,9 @@ FULL_METRICS = [
     "smsp__issue_active.avg.pct_of_peak_sustained_active",
     "sm__warps_active.avg.pct_of_peak_sustained_active",
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "sm__cycles_active.avg",
+    "sm__cycles_elapsed.avg",
     "lts__t_sector_hit_rate.pct",
     "launch__registers_per_thread",
     "launch__grid_size",
