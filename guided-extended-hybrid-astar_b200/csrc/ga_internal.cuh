@@ -65,6 +65,11 @@ struct ga_ctx
   uint8_t* d_fence = nullptr;
   double* d_mc = nullptr;
   double* d_prox = nullptr;
+  // tensor map of d_patch for the safety kernel's bulk copy (a CUtensorMap, kept opaque here), and what it was made for
+  alignas(64) unsigned char tm_patch[128];
+  const void* tm_ptr = nullptr;
+  int tm_dim = 0, tm_rows = 0;
+  bool tm_ok = false, use_tma = true;
   bool prox_zero = false;  // d_prox is all zero (set by ga_patch_reset, cleared by whatever may write the plane)
   double* d_mres = nullptr;
   float* d_odist = nullptr;

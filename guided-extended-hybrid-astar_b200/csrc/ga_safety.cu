@@ -22,6 +22,8 @@
 //   P  4x4 max-pool of the tile from the same shared words (8 pooled cells per thread).
 // HBM traffic is the compulsory 1 B/cell read + 1 B/cell write + 1/16 B/cell pooled write; the halo
 // re-reads (1.5x) hit L2.
+#include <cuda.h>  // CUtensorMap (types only: the encoder is looked up through the runtime, libcuda is not linked)
+
 #include "ga_internal.cuh"
 
 #define DT_TW 8            // tile width in words (256 cells)
@@ -58,18 +60,21 @@ __device__ constexpr int K10_LVL_H[K10_NLVL] = { 3, 5, 6, 7, 8, 9, 10 };
 __device__ constexpr int K10_LVL_OF_W[K10_R + 1] = { 6, 5, 5, 5, 5, 4, 4, 3, 2, 1, 0 };
 
 // LOADW: widest aligned access the row pitch allows -- 16 (dim % 16 == 0), 4 (dim % 4 == 0) or 1.
-template <bool SPEC10, int LOADW>
+// TMA: the raw bytes of the tile + halo arrive as ONE cp.async.bulk.tensor.2d (needs LOADW == 16: the row pitch must be a
+// multiple of 16 bytes); otherwise by per-thread cp.async (LOADW 16 / 4) or byte loads (LOADW 1).
+template <bool SPEC10, int LOADW, bool TMA>
 __global__ void __launch_bounds__(DT_THREADS, SPEC10 ? 7 : 1)
 safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ safety, uint8_t* __restrict__ astar,
-              int astar_dim, const ga_se se, const uint32_t lo, const uint4 thr)
+              int astar_dim, const ga_se se, const uint32_t lo, const uint4 thr, const __grid_constant__ CUtensorMap tmap)
 {
-  extern __shared__ __align__(16) uint32_t smem[];
+  extern __shared__ __align__(128) uint32_t smem[];
   __shared__ uint32_t s_lut[256];   // (P1 nibble | P2 nibble << 4) -> 4 cell bytes
+  __shared__ __align__(8) unsigned long long s_mbar;
   const int r = SPEC10 ? K10_R : se.r;
   const int n_lvl = SPEC10 ? K10_NLVL : se.n_lvl;
   const int rows_in = DT_TH + 2 * r;
   uint32_t* sP = smem;                          // [plane][rows_in][DT_SW]   thresholded bit planes
-  uint32_t* sV = sP + 2 * rows_in * DT_SW;      // [level][DT_TH][DT_SW]  vertical ORs over |dy| <= hmax(level) of ONE plane at a time
+  uint32_t* sV = sP + ((2 * rows_in * DT_SW + 31) & ~31);  // (128-byte aligned: the bulk copy's destination) [level][DT_TH][DT_SW]  vertical ORs over |dy| <= hmax(level) of ONE plane at a time
   uint32_t* sOut = sV + n_lvl * DT_TH * DT_SW;  // [plane][DT_TH][DT_SW]  dilated planes
   constexpr int lvl_stride = DT_TH * DT_SW;
   const int w0 = blockIdx.x * DT_TW, y0 = blockIdx.y * DT_TH;
@@ -100,6 +105,32 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
     uint8_t* sRaw = reinterpret_cast<uint8_t*>(sV);
     const uint32_t raw0 = (uint32_t)__cvta_generic_to_shared(sRaw) + tid * 16;
     int rl = tid / DT_NH, c = tid - rl * DT_NH;
+    if (TMA)
+    {
+      // one bulk tensor copy per tile: box = DT_NH * 4 words x rows_in rows of the patch seen as a 2-D array of 32-bit
+      // words, rows and columns outside the image are zero-filled by the copy engine; completion on an mbarrier
+      const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+      if (tid == 0)
+      {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar) : "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(rows_in * DT_NH * 16) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(sRaw)), "l"(reinterpret_cast<uint64_t>(&tmap)), "r"(mbar), "r"(xh0 / 4),
+                     "r"(y0 - r)
+                     : "memory");
+      }
+      __syncthreads();  // the barrier object exists before anybody waits on it
+      uint32_t done = 0;
+      for (int spin = 0; !done; ++spin)
+      {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(mbar) : "memory");
+        if (spin > (1 << 22)) __trap();  // a copy that never completes is an error, not a hang
+      }
+    }
+    else
+    {
 #pragma unroll
     for (int j = 0; j < P0_N; ++j)
     {
@@ -136,6 +167,7 @@ safety_kernel(const uint8_t* __restrict__ patch, int dim, uint8_t* __restrict__ 
       if (c >= DT_NH) { c -= DT_NH; ++rl; }
     }
     if (LOADW >= 4) asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    }
     rl = tid / DT_NH; c = tid - rl * DT_NH;
 #pragma unroll
     for (int j = 0; j < P0_N; ++j)
@@ -378,6 +410,50 @@ extern "C" int ga_patch_insert(ga_ctx* c, const uint8_t* window, int ox, int oy,
   return GA_OK;
 }
 
+// The patch as a 2-D tensor of 32-bit words for cp.async.bulk.tensor: box = the DT_NH halves (x 4 words) a tile row
+// needs x rows_in rows, zero fill outside.  cuTensorMapEncodeTiled is a driver entry point; it is looked up through
+// the runtime so that the library keeps linking against cudart only.  false = not available: the kernel then stages
+// with per-thread cp.async (same result).
+static bool patch_tensor_map(ga_ctx* c, int dim, int rows_in)
+{
+  typedef CUresult (*encode_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static encode_t encode = nullptr;
+  static bool looked = false;
+  if (!looked)
+  {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      encode = reinterpret_cast<encode_t>(fn);
+    else
+      (void)cudaGetLastError();
+    looked = true;
+  }
+  c->tm_ptr = c->d_patch;
+  c->tm_dim = dim;
+  c->tm_rows = rows_in;
+  if (!encode) return false;
+  CUtensorMap tm;
+  const cuuint64_t gdim[2] = { (cuuint64_t)(dim / 4), (cuuint64_t)dim };
+  const cuuint64_t gstride[1] = { (cuuint64_t)dim };  // bytes between rows: a multiple of 16 (LOADW == 16)
+  const cuuint32_t box[2] = { (cuuint32_t)(DT_NH * 4), (cuuint32_t)rows_in };
+  const cuuint32_t estr[2] = { 1, 1 };
+  if (encode(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, c->d_patch, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  static_assert(sizeof(tm) <= sizeof(c->tm_patch), "tensor map storage");
+  memcpy(c->tm_patch, &tm, sizeof(tm));
+  return true;
+}
+
+extern "C" int ga_set_safety_staging(ga_ctx* c, int use_tma)
+{
+  if (!c) return GA_ERR_ARG;
+  c->use_tma = use_tma != 0;
+  return GA_OK;
+}
+
 extern "C" int ga_build_safety(ga_ctx* c)
 {
   if (!c) return GA_ERR_ARG;
@@ -391,7 +467,7 @@ extern "C" int ga_build_safety(ga_ctx* c)
     const int rows_in = DT_TH + 2 * c->se.r;
     // thresholded planes + the vertical ORs of every level (one plane at a time) + the dilated planes
     const size_t stage = (size_t)rows_in * DT_NH * 16;  // raw bytes of the tile + halo, staged where the vertical ORs and the dilated planes go later
-    const size_t smem = sizeof(uint32_t) * (size_t)2 * rows_in * DT_SW + std::max(stage, sizeof(uint32_t) * (size_t)(c->se.n_lvl + 2) * DT_TH * DT_SW);
+    const size_t smem = sizeof(uint32_t) * (size_t)((2 * rows_in * DT_SW + 31) & ~31) + std::max(stage, sizeof(uint32_t) * (size_t)(c->se.n_lvl + 2) * DT_TH * DT_SW);
     const int words = (dim + 31) / 32;
     dim3 grid((words + DT_TW - 1) / DT_TW, (dim + DT_TH - 1) / DT_TH);
     // the shipped 21 x 21 disk has compile-time tables
@@ -403,12 +479,23 @@ extern "C" int ga_build_safety(ga_ctx* c)
     const uint32_t lm = (lo - 1u) & 0xFFu;
     const uint4 thr = make_uint4(0x01010101u * (127u - (hi & 127u)), hi >= 128u ? 0xFFFFFFFFu : 0u,
                                  0x01010101u * (127u - (lm & 127u)), lm >= 128u ? 0xFFFFFFFFu : 0u);
-    void (*kern)(const uint8_t*, int, uint8_t*, uint8_t*, int, const ga_se, const uint32_t, const uint4) =
-        spec10 ? (loadw == 16 ? safety_kernel<true, 16> : loadw == 4 ? safety_kernel<true, 4> : safety_kernel<true, 1>)
-               : (loadw == 16 ? safety_kernel<false, 16> : loadw == 4 ? safety_kernel<false, 4> : safety_kernel<false, 1>);
+    // 16-byte row pitch: the tile + halo comes in as one bulk tensor copy (TMA), described once per patch
+    CUtensorMap tm;
+    memset(&tm, 0, sizeof(tm));
+    bool tma = false;
+    if (loadw == 16 && c->use_tma)
+    {
+      if (c->tm_ptr != c->d_patch || c->tm_dim != dim || c->tm_rows != rows_in) c->tm_ok = patch_tensor_map(c, dim, rows_in);
+      tma = c->tm_ok;
+      if (tma) memcpy(&tm, c->tm_patch, sizeof(tm));
+    }
+    typedef void (*kern_t)(const uint8_t*, int, uint8_t*, uint8_t*, int, const ga_se, const uint32_t, const uint4, const CUtensorMap);
+    const kern_t kern = tma      ? (spec10 ? safety_kernel<true, 16, true> : safety_kernel<false, 16, true>)
+                        : spec10 ? (loadw == 16 ? safety_kernel<true, 16, false> : loadw == 4 ? safety_kernel<true, 4, false> : safety_kernel<true, 1, false>)
+                                 : (loadw == 16 ? safety_kernel<false, 16, false> : loadw == 4 ? safety_kernel<false, 4, false> : safety_kernel<false, 1, false>);
     GA_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     GA_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    kern<<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo, thr);
+    kern<<<grid, DT_THREADS, smem, c->stream>>>(c->d_patch, dim, c->d_safety, c->d_astar, c->astar_dim, c->se, lo, thr, tm);
   }
   GA_CUDA(c, cudaGetLastError());
   return GA_OK;

@@ -126,6 +126,7 @@ SYMBOLS = {
     "ga_launch_count": (C.c_longlong, [_P]),
     "ga_heur_stats": (C.c_int, [_P, C.POINTER(C.c_longlong)]),
     "ga_set_heur_knobs": (C.c_int, [_P, _P]),
+    "ga_set_safety_staging": (C.c_int, [_P, C.c_int]),
     "ga_build_heuristic_ex": (C.c_int, [_P, C.c_int, C.POINTER(HeurQuery), C.POINTER(C.c_int)]),
     "ga_heur_near_nodes": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.POINTER(C.c_int)]),
     "ga_heur_closing_order": (C.c_int, [_P, _P, C.c_int, C.POINTER(C.c_int)]),

@@ -417,6 +417,10 @@ GA_API int ga_heur_stats(ga_ctx* ctx, long long* out7);
  * rounds, in-place halo refresh, linger ns, stage-ahead }; -1 = chosen per launch.  Every setting yields the same
  * fixed point (tests/test_gpu_parity.py::test_heuristic_schedules_agree); this exists for that test and for tuning. */
 GA_API int ga_set_heur_knobs(ga_ctx* ctx, const int* k7);
+/* how ga_build_safety stages a tile's raw bytes when the patch side is a multiple of 16: 1 (default) = one bulk tensor
+ * copy per tile (TMA), 0 = per-thread cp.async.  Same result either way (tests/test_gpu_parity.py::test_safety_staging_modes);
+ * this exists for that test and for measurement. */
+GA_API int ga_set_safety_staging(ga_ctx* ctx, int use_tma);
 /* launches of ALL library kernels since ga_create / ga_prof_reset (always counted) */
 GA_API long long ga_launch_count(const ga_ctx* ctx);
 

@@ -52,6 +52,48 @@ def test_dilation_radii(planner, oracle, r):
     assert np.array_equal(cc.patch_safety_arr_, oracle.process_safety_patch(patch, 100, 130, r))
 
 
+@pytest.mark.parametrize("lo,hi", [(0, 130), (0, 255), (1, 127), (100, 127), (100, 128), (128, 128), (129, 200), (200, 255), (255, 255)])
+@pytest.mark.parametrize("dim", [320, 300, 301])
+def test_threshold_edges(planner, oracle, lo, hi, dim):
+    """MIN_THRESH / MAX_THRESH at the edges of the SWAR byte compare (0: nothing is below; 127 / 128: the carry bit of
+    the compare; 255: nothing is above) on uniformly random bytes, for the 16-byte, 4-byte and byte-wise row modes
+    (dim % 16 == 0, % 4 == 0, neither) -- collision_checking.cpp:213-220."""
+    ctx, cc, astar = planner
+    cc.calculateDisks()
+    p = _abi.CollisionParams(lo, hi, 2, 3, cc.nb_disks_, 4)
+    cen = np.ascontiguousarray(cc.disk_centers_, np.int32)
+    ctx.check(ctx.lib.ga_set_collision_params(ctx.h, C.byref(p), _abi.ptr(cen)))
+    cc.resetPatch(dim)
+    rng = np.random.default_rng(lo * 256 + hi + dim)
+    patch = rng.integers(0, 256, (dim, dim)).astype(np.uint8)
+    patch[rng.random((dim, dim)) < 0.9] = max(lo - 1, 0)   # mostly FREE (when anything is), so that dilation has room
+    ctx.upload(_abi.GRID_PATCH, patch)
+    cc.processSafetyPatch()
+    want = oracle.process_safety_patch(patch, lo, hi, 2)
+    assert np.array_equal(cc.patch_safety_arr_, want)
+    assert np.array_equal(astar.astar_grid_, oracle.pool_max(want))
+
+
+@pytest.mark.parametrize("dim", [64, 1008, 2048])
+def test_safety_staging_modes(planner, oracle, dim):
+    """the tile's raw bytes by one bulk tensor copy (TMA, zero fill outside the image) or by per-thread cp.async: same bytes"""
+    patch = ga_b200.gen_map(dim, dim)
+    rng = np.random.default_rng(dim)
+    patch[0, :] = rng.integers(0, 256, dim)      # the image borders are where the two stagings differ in mechanism
+    patch[-1, :] = rng.integers(0, 256, dim)
+    patch[:, 0] = rng.integers(0, 256, dim)
+    patch[:, -1] = rng.integers(0, 256, dim)
+    ctx, cc, astar = planner
+    cc.initialize(dim)
+    ctx.upload(_abi.GRID_PATCH, patch)
+    want = oracle.process_safety_patch(patch, 100, 130, cc.disk_r_c_)
+    for use_tma in (0, 1):
+        ctx.check(ctx.lib.ga_set_safety_staging(ctx.h, use_tma))
+        cc.processSafetyPatch()
+        assert np.array_equal(cc.patch_safety_arr_, want), use_tma
+        assert np.array_equal(astar.astar_grid_, oracle.pool_max(want)), use_tma
+
+
 def test_empty_and_full_patches(planner, oracle):
     ctx, cc, astar = planner
     cc.initialize(256)
