@@ -11,6 +11,7 @@
 // ga_expand flags primitives whose poses come within 1e-9 cells of a discretisation boundary.
 #include <climits>
 #include <cmath>
+#include <mutex>
 
 #include "ga_prox.cuh"
 
@@ -441,6 +442,124 @@ extern "C" int ga_valid_close_pose(ga_ctx* c, const double* center_pose, const i
   const int idx = *h_arg;
   if (idx < 0) return GA_OK;
   // the winning pose, with the loop's own arithmetic (:1632-1640)
+  const int dphii = idx % (2 * v.nphi) - v.nphi, r = idx / (2 * v.nphi);
+  const int dyi = r % (2 * v.nxy) - v.nxy, dxi = r / (2 * v.nxy) - v.nxy;
+  out_pose[0] = v.cx + dxi * CP_GM_RES;
+  out_pose[1] = v.cy + dyi * CP_GM_RES;
+  out_pose[2] = v.cyaw + dphii * v.phi_res;
+  *found = 1;
+  return GA_OK;
+}
+
+// ---- ga_valid_close_pose_noalloc ------------------------------------------------------------------
+// The same search for callers that must not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): no counterpart in the reference.  ga_valid_close_pose keeps
+// its scratch (cell list, membership map, one key per candidate, the two result words) in the context's staging buffer,
+// which grows by cudaMalloc / cudaMallocHost; here the scratch is a file-scope device array of fixed size (every GPU
+// that loads the library holds GA_NOALLOC_SCRATCH_BYTES until exit) and the per-candidate keys are not stored at all:
+// the second pass evaluates the candidates again (same instructions, same bits) instead of reading them back.
+//   layout: [0, 256)                       best key (u64), arg (i32)
+//           [256, +4 * MAX_NEAR)           near_cells as uploaded
+//           [.., +MAX_ASTAR_DIM^2)         membership map, 1 byte per astar cell
+// All calls, from every context and stream of a process, share the array on a device: calls that overlap on the GPU
+// race.  It keeps the last call's contents; what must start clean (the map, the two result words) is cleared per call.
+#define NA_OFF_NEAR 256
+#define NA_OFF_MEMBER (NA_OFF_NEAR + 4 * GA_NOALLOC_MAX_NEAR)
+static_assert(NA_OFF_MEMBER + GA_NOALLOC_MAX_ASTAR_DIM * GA_NOALLOC_MAX_ASTAR_DIM == GA_NOALLOC_SCRATCH_BYTES, "scratch layout");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[GA_NOALLOC_SCRATCH_BYTES];
+
+__global__ void __launch_bounds__(256) close_pose_min_nokeys_kernel(close_pose_view v, int n, unsigned long long* __restrict__ best)
+{
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long key = ~0ull;
+  if (idx < n)
+  {
+    unsigned long long k;
+    if (close_pose_eval(v, idx, &k)) key = k;
+  }
+  for (int o = 16; o > 0; o >>= 1)
+  {
+    const unsigned long long other = __shfl_xor_sync(0xFFFFFFFFu, key, o);
+    key = other < key ? other : key;
+  }
+  if ((threadIdx.x & 31) == 0 && key != ~0ull) atomicMin(best, key);
+}
+
+__global__ void __launch_bounds__(256) close_pose_arg_nokeys_kernel(close_pose_view v, int n, const unsigned long long* __restrict__ best,
+                                                                    int* __restrict__ arg)
+{
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long b = *best;
+  if (idx >= n || b == ~0ull) return;
+  unsigned long long k;
+  if (close_pose_eval(v, idx, &k) && k == b) atomicMax(arg, idx);
+}
+
+// device address of the scratch array on `device` (which must be current).  In host code the array's name is a
+// host-side stand-in, not a device address: it is resolved once per device and the pointer is what kernels get.
+static int noalloc_scratch(ga_ctx* c, unsigned char** out)
+{
+  static std::mutex mu;
+  static unsigned char* ptr[64] = { nullptr };
+  GA_REQUIRE(c, c->device >= 0 && c->device < 64, GA_ERR_ARG, "device index out of range for the no-alloc scratch table");
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptr[c->device])
+  {
+    void* p = nullptr;
+    GA_CUDA(c, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    ptr[c->device] = static_cast<unsigned char*>(p);
+  }
+  *out = ptr[c->device];
+  return GA_OK;
+}
+
+extern "C" int ga_valid_close_pose_noalloc(ga_ctx* c, const double* center_pose, const int* near_cells, int n_near, double* out_pose,
+                                           int* found)
+{
+  if (!c) return GA_ERR_ARG;
+  GA_REQUIRE(c, c->patch_dim > 0 && c->have_cp, GA_ERR_STATE, "no patch / collision params");
+  GA_REQUIRE(c, c->have_pp, GA_ERR_STATE, "no prox params (call ga_set_prox_params)");
+  GA_REQUIRE(c, center_pose && out_pose && found && n_near >= 0 && (n_near == 0 || near_cells), GA_ERR_ARG, "bad arguments");
+  GA_REQUIRE(c, n_near <= GA_NOALLOC_MAX_NEAR, GA_ERR_ARG, "ga_valid_close_pose_noalloc: n_near exceeds GA_NOALLOC_MAX_NEAR (65536)");
+  GA_REQUIRE(c, c->astar_dim <= GA_NOALLOC_MAX_ASTAR_DIM, GA_ERR_ARG,
+             "ga_valid_close_pose_noalloc: astar grid larger than GA_NOALLOC_MAX_ASTAR_DIM (1024) cells per side");
+  GA_CUDA(c, cudaSetDevice(c->device));
+  unsigned char* scratch = nullptr;
+  const int rc = noalloc_scratch(c, &scratch);
+  if (rc) return rc;
+  close_pose_view v;
+  v.cv = make_view(c);
+  v.pa = prox_args{ c->d_prox, c->astar_dim, c->pp };
+  v.cx = center_pose[0];
+  v.cy = center_pose[1];
+  v.cyaw = center_pose[2];
+  v.phi_res = c->yaw_res_coll_rad;
+  v.nxy = static_cast<int>(std::floor(CP_DXY_MAX) / CP_GM_RES);
+  v.nphi = static_cast<int>(std::floor(GA_PI) / v.phi_res);
+  const int n = 2 * v.nxy * 2 * v.nxy * 2 * v.nphi;
+  *found = 0;
+  if (n <= 0 || n_near == 0) return GA_OK;
+  const size_t cells = (size_t)c->astar_dim * c->astar_dim;
+  unsigned long long* d_best = reinterpret_cast<unsigned long long*>(scratch);
+  int* d_arg = reinterpret_cast<int*>(scratch + 8);
+  int* d_near = reinterpret_cast<int*>(scratch + NA_OFF_NEAR);
+  uint8_t* d_mem = scratch + NA_OFF_MEMBER;
+  // pageable source: the driver has taken the bytes when the call returns
+  GA_CUDA(c, cudaMemcpyAsync(d_near, near_cells, sizeof(int) * (size_t)n_near, cudaMemcpyHostToDevice, c->stream));
+  GA_CUDA(c, cudaMemsetAsync(d_mem, 0, cells, c->stream));
+  GA_CUDA(c, cudaMemsetAsync(d_best, 0xFF, 16, c->stream));  // best = all ones, arg = -1
+  v.member = d_mem;
+  {
+    ga_launch_scope ls(c, GA_K_COLLISION, 3);
+    fill_u8_scatter_kernel<<<(n_near + 255) / 256, 256, 0, c->stream>>>(d_mem, d_near, n_near, (int)cells);
+    close_pose_min_nokeys_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(v, n, d_best);
+    close_pose_arg_nokeys_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(v, n, d_best, d_arg);
+  }
+  GA_CUDA(c, cudaGetLastError());
+  int idx = -1;
+  GA_CUDA(c, cudaMemcpyAsync(&idx, d_arg, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  GA_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (idx < 0) return GA_OK;
   const int dphii = idx % (2 * v.nphi) - v.nphi, r = idx / (2 * v.nphi);
   const int dyi = r % (2 * v.nxy) - v.nxy, dxi = r / (2 * v.nxy) - v.nxy;
   out_pose[0] = v.cx + dxi * CP_GM_RES;

@@ -107,6 +107,7 @@ SYMBOLS = {
     "ga_set_prox_params": (C.c_int, [_P, C.POINTER(ProxParams)]),
     "ga_prox_of_corners": (C.c_int, [_P, C.c_void_p, C.c_int, C.c_void_p]),
     "ga_valid_close_pose": (C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int)]),
+    "ga_valid_close_pose_noalloc": (C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int)]),
     "ga_path_prox_costs": (C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "ga_build_heuristic": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ga_build_heuristic_batch": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -284,6 +284,21 @@ GA_API int ga_path_prox_costs(ga_ctx* ctx, const double* poses, const int* path_
 GA_API int ga_valid_close_pose(ga_ctx* ctx, const double* center_pose, const int* near_cells, int n_near, double* out_pose,
                                int* found);
 
+/* ga_valid_close_pose for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.  Same
+ * arguments and the same result as ga_valid_close_pose, bit for bit; the call performs no cudaMalloc / cudaMallocHost /
+ * cudaFree: its scratch (cell list, membership map, result words) is a static device array of
+ * GA_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit, and the candidates are evaluated
+ * twice instead of being stored.  Limits: n_near <= GA_NOALLOC_MAX_NEAR and an astar grid of at most
+ * GA_NOALLOC_MAX_ASTAR_DIM cells per side (patch_dim <= 4096), else GA_ERR_ARG with a message in ga_last_error.
+ * All calls on a device share the array: calls that overlap on the GPU (two contexts, two streams, two threads) race;
+ * the array keeps the last call's contents and is cleared per call where it must start clean. */
+#define GA_NOALLOC_MAX_NEAR 65536
+#define GA_NOALLOC_MAX_ASTAR_DIM 1024
+#define GA_NOALLOC_SCRATCH_BYTES (256 + 4 * GA_NOALLOC_MAX_NEAR + GA_NOALLOC_MAX_ASTAR_DIM * GA_NOALLOC_MAX_ASTAR_DIM)
+GA_API int ga_valid_close_pose_noalloc(ga_ctx* ctx, const double* center_pose, const int* near_cells, int n_near,
+                                       double* out_pose, int* found);
+
 /* ---- heuristic grid ------------------------------------------------------------------------- */
 
 typedef struct
