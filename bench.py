@@ -430,12 +430,12 @@ def run_plan_leg(args, local_rank, rank):
     return out
 
 
-def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak):
+def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak, nq=None):
     """BASELINE config 5's shape on one GPU: a batch of independent queries on 2048^2 maps (64 queries
     share a map), one heuristic grid per query, all grids relaxed by ONE kernel chain
     (ga_build_heuristic_batch).  Reports grids/s, Mcells/s and the algorithmic-bytes rate."""
     from ga_b200 import _abi
-    nq, dim = args.batch, 2048
+    nq, dim = (nq or args.batch), 2048
     maps = {}
     ctxs, astars, goals = [], [], []
     for qi in range(nq):
@@ -460,7 +460,7 @@ def run_batch_leg(ga, torch, device, rank, args, sampler, hbm_peak):
     hs = (C.c_void_p * nq)(*[c.h for c in ctxs])
     g = np.ascontiguousarray(goals, np.int32).reshape(nq, 2)
     gp = g.ctypes.data_as(C.POINTER(C.c_int))
-    reps = max(3, min(20, args.steps // 10))
+    reps = max(3, min(20, args.steps // 10)) if nq <= 256 else 3
     for _ in range(2):
         lead.check(lead.lib.ga_build_heuristic_batch(hs, nq, 0, gp, None))
     lead.sync()
@@ -697,6 +697,7 @@ def main():
     ap.add_argument("--no-mps", action="store_true", help="plan leg: do not start a CUDA MPS daemon for the planner processes")
     ap.add_argument("--plan-only", action="store_true", help="run only the plan leg (development)")
     ap.add_argument("--batch", type=int, default=128, help="queries of the batched-heuristic leg (0 = skip)")
+    ap.add_argument("--batch-large", type=int, default=1024, help="queries of the large batched-heuristic run on rank 0 (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -843,6 +844,9 @@ def main():
     e2e_wall_ms, e2e_cells, _ = timed_e2e(e2e_steps, True, False)
     lean_wall_ms, lean_cells, _ = timed_e2e(e2e_steps, True, True)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
+    # the same with 1024 queries in one chain (rank 0 only: it is a statement about the kernel, not about scaling)
+    batch_large = (run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak, nq=args.batch_large)
+                   if (rank == 0 and args.batch > 0 and args.batch_large > 0) else None)
     collision = run_collision_leg(envs[0], args, ga_b200) if (rank == 0 and not args.no_collision) else None
     replan = run_replan_leg(ga_b200, local_rank, args) if (rank == 0 and not args.no_replan) else None
     sampler.stop_flag = True
@@ -923,6 +927,9 @@ def main():
         if batch:
             batch["grids_per_s_all_ranks"] = batch_n / (batch_ms * 1e-3)
             line["batch"] = batch
+        if batch_large:
+            batch_large.pop("grids_per_s_all_ranks", None)
+            line["batch_large"] = batch_large
         if collision:
             line["collision"] = collision
         if replan:
