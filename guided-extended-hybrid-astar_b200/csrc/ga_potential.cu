@@ -19,9 +19,12 @@
 #include "ga_internal.cuh"
 
 #define PB 2            // border rows above / below the staged window
-#define PX 7            // border columns (DT_K + 2) on either side
+#ifndef DT_K
 #define DT_K 5          // cells per lane and step
-#define DT_PITCH(V) ((((V) + 2 * PX) & 1) ? (V) + 2 * PX + 1 : (V) + 2 * PX)  // even pitch: consecutive lanes' block starts are pitch - DT_K - 2 words apart, odd = distinct banks
+#endif
+#define PX (DT_K + 2)   // border columns on either side
+// consecutive lanes' block starts are pitch - DT_K - 2 words apart: the pitch makes that odd (distinct banks)
+#define DT_PITCH(V) (((((V) + 2 * PX) - DT_K) & 1) ? (V) + 2 * PX : (V) + 2 * PX + 1)
 #define P_THREADS 256   // >= vor_dim
 
 template <bool IPP>
@@ -154,15 +157,14 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
     int y = lane;
     for (int t = 0; t < steps; ++t)
     {
-      int x0 = DT_K * (t - y) - 2 * y;
-      if (y < V && x0 >= V)  // this row is finished: on to the lane's next one
+      // branch-free step: a lane without work (row not begun, finished, or no row left) computes on clamped addresses
+      // and stores nothing -- the divergent branches cost a quarter of the single warp's issue time
+      if (y < V && DT_K * (t - y) - 2 * y >= V) y += 32;  // this row is finished: on to the lane's next one (a select)
+      const int x0r = DT_K * (t - y) - 2 * y;
+      const bool act = y < V && x0r + DT_K - 1 >= 0 && x0r < V;
+      const int x0 = min(max(x0r, -(DT_K - 1)), V - 1);
       {
-        y += 32;
-        x0 = DT_K * (t - y) - 2 * y;
-      }
-      if (y < V && x0 + DT_K - 1 >= 0 && x0 < V)
-      {
-        T* row = s + (size_t)(y + PB) * S + PX;
+        T* row = s + (size_t)(min(y, V - 1) + PB) * S + PX;
         T u1[DT_K + 4], u2[DT_K + 2], own[DT_K];
 #pragma unroll
         for (int j = 0; j < DT_K + 4; ++j) u1[j] = row[x0 - 2 + j - S];
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
           T t0 = min(up[j], left + TR::hv());                              // (y, x-1)
           if (IPP) t0 = min(t0, TR::big());
           const T v = own[j] != (T)0 ? t0 : own[j];
-          if (x >= 0 && x < V) row[x] = v;
+          if (act && x >= 0 && x < V) row[x] = v;
           left = v;
         }
       }
@@ -199,15 +201,12 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
     y = lane;
     for (int t = 0; t < steps; ++t)
     {
-      int m0 = DT_K * (t - y) - 2 * y;  // first mirrored column of the block; real column = V - 1 - m
-      if (y < V && m0 >= V)
+      if (y < V && DT_K * (t - y) - 2 * y >= V) y += 32;
+      const int m0r = DT_K * (t - y) - 2 * y;  // first mirrored column of the block; real column = V - 1 - m
+      const bool act = y < V && m0r + DT_K - 1 >= 0 && m0r < V;
+      const int m0 = min(max(m0r, -(DT_K - 1)), V - 1);
       {
-        y += 32;
-        m0 = DT_K * (t - y) - 2 * y;
-      }
-      if (y < V && m0 + DT_K - 1 >= 0 && m0 < V)
-      {
-        T* row = s + (size_t)(V - 1 - y + PB) * S + PX;
+        T* row = s + (size_t)(V - 1 - min(y, V - 1) + PB) * S + PX;
         const int xr = V - 1 - m0;            // real column of the block's first cell (blocks run right to left)
         T d1[DT_K + 4], d2[DT_K + 2], own[DT_K];
 #pragma unroll
@@ -232,7 +231,7 @@ __global__ void __launch_bounds__(P_THREADS) dt_kernel(pot_args a)
           const int x = xr - j;
           const T t0 = min(min(own[j], dn[j]), right + TR::hv());          // (y, x+1)
           const T v = (IPP || own[j] > TR::hv()) ? t0 : own[j];
-          if (x >= 0 && x < V) row[x] = v;
+          if (act && x >= 0 && x < V) row[x] = v;
           right = v;
         }
       }
