@@ -167,27 +167,70 @@ __device__ __forceinline__ int q_pop_warp(const heur_queue& q, const int lane)
   return e;
 }
 
-// one grid per blockIdx.y.  The control block (cursors, pending count) was zeroed by the host.
+// every tile whose staged block [t * edge - 1, t * edge + edge] holds cell i carries a prox cost (at most 2 x 2 tiles)
+__device__ __forceinline__ void init_stamp_prox(const heur_grid& G, size_t i)
+{
+  const int x = (int)(i % G.dim), y = (int)(i / G.dim);
+  for (int ty = y / G.edge - 1; ty <= y / G.edge + 1; ++ty)
+    for (int tx = x / G.edge - 1; tx <= x / G.edge + 1; ++tx)
+      if (tx >= 0 && ty >= 0 && tx < G.tiles_x && ty < G.tiles_x && x >= tx * G.edge - 1 && x <= tx * G.edge + G.edge &&
+          y >= ty * G.edge - 1 && y <= ty * G.edge + G.edge)
+        G.tprox[ty * G.tiles_x + tx] = G.epoch;
+}
+
+// verifyNode (a_star.cpp:325-343) and unknown_cost (:253-254) inputs, folded once per build
+__device__ __forceinline__ uint8_t init_cls(uint8_t cell, uint8_t fence)
+{
+  return (uint8_t)((cell == GA_UNKNOWN ? 1 : 0) | ((cell == GA_OCC || fence == 1) ? 2 : 0));
+}
+
+// one grid per blockIdx.y.  The control block (cursors, pending count) was zeroed by the host.  Four cells per thread
+// and step (4-byte loads of the byte planes, 16-byte stores of the cost plane); G.prox == nullptr: the context's
+// proximity plane is known to be zero (prox_free), it is not read at all.
 __global__ void heur_init_kernel(heur_grid single, const heur_grid* many, heur_queue q)
 {
   const int gi = blockIdx.y;
   const heur_grid& G = many ? many[gi] : single;
-  const size_t n = (size_t)G.dim * G.dim;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+  const size_t n = (size_t)G.dim * G.dim, n4 = n / 4;
+  const size_t goal = (size_t)G.goal;
+  const double w_prox = G.w_prox;
+  const bool with_prox = G.prox != nullptr && w_prox != 0.0;
+  for (size_t i4 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i4 < n4; i4 += (size_t)gridDim.x * blockDim.x)
   {
-    G.g[i] = (i == (size_t)G.goal) ? 0.0 : INFINITY;
-    const uint8_t cell = G.grid[i];  // verifyNode (a_star.cpp:325-343) and unknown_cost (:253-254) inputs, folded once per build
-    G.cls[i] = (cell == GA_UNKNOWN ? 1 : 0) | ((cell == GA_OCC || G.fence[i] == 1) ? 2 : 0);
-    if (G.prox[i] * G.w_prox != 0.0)
+    const size_t i = 4 * i4;
+    const uchar4 cell = *reinterpret_cast<const uchar4*>(G.grid + i), fc = *reinterpret_cast<const uchar4*>(G.fence + i);
+    double2 p0 = make_double2(0.0, 0.0), p1 = p0;
+    if (with_prox)
     {
-      // every tile whose staged block [t * edge - 1, t * edge + edge] holds the cell (at most 2 x 2)
-      const int x = (int)(i % G.dim), y = (int)(i / G.dim);
-      for (int ty = y / G.edge - 1; ty <= y / G.edge + 1; ++ty)
-        for (int tx = x / G.edge - 1; tx <= x / G.edge + 1; ++tx)
-          if (tx >= 0 && ty >= 0 && tx < G.tiles_x && ty < G.tiles_x && x >= tx * G.edge - 1 && x <= tx * G.edge + G.edge &&
-              y >= ty * G.edge - 1 && y <= ty * G.edge + G.edge)
-            G.tprox[ty * G.tiles_x + tx] = G.epoch;
+      p0 = *reinterpret_cast<const double2*>(G.prox + i);
+      p1 = *reinterpret_cast<const double2*>(G.prox + i + 2);
     }
+    double2 g0 = make_double2(INFINITY, INFINITY), g1 = g0;
+    if (goal - i < 4)  // the root (unsigned difference: goal in [i, i + 4))
+    {
+      if (goal == i) g0.x = 0.0;
+      if (goal == i + 1) g0.y = 0.0;
+      if (goal == i + 2) g1.x = 0.0;
+      if (goal == i + 3) g1.y = 0.0;
+    }
+    *reinterpret_cast<double2*>(G.g + i) = g0;
+    *reinterpret_cast<double2*>(G.g + i + 2) = g1;
+    *reinterpret_cast<uchar4*>(G.cls + i) = make_uchar4(init_cls(cell.x, fc.x), init_cls(cell.y, fc.y), init_cls(cell.z, fc.z), init_cls(cell.w, fc.w));
+    if (with_prox)
+    {
+      if (p0.x * w_prox != 0.0) init_stamp_prox(G, i);
+      if (p0.y * w_prox != 0.0) init_stamp_prox(G, i + 1);
+      if (p1.x * w_prox != 0.0) init_stamp_prox(G, i + 2);
+      if (p1.y * w_prox != 0.0) init_stamp_prox(G, i + 3);
+    }
+  }
+  // the last n mod 4 cells
+  if (blockIdx.x == 0 && threadIdx.x < (unsigned)(n - 4 * n4))
+  {
+    const size_t i = 4 * n4 + threadIdx.x;
+    G.g[i] = (i == goal) ? 0.0 : INFINITY;
+    G.cls[i] = init_cls(G.grid[i], G.fence[i]);
+    if (with_prox && G.prox[i] * w_prox != 0.0) init_stamp_prox(G, i);
   }
   const int gx = G.goal % G.dim, gy = G.goal / G.dim;
   const int goal_tile = (gy / G.edge) * G.tiles_x + gx / G.edge;
@@ -935,7 +978,7 @@ __device__ __forceinline__ unsigned fin_match(const double* sg, const double* sb
   return match;
 }
 
-__global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single, const heur_args* many)
+__global__ void __launch_bounds__(FB * FB, 2) heur_finish_a_kernel(heur_args single, const heur_args* many)
 {
   __shared__ double sg[FS * FS];
   __shared__ double sb[FS * FS];
@@ -948,25 +991,46 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
   const int ox = bx * FB - 1, oy = by * FB - 1;
   const double w_prox = a.w_prox, unk_w = a.unk_w;
   int any_prox = 0;
-  // the cell's own movement cost: issued with the staging loads, one memory round trip for both
+  // staging without a division: every thread loads its own cell (row-wise coalesced) and the first 4 * FB + 4 threads
+  // one cell of the halo ring; the cell's own movement cost goes out with them (one memory round trip for all).
+  // a.prox == nullptr: the proximity plane is known to be zero (prox_free) and is not read.
+  const bool with_prox = a.prox != nullptr;
   const int own_x = bx * FB + (int)(threadIdx.x % FB), own_y = by * FB + (int)(threadIdx.x / FB);
   const double m_own = (own_x < dim && own_y < dim) ? __ldg(a.mc + (size_t)own_y * dim + own_x) : 0.0;
-  for (int i = threadIdx.x; i < FS * FS; i += FB * FB)
   {
-    const int x = ox + i % FS, y = oy + i / FS;
-    double gv = INFINITY, bv = 0.0;
-    uint8_t u = 0;
-    if (x >= 0 && y >= 0 && x < dim && y < dim)
+    const int k = threadIdx.x;
+    // ring position of thread k: top row, bottom row, left column, right column (corners belong to the rows)
+    int rx = -1, ry = -1;
+    if (k < FS) { rx = k; ry = 0; }
+    else if (k < 2 * FS) { rx = k - FS; ry = FS - 1; }
+    else if (k < 2 * FS + FB) { rx = 0; ry = k - 2 * FS + 1; }
+    else if (k < 2 * FS + 2 * FB) { rx = FS - 1; ry = k - 2 * FS - FB + 1; }
+    const int px[2] = { (int)(threadIdx.x % FB) + 1, rx }, py[2] = { (int)(threadIdx.x / FB) + 1, ry };
+    double gv[2] = { INFINITY, INFINITY }, bv[2] = { 0.0, 0.0 };
+    uint8_t u[2] = { 0, 0 };
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
     {
-      const size_t id = (size_t)y * dim + x;
-      gv = __ldcg(a.g + id);
-      bv = __ldg(a.prox + id) * w_prox;
-      u = __ldg(a.grid + id) == GA_UNKNOWN;
+      const int x = ox + px[j], y = oy + py[j];
+      if (px[j] >= 0 && x >= 0 && y >= 0 && x < dim && y < dim)
+      {
+        const size_t id = (size_t)y * dim + x;
+        gv[j] = __ldcg(a.g + id);
+        if (with_prox) bv[j] = __ldg(a.prox + id);
+        u[j] = __ldg(a.grid + id);
+      }
     }
-    sg[i] = gv;
-    sb[i] = bv;
-    su[i] = u;
-    any_prox |= (bv != 0.0);
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      if (px[j] >= 0)
+      {
+        const int i = py[j] * FS + px[j];
+        const double b = bv[j] * w_prox;
+        sg[i] = gv[j];
+        if (with_prox) sb[i] = b;
+        su[i] = u[j] == GA_UNKNOWN;
+        any_prox |= (b != 0.0);
+      }
   }
   const int has_prox = __syncthreads_or(any_prox);
   const int lx = threadIdx.x % FB, ly = threadIdx.x / FB, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1053,23 +1117,26 @@ __global__ void __launch_bounds__(FB * FB) heur_finish_a_kernel(heur_args single
   // log2(chain length) rounds instead of one hop per step (a warp used to wait for its longest chain: ~360 of the
   // ~560 warp instructions per cell).  Parent pointers cannot form a cycle while every edge weight is positive
   // (ga_set_astar_params and ga_upload enforce that); the round cap keeps a corrupted plane from hanging the kernel.
-  unsigned* sj = reinterpret_cast<unsigned*>(sb);  // the prox plane is not needed any more
+  unsigned* sj = reinterpret_cast<unsigned*>(sb);  // the prox plane is not needed any more: two buffers of FB * FB words
+  static_assert(sizeof(double) * FS * FS >= 2 * sizeof(unsigned) * FB * FB, "pointer-jumping buffers");
   __syncthreads();
   {
     const unsigned diag = lpar >= 0 ? (unsigned)(lpar >> 10) : 0u;
     sj[threadIdx.x] = lpar >= 0 ? ((unsigned)(lpar & 1023) | ((1u - diag) << 10) | (diag << 21)) : (unsigned)threadIdx.x;
   }
   __syncthreads();
+  int buf = 0;  // rounds read one buffer and write the other: one barrier per round
   for (int round = 0; round < 11; ++round)
   {
-    const unsigned w = sj[threadIdx.x];
-    const unsigned wp = sj[w & 1023u];
+    const unsigned* src = sj + buf * (FB * FB);
+    const unsigned w = src[threadIdx.x];
+    const unsigned wp = src[w & 1023u];
     const bool changed = (wp & 1023u) != (w & 1023u);
-    const unsigned nw = (wp & 1023u) | ((w & ~1023u) + (wp & ~1023u));  // steps add field by field (each < 1024: no carry across)
-    __syncthreads();
-    sj[threadIdx.x] = nw;
+    buf ^= 1;
+    sj[buf * (FB * FB) + threadIdx.x] = (wp & 1023u) | ((w & ~1023u) + (wp & ~1023u));  // steps add field by field (each < 1024: no carry across)
     if (!__syncthreads_or(changed)) break;
   }
+  sj += buf * (FB * FB);
   const unsigned fin = sj[threadIdx.x];
   const int cur = (int)(fin & 1023u), cs = (int)((fin >> 10) & 2047u), cd = (int)(fin >> 21);
   if (in) a.scratch[n] = fin_pack(cur % FB - lx, cur / FB - ly, cs, cd);
@@ -1109,27 +1176,38 @@ __global__ void __launch_bounds__(FIN_SLOTS) heur_finish_b_kernel(heur_args sing
   __stcg(reinterpret_cast<long long*>(a.tot) + c, ((long long)cd << 32) | (unsigned)cs);  // one 8-byte store: never seen half written
 }
 
+__device__ __forceinline__ double fin_dist(const heur_args& a, int c, unsigned flag, unsigned s, int dim)
+{
+  if (!(flag & GA_H_CLOSED)) return INFINITY;
+  int cs = (s >> 12) & 1023, cd = (s >> 22) & 1023;
+  const int t = fin_target(s, c, dim);
+  if (t != a.goal)
+  {
+    const int2 tt = a.tot[t];
+    cs += tt.x;
+    cd += tt.y;
+  }
+  return (double)cs * a.L1 + (double)cd * a.L2;  // NodeDisc::cost_dist_
+}
+
+// four cells per thread: 4-byte / 16-byte loads of the flag and scratch planes, 16-byte stores of cost_dist
 __global__ void __launch_bounds__(256) heur_finish_c_kernel(heur_args single, const heur_args* many)
 {
   const heur_args& a = many ? many[blockIdx.y] : single;
   const int dim = a.dim, ncell = dim * dim;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
   if (c >= ncell) return;
-  double d = INFINITY;
-  if (a.flags[c] & GA_H_CLOSED)
+  if (c + 4 <= ncell)
   {
-    const unsigned s = a.scratch[c];
-    int cs = (s >> 12) & 1023, cd = (s >> 22) & 1023;
-    const int t = fin_target(s, c, dim);
-    if (t != a.goal)
-    {
-      const int2 tt = a.tot[t];
-      cs += tt.x;
-      cd += tt.y;
-    }
-    d = (double)cs * a.L1 + (double)cd * a.L2;  // NodeDisc::cost_dist_
+    const uchar4 f = *reinterpret_cast<const uchar4*>(a.flags + c);
+    const uint4 s = *reinterpret_cast<const uint4*>(a.scratch + c);
+    const double d0 = fin_dist(a, c, f.x, s.x, dim), d1 = fin_dist(a, c + 1, f.y, s.y, dim);
+    const double d2 = fin_dist(a, c + 2, f.z, s.z, dim), d3 = fin_dist(a, c + 3, f.w, s.w, dim);
+    *reinterpret_cast<double2*>(a.dist + c) = make_double2(d0, d1);
+    *reinterpret_cast<double2*>(a.dist + c + 2) = make_double2(d2, d3);
   }
-  a.dist[c] = d;
+  else
+    for (int k = c; k < ncell; ++k) a.dist[k] = fin_dist(a, k, a.flags[k], a.scratch[k], dim);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1182,13 +1260,17 @@ int ga_heur_alloc(ga_ctx* c)
   return GA_OK;
 }
 
+// no cell of the context's h_prox plane can hold a cost: the plane is all zero since ga_patch_reset (nothing was
+// uploaded into it, no potential field built, its device pointer not handed out), or the weight is zero
+static bool prox_free(const ga_ctx* c) { return c->prox_zero || c->ap.astar_prox_cost == 0.0; }
+
 static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed, heur_grid* G, heur_args* a)
 {
   ++c->heur_epoch;
   G->grid = c->d_astar;
   G->fence = c->d_fence;
   G->mc = c->d_mc;
-  G->prox = c->d_prox;
+  G->prox = prox_free(c) ? nullptr : c->d_prox;  // nullptr: known to be all zero, never read
   G->g = c->d_hcost[slot];
   G->cls = c->d_hcls;
   G->state = c->d_tile_active;
@@ -1203,7 +1285,7 @@ static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed,
   G->unk_w = c->ap.unknown_cost_w;
   a->grid = c->d_astar;
   a->mc = c->d_mc;
-  a->prox = c->d_prox;
+  a->prox = G->prox;
   a->g = c->d_hcost[slot];
   a->parent = c->d_hparent[slot];
   a->dist = c->d_hdist[slot];
@@ -1237,10 +1319,6 @@ static void queue_knobs(const ga_ctx* c, int n_grids, heur_queue* q)
   q->prefetch = c->sw_prefetch >= 0 ? (unsigned)c->sw_prefetch : (lat ? 1u : 0u);
 }
 
-// no cell of the context's h_prox plane can hold a cost: the plane is all zero since ga_patch_reset (nothing was
-// uploaded into it, no potential field built, its device pointer not handed out), or the weight is zero
-static bool prox_free(const ga_ctx* c) { return c->prox_zero || c->ap.astar_prox_cost == 0.0; }
-
 static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& a0, const heur_grid* dG, const heur_args* dA,
                         const heur_queue& q, int max_dim, size_t total_tiles, bool lean)
 {
@@ -1248,7 +1326,7 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
   {
     ga_launch_scope ls(c, GA_K_HEUR_INIT);
     // two cells per thread for one grid (latency bound otherwise), fewer blocks per grid in large batches
-    const int per_grid = n > 4 ? c->sm_count : (max_dim * max_dim + 511) / 512;
+    const int per_grid = n > 4 ? c->sm_count : (max_dim * max_dim / 4 + 255) / 256;  // one step per thread for one grid (latency bound)
     heur_init_kernel<<<dim3(per_grid, n), 256, 0, c->stream>>>(G0, dG, q);
   }
   GA_CUDA(c, cudaGetLastError());
@@ -1264,7 +1342,7 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
   GA_CUDA(c, cudaGetLastError());
   {
     ga_launch_scope ls(c, GA_K_HEUR_FINISH, 3);
-    const int nb = (max_dim + FB - 1) / FB, cells = (max_dim * max_dim + 255) / 256;
+    const int nb = (max_dim + FB - 1) / FB, cells = ((max_dim * max_dim + 3) / 4 + 255) / 256;
     heur_finish_a_kernel<<<dim3(nb * nb, n), FB * FB, 0, c->stream>>>(a0, dA);
     heur_finish_b_kernel<<<dim3(nb * nb, n), FIN_SLOTS, 0, c->stream>>>(a0, dA);
     heur_finish_c_kernel<<<dim3(cells, n), 256, 0, c->stream>>>(a0, dA);
