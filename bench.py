@@ -13,7 +13,8 @@ value : inputs resident in HBM (patch, window, sweep end points), device-timed w
         safety + pool, potential field, heuristic (GPU fixed point: every reachable cell closed).
 e2e   : the same build through the host API with HOST buffers, as the drop-in planner classes issue it: pinned 801^2
         window -> ga_patch_insert (H2D), safety, ga_potential_sites (D2H), Fortune sweep on the host, ga_build_potential
-        (H2D), heuristic, D2H of what the serial search reads (h_prox / motion_res windows + the four closed-set planes).
+        (H2D), heuristic, D2H of what the serial search reads (h_prox / motion_res windows + the closed set as 12-byte
+        records, GA_GRID_HEUR_REC; e2e.planes_*: the same with the four planes, 21 B per cell).
         e2e.lean_* : the same with the packed 1-byte plane instead of the four planes (planner that takes its per-successor
         costs from ga_expand's epilogue).
 N > 1 : one process per GPU (torchrun), every rank builds its own environments (independent queries, no data-path
@@ -183,10 +184,11 @@ def make_env(ga, device, seed, torch):
     outs = {gid: torch.empty((adim, adim), dtype=dt).pin_memory() for gid, dt in
             ((_abi.GRID_HEUR_COST, torch.float64), (_abi.GRID_HEUR_DIST, torch.float64),
              (_abi.GRID_HEUR_PARENT, torch.int32), (_abi.GRID_HEUR_FLAGS, torch.uint8))}
+    rec = torch.empty((adim * adim * 12,), dtype=torch.uint8).pin_memory()
     wins = {gid: torch.empty((VOR_DIM, VOR_DIM), dtype=torch.float64).pin_memory() for gid in (_abi.GRID_H_PROX, _abi.GRID_MOTION_RES)}
     h_sites = np.empty((VOR_DIM * VOR_DIM, 2), np.int32)
     return dict(ctx=ctx, cc=cc, astar=astar, patch=patch, h_win=h_win, win_origin=wo, ego=ego, goal=goal, vor=vor,
-                n_sites=len(sites), outs=outs, wins=wins, h_sites=h_sites,
+                n_sites=len(sites), outs=outs, rec=rec, wins=wins, h_sites=h_sites,
                 vor_origin=(max(ego[0] - VOR_DIM // 2, 0), max(ego[1] - VOR_DIM // 2, 0)))
 
 
@@ -218,7 +220,7 @@ def _e2e_front(env, sweep_s):
     ctx.check(lib.ga_build_heuristic(h, 0, env["goal"][0], env["goal"][1], None))
 
 
-def step_e2e(env, sweep_s, wait=True, lean=False):
+def step_e2e(env, sweep_s, wait=True, lean=False, planes=False):
     from ga_b200 import _abi
     ctx = env["ctx"]
     lib, h = ctx.lib, ctx.h
@@ -229,15 +231,19 @@ def step_e2e(env, sweep_s, wait=True, lean=False):
     if lean:
         t = env["outs"][_abi.GRID_HEUR_FLAGS]
         ctx.check(lib.ga_download_async(h, _abi.GRID_HEUR_PACKED, C.c_void_p(t.data_ptr()), t.numel()))
-    else:
+    elif planes:
         for gid, t in env["outs"].items():
             ctx.check(lib.ga_download_async(h, gid, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+    else:  # what the drop-in's closed sets read in place: the four planes as 12-byte records
+        t = env["rec"]
+        ctx.check(lib.ga_download_async(h, _abi.GRID_HEUR_REC, C.c_void_p(t.data_ptr()), t.numel()))
     if wait:
         ctx.sync()
 
 
 E2E_H2D = WIN_DIM * WIN_DIM          # + the sweep's end points (a few KB, counted per run)
-E2E_D2H_FULL = 2 * VOR_DIM * VOR_DIM * 8 + (PATCH_DIM // 4) ** 2 * 21
+E2E_D2H_FULL = 2 * VOR_DIM * VOR_DIM * 8 + (PATCH_DIM // 4) ** 2 * 12
+E2E_D2H_PLANES = 2 * VOR_DIM * VOR_DIM * 8 + (PATCH_DIM // 4) ** 2 * 21
 E2E_D2H_LEAN = 2 * VOR_DIM * VOR_DIM * 8 + (PATCH_DIM // 4) ** 2
 
 
@@ -788,14 +794,14 @@ def main():
                 e["ctx"].prof_enable(False)
         return dev_ms, wall * 1e3, launches, cells
 
-    def timed_e2e(steps, threaded, lean):
+    def timed_e2e(steps, threaded, lean, planes=False):
         """host-clocked: every step copies its window in and its results out inside the timed region and waits for them.
         threaded: one host thread per planner context (its own stream and pinned buffers), as a planner service with a
         thread pool per GPU runs it: the Fortune sweeps of different contexts run on different host cores and one
         context's copies overlap the other contexts' kernels."""
         sweep_s = [0.0]
         for e in envs_e2e:
-            step_e2e(e, sweep_s, wait=True, lean=lean)
+            step_e2e(e, sweep_s, wait=True, lean=lean, planes=planes)
         barrier()
         nenv = len(envs_e2e) if threaded else N_ROT
         per = [steps // nenv + (1 if i < steps % nenv else 0) for i in range(nenv)]
@@ -803,7 +809,7 @@ def main():
 
         def worker(i):
             for _ in range(per[i]):
-                step_e2e(envs_e2e[i], sweeps[i], wait=True, lean=lean)
+                step_e2e(envs_e2e[i], sweeps[i], wait=True, lean=lean, planes=planes)
 
         sampler.active = True
         t0 = time.perf_counter()
@@ -815,7 +821,7 @@ def main():
                 th.join()
         else:
             for i in range(steps):
-                step_e2e(envs_e2e[i % N_ROT], sweeps[i % N_ROT], wait=True, lean=lean)
+                step_e2e(envs_e2e[i % N_ROT], sweeps[i % N_ROT], wait=True, lean=lean, planes=planes)
         barrier()
         wall = time.perf_counter() - t0
         sampler.active = False
@@ -843,6 +849,7 @@ def main():
     e2e_serial_ms, e2e_serial_cells, sweep_ms = timed_e2e(e2e_steps, False, False)
     e2e_wall_ms, e2e_cells, _ = timed_e2e(e2e_steps, True, False)
     lean_wall_ms, lean_cells, _ = timed_e2e(e2e_steps, True, True)
+    planes_wall_ms, planes_cells, _ = timed_e2e(e2e_steps, True, False, planes=True)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
     # the same with 1024 queries in one chain (rank 0 only: it is a statement about the kernel, not about scaling)
     batch_large = (run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak, nq=args.batch_large)
@@ -869,7 +876,8 @@ def main():
     plan_q = float(plan["b200"]["queries"]) if plan_qps else 0.0
     batch_ms = batch["ms_per_batch"] if batch else 0.0
     t = torch.tensor([dev_ms, e2e_wall_ms, float(cells), float(e2e_cells), float(launches), e2e_serial_ms, lean_wall_ms,
-                      float(lean_cells), plan_t, plan_q, batch_ms, float(args.batch if batch else 0)], dtype=torch.float64, device="cuda")
+                      float(lean_cells), plan_t, plan_q, batch_ms, float(args.batch if batch else 0), planes_wall_ms, float(planes_cells)],
+                     dtype=torch.float64, device="cuda")
     if world > 1:
         tmax = t.clone()
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -878,6 +886,7 @@ def main():
         dev_ms, e2e_wall_ms, e2e_serial_ms, lean_wall_ms, plan_t, batch_ms = (float(tmax[i]) for i in (0, 1, 5, 6, 8, 10))
         cells, e2e_cells, launches, lean_cells, plan_q = float(tsum[2]), float(tsum[3]), int(tsum[4]), float(tsum[7]), float(tsum[9])
         batch_n = float(tsum[11])
+        planes_wall_ms, planes_cells = float(tmax[12]), float(tsum[13])
     else:
         batch_n = float(args.batch if batch else 0)
     value = cells / (dev_ms * 1e-3) / 1e6
@@ -903,11 +912,16 @@ def main():
                         "d2h_bytes_per_step": E2E_D2H_FULL + 8 * int(np.mean([e["n_sites"] for e in envs])),
                         "ms_per_step": e2e_wall_ms / e2e_steps, "steps": e2e_steps,
                         "what": "801^2 window in (ga_patch_insert), safety, sites out, Fortune sweep on the host, potential field, "
-                                "heuristic, h_prox / motion_res windows + four closed-set planes out",
+                                "heuristic, h_prox / motion_res windows + the closed set out as 12-byte records (GA_GRID_HEUR_REC: "
+                                "cost, parent direction, unknown flag and step counts of every cell -- what the drop-in's closed "
+                                "sets read in place; lossless against the four planes)",
                         "pipeline": "%d planner contexts, one host thread each (own stream and pinned buffers)" % n_thr,
                         "host_sweep_ms_per_step": sweep_ms / e2e_steps,
                         "serial_value": e2e_serial_cells / (e2e_serial_ms * 1e-3) / 1e6,
                         "serial_ms_per_step": e2e_serial_ms / e2e_steps,
+                        "planes_value": planes_cells / (planes_wall_ms * 1e-3) / 1e6, "planes_ms_per_step": planes_wall_ms / e2e_steps,
+                        "planes_d2h_bytes_per_step": E2E_D2H_PLANES,
+                        "planes_what": "the same with the four planes (cost, cost_dist, parent, flags: 21 B per cell) instead of the records",
                         "lean_value": lean_cells / (lean_wall_ms * 1e-3) / 1e6, "lean_ms_per_step": lean_wall_ms / e2e_steps,
                         "lean_d2h_bytes_per_step": E2E_D2H_LEAN,
                         "lean_what": "the packed 1-byte plane (GA_GRID_HEUR_PACKED) instead of the four planes: a planner that "

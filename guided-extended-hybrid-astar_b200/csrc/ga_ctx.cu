@@ -77,7 +77,8 @@ static void free_grids(ga_ctx* c)
                     (void**)&c->d_astar,   (void**)&c->d_fence,  (void**)&c->d_mc,        (void**)&c->d_prox,
                     (void**)&c->d_mres,    (void**)&c->d_odist,  (void**)&c->d_vdist,     (void**)&c->d_hcost[0],
                     (void**)&c->d_hcost[1], (void**)&c->d_hdist[0], (void**)&c->d_hdist[1], (void**)&c->d_hparent[0],
-                    (void**)&c->d_hparent[1], (void**)&c->d_hflags[0], (void**)&c->d_hflags[1], (void**)&c->d_hpacked };
+                    (void**)&c->d_hparent[1], (void**)&c->d_hflags[0], (void**)&c->d_hflags[1], (void**)&c->d_hpacked,
+                    (void**)&c->d_hsteps[0], (void**)&c->d_hsteps[1], (void**)&c->d_hrec, (void**)&c->d_rec_ovf };
   for (void** p : ptrs)
   {
     if (*p) cudaFree(*p);
@@ -100,6 +101,7 @@ extern "C" int ga_destroy(ga_ctx* c)
   if (c->d_stage) cudaFree(c->d_stage);
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_ll) cudaFreeHost(c->h_ll);
+  if (c->h_rec_ovf) cudaFreeHost(c->h_rec_ovf);
   for (auto& r : c->prof)
   {
     cudaEventDestroy(r.e0);
@@ -113,12 +115,14 @@ extern "C" int ga_destroy(ga_ctx* c)
 
 extern "C" const char* ga_last_error(const ga_ctx* c) { return c ? c->err : "null context"; }
 
+static int rec_check(ga_ctx* c);
+
 extern "C" int ga_sync(ga_ctx* c)
 {
   if (!c) return GA_ERR_ARG;
   GA_CUDA(c, cudaSetDevice(c->device));
   GA_CUDA(c, cudaStreamSynchronize(c->stream));
-  return GA_OK;
+  return rec_check(c);
 }
 
 extern "C" void* ga_stream(ga_ctx* c) { return c ? (void*)c->stream : nullptr; }
@@ -288,12 +292,19 @@ static int alloc_grids(ga_ctx* c, int patch_dim, int astar_dim)
     GA_CUDA(c, cudaMalloc(&c->d_vdist, nv * 4));
     c->vor_alloc = c->ap.vor_dim;
     GA_CUDA(c, cudaMalloc(&c->d_hpacked, na));
+    GA_CUDA(c, cudaMalloc(&c->d_hrec, na * 12));
+    GA_CUDA(c, cudaMalloc(&c->d_rec_ovf, sizeof(int)));
+    GA_CUDA(c, cudaMemsetAsync(c->d_rec_ovf, 0, sizeof(int), c->stream));
+    if (!c->h_rec_ovf) GA_CUDA(c, cudaMallocHost(&c->h_rec_ovf, sizeof(int)));
+    *c->h_rec_ovf = 0;
+    c->rec_valid[0] = c->rec_valid[1] = false;
     for (int s = 0; s < 2; ++s)
     {
       GA_CUDA(c, cudaMalloc(&c->d_hcost[s], na * 8));
       GA_CUDA(c, cudaMalloc(&c->d_hdist[s], na * 8));
       GA_CUDA(c, cudaMalloc(&c->d_hparent[s], na * 4));
       GA_CUDA(c, cudaMalloc(&c->d_hflags[s], na));
+      GA_CUDA(c, cudaMalloc(&c->d_hsteps[s], na * 4));
     }
   }
   return ga_heur_alloc(c);
@@ -349,6 +360,66 @@ extern "C" int ga_patch_dim(const ga_ctx* c) { return c ? c->patch_dim : GA_ERR_
 extern "C" int ga_astar_dim(const ga_ctx* c) { return c ? c->astar_dim : GA_ERR_ARG; }
 extern "C" int ga_cart_dim(const ga_ctx* c) { return c ? c->cart_dim : GA_ERR_ARG; }
 
+// GA_GRID_HEUR_REC: everything the four result planes hold in 12 bytes per cell (three 32-bit words): the cost's 64
+// bits, then dir:3 (index i of motion_, parent = cell - motion_[i]) | unknown:1 | straight:14 | diagonal:14 steps to the
+// root.  closed <=> cost finite; the root is the closed cell with zero steps; cost_dist = straight * L1 + diagonal * L2
+// (the arithmetic of finish C, two products and one sum).  A chain with 16383 or more steps of a kind does not fit:
+// the kernel raises *ovf.
+__global__ void heur_rec_kernel(const double* __restrict__ cost, const int32_t* __restrict__ parent, const uint8_t* __restrict__ flags,
+                                const uint32_t* __restrict__ steps, uint32_t* __restrict__ out, int dim, int* __restrict__ ovf)
+{
+  const int n = dim * dim;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x)
+  {
+    const uint8_t f = flags[c];
+    double g = INFINITY;
+    uint32_t w = 0;
+    if (f & GA_H_CLOSED)
+    {
+      g = cost[c];
+      const uint32_t st = steps[c];
+      const int p = parent[c];
+      unsigned dir = 0;
+      if (p >= 0)
+      {
+        const int dx = c % dim - p % dim, dy = c / dim - p / dim;  // motion_[i] = (dx, dy)
+        const unsigned lut[9] = { 4, 3, 6, 2, 0, 0, 5, 1, 7 };
+        dir = lut[(dy + 1) * 3 + (dx + 1)];
+      }
+      if ((st & 16383u) == 16383u || (st >> 14) == 16383u) *ovf = 1;
+      w = dir | ((f & GA_H_UNKNOWN) ? 8u : 0u) | (st << 4);
+    }
+    const unsigned long long gb = (unsigned long long)__double_as_longlong(g);
+    out[3 * (size_t)c] = (uint32_t)gb;
+    out[3 * (size_t)c + 1] = (uint32_t)(gb >> 32);
+    out[3 * (size_t)c + 2] = w;
+  }
+}
+
+static int launch_rec(ga_ctx* c, int slot)
+{
+  GA_REQUIRE(c, c->rec_valid[slot], GA_ERR_STATE,
+             "GA_GRID_HEUR_REC needs a device (fixed-point) build of this slot: after a GA_HEUR_REFORDER build or an upload use the four planes");
+  ga_launch_scope ls(c, GA_K_HEUR_FINISH);
+  heur_rec_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(c->d_hcost[slot], c->d_hparent[slot], c->d_hflags[slot], c->d_hsteps[slot],
+                                                          reinterpret_cast<uint32_t*>(c->d_hrec), c->astar_dim, c->d_rec_ovf);
+  GA_CUDA(c, cudaMemcpyAsync(c->h_rec_ovf, c->d_rec_ovf, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  c->rec_check = true;
+  return GA_OK;
+}
+
+// after the stream has been synchronised: did a record kernel meet a chain it cannot hold?
+static int rec_check(ga_ctx* c)
+{
+  if (!c->rec_check) return GA_OK;
+  c->rec_check = false;
+  if (*c->h_rec_ovf == 0) return GA_OK;
+  *c->h_rec_ovf = 0;
+  cudaMemsetAsync(c->d_rec_ovf, 0, sizeof(int), c->stream);
+  GA_REQUIRE(c, false, GA_ERR_STATE, "GA_GRID_HEUR_REC: a parent chain has 16383 or more steps of one kind; download the four planes instead");
+  return GA_OK;
+}
+
 // GA_GRID_HEUR_PACKED: one byte per cell for consumers that only need membership and the parent chain
 // (getAstarPath, findValidNeighborIndex, OUT_OF_HEURISTIC tests): bits 0-3 = index i of motion_ (a_star.hpp:50-52)
 // with parent = cell - motion_[i], 8 = root, 15 = none; bit 4 = in the closed set; bit 5 = is_unknown_
@@ -401,6 +472,7 @@ static int grid_lookup(const ga_ctx* c, int id, void** p, size_t* bytes)
     case GA_GRID_HEUR_PARENT: case GA_GRID_HEUR_PARENT + 1: *p = c->d_hparent[id - GA_GRID_HEUR_PARENT]; *bytes = na * 4; return 0;
     case GA_GRID_HEUR_FLAGS: case GA_GRID_HEUR_FLAGS + 1: *p = c->d_hflags[id - GA_GRID_HEUR_FLAGS]; *bytes = na; return 0;
     case GA_GRID_HEUR_PACKED: case GA_GRID_HEUR_PACKED + 1: *p = c->d_hpacked; *bytes = na; return 0;
+    case GA_GRID_HEUR_REC: case GA_GRID_HEUR_REC + 1: *p = c->d_hrec; *bytes = na * 12; return 0;
     default: return -1;
   }
 }
@@ -448,6 +520,7 @@ extern "C" int ga_upload(ga_ctx* c, int grid_id, const void* src, size_t bytes)
   }
   GA_CUDA(c, cudaSetDevice(c->device));
   if (grid_id == GA_GRID_H_PROX) c->prox_zero = false;
+  if (grid_id >= GA_GRID_HEUR_COST && grid_id < GA_GRID_HEUR_PACKED) c->rec_valid[(grid_id - GA_GRID_HEUR_COST) & 1] = false;
   GA_CUDA(c, cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, c->stream));
   // pageable sources are staged by the driver before the call returns; pinned ones are the
   // caller's to keep alive until ga_sync
@@ -470,9 +543,14 @@ extern "C" int ga_download(ga_ctx* c, int grid_id, void* dst, size_t bytes)
     ga_launch_scope ls(c, GA_K_HEUR_FINISH);
     heur_pack_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(c->d_hparent[slot], c->d_hflags[slot], c->d_hpacked, c->astar_dim);
   }
+  if (grid_id == GA_GRID_HEUR_REC || grid_id == GA_GRID_HEUR_REC + 1)
+  {
+    const int rc = launch_rec(c, grid_id - GA_GRID_HEUR_REC);
+    if (rc) return rc;
+  }
   GA_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
   GA_CUDA(c, cudaStreamSynchronize(c->stream));
-  return GA_OK;
+  return rec_check(c);
 }
 
 // a w x h window of an astar-sized grid (row pitch = astar_dim) into a dense host array
@@ -515,6 +593,11 @@ extern "C" int ga_download_async(ga_ctx* c, int grid_id, void* dst, size_t bytes
     const int slot = grid_id - GA_GRID_HEUR_PACKED;
     ga_launch_scope ls(c, GA_K_HEUR_FINISH);
     heur_pack_kernel<<<c->sm_count * 4, 256, 0, c->stream>>>(c->d_hparent[slot], c->d_hflags[slot], c->d_hpacked, c->astar_dim);
+  }
+  if (grid_id == GA_GRID_HEUR_REC || grid_id == GA_GRID_HEUR_REC + 1)
+  {
+    const int rc = launch_rec(c, grid_id - GA_GRID_HEUR_REC);  // an over-long chain is reported by the next ga_sync
+    if (rc) return rc;
   }
   GA_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
   return GA_OK;

@@ -274,6 +274,7 @@ int ga_heur_reforder_build(ga_ctx* c, int slot, const ga_heur_query* q, int* n_c
   GA_CUDA(c, cudaMemcpyAsync(c->d_hdist[slot], h.dist, cells * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   GA_CUDA(c, cudaMemcpyAsync(c->d_hparent[slot], h.parent, cells * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
   GA_CUDA(c, cudaMemcpyAsync(c->d_hflags[slot], h.flags, cells, cudaMemcpyHostToDevice, c->stream));
+  c->rec_valid[slot] = false;  // the planes are the replay's: no steps plane belongs to them
   c->near_slot = slot;
   c->heur_host_valid[slot] = true;
   if (n_closed) *n_closed = n;

@@ -88,6 +88,7 @@ struct heur_args  // finish kernel
   int* tcount;        // [blocks] how many
   unsigned* scratch;  // [ncell] finish A: displacement of the block's terminal cell and (straight, diagonal) steps to it
   int2* tot;          // [ncell] finish B: (straight, diagonal) steps of a terminal cell to the root
+  uint32_t* steps;    // [ncell] finish C: straight | diagonal << 14 steps of a closed cell to the root (saturating; GA_GRID_HEUR_REC)
   int dim, goal;
   double w_prox, unk_w, L1, L2;
 };
@@ -1176,8 +1177,9 @@ __global__ void __launch_bounds__(FIN_SLOTS) heur_finish_b_kernel(heur_args sing
   __stcg(reinterpret_cast<long long*>(a.tot) + c, ((long long)cd << 32) | (unsigned)cs);  // one 8-byte store: never seen half written
 }
 
-__device__ __forceinline__ double fin_dist(const heur_args& a, int c, unsigned flag, unsigned s, int dim)
+__device__ __forceinline__ double fin_dist(const heur_args& a, int c, unsigned flag, unsigned s, int dim, uint32_t* steps)
 {
+  *steps = 0;
   if (!(flag & GA_H_CLOSED)) return INFINITY;
   int cs = (s >> 12) & 1023, cd = (s >> 22) & 1023;
   const int t = fin_target(s, c, dim);
@@ -1187,6 +1189,7 @@ __device__ __forceinline__ double fin_dist(const heur_args& a, int c, unsigned f
     cs += tt.x;
     cd += tt.y;
   }
+  *steps = (uint32_t)min(cs, 16383) | ((uint32_t)min(cd, 16383) << 14);
   return (double)cs * a.L1 + (double)cd * a.L2;  // NodeDisc::cost_dist_
 }
 
@@ -1201,13 +1204,15 @@ __global__ void __launch_bounds__(256) heur_finish_c_kernel(heur_args single, co
   {
     const uchar4 f = *reinterpret_cast<const uchar4*>(a.flags + c);
     const uint4 s = *reinterpret_cast<const uint4*>(a.scratch + c);
-    const double d0 = fin_dist(a, c, f.x, s.x, dim), d1 = fin_dist(a, c + 1, f.y, s.y, dim);
-    const double d2 = fin_dist(a, c + 2, f.z, s.z, dim), d3 = fin_dist(a, c + 3, f.w, s.w, dim);
+    uint4 st;
+    const double d0 = fin_dist(a, c, f.x, s.x, dim, &st.x), d1 = fin_dist(a, c + 1, f.y, s.y, dim, &st.y);
+    const double d2 = fin_dist(a, c + 2, f.z, s.z, dim, &st.z), d3 = fin_dist(a, c + 3, f.w, s.w, dim, &st.w);
     *reinterpret_cast<double2*>(a.dist + c) = make_double2(d0, d1);
     *reinterpret_cast<double2*>(a.dist + c + 2) = make_double2(d2, d3);
+    *reinterpret_cast<uint4*>(a.steps + c) = st;
   }
   else
-    for (int k = c; k < ncell; ++k) a.dist[k] = fin_dist(a, k, a.flags[k], a.scratch[k], dim);
+    for (int k = c; k < ncell; ++k) a.dist[k] = fin_dist(a, k, a.flags[k], a.scratch[k], dim, a.steps + k);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1295,6 +1300,8 @@ static void make_descs(ga_ctx* c, int slot, int goal_x, int goal_y, int* closed,
   a->tlist = c->d_jump + (size_t)c->astar_dim * c->astar_dim;
   a->tcount = a->tlist + (size_t)((c->astar_dim + FB - 1) / FB) * ((c->astar_dim + FB - 1) / FB) * FIN_SLOTS;
   a->tot = reinterpret_cast<int2*>(c->d_cnt);
+  a->steps = c->d_hsteps[slot];
+  c->rec_valid[slot] = true;  // a device build follows (a reference-order replay clears it again)
   a->dim = c->astar_dim;
   a->goal = G->goal;
   a->w_prox = G->w_prox;

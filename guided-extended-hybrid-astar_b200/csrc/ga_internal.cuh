@@ -80,6 +80,12 @@ struct ga_ctx
   int32_t* d_hparent[2] = { nullptr, nullptr };
   uint8_t* d_hflags[2] = { nullptr, nullptr };
   uint8_t* d_hpacked = nullptr;  // GA_GRID_HEUR_PACKED scratch (filled on demand by ga_download)
+  uint32_t* d_hsteps[2] = { nullptr, nullptr };  // (straight | diagonal << 14) steps of every closed cell to the root, written by finish C
+  uint8_t* d_hrec = nullptr;     // GA_GRID_HEUR_REC scratch: 12 B per cell (filled on demand by ga_download)
+  bool rec_valid[2] = { false, false };  // the slot's planes come from the device fixed point (steps plane is theirs)
+  int* d_rec_ovf = nullptr;      // set by the record kernel when a chain is longer than the record holds
+  int* h_rec_ovf = nullptr;      // pinned copy, looked at by ga_download / ga_sync
+  bool rec_check = false;
 
   // ---- accumulated map (Cartographing::patch_arr_ / temp_patch_)
   uint8_t* d_cart = nullptr;

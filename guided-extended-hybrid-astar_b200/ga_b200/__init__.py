@@ -5,5 +5,5 @@ reference's pybind module `_hybridastar_planning_lib_api`
 (LIB/src/hybridastar_planning_lib/wrapper_hybrid_a_star_lib.cpp:176-199, 327-346)."""
 from ._abi import GaError, LIB_PATH, load  # noqa: F401
 from .planner import (AStar, Cartographing, CollisionChecker, GridContext, GridMapSim, HybridAStar, Vehicle, VehConfig, LibConfig,  # noqa: F401
-                      calc_disks, GM_RES, ASTAR_RES)
+                      calc_disks, unpack_heur_records, GM_RES, ASTAR_RES)
 from .synth import gen_map, sample_free_cells  # noqa: F401

@@ -58,7 +58,10 @@ assert NODE_DTYPE.itemsize == 40 and SUCC_DTYPE.itemsize == 48 and SUCC_COST_DTY
 # ga_grid_id
 GRID_PATCH, GRID_SAFETY, GRID_ASTAR, GRID_GEOFENCE, GRID_MOVEMENT_COST, GRID_H_PROX, \
     GRID_MOTION_RES, GRID_OBSTACLE_DIST, GRID_VORONOI_DIST, GRID_CART, GRID_PMAP = range(11)
-GRID_HEUR_COST, GRID_HEUR_DIST, GRID_HEUR_PARENT, GRID_HEUR_FLAGS, GRID_HEUR_PACKED = 16, 18, 20, 22, 24
+GRID_HEUR_COST, GRID_HEUR_DIST, GRID_HEUR_PARENT, GRID_HEUR_FLAGS, GRID_HEUR_PACKED, GRID_HEUR_REC = 16, 18, 20, 22, 24, 26
+# GA_GRID_HEUR_REC: 12 bytes per cell -- cost_ (two 32-bit words, low first), then dir:3 | unknown:1 | straight:14 | diagonal:14
+HEUR_REC_DTYPE = np.dtype([("cost_lo", np.uint32), ("cost_hi", np.uint32), ("w", np.uint32)])
+assert HEUR_REC_DTYPE.itemsize == 12
 GRID_DTYPES = {GRID_PATCH: np.uint8, GRID_SAFETY: np.uint8, GRID_ASTAR: np.uint8,
                GRID_GEOFENCE: np.uint8, GRID_MOVEMENT_COST: np.float64, GRID_H_PROX: np.float64,
                GRID_MOTION_RES: np.float64, GRID_OBSTACLE_DIST: np.float32,
@@ -69,6 +72,7 @@ for _s in (0, 1):
     GRID_DTYPES[GRID_HEUR_PARENT + _s] = np.int32
     GRID_DTYPES[GRID_HEUR_FLAGS + _s] = np.uint8
     GRID_DTYPES[GRID_HEUR_PACKED + _s] = np.uint8
+    GRID_DTYPES[GRID_HEUR_REC + _s] = HEUR_REC_DTYPE
 
 K_PACK, K_DILATE, K_HEUR_INIT, K_HEUR_RELAX, K_HEUR_FINISH, K_COLLISION, K_EXPAND, K_DT, \
     K_POTENTIAL, K_CARTOGRAPH, K_RAYTRACE, K_PROX, K_COUNT = range(13)

@@ -531,6 +531,28 @@ class HybridAStar:
         return out
 
 
+def unpack_heur_records(rec):
+    """GA_GRID_HEUR_REC (12 B per cell) -> the four result planes (cost, cost_dist, parent, flags), bit for bit what
+    GA_GRID_HEUR_COST / _DIST / _PARENT / _FLAGS hold after a device build."""
+    rec = np.ascontiguousarray(rec)
+    dim = rec.shape[0]
+    cost = (rec["cost_lo"].astype(np.uint64) | (rec["cost_hi"].astype(np.uint64) << np.uint64(32))).view(np.float64)
+    w = rec["w"]
+    closed = np.isfinite(cost)
+    straight, diag = ((w >> 4) & 16383).astype(np.float64), ((w >> 18) & 16383).astype(np.float64)
+    dist = np.where(closed, straight * 0.625 + diag * (0.625 * math.sqrt(2.0)), np.inf)   # finish C: two products, one sum
+    # motion_ (a_star.hpp:50-52): parent = cell - motion_[dir]
+    mdx = np.array([1, 0, -1, 0, -1, -1, 1, 1]); mdy = np.array([0, 1, 0, -1, -1, 1, -1, 1])
+    d = (w & 7).astype(np.int64)
+    ys, xs = np.mgrid[0:dim, 0:dim]
+    parent = ((ys - mdy[d]) * dim + (xs - mdx[d])).astype(np.int32)
+    root = closed & (((w >> 4) & 0x0FFFFFFF) == 0)
+    parent[root] = -1
+    parent[~closed] = -2
+    flags = (closed.astype(np.uint8) * _abi.H_CLOSED) | (((w >> 3) & 1).astype(np.uint8) * _abi.H_UNKNOWN * closed)
+    return cost, dist, parent, flags.astype(np.uint8)
+
+
 class NodeDisc:
     """data_structures2.hpp:47-67"""
     __slots__ = ("pos", "cost_", "cost_dist_", "parent_index_", "is_unknown_")

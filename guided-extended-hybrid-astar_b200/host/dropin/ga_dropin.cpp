@@ -940,14 +940,38 @@ void AStar::calcDistanceHeuristic(const Point<int>& goal_pos, const Point<int>& 
   const size_t cells = (size_t)astar_dim_ * astar_dim_;
   ClosedPlanes& p = cs.planes;
   p.dim = astar_dim_;
-  p.cost.resize(cells);
-  p.dist.resize(cells);
-  p.parent.resize(cells);
-  p.flags.resize(cells);
-  check(ga_download(c, GA_GRID_HEUR_COST + slot, p.cost.data(), cells * 8));
-  check(ga_download(c, GA_GRID_HEUR_DIST + slot, p.dist.data(), cells * 8));
-  check(ga_download(c, GA_GRID_HEUR_PARENT + slot, p.parent.data(), cells * 4));
-  check(ga_download(c, GA_GRID_HEUR_FLAGS + slot, p.flags.data(), cells));
+  p.cells = cells;
+  if (q.flags & GA_HEUR_REFORDER)
+  {
+    p.packed = false;
+    p.cost.resize(cells);
+    p.dist.resize(cells);
+    p.parent.resize(cells);
+    p.flags.resize(cells);
+    check(ga_download(c, GA_GRID_HEUR_COST + slot, p.cost.data(), cells * 8));
+    check(ga_download(c, GA_GRID_HEUR_DIST + slot, p.dist.data(), cells * 8));
+    check(ga_download(c, GA_GRID_HEUR_PARENT + slot, p.parent.data(), cells * 4));
+    check(ga_download(c, GA_GRID_HEUR_FLAGS + slot, p.flags.data(), cells));
+  }
+  else
+  {
+    // device build: the planes come as 12-byte records and are read in place by the closed set's accessors
+    p.rec.resize(3 * cells);
+    if (ga_download(c, GA_GRID_HEUR_REC + slot, p.rec.data(), cells * 12) == GA_OK)
+      p.packed = true;
+    else  // a parent chain too long for the record format: the four planes
+    {
+      p.packed = false;
+      p.cost.resize(cells);
+      p.dist.resize(cells);
+      p.parent.resize(cells);
+      p.flags.resize(cells);
+      check(ga_download(c, GA_GRID_HEUR_COST + slot, p.cost.data(), cells * 8));
+      check(ga_download(c, GA_GRID_HEUR_DIST + slot, p.dist.data(), cells * 8));
+      check(ga_download(c, GA_GRID_HEUR_PARENT + slot, p.parent.data(), cells * 4));
+      check(ga_download(c, GA_GRID_HEUR_FLAGS + slot, p.flags.data(), cells));
+    }
+  }
   p.n_closed = (size_t)n;
 
   nodes_near_goal_.clear();
@@ -980,7 +1004,7 @@ std::pair<std::vector<int>, std::vector<int>> AStar::getAstarPath(int x_index, i
     idx = static_cast<size_t>(index);
   }
   const ClosedPlanes& p = closed_set_guidance_.planes;
-  for (int cur = (int)idx; cur != -1; cur = p.parent[(size_t)cur])
+  for (int cur = (int)idx; cur != -1; cur = p.parent_of((size_t)cur))
   {
     x_list.push_back(cur % astar_dim_);
     y_list.push_back(cur / astar_dim_);

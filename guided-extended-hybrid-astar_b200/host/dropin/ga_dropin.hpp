@@ -24,6 +24,7 @@
 #include <array>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <exception>
 #include <iostream>
 #include <map>
@@ -65,11 +66,47 @@ namespace ga_dropin
 {
 struct ClosedPlanes
 {
+  // either the four planes (after a reference-order replay: GA_GRID_HEUR_COST / _DIST / _PARENT / _FLAGS) ...
   std::vector<double> cost, dist;
   std::vector<int32_t> parent;
   std::vector<uint8_t> flags;
+  // ... or the 12-byte records of a device build (GA_GRID_HEUR_REC: 12 B per cell over PCIe instead of 21), read in place
+  std::vector<uint32_t> rec;
+  bool packed = false;
   int dim = 0;
-  size_t n_closed = 0;
+  size_t cells = 0, n_closed = 0;
+
+  bool closed(size_t i) const
+  {
+    return packed ? (rec[3 * i + 1] & 0x7FF00000u) != 0x7FF00000u  // cost_ finite
+                  : (flags[i] & GA_H_CLOSED) != 0;
+  }
+  bool unknown(size_t i) const { return packed ? ((rec[3 * i + 2] >> 3) & 1u) != 0 : (flags[i] & GA_H_UNKNOWN) != 0; }
+  double cost_of(size_t i) const
+  {
+    if (!packed) return cost[i];
+    double g;
+    std::memcpy(&g, &rec[3 * i], sizeof g);
+    return g;
+  }
+  // cost_dist_ = straight * ASTAR_RES + diagonal * (ASTAR_RES * sqrt 2): two products and one sum, as the device forms it
+  __attribute__((optimize("fp-contract=off"))) double dist_of(size_t i) const
+  {
+    if (!packed) return dist[i];
+    const uint32_t w = rec[3 * i + 2];
+    const double a = (double)((w >> 4) & 16383u) * 0.625, b = (double)((w >> 18) & 16383u) * (0.625 * std::sqrt(2.0));
+    return a + b;
+  }
+  int32_t parent_of(size_t i) const
+  {
+    if (!packed) return parent[i];
+    const uint32_t w = rec[3 * i + 2];
+    if ((w >> 4) == 0) return -1;  // the root: the closed cell with no step
+    // motion_ (a_star.hpp:50-52): parent = cell - motion_[dir]
+    static constexpr int mdx[8] = { 1, 0, -1, 0, -1, -1, 1, 1 }, mdy[8] = { 0, 1, 0, -1, -1, 1, -1, 1 };
+    const int d = (int)(w & 7u);
+    return (int32_t)(((int)(i / (size_t)dim) - mdy[d]) * dim + ((int)(i % (size_t)dim) - mdx[d]));
+  }
 };
 }  // namespace ga_dropin
 
@@ -115,16 +152,16 @@ public:
     bool operator!=(const const_iterator& o) const { return i_ != o.i_; }
     void skip()
     {
-      const size_t n = p_->flags.size();
-      while (i_ < n && !(p_->flags[i_] & GA_H_CLOSED)) ++i_;
+      const size_t n = p_->cells;
+      while (i_ < n && !p_->closed(i_)) ++i_;
     }
 
   private:
     void load() const
     {
       const int d = p_->dim;
-      new (buf_) value_type(i_, NodeDisc(Point<int>((int)(i_ % (size_t)d), (int)(i_ / (size_t)d)), p_->cost[i_], p_->dist[i_],
-                                         p_->parent[i_], (p_->flags[i_] & GA_H_UNKNOWN) != 0));
+      new (buf_) value_type(i_, NodeDisc(Point<int>((int)(i_ % (size_t)d), (int)(i_ / (size_t)d)), p_->cost_of(i_), p_->dist_of(i_),
+                                         p_->parent_of(i_), p_->unknown(i_)));
     }
     const ga_dropin::ClosedPlanes* p_ = nullptr;
     size_t i_ = 0;
@@ -132,7 +169,7 @@ public:
   };
   using iterator = const_iterator;
 
-  bool contains(size_t id) const { return id < planes.flags.size() && (planes.flags[id] & GA_H_CLOSED); }
+  bool contains(size_t id) const { return id < planes.cells && planes.closed(id); }
   size_t count(size_t id) const { return contains(id) ? 1 : 0; }
   const_iterator find(size_t id) const { return contains(id) ? const_iterator(&planes, id) : end(); }
   const_iterator begin() const
@@ -141,7 +178,7 @@ public:
     it.skip();
     return it;
   }
-  const_iterator end() const { return const_iterator(&planes, planes.flags.size()); }
+  const_iterator end() const { return const_iterator(&planes, planes.cells); }
   const_iterator cbegin() const { return begin(); }
   const_iterator cend() const { return end(); }
   NodeDisc at(size_t id) const
@@ -154,7 +191,8 @@ public:
   void clear()
   {
     planes.n_closed = 0;
-    std::fill(planes.flags.begin(), planes.flags.end(), (uint8_t)0);
+    planes.packed = false;
+    planes.flags.assign(planes.cells, (uint8_t)0);
   }
 
   ga_dropin::ClosedPlanes planes;  // filled by AStar::calcDistanceHeuristic

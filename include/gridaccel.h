@@ -79,7 +79,14 @@ typedef enum
    * the device (getAstarPath a_star.cpp:386-421, findValidNeighborIndex :351-378, calcCost's OUT_OF_HEURISTIC test
    * hybrid_a_star_lib.cpp:242-247): bits 0-3 = i with parent = cell - motion_[i] (a_star.hpp:50-52), 8 = root,
    * 15 = none; bit 4 = closed; bit 5 = is_unknown_.  1 B/cell over PCIe instead of 21. */
-  GA_GRID_HEUR_PACKED = 24
+  GA_GRID_HEUR_PACKED = 24,
+  /* (+slot) download only, after a device (GA_HEUR_FIXEDPOINT) build of the slot: the four result planes in 12 bytes
+   * per cell instead of 21 -- three 32-bit words: the 64 bits of cost_ (low word first; +inf = not in the set), then
+   * dir:3 | is_unknown_:1 | straight:14 | diagonal:14 with parent = cell - motion_[dir] (a_star.hpp:50-52) and
+   * cost_dist_ = straight * 0.625 + diagonal * (0.625 * sqrt 2) (two products, one sum: what the device computes).
+   * The root is the closed cell with zero steps.  A chain of 16383 or more steps of one kind does not fit:
+   * ga_download (or the ga_sync after ga_download_async) then fails with GA_ERR_STATE; use the four planes. */
+  GA_GRID_HEUR_REC = 26
 } ga_grid_id;
 
 enum { GA_H_CLOSED = 1, GA_H_UNKNOWN = 2 };

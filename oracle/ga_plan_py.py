@@ -386,6 +386,12 @@ def main():
         if a.heuristic:
             for w, nm in ((0, "hg_"), (1, "hp_")):
                 _flatten(nm, pl.heuristic(w), out)
+                if a.arm == "b200":  # the device's own planes beside what the closed set's accessors return
+                    d = pl.L.gap_astar_dim()
+                    dev = dict(cost=np.zeros((d, d)), dist=np.zeros((d, d)), parent=np.zeros((d, d), np.int32), flags=np.zeros((d, d), np.uint8))
+                    pl.L.gap_b200_heur_planes.argtypes = [C.c_int] + [C.c_void_p] * 4
+                    pl._ck(pl.L.gap_b200_heur_planes(w, _p(dev["cost"]), _p(dev["dist"]), _p(dev["parent"]), _p(dev["flags"])))
+                    _flatten("dev_" + nm, dev, out)
             out["h_prox"] = pl.get_map(1)
             out["motion_res"] = pl.get_map(2)
             out["astar_grid"] = pl.get_map(0)

@@ -413,6 +413,18 @@ int gap_b200_device_map(int which, double* dst)
     ga_dropin::check(ga_download(ga_dropin::ctx(), id, dst, n * sizeof(double)));
   })
 }
+// the DEVICE's four result planes of a heuristic slot (0 guidance, 1 path): what the closed set's accessors must reproduce
+int gap_b200_heur_planes(int which, double* cost, double* dist, int32_t* parent, uint8_t* flags)
+{
+  GAP_TRY({
+    const size_t n = (size_t)AStar::astar_dim_ * AStar::astar_dim_;
+    ga_ctx* c = ga_dropin::ctx();
+    ga_dropin::check(ga_download(c, GA_GRID_HEUR_COST + which, cost, n * 8));
+    ga_dropin::check(ga_download(c, GA_GRID_HEUR_DIST + which, dist, n * 8));
+    ga_dropin::check(ga_download(c, GA_GRID_HEUR_PARENT + which, parent, n * 4));
+    ga_dropin::check(ga_download(c, GA_GRID_HEUR_FLAGS + which, flags, n));
+  })
+}
 #else
 int gap_set_dt_variant(int v)
 {

@@ -53,6 +53,13 @@ def test_config1_fixed_point_heuristic_reports_difference(tmp_path):
     a = gp.run_query_subprocess("ref", str(tmp_path / "a.npz"), scenario="Valet_parking_015", extra=["--heuristic"])
     b = gp.run_query_subprocess("b200", str(tmp_path / "b.npz"), scenario="Valet_parking_015", mode=1, extra=["--heuristic"])
     assert int(b["found"]) == 1
+    # the drop-in's closed sets read the device's 12-byte records in place (GA_GRID_HEUR_REC): what their accessors
+    # return equals the device's four planes bit for bit (unclosed cells: the dump leaves its zero defaults)
+    for s in ("hg_", "hp_"):
+        m = (b["dev_" + s + "flags"] & 1) != 0
+        assert np.array_equal((b[s + "flags"] & 1) != 0, m) and m.sum() > 1000
+        for f in ("cost", "dist", "parent", "flags"):
+            assert np.array_equal(b[s + f][m], b["dev_" + s + f][m]), s + f
     closed = (a["hp_flags"] & 1) != 0
     assert np.all(((b["hp_flags"] & 1) != 0)[closed])             # the fixed point closes a superset
     ra, rb = a["hp_cost"][closed], b["hp_cost"][closed]

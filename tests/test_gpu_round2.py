@@ -104,6 +104,36 @@ def test_near_nodes_after_fixed_point(planner):
     assert [i for _, i in astar.nodes_near_goal_] == want
 
 
+@pytest.mark.parametrize("dim,seed,unk,slot", [(1000, 21, 0.0, 0), (1492, 22, 2.5, 1), (4096, 23, 0.0, 0)])
+def test_heur_records_equal_the_four_planes(planner, dim, seed, unk, slot):
+    """GA_GRID_HEUR_REC (12 B per cell) unpacks to GA_GRID_HEUR_COST / _DIST / _PARENT / _FLAGS bit for bit after a device
+    build (random proximity field, with and without the unknown cost, both slots); after a reference-order replay of the
+    slot the record is refused (its planes are not the device's)."""
+    ctx, cc, astar = _env(planner, dim, seed, ASTAR_UNKNOWN_COST=unk)
+    ad = astar.astar_dim_
+    rng = np.random.default_rng(seed)
+    ctx.upload(_abi.GRID_H_PROX, rng.random((ad, ad)) * (rng.random((ad, ad)) < 0.3))
+    free = ga_b200.sample_free_cells(astar.astar_grid_, 2, seed)
+    goal, start = free[0], free[1]
+    astar.calcDistanceHeuristic(goal, None, for_path=bool(slot), reference_order=False)
+    planes = [ctx.download(g + slot) for g in (_abi.GRID_HEUR_COST, _abi.GRID_HEUR_DIST, _abi.GRID_HEUR_PARENT, _abi.GRID_HEUR_FLAGS)]
+    rec = ctx.download(_abi.GRID_HEUR_REC + slot)
+    assert rec.nbytes == 12 * ad * ad
+    got = ga_b200.unpack_heur_records(rec)
+    assert int((planes[3] & 1).sum()) > ad * ad // 4
+    for name, a, b in zip(("cost", "dist", "parent", "flags"), planes, got):
+        assert np.array_equal(a, b), name
+    # asynchronous download into caller memory + ga_sync gives the same bytes
+    rec2 = np.zeros_like(rec)
+    ctx.check(ctx.lib.ga_download_async(ctx.h, _abi.GRID_HEUR_REC + slot, _abi.ptr(rec2), rec2.nbytes))
+    ctx.sync()
+    assert np.array_equal(rec.view(np.uint32), rec2.view(np.uint32))
+    if dim <= 1500:
+        astar.calcDistanceHeuristic(goal, start, for_path=bool(slot), reference_order=True)
+        with pytest.raises(ga_b200.GaError, match="GA_GRID_HEUR_REC"):
+            ctx.download(_abi.GRID_HEUR_REC + slot)
+
+
 def test_download_window(planner):
     ctx, cc, astar = _env(planner, 1024, 3)
     ad = 256
