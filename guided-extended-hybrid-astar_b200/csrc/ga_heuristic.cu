@@ -1006,32 +1006,49 @@ __global__ void __launch_bounds__(FB * FB, 2) heur_finish_a_kernel(heur_args sin
     else if (k < 2 * FS) { rx = k - FS; ry = FS - 1; }
     else if (k < 2 * FS + FB) { rx = 0; ry = k - 2 * FS + 1; }
     else if (k < 2 * FS + 2 * FB) { rx = FS - 1; ry = k - 2 * FS - FB + 1; }
-    const int px[2] = { (int)(threadIdx.x % FB) + 1, rx }, py[2] = { (int)(threadIdx.x / FB) + 1, ry };
-    double gv[2] = { INFINITY, INFINITY }, bv[2] = { 0.0, 0.0 };
-    uint8_t u[2] = { 0, 0 };
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
+    // own cell first, then (warps 0..4 only: a real branch, the other warps skip it) the ring cell; all loads of a
+    // thread are issued before the first shared store
+    const int px0 = (int)(threadIdx.x % FB) + 1, py0 = (int)(threadIdx.x / FB) + 1;
+    double g0 = INFINITY, b0 = 0.0, g1 = INFINITY, b1 = 0.0;
+    uint8_t u0 = 0, u1 = 0;
     {
-      const int x = ox + px[j], y = oy + py[j];
-      if (px[j] >= 0 && x >= 0 && y >= 0 && x < dim && y < dim)
+      const int x = ox + px0, y = oy + py0;
+      if (x < dim && y < dim)  // own cells have x, y >= 0
       {
         const size_t id = (size_t)y * dim + x;
-        gv[j] = __ldcg(a.g + id);
-        if (with_prox) bv[j] = __ldg(a.prox + id);
-        u[j] = __ldg(a.grid + id);
+        g0 = __ldcg(a.g + id);
+        if (with_prox) b0 = __ldg(a.prox + id);
+        u0 = __ldg(a.grid + id);
       }
     }
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
-      if (px[j] >= 0)
+    if (rx >= 0)
+    {
+      const int x = ox + rx, y = oy + ry;
+      if (x >= 0 && y >= 0 && x < dim && y < dim)
       {
-        const int i = py[j] * FS + px[j];
-        const double b = bv[j] * w_prox;
-        sg[i] = gv[j];
-        if (with_prox) sb[i] = b;
-        su[i] = u[j] == GA_UNKNOWN;
-        any_prox |= (b != 0.0);
+        const size_t id = (size_t)y * dim + x;
+        g1 = __ldcg(a.g + id);
+        if (with_prox) b1 = __ldg(a.prox + id);
+        u1 = __ldg(a.grid + id);
       }
+    }
+    {
+      const int i = py0 * FS + px0;
+      const double b = b0 * w_prox;
+      sg[i] = g0;
+      if (with_prox) sb[i] = b;
+      su[i] = u0 == GA_UNKNOWN;
+      any_prox |= (b != 0.0);
+    }
+    if (rx >= 0)
+    {
+      const int i = ry * FS + rx;
+      const double b = b1 * w_prox;
+      sg[i] = g1;
+      if (with_prox) sb[i] = b;
+      su[i] = u1 == GA_UNKNOWN;
+      any_prox |= (b != 0.0);
+    }
   }
   const int has_prox = __syncthreads_or(any_prox);
   const int lx = threadIdx.x % FB, ly = threadIdx.x / FB, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1118,26 +1135,23 @@ __global__ void __launch_bounds__(FB * FB, 2) heur_finish_a_kernel(heur_args sin
   // log2(chain length) rounds instead of one hop per step (a warp used to wait for its longest chain: ~360 of the
   // ~560 warp instructions per cell).  Parent pointers cannot form a cycle while every edge weight is positive
   // (ga_set_astar_params and ga_upload enforce that); the round cap keeps a corrupted plane from hanging the kernel.
-  unsigned* sj = reinterpret_cast<unsigned*>(sb);  // the prox plane is not needed any more: two buffers of FB * FB words
-  static_assert(sizeof(double) * FS * FS >= 2 * sizeof(unsigned) * FB * FB, "pointer-jumping buffers");
+  unsigned* sj = reinterpret_cast<unsigned*>(sb);  // the prox plane is not needed any more
   __syncthreads();
   {
     const unsigned diag = lpar >= 0 ? (unsigned)(lpar >> 10) : 0u;
     sj[threadIdx.x] = lpar >= 0 ? ((unsigned)(lpar & 1023) | ((1u - diag) << 10) | (diag << 21)) : (unsigned)threadIdx.x;
   }
   __syncthreads();
-  int buf = 0;  // rounds read one buffer and write the other: one barrier per round
   for (int round = 0; round < 11; ++round)
   {
-    const unsigned* src = sj + buf * (FB * FB);
-    const unsigned w = src[threadIdx.x];
-    const unsigned wp = src[w & 1023u];
+    const unsigned w = sj[threadIdx.x];
+    const unsigned wp = sj[w & 1023u];
     const bool changed = (wp & 1023u) != (w & 1023u);
-    buf ^= 1;
-    sj[buf * (FB * FB) + threadIdx.x] = (wp & 1023u) | ((w & ~1023u) + (wp & ~1023u));  // steps add field by field (each < 1024: no carry across)
+    const unsigned nw = (wp & 1023u) | ((w & ~1023u) + (wp & ~1023u));  // steps add field by field (each < 1024: no carry across)
+    __syncthreads();
+    sj[threadIdx.x] = nw;
     if (!__syncthreads_or(changed)) break;
   }
-  sj += buf * (FB * FB);
   const unsigned fin = sj[threadIdx.x];
   const int cur = (int)(fin & 1023u), cs = (int)((fin >> 10) & 2047u), cd = (int)(fin >> 21);
   if (in) a.scratch[n] = fin_pack(cur % FB - lx, cur / FB - ly, cs, cd);
