@@ -272,7 +272,7 @@ struct sweep_tile_t
 {
   double g[32 * SW_P];   // cost plane, relaxed in place
   double mc[32 * SW_P];  // movement_cost_map_ of the cell (edge length factor of the DESTINATION); +inf = blocked
-  double pb[HAS_PB ? 32 * SW_P : 1];  // h_prox_arr_ of the cell (x astar_prox_cost_ = prox_cost, term of the PREDECESSOR)
+  double pb[HAS_PB ? 32 * SW_P : 1];  // prox_cost of the cell = h_prox_arr_ x astar_prox_cost_ (term of the PREDECESSOR)
   unsigned urow[32], ucol[32];  // UNKNOWN masks: urow[y] bit x / ucol[x] bit y
   unsigned dirty[32];           // dirty[y] bit x: cell improved since it was last written to global memory
 };
@@ -323,9 +323,9 @@ __device__ __forceinline__ double sweep_step(const TILE& S, const int lane, cons
   if (PROX)
   {
     const int pi = sp * ds;
-    c0 = c0 + S.pb[pi + lane * dl] * w_prox;  // prox_cost of the predecessor, a_star.cpp:251
-    c1 = c1 + S.pb[pi + lm * dl] * w_prox;
-    c2 = c2 + S.pb[pi + lp * dl] * w_prox;
+    c0 = c0 + S.pb[pi + lane * dl];  // prox_cost of the predecessor (h_prox x astar_prox_cost_, multiplied once at staging), a_star.cpp:251
+    c1 = c1 + S.pb[pi + lm * dl];
+    c2 = c2 + S.pb[pi + lp * dl];
   }
   if (UNK)
   {
@@ -861,6 +861,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
 #pragma unroll 8
     for (int r = 0; r < 32; ++r)
       if ((bc >> r) & 1u) S.mc[r * SW_P + lane] = INFINITY;
+    if (HAS_PB && has_prox)
+    {
+      // prox_cost = h_prox x astar_prox_cost_ once per staged cell instead of three times per line step (the product is
+      // rounded before it is added either way)
+#pragma unroll 8
+      for (int r = 0; r < 32; ++r) S.pb[r * SW_P + lane] = S.pb[r * SW_P + lane] * w_prox;
+    }
     __syncwarp();
 #ifdef SW_DBG
     const long long td = clock64();
