@@ -72,6 +72,7 @@ struct heur_queue
   unsigned prefetch; // 1: a tile the wave reaches for the first time queues its idle neighbours before sweeping
   unsigned refresh;  // a running visit picks up new halo values between sweeps: 1 = state word read during the sweep, 2 = waited for before it
   unsigned round;    // 1: the four sweeps run in lock step (sweep_round), 0: one after the other
+  unsigned pair;     // 1 (needs round == 0, an even worker-warp count): two warps per tile, perpendicular sweeps at the same time
 };
 
 struct heur_args  // finish kernel
@@ -275,6 +276,11 @@ struct sweep_tile_t
   double pb[HAS_PB ? 32 * SW_P : 1];  // prox_cost of the cell = h_prox_arr_ x astar_prox_cost_ (term of the PREDECESSOR)
   unsigned urow[32], ucol[32];  // UNKNOWN masks: urow[y] bit x / ucol[x] bit y
   unsigned dirty[32];           // dirty[y] bit x: cell improved since it was last written to global memory
+  // pair mode (latency): a helper warp sweeps the perpendicular direction at the same time; its share of the dirty map,
+  // the command word (direction | PROX << 2 | UNK << 3, -1 = leave), its "changed" answer and the two weights
+  unsigned dirty2[32];
+  int cmd, ch1;
+  double par_w, par_u;
 };
 
 // NaN-safe minimum (a NaN candidate, 0/0 in h_prox_arr_, never wins -- a_star.cpp:492-497)
@@ -340,15 +346,16 @@ __device__ __forceinline__ double sweep_step(const TILE& S, const int lane, cons
 }
 
 // one sweep over the 30 owned lines; dir = +1 / -1: line order.  Returns 1 if this lane improved a cell.
-template <int ORIENT, bool PROX, bool UNK, class TILE>
+template <int ORIENT, bool PROX, bool UNK, bool HELPER, class TILE>
 __device__ __forceinline__ int sweep_lines(TILE& S, const int lane, const int dir, const double w_prox, const double unk_w,
                                            const double L1, const double L2)
 {
+  unsigned* const dirty = HELPER ? S.dirty2 : S.dirty;  // (a member of the shared tile either way)
   constexpr int dl = ORIENT == 0 ? 1 : SW_P, ds = ORIENT == 0 ? SW_P : 1;
   int s = dir > 0 ? 0 : 31;
   double a = S.g[s * ds + lane * dl];
   int changed = 0;
-  unsigned dm = S.dirty[lane];  // this lane keeps row `lane` of the dirty map, whichever way the sweep runs
+  unsigned dm = dirty[lane];  // this lane keeps row `lane` of the dirty map, whichever way the sweep runs
 #pragma unroll 5
   for (int k = 0; k < SW_O; ++k)
   {
@@ -367,7 +374,7 @@ __device__ __forceinline__ int sweep_lines(TILE& S, const int lane, const int di
     else dm |= (unsigned)imp << s;                     // lane = y, line = column s
     a = nv;
   }
-  S.dirty[lane] = dm;
+  dirty[lane] = dm;
   return changed;
 }
 
@@ -385,15 +392,15 @@ __device__ __forceinline__ int halo_improves(const TILE& S, const int lane, cons
   return __any_sync(SW_FULL, imp);
 }
 
-template <bool PROX, bool UNK, class TILE>
+template <bool PROX, bool UNK, bool HELPER, class TILE>
 __device__ __forceinline__ int sweep_once(TILE& S, const int lane, const int d, const double w_prox, const double unk_w, const double L1,
                                           const double L2)
 {
   int ch;
-  if (d == 0) ch = sweep_lines<0, PROX, UNK>(S, lane, +1, w_prox, unk_w, L1, L2);
-  else if (d == 1) ch = sweep_lines<1, PROX, UNK>(S, lane, +1, w_prox, unk_w, L1, L2);
-  else if (d == 2) ch = sweep_lines<0, PROX, UNK>(S, lane, -1, w_prox, unk_w, L1, L2);
-  else ch = sweep_lines<1, PROX, UNK>(S, lane, -1, w_prox, unk_w, L1, L2);
+  if (d == 0) ch = sweep_lines<0, PROX, UNK, HELPER>(S, lane, +1, w_prox, unk_w, L1, L2);
+  else if (d == 1) ch = sweep_lines<1, PROX, UNK, HELPER>(S, lane, +1, w_prox, unk_w, L1, L2);
+  else if (d == 2) ch = sweep_lines<0, PROX, UNK, HELPER>(S, lane, -1, w_prox, unk_w, L1, L2);
+  else ch = sweep_lines<1, PROX, UNK, HELPER>(S, lane, -1, w_prox, unk_w, L1, L2);
   ch = __any_sync(SW_FULL, ch);
   __syncwarp();
   return ch;
@@ -625,15 +632,41 @@ __device__ __forceinline__ void sweep_prefetch(const sweep_visit& V, const heur_
   *n_unused += __reduce_add_sync(SW_FULL, unused);
 }
 
+// named barrier of a leader / helper pair (64 threads); also orders their shared-memory accesses
+__device__ __forceinline__ void pair_bar(const int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+
+// the helper warp of a pair: sweeps on command, touches nothing else (its dirty bits go to dirty2, merged by the leader)
+template <class TILE>
+__device__ __forceinline__ void sweep_helper(TILE& S, const int lane, const int pbar, const double L1, const double L2)
+{
+  for (;;)
+  {
+    pair_bar(pbar);
+    const int cmd = S.cmd;
+    if (cmd < 0) return;
+    const int d = cmd & 3;
+    const double w_prox = S.par_w, unk_w = S.par_u;
+    S.dirty2[lane] = 0;
+    int ch;
+    if (cmd & 4)
+      ch = (cmd & 8) ? sweep_once<true, true, true>(S, lane, d, w_prox, unk_w, L1, L2) : sweep_once<true, false, true>(S, lane, d, w_prox, unk_w, L1, L2);
+    else
+      ch = (cmd & 8) ? sweep_once<false, true, true>(S, lane, d, w_prox, unk_w, L1, L2) : sweep_once<false, false, true>(S, lane, d, w_prox, unk_w, L1, L2);
+    if (lane == 0) S.ch1 = ch;
+    pair_bar(pbar + 1);
+  }
+}
+
 // relax the staged tile to its fixed point.  Publication: once after `early` changing sweeps (0 =
 // never) plus the final one by the caller, or after every changing sweep (SW_EARLY_ALL).  With
 // `refresh` a neighbour's publication is picked up between sweeps; with `linger` (SM cycles; needs
 // SW_EARLY_ALL, everything is published then) the converged tile stays staged that long waiting for
 // the next one.
-template <bool PROX, bool UNK, class TILE>
+template <bool PROX, bool UNK, bool PAIR, class TILE>
 __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, const heur_queue& q, const int lane,
                                                int d, const bool must_run, const bool fresh, const double w_prox, const double unk_w,
-                                               const double L1, const double L2, int* n_sweeps, int* n_act, int* n_unused, int* n_reserved)
+                                               const double L1, const double L2, int* n_sweeps, int* n_act, int* n_unused, int* n_reserved,
+                                               const int pbar)
 {
   int n = 0, n_changing = 0, n_pub = 0;
   const bool run0 = must_run || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
@@ -646,6 +679,8 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
   // one counts for its own direction); 15 = fixed point.  prim = the next sweep's direction: round
   // robin, restarted away from the side the news came from after a halo refresh.
   unsigned mask = run0 ? 0u : 15u;
+  int pref_h = (d >> 2) & 3, pref_v = (d >> 4) & 3, help_d = -1;  // pair mode: preferred perpendiculars, the helper's last direction (-1: restart)
+  d &= 3;
   int prim = d, last_ch = 0;
   for (;;)
   {
@@ -672,6 +707,8 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
         {
           mask = 0;
           prim = dn;
+          if (dn & 1) pref_h = dn; else pref_v = dn;
+          help_d = -1;
         }
         st = T_RUNNING;
       }
@@ -689,10 +726,34 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       mask = ch ? 0u : 15u;  // a clean round has looked at every cell from all eight sides
       n += 4;
     }
+    else if (PAIR)
+    {
+      // pair mode: the helper warp sweeps the next (perpendicular) direction while this warp sweeps `prim` -- a wave that
+      // crosses the tile diagonally needs both, one after the other they cost two sweep times per tile
+      d = prim;
+      // after news: the perpendicular that leaves the side the wave comes from; then the opposite pair, and so on
+      const int d2 = help_d < 0 ? ((d & 1) ? pref_v : pref_h) : ((help_d + 2) & 3);
+      help_d = d2;
+      if (lane == 0) S.cmd = d2 | (PROX ? 4 : 0) | (UNK ? 8 : 0);
+      pair_bar(pbar);
+      const int ch_a = sweep_once<PROX, UNK, false>(S, lane, d, w_prox, unk_w, L1, L2);
+      pair_bar(pbar + 1);
+      const int ch_b = S.ch1;
+      S.dirty[lane] |= S.dirty2[lane];
+      __syncwarp();
+      // a clean sweep only counts when nothing changed while it ran; a changing one counts for itself when the other was clean
+      if (ch_a && ch_b) mask = 0u;
+      else if (ch_a) mask = 1u << d;
+      else if (ch_b) mask = 1u << d2;
+      else mask |= (1u << d) | (1u << d2);
+      ch = ch_a | ch_b;
+      prim = (d + 2) & 3;
+      n += 2;
+    }
     else
     {
       d = prim;
-      ch = sweep_once<PROX, UNK>(S, lane, d, w_prox, unk_w, L1, L2);
+      ch = sweep_once<PROX, UNK, false>(S, lane, d, w_prox, unk_w, L1, L2);
       mask = ch ? (1u << d) : (mask | (1u << d));
       prim = (d + 1) & 3;  // round robin (trying the perpendiculars before the way back measured slower)
       ++n;
@@ -719,6 +780,8 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       {
         mask = 0;
         prim = dn;
+        if (dn & 1) pref_h = dn; else pref_v = dn;
+        help_d = -1;
       }
     }
   }
@@ -733,13 +796,20 @@ __device__ __forceinline__ void cp_async8(const unsigned dst_smem, const void* s
 
 #define SW_RESERVE 24  // pending counts reserved per visit: (two publications + the prefetch) x 8 neighbours
 
-template <bool HAS_PB, int WARPS>
+template <bool HAS_PB, int WARPS, bool PAIR>
 __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid single, const heur_grid* many, heur_queue q)
 {
   extern __shared__ __align__(16) unsigned char sw_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  sweep_tile_t<HAS_PB>& S = reinterpret_cast<sweep_tile_t<HAS_PB>*>(sw_smem)[warp];
+  // pair mode (q.pair, latency mode only): warps 2p / 2p + 1 are the leader / helper of worker p and share one tile
+  const int pbar = PAIR ? 1 + 2 * (warp >> 1) : 0;  // named barriers pbar (go) and pbar + 1 (done) of the pair
+  sweep_tile_t<HAS_PB>& S = reinterpret_cast<sweep_tile_t<HAS_PB>*>(sw_smem)[PAIR ? (warp >> 1) : warp];
   const double L1 = 0.625, L2 = 0.625 * 1.4142135623730951;  // movement_distances_ (a_star.hpp:54-57)
+  if (PAIR && (warp & 1))
+  {
+    sweep_helper(S, lane, pbar, L1, L2);
+    return;
+  }
   int cont = 0;
 
   for (;;)
@@ -749,7 +819,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
     if (!e) e = q_pop_warp(q, lane);
     const long long t1 = clock64();
     cont = 0;
-    if (e < 0) return;
+    if (e < 0)
+    {
+      if (PAIR)  // send the helper home
+      {
+        if (lane == 0) S.cmd = -1;
+        pair_bar(pbar);
+      }
+      return;
+    }
     sweep_visit V;
     V.gi = (e - 1) >> 20;
     const int gi = V.gi, tile = (e - 1) & 0xFFFFF;
@@ -845,6 +923,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
     if (lane == glx && gly >= 0 && gly < 32) bc |= 1u << gly;
     const bool must_run = glx >= 1 && glx <= SW_O && gly >= 1 && gly <= SW_O;  // the root's tile is not a fixed point of its old halo
     S.dirty[lane] = 0;
+    if (PAIR && lane == 0)
+    {
+      S.par_w = w_prox;
+      S.par_u = unk_w;
+    }
     if (unk_w != 0)
     {
       S.ucol[lane] = uc;
@@ -884,6 +967,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
       if (m_l < best) { best = m_l; d0 = 1; }
       if (m_b < best) { best = m_b; d0 = 2; }
       if (m_r < best) { best = m_r; d0 = 3; }
+      // pair mode: the helper's perpendicular direction also leaves the side with the smaller halo values
+      // (bits 2-3: rightwards 1 / leftwards 3, bits 4-5: downwards 0 / upwards 2)
+      d0 |= ((m_l <= m_r) ? 1 : 3) << 2;
+      d0 |= ((m_t <= m_b) ? 0 : 2) << 4;
     }
     __syncwarp();
     const long long t2 = clock64();
@@ -892,18 +979,18 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
     int any, n_sweeps = 0, n_act = 0, n_unused = 0, n_reserved = SW_RESERVE;
     if constexpr (!HAS_PB)
     {
-      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
-      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+      if (unk_w != 0) any = sweep_tile_loop<false, true, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      else any = sweep_tile_loop<false, false, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
     }
     else if (has_prox)
     {
-      if (unk_w != 0) any = sweep_tile_loop<true, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
-      else any = sweep_tile_loop<true, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+      if (unk_w != 0) any = sweep_tile_loop<true, true, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      else any = sweep_tile_loop<true, false, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
     }
     else
     {
-      if (unk_w != 0) any = sweep_tile_loop<false, true>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
-      else any = sweep_tile_loop<false, false>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved);
+      if (unk_w != 0) any = sweep_tile_loop<false, true, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      else any = sweep_tile_loop<false, false, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
     }
     const long long t3 = clock64();
 
@@ -1279,10 +1366,14 @@ int ga_heur_alloc(ga_ctx* c)
   GA_CUDA(c, cudaMalloc(&c->d_hcls, na));
   GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * (na + (size_t)((c->astar_dim + 31) / 32) * ((c->astar_dim + 31) / 32) * 129)));  // scratch words + per-block terminal slots and counts
   GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS * sizeof(sweep_tile_t<true>))));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS_LEAN * sizeof(sweep_tile_t<false>))));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS / 2 * sizeof(sweep_tile_t<true>))));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS_LEAN / 2 * sizeof(sweep_tile_t<false>))));
   return GA_OK;
 }
 
@@ -1344,7 +1435,8 @@ static void queue_knobs(const ga_ctx* c, int n_grids, heur_queue* q)
   q->round = c->sw_round >= 0 ? (unsigned)c->sw_round : (lat ? 0u : 1u);
   q->refresh = c->sw_refresh >= 0 ? (unsigned)c->sw_refresh : (lat ? 2u : 1u);
   q->linger = c->sw_linger >= 0 ? (unsigned)c->sw_linger : (lat ? 8000u : 0u);
-  q->prefetch = c->sw_prefetch >= 0 ? (unsigned)c->sw_prefetch : (lat ? 1u : 0u);
+  q->prefetch = c->sw_prefetch >= 0 ? (unsigned)(c->sw_prefetch & 1) : (lat ? 1u : 0u);
+  q->pair = (lat && q->round == 0 && !(c->sw_prefetch >= 0 && (c->sw_prefetch & 4))) ? 1u : 0u;  // stage-ahead knob + 4: no helper warps
 }
 
 static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& a0, const heur_grid* dG, const heur_args* dA,
@@ -1362,10 +1454,21 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
     ga_launch_scope ls(c, GA_K_HEUR_RELAX);
     // no grid of the launch carries a proximity cost: the tiles need no prox plane and 12 workers fit an SM
     const int nw = lean ? (c->sw_warps == SW_WARPS ? SW_WARPS_LEAN : c->sw_warps) : c->sw_warps;
-    const size_t want = (total_tiles + nw - 1) / nw;
+    heur_queue qk = q;
+    if (nw & 1) qk.pair = 0;  // pairs need an even number of warps
+    const int workers = qk.pair ? nw / 2 : nw;
+    const size_t want = (total_tiles + workers - 1) / workers;
     const int g = (size_t)c->sm_count < want ? c->sm_count : (int)want;
-    if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN><<<g, nw * 32, nw * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, q);
-    else heur_sweep_kernel<true, SW_WARPS><<<g, nw * 32, nw * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, q);
+    if (qk.pair)
+    {
+      if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN, true><<<g, nw * 32, workers * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, qk);
+      else heur_sweep_kernel<true, SW_WARPS, true><<<g, nw * 32, workers * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, qk);
+    }
+    else
+    {
+      if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN, false><<<g, nw * 32, workers * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, qk);
+      else heur_sweep_kernel<true, SW_WARPS, false><<<g, nw * 32, workers * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, qk);
+    }
   }
   GA_CUDA(c, cudaGetLastError());
   {

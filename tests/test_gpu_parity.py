@@ -706,7 +706,7 @@ def test_download_async_and_interleaved_contexts(oracle):
         ctx.close()
 
 
-# ga_set_heur_knobs: { workers per SM, idle back-off ns, early publications, lock-step rounds, halo refresh, linger ns, stage-ahead }
+# ga_set_heur_knobs: { warps per SM, idle back-off ns, early publications, lock-step rounds, halo refresh, linger ns, stage-ahead (+ 4: no helper warps) }
 @pytest.mark.parametrize("knobs", [
     (8, 20, 0, 0, 0, 0, 0),            # plain: publish when converged
     (8, 20, 1, 0, 1, 0, 0),
@@ -715,6 +715,8 @@ def test_download_async_and_interleaved_contexts(oracle):
     (8, 20, 255, 0, 2, 8000, 1),       # latency mode
     (1, 20, 255, 0, 2, 100000, 1),     # one worker per SM
     (2, 20, 3, 0, 2, 0, 1),
+    (8, 20, 255, 0, 2, 8000, 5),       # latency mode without helper warps (stage-ahead knob + 4)
+    (6, 20, 255, 0, 1, 0, 0),          # three leader / helper pairs
 ])
 def test_heuristic_schedules_agree(oracle, knobs):
     """the sweep kernel's scheduling knobs (sweep order, when a tile publishes, in-place halo refresh, waiting,
