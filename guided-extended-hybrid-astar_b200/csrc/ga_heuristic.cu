@@ -72,7 +72,7 @@ struct heur_queue
   unsigned prefetch; // 1: a tile the wave reaches for the first time queues its idle neighbours before sweeping
   unsigned refresh;  // a running visit picks up new halo values between sweeps: 1 = state word read during the sweep, 2 = waited for before it
   unsigned round;    // 1: the four sweeps run in lock step (sweep_round), 0: one after the other
-  unsigned pair;     // 1 (needs round == 0, an even worker-warp count): two warps per tile, perpendicular sweeps at the same time
+  unsigned pair;     // 0 / 2 / 4 (needs round == 0): warps per tile in single builds, sweeping different directions at the same time
 };
 
 struct heur_args  // finish kernel
@@ -278,8 +278,8 @@ struct sweep_tile_t
   unsigned dirty[32];           // dirty[y] bit x: cell improved since it was last written to global memory
   // pair mode (latency): a helper warp sweeps the perpendicular direction at the same time; its share of the dirty map,
   // the command word (direction | PROX << 2 | UNK << 3, -1 = leave), its "changed" answer and the two weights
-  unsigned dirty2[32];
-  int cmd, ch1;
+  unsigned dirty2[3][32];
+  int cmd[4], chh[4];
   double par_w, par_u;
 };
 
@@ -348,9 +348,9 @@ __device__ __forceinline__ double sweep_step(const TILE& S, const int lane, cons
 // one sweep over the 30 owned lines; dir = +1 / -1: line order.  Returns 1 if this lane improved a cell.
 template <int ORIENT, bool PROX, bool UNK, bool HELPER, class TILE>
 __device__ __forceinline__ int sweep_lines(TILE& S, const int lane, const int dir, const double w_prox, const double unk_w,
-                                           const double L1, const double L2)
+                                           const double L1, const double L2, const int hidx)
 {
-  unsigned* const dirty = HELPER ? S.dirty2 : S.dirty;  // (a member of the shared tile either way)
+  unsigned* const dirty = HELPER ? S.dirty2[hidx - 1] : S.dirty;  // (a member of the shared tile either way)
   constexpr int dl = ORIENT == 0 ? 1 : SW_P, ds = ORIENT == 0 ? SW_P : 1;
   int s = dir > 0 ? 0 : 31;
   double a = S.g[s * ds + lane * dl];
@@ -394,13 +394,13 @@ __device__ __forceinline__ int halo_improves(const TILE& S, const int lane, cons
 
 template <bool PROX, bool UNK, bool HELPER, class TILE>
 __device__ __forceinline__ int sweep_once(TILE& S, const int lane, const int d, const double w_prox, const double unk_w, const double L1,
-                                          const double L2)
+                                          const double L2, const int hidx = 0)
 {
   int ch;
-  if (d == 0) ch = sweep_lines<0, PROX, UNK, HELPER>(S, lane, +1, w_prox, unk_w, L1, L2);
-  else if (d == 1) ch = sweep_lines<1, PROX, UNK, HELPER>(S, lane, +1, w_prox, unk_w, L1, L2);
-  else if (d == 2) ch = sweep_lines<0, PROX, UNK, HELPER>(S, lane, -1, w_prox, unk_w, L1, L2);
-  else ch = sweep_lines<1, PROX, UNK, HELPER>(S, lane, -1, w_prox, unk_w, L1, L2);
+  if (d == 0) ch = sweep_lines<0, PROX, UNK, HELPER>(S, lane, +1, w_prox, unk_w, L1, L2, hidx);
+  else if (d == 1) ch = sweep_lines<1, PROX, UNK, HELPER>(S, lane, +1, w_prox, unk_w, L1, L2, hidx);
+  else if (d == 2) ch = sweep_lines<0, PROX, UNK, HELPER>(S, lane, -1, w_prox, unk_w, L1, L2, hidx);
+  else ch = sweep_lines<1, PROX, UNK, HELPER>(S, lane, -1, w_prox, unk_w, L1, L2, hidx);
   ch = __any_sync(SW_FULL, ch);
   __syncwarp();
   return ch;
@@ -633,27 +633,28 @@ __device__ __forceinline__ void sweep_prefetch(const sweep_visit& V, const heur_
 }
 
 // named barrier of a leader / helper pair (64 threads); also orders their shared-memory accesses
-__device__ __forceinline__ void pair_bar(const int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+template <int GROUP>
+__device__ __forceinline__ void pair_bar(const int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(32 * GROUP) : "memory"); }
 
 // the helper warp of a pair: sweeps on command, touches nothing else (its dirty bits go to dirty2, merged by the leader)
-template <class TILE>
-__device__ __forceinline__ void sweep_helper(TILE& S, const int lane, const int pbar, const double L1, const double L2)
+template <int GROUP, class TILE>
+__device__ __forceinline__ void sweep_helper(TILE& S, const int lane, const int pbar, const int hidx, const double L1, const double L2)
 {
   for (;;)
   {
-    pair_bar(pbar);
-    const int cmd = S.cmd;
+    pair_bar<GROUP>(pbar);
+    const int cmd = S.cmd[hidx];
     if (cmd < 0) return;
     const int d = cmd & 3;
     const double w_prox = S.par_w, unk_w = S.par_u;
-    S.dirty2[lane] = 0;
+    S.dirty2[hidx - 1][lane] = 0;
     int ch;
     if (cmd & 4)
-      ch = (cmd & 8) ? sweep_once<true, true, true>(S, lane, d, w_prox, unk_w, L1, L2) : sweep_once<true, false, true>(S, lane, d, w_prox, unk_w, L1, L2);
+      ch = (cmd & 8) ? sweep_once<true, true, true>(S, lane, d, w_prox, unk_w, L1, L2, hidx) : sweep_once<true, false, true>(S, lane, d, w_prox, unk_w, L1, L2, hidx);
     else
-      ch = (cmd & 8) ? sweep_once<false, true, true>(S, lane, d, w_prox, unk_w, L1, L2) : sweep_once<false, false, true>(S, lane, d, w_prox, unk_w, L1, L2);
-    if (lane == 0) S.ch1 = ch;
-    pair_bar(pbar + 1);
+      ch = (cmd & 8) ? sweep_once<false, true, true>(S, lane, d, w_prox, unk_w, L1, L2, hidx) : sweep_once<false, false, true>(S, lane, d, w_prox, unk_w, L1, L2, hidx);
+    if (lane == 0) S.chh[hidx] = ch;
+    pair_bar<GROUP>(pbar + 1);
   }
 }
 
@@ -662,7 +663,7 @@ __device__ __forceinline__ void sweep_helper(TILE& S, const int lane, const int 
 // `refresh` a neighbour's publication is picked up between sweeps; with `linger` (SM cycles; needs
 // SW_EARLY_ALL, everything is published then) the converged tile stays staged that long waiting for
 // the next one.
-template <bool PROX, bool UNK, bool PAIR, class TILE>
+template <bool PROX, bool UNK, int GROUP, class TILE>
 __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, const heur_queue& q, const int lane,
                                                int d, const bool must_run, const bool fresh, const double w_prox, const double unk_w,
                                                const double L1, const double L2, int* n_sweeps, int* n_act, int* n_unused, int* n_reserved,
@@ -726,7 +727,7 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       mask = ch ? 0u : 15u;  // a clean round has looked at every cell from all eight sides
       n += 4;
     }
-    else if (PAIR)
+    else if (GROUP == 2)
     {
       // pair mode: the helper warp sweeps the next (perpendicular) direction while this warp sweeps `prim` -- a wave that
       // crosses the tile diagonally needs both, one after the other they cost two sweep times per tile
@@ -734,12 +735,12 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       // after news: the perpendicular that leaves the side the wave comes from; then the opposite pair, and so on
       const int d2 = help_d < 0 ? ((d & 1) ? pref_v : pref_h) : ((help_d + 2) & 3);
       help_d = d2;
-      if (lane == 0) S.cmd = d2 | (PROX ? 4 : 0) | (UNK ? 8 : 0);
-      pair_bar(pbar);
+      if (lane == 0) S.cmd[1] = d2 | (PROX ? 4 : 0) | (UNK ? 8 : 0);
+      pair_bar<GROUP>(pbar);
       const int ch_a = sweep_once<PROX, UNK, false>(S, lane, d, w_prox, unk_w, L1, L2);
-      pair_bar(pbar + 1);
-      const int ch_b = S.ch1;
-      S.dirty[lane] |= S.dirty2[lane];
+      pair_bar<GROUP>(pbar + 1);
+      const int ch_b = S.chh[1];
+      S.dirty[lane] |= S.dirty2[0][lane];
       __syncwarp();
       // a clean sweep only counts when nothing changed while it ran; a changing one counts for itself when the other was clean
       if (ch_a && ch_b) mask = 0u;
@@ -749,6 +750,24 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       ch = ch_a | ch_b;
       prim = (d + 2) & 3;
       n += 2;
+    }
+    else if (GROUP == 4)
+    {
+      // quad mode: all four directions at once, one warp each
+      d = prim;
+      if (lane >= 1 && lane < 4) S.cmd[lane] = ((d + lane) & 3) | (PROX ? 4 : 0) | (UNK ? 8 : 0);
+      pair_bar<GROUP>(pbar);
+      const int ch_a = sweep_once<PROX, UNK, false>(S, lane, d, w_prox, unk_w, L1, L2);
+      pair_bar<GROUP>(pbar + 1);
+      const int c1 = S.chh[1], c2 = S.chh[2], c3 = S.chh[3];
+      S.dirty[lane] |= S.dirty2[0][lane] | S.dirty2[1][lane] | S.dirty2[2][lane];
+      __syncwarp();
+      const int nch = ch_a + c1 + c2 + c3;
+      if (nch == 0) mask = 15u;
+      else if (nch > 1) mask = 0u;
+      else mask = ch_a ? (1u << d) : c1 ? (1u << ((d + 1) & 3)) : c2 ? (1u << ((d + 2) & 3)) : (1u << ((d + 3) & 3));
+      ch = nch > 0;
+      n += 4;
     }
     else
     {
@@ -796,18 +815,18 @@ __device__ __forceinline__ void cp_async8(const unsigned dst_smem, const void* s
 
 #define SW_RESERVE 24  // pending counts reserved per visit: (two publications + the prefetch) x 8 neighbours
 
-template <bool HAS_PB, int WARPS, bool PAIR>
+template <bool HAS_PB, int WARPS, int GROUP>
 __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid single, const heur_grid* many, heur_queue q)
 {
   extern __shared__ __align__(16) unsigned char sw_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // pair mode (q.pair, latency mode only): warps 2p / 2p + 1 are the leader / helper of worker p and share one tile
-  const int pbar = PAIR ? 1 + 2 * (warp >> 1) : 0;  // named barriers pbar (go) and pbar + 1 (done) of the pair
-  sweep_tile_t<HAS_PB>& S = reinterpret_cast<sweep_tile_t<HAS_PB>*>(sw_smem)[PAIR ? (warp >> 1) : warp];
+  const int pbar = GROUP > 1 ? 1 + 2 * (warp / GROUP) : 0;  // named barriers pbar (go) and pbar + 1 (done) of the group
+  sweep_tile_t<HAS_PB>& S = reinterpret_cast<sweep_tile_t<HAS_PB>*>(sw_smem)[warp / GROUP];
   const double L1 = 0.625, L2 = 0.625 * 1.4142135623730951;  // movement_distances_ (a_star.hpp:54-57)
-  if (PAIR && (warp & 1))
+  if (GROUP > 1 && (warp % GROUP))
   {
-    sweep_helper(S, lane, pbar, L1, L2);
+    sweep_helper<GROUP>(S, lane, pbar, warp % GROUP, L1, L2);
     return;
   }
   int cont = 0;
@@ -821,10 +840,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
     cont = 0;
     if (e < 0)
     {
-      if (PAIR)  // send the helper home
+      if (GROUP > 1)  // send the helpers home
       {
-        if (lane == 0) S.cmd = -1;
-        pair_bar(pbar);
+        if (lane < 4) S.cmd[lane] = -1;
+        pair_bar<GROUP>(pbar);
       }
       return;
     }
@@ -923,7 +942,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
     if (lane == glx && gly >= 0 && gly < 32) bc |= 1u << gly;
     const bool must_run = glx >= 1 && glx <= SW_O && gly >= 1 && gly <= SW_O;  // the root's tile is not a fixed point of its old halo
     S.dirty[lane] = 0;
-    if (PAIR && lane == 0)
+    if (GROUP > 1 && lane == 0)
     {
       S.par_w = w_prox;
       S.par_u = unk_w;
@@ -979,18 +998,18 @@ __global__ void __launch_bounds__(WARPS * 32, 1) heur_sweep_kernel(heur_grid sin
     int any, n_sweeps = 0, n_act = 0, n_unused = 0, n_reserved = SW_RESERVE;
     if constexpr (!HAS_PB)
     {
-      if (unk_w != 0) any = sweep_tile_loop<false, true, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
-      else any = sweep_tile_loop<false, false, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      if (unk_w != 0) any = sweep_tile_loop<false, true, GROUP>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      else any = sweep_tile_loop<false, false, GROUP>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
     }
     else if (has_prox)
     {
-      if (unk_w != 0) any = sweep_tile_loop<true, true, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
-      else any = sweep_tile_loop<true, false, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      if (unk_w != 0) any = sweep_tile_loop<true, true, GROUP>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      else any = sweep_tile_loop<true, false, GROUP>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
     }
     else
     {
-      if (unk_w != 0) any = sweep_tile_loop<false, true, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
-      else any = sweep_tile_loop<false, false, PAIR>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      if (unk_w != 0) any = sweep_tile_loop<false, true, GROUP>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
+      else any = sweep_tile_loop<false, false, GROUP>(S, V, q, lane, d0, must_run, fresh, w_prox, unk_w, L1, L2, &n_sweeps, &n_act, &n_unused, &n_reserved, pbar);
     }
     const long long t3 = clock64();
 
@@ -1366,14 +1385,18 @@ int ga_heur_alloc(ga_ctx* c)
   GA_CUDA(c, cudaMalloc(&c->d_hcls, na));
   GA_CUDA(c, cudaMalloc(&c->d_jump, sizeof(int32_t) * (na + (size_t)((c->astar_dim + 31) / 32) * ((c->astar_dim + 31) / 32) * 129)));  // scratch words + per-block terminal slots and counts
   GA_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(int32_t) * 2 * na));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS * sizeof(sweep_tile_t<true>))));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS_LEAN * sizeof(sweep_tile_t<false>))));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS / 2 * sizeof(sweep_tile_t<true>))));
-  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(SW_WARPS_LEAN / 2 * sizeof(sweep_tile_t<false>))));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<true, SW_WARPS, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS / 4 * sizeof(sweep_tile_t<true>))));
+  GA_CUDA(c, cudaFuncSetAttribute(heur_sweep_kernel<false, SW_WARPS_LEAN, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(SW_WARPS_LEAN / 4 * sizeof(sweep_tile_t<false>))));
   return GA_OK;
 }
 
@@ -1436,7 +1459,8 @@ static void queue_knobs(const ga_ctx* c, int n_grids, heur_queue* q)
   q->refresh = c->sw_refresh >= 0 ? (unsigned)c->sw_refresh : (lat ? 2u : 1u);
   q->linger = c->sw_linger >= 0 ? (unsigned)c->sw_linger : (lat ? 8000u : 0u);
   q->prefetch = c->sw_prefetch >= 0 ? (unsigned)(c->sw_prefetch & 1) : (lat ? 1u : 0u);
-  q->pair = (lat && q->round == 0 && !(c->sw_prefetch >= 0 && (c->sw_prefetch & 4))) ? 1u : 0u;  // stage-ahead knob + 4: no helper warps
+  // warps per tile in single builds: 4 (leader + three helpers, one direction each); stage-ahead knob + 4: no helpers, + 8: pairs
+  q->pair = (lat && q->round == 0) ? ((c->sw_prefetch >= 0 && (c->sw_prefetch & 4)) ? 0u : (c->sw_prefetch >= 0 && (c->sw_prefetch & 8)) ? 2u : 4u) : 0u;
 }
 
 static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& a0, const heur_grid* dG, const heur_args* dA,
@@ -1455,20 +1479,21 @@ static int launch_build(ga_ctx* c, int n, const heur_grid& G0, const heur_args& 
     // no grid of the launch carries a proximity cost: the tiles need no prox plane and 12 workers fit an SM
     const int nw = lean ? (c->sw_warps == SW_WARPS ? SW_WARPS_LEAN : c->sw_warps) : c->sw_warps;
     heur_queue qk = q;
-    if (nw & 1) qk.pair = 0;  // pairs need an even number of warps
-    const int workers = qk.pair ? nw / 2 : nw;
+    if (qk.pair && nw % (int)qk.pair) qk.pair = (nw & 1) ? 0 : 2;  // groups need a multiple of their size
+    const int grp = qk.pair ? (int)qk.pair : 1;
+    const int workers = nw / grp;
     const size_t want = (total_tiles + workers - 1) / workers;
     const int g = (size_t)c->sm_count < want ? c->sm_count : (int)want;
-    if (qk.pair)
-    {
-      if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN, true><<<g, nw * 32, workers * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, qk);
-      else heur_sweep_kernel<true, SW_WARPS, true><<<g, nw * 32, workers * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, qk);
-    }
-    else
-    {
-      if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN, false><<<g, nw * 32, workers * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, qk);
-      else heur_sweep_kernel<true, SW_WARPS, false><<<g, nw * 32, workers * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, qk);
-    }
+#define SW_LAUNCH(G)                                                                                                                  \
+  do                                                                                                                                  \
+  {                                                                                                                                   \
+    if (lean) heur_sweep_kernel<false, SW_WARPS_LEAN, G><<<g, nw * 32, workers * sizeof(sweep_tile_t<false>), c->stream>>>(G0, dG, qk); \
+    else heur_sweep_kernel<true, SW_WARPS, G><<<g, nw * 32, workers * sizeof(sweep_tile_t<true>), c->stream>>>(G0, dG, qk);           \
+  } while (0)
+    if (grp == 4) SW_LAUNCH(4);
+    else if (grp == 2) SW_LAUNCH(2);
+    else SW_LAUNCH(1);
+#undef SW_LAUNCH
   }
   GA_CUDA(c, cudaGetLastError());
   {

@@ -435,8 +435,8 @@ GA_API int ga_prof_get(ga_ctx* ctx, int k, double* ms_total, long long* launches
  * line sweeps summed over visits, visits that improved a cell, SM cycles summed over
  * visits spent waiting for a tile / staging / sweeping / publishing } (syncs the stream) */
 GA_API int ga_heur_stats(ga_ctx* ctx, long long* out7);
-/* scheduling of the sweep kernel, k7 = { worker warps per SM (1..8; single builds pair them: leader + helper per tile), idle back-off ns, early publications, lock-step
- * rounds, in-place halo refresh, linger ns, stage-ahead (+ 4: single builds without helper warps) }; -1 = chosen per launch.  Every setting yields the same
+/* scheduling of the sweep kernel, k7 = { worker warps per SM (1..8; single builds group them: four warps per tile), idle back-off ns, early publications, lock-step
+ * rounds, in-place halo refresh, linger ns, stage-ahead (+ 4: single builds with one warp per tile, + 8: with two) }; -1 = chosen per launch.  Every setting yields the same
  * fixed point (tests/test_gpu_parity.py::test_heuristic_schedules_agree); this exists for that test and for tuning. */
 GA_API int ga_set_heur_knobs(ga_ctx* ctx, const int* k7);
 /* how ga_build_safety stages a tile's raw bytes when the patch side is a multiple of 16: 1 (default) = one bulk tensor

@@ -706,7 +706,7 @@ def test_download_async_and_interleaved_contexts(oracle):
         ctx.close()
 
 
-# ga_set_heur_knobs: { warps per SM, idle back-off ns, early publications, lock-step rounds, halo refresh, linger ns, stage-ahead (+ 4: no helper warps) }
+# ga_set_heur_knobs: { warps per SM, idle back-off ns, early publications, lock-step rounds, halo refresh, linger ns, stage-ahead (+ 4: one warp per tile, + 8: two; default four in single builds) }
 @pytest.mark.parametrize("knobs", [
     (8, 20, 0, 0, 0, 0, 0),            # plain: publish when converged
     (8, 20, 1, 0, 1, 0, 0),
@@ -716,7 +716,8 @@ def test_download_async_and_interleaved_contexts(oracle):
     (1, 20, 255, 0, 2, 100000, 1),     # one worker per SM
     (2, 20, 3, 0, 2, 0, 1),
     (8, 20, 255, 0, 2, 8000, 5),       # latency mode without helper warps (stage-ahead knob + 4)
-    (6, 20, 255, 0, 1, 0, 0),          # three leader / helper pairs
+    (6, 20, 255, 0, 1, 0, 8),          # three leader / helper pairs
+    (8, 20, 255, 0, 2, 8000, 9),       # leader / helper pairs instead of four warps per tile (stage-ahead knob + 8)
 ])
 def test_heuristic_schedules_agree(oracle, knobs):
     """the sweep kernel's scheduling knobs (sweep order, when a tile publishes, in-place halo refresh, waiting,
