@@ -332,6 +332,12 @@ def test_heuristic_batch_matches_oracle(oracle):
                 assert np.array_equal(cs.flags, want["flags"])
                 m = want["flags"] & 1 > 0
                 assert np.array_equal(cs.dist[m], want["dist"][m])
+        # a batch of three runs in the latency mode (<= 4 grids: four warps per tile, every changing sweep published)
+        n3 = ga_b200.AStar.calcDistanceHeuristicBatch(astars[1:4], goals[1:4], for_path=False)
+        for i, (astar, want) in enumerate(zip(astars[1:4], wants[1:4])):
+            cs = astar.closed_set_guidance_
+            assert n3[i] == want["n_closed"]
+            assert np.array_equal(cs.cost, want["cost"]) and np.array_equal(cs.parent, want["parent"])
         # a single build on one of the contexts afterwards still works (own ring, own counters)
         assert astars[1].calcDistanceHeuristic(goals[1], None, for_path=False) == wants[1]["n_closed"]
         assert np.array_equal(astars[1].closed_set_guidance_.cost, wants[1]["cost"])
