@@ -14,8 +14,10 @@
 //     relaxed by Gauss-Seidel line sweeps (see the sweep section below), improved cells written back;
 //   - tiles whose facing border (or corner) cell improved are activated; activation is dataflow: a
 //     per-tile state word (idle / queued / running / running+dirty) and one device-wide ticket ring
-//     of tile ids.  Persistent warps (6 per SM) take tickets, so the wavefront is balanced
+//     of tile ids.  Persistent warps (8 or 12 per SM) take tickets, so the wavefront is balanced
 //     dynamically over the 148 SMs and a worker never waits for another one;
+//   - single builds (latency mode) put FOUR warps on a tile, one sweep direction each: the leader runs the
+//     protocol, three helpers sweep on command between two named barriers (GROUP template parameter);
 //   - termination: a counter of queued-or-running tiles reaches zero;
 //   - the same kernel serves a BATCH of independent grids (one descriptor per grid, ring entries
 //     carry the grid index): many queries' wavefronts fill the SMs where one grid cannot.
