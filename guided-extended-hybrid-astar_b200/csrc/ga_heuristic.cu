@@ -723,7 +723,7 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       prefetch = false;
     }
     int ch;
-    if (q.round)
+    if (GROUP == 1 && q.round)  // (groups are only formed without lock-step rounds: the path is compiled out of their kernels)
     {
       ch = sweep_round<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
       mask = ch ? 0u : 15u;  // a clean round has looked at every cell from all eight sides
