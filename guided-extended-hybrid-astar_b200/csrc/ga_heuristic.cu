@@ -704,7 +704,7 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
       if (st == T_DIRTY)
       {
         const int dn = sweep_refresh_halo(S, V, lane);
-        const bool news = dn >= 0 && halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2);
+        const bool news = dn >= 0 && (GROUP == 4 || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2));
         TRACE(lane, V.tile, 5, (dn + 1) | ((int)news << 3));
         if (news)
         {
