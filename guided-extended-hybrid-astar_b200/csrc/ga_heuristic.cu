@@ -566,10 +566,19 @@ __device__ __forceinline__ void sweep_publish_border(TILE& S, const sweep_visit&
 // mark back and re-read the halo ring only -- the owned cells are written by nobody else and the
 // static planes have not changed.  Replaces release + ring + pop + a full re-stage on the chain a
 // corrected value travels along.
-template <class TILE>
-__device__ __forceinline__ int sweep_refresh_halo(TILE& S, const sweep_visit& V, const int lane)
+// the state word taken and reset to RUNNING in one atomic (acquire): DIRTY = a neighbour's mark, consumed by this call
+__device__ __forceinline__ int state_take(const sweep_visit& V, const int lane)
 {
+  int old_state = 0;
   if (lane == 0)
+    asm volatile("atom.acquire.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old_state) : "l"(V.state + V.tile), "r"((int)T_RUNNING) : "memory");
+  return __shfl_sync(SW_FULL, old_state, 0);
+}
+
+template <class TILE>
+__device__ __forceinline__ int sweep_refresh_halo(TILE& S, const sweep_visit& V, const int lane, const bool taken = false)
+{
+  if (lane == 0 && !taken)
   {
     int old_state;  // acquire: the marker's cost-plane writes are visible to the loads below
     asm volatile("atom.acquire.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old_state) : "l"(V.state + V.tile), "r"((int)T_RUNNING) : "memory");
@@ -687,7 +696,10 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
   int prim = d, last_ch = 0;
   for (;;)
   {
-    int st = ld_volatile(V.state + V.tile);  // refresh 1: looked at after the sweep, 2: waited for now
+    // refresh 1: looked at after the sweep, 2: waited for now.  Groups look with the exchange itself: a mark is seen
+    // and taken back in one round trip instead of a load followed by the exchange
+    const bool take = GROUP > 1 && q.refresh == 2;
+    int st = take ? state_take(V, lane) : ld_volatile(V.state + V.tile);
     if (q.refresh == 2)
     {
       if (st != T_DIRTY && may_linger && !last_ch)
@@ -696,14 +708,14 @@ __device__ __forceinline__ int sweep_tile_loop(TILE& S, const sweep_visit& V, co
         // confirming sweeps later -- nobody waits for those
         TRACE(lane, V.tile, 6, 0);
         const long long t_end = clock64() + (long long)q.linger;
-        do st = ld_volatile(V.state + V.tile);
+        do st = take ? state_take(V, lane) : ld_volatile(V.state + V.tile);
         while (st != T_DIRTY && __all_sync(SW_FULL, clock64() < t_end));
         may_linger = false;
         TRACE(lane, V.tile, 8, st == T_DIRTY);
       }
       if (st == T_DIRTY)
       {
-        const int dn = sweep_refresh_halo(S, V, lane);
+        const int dn = sweep_refresh_halo(S, V, lane, take);
         const bool news = dn >= 0 && (GROUP == 4 || halo_improves<PROX, UNK>(S, lane, w_prox, unk_w, L1, L2));
         TRACE(lane, V.tile, 5, (dn + 1) | ((int)news << 3));
         if (news)
