@@ -699,7 +699,8 @@ def main():
     ap.add_argument("--plan-procs", type=int, default=4, help="planner processes per GPU of the plan leg (fixed per GPU: weak scaling)")
     ap.add_argument("--plan-queries", type=int, default=6, help="queries per planner process of the plan leg")
     ap.add_argument("--plan-total", type=int, default=0, help="plan leg: total queries of the job over all ranks (4096 = BASELINE config 5); 0 = procs x queries per GPU")
-    ap.add_argument("--e2e-threads", type=int, default=16, help="planner contexts / host threads of the e2e leg (capped by the host cores per rank)")
+    ap.add_argument("--e2e-threads", type=int, default=0, help="planner contexts / host threads of the e2e leg (0 = as many as --e2e-per-core allows)")
+    ap.add_argument("--e2e-per-core", type=float, default=1.0, help="e2e planner threads per host core of this rank")
     ap.add_argument("--no-mps", action="store_true", help="plan leg: do not start a CUDA MPS daemon for the planner processes")
     ap.add_argument("--plan-only", action="store_true", help="run only the plan leg (development)")
     ap.add_argument("--batch", type=int, default=128, help="queries of the batched-heuristic leg (0 = skip)")
@@ -727,7 +728,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     # one host thread per planner context; the Fortune sweep (7 ms of host work per step) scales with the cores a rank has
-    n_thr = max(N_ROT, min(args.e2e_threads, len(os.sched_getaffinity(0)) // max(world, 1)))
+    n_thr = max(N_ROT, min(args.e2e_threads if args.e2e_threads > 0 else 1 << 30, int(args.e2e_per_core * len(os.sched_getaffinity(0))) // max(world, 1)))
     if args.plan_only:
         plan = run_plan_leg(args, local_rank, rank)
         if world > 1:
@@ -847,7 +848,7 @@ def main():
     e2e_steps = max(20, args.steps // 2)
     e2e_steps = max(e2e_steps, 4 * n_thr)
     e2e_serial_ms, e2e_serial_cells, sweep_ms = timed_e2e(e2e_steps, False, False)
-    e2e_wall_ms, e2e_cells, _ = timed_e2e(e2e_steps, True, False)
+    e2e_wall_ms, e2e_cells, sweep_thr_ms = timed_e2e(e2e_steps, True, False)
     lean_wall_ms, lean_cells, _ = timed_e2e(e2e_steps, True, True)
     planes_wall_ms, planes_cells, _ = timed_e2e(e2e_steps, True, False, planes=True)
     batch = run_batch_leg(ga_b200, torch, local_rank, rank, args, sampler, hbm_peak) if args.batch > 0 else None
@@ -917,6 +918,7 @@ def main():
                                 "sets read in place; lossless against the four planes)",
                         "pipeline": "%d planner contexts, one host thread each (own stream and pinned buffers)" % n_thr,
                         "host_sweep_ms_per_step": sweep_ms / e2e_steps,
+                        "host_sweep_ms_per_step_under_load": sweep_thr_ms / e2e_steps,
                         "serial_value": e2e_serial_cells / (e2e_serial_ms * 1e-3) / 1e6,
                         "serial_ms_per_step": e2e_serial_ms / e2e_steps,
                         "planes_value": planes_cells / (planes_wall_ms * 1e-3) / 1e6, "planes_ms_per_step": planes_wall_ms / e2e_steps,
