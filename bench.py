@@ -50,7 +50,7 @@ BYTES_PER_CELL_HEUR = 39.0   # read 1+1+8+8, write 8+8+4+1 per asta
 BYTES_PER_CELL_SAFETY = 2.0 + 1.0 / 16
 # dram__bytes_read.sum + dram__bytes_write.sum of one heur_sweep_kernel launch on the 1024^2 grid of this workload,
 # from the `ncu --set full` capture summarised in profiles/ (None until captured for this round's kernel)
-NCU_TRAFFIC_BYTES = 18425600 + 3584   # profiles/r2_ncu_full_summary.csv, heur_sweep_kernel
+NCU_TRAFFIC_BYTES = 18417700 + 33536   # profiles/r2_ncu_full_summary.csv, heur_sweep_kernel
 
 
 def cpu_model():
